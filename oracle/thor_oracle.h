@@ -1,0 +1,78 @@
+/*
+ * thor_oracle.h -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU restatement (plain C99, scalar, single thread) of the Thor pixel pipeline that
+ * libthorcuda implements on the GPU.  Every function cites the reference file:line
+ * (paths relative to the awakecoding/thor tree) whose arithmetic it restates.
+ * Parity status: PINNED -- tests/test_oracle_vs_ref.py checks every function here against
+ * the unmodified reference compiled by oracle/Makefile into oracle/_ref/libthorref.so
+ * (both its SIMD and its plain-C paths), and tests/golden/ holds vectors produced by that
+ * build (tests/golden/make_golden.py).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg
+ * may include, link or call this.  libthorcuda never does.
+ */
+#ifndef THOR_ORACLE_H
+#define THOR_ORACLE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Per-4x4-unit side information, laid out exactly like the reference's deblock_data_t
+ * (common/types.h:127-135; 44 bytes, probed).  Block modes: common/types.h:76-83. */
+typedef struct { int16_t x, y; } orc_mv_t;
+typedef struct {
+  int32_t mode;                 /* 0 SKIP 1 INTRA 2 INTER 3 BIPRED 4 MERGE */
+  int32_t cbp_y, cbp_u, cbp_v;
+  uint8_t size;                 /* coding block size 8..64 */
+  uint8_t tb_split;
+  int32_t pb_part;              /* 0 NONE 1 HOR 2 VER 3 QUAD */
+  orc_mv_t mv0, mv1;
+  uint32_t ref_idx0, ref_idx1, bipred_flag;
+} orc_blockinfo_t;
+
+/* ---- in-loop filters (common/common_frame.c) ---- */
+void orc_deblock_frame_y(uint8_t *y, int stride, const orc_blockinfo_t *bi, int width, int height, int qp);
+void orc_deblock_frame_uv(uint8_t *u, uint8_t *v, int stride_c, const orc_blockinfo_t *bi, int width, int height, int qpc);
+int  orc_chroma_qp(int qp);
+/* CLPF over all full 64x64 superblocks.  org==NULL: decoder mode, sb_bits_in[k*nsbx+l] gives the
+ * signalled bit of each candidate SB.  org!=NULL: encoder mode, decision from SSDs, bits written to
+ * sb_bits_out (0xff for SBs that signal nothing).  Returns number of signalled SBs. */
+int  orc_clpf_frame(uint8_t *y, uint8_t *u, uint8_t *v, int stride_y, int stride_c,
+                    const uint8_t *org_y, int org_stride, const orc_blockinfo_t *bi,
+                    int width, int height, const uint8_t *sb_bits_in, uint8_t *sb_bits_out);
+void orc_clpf_block(const uint8_t *src, uint8_t *dst, int sstride, int dstride, int x0, int y0, int size, int width, int height);
+void orc_detect_clpf(const uint8_t *rec, const uint8_t *org, int x0, int y0, int width, int height, int so, int stride, int *sum0, int *sum1);
+/* Replicate the visible picture into its borders; p points at the visible origin. */
+void orc_pad_plane(uint8_t *p, int stride, int w, int h, int pad_hor, int pad_ver);
+
+/* ---- inter prediction (common/inter_prediction.c:72-180) ---- */
+void orc_inter_luma(uint8_t *pblock, const uint8_t *ref, int width, int height, int stride, int pstride, int mvx, int mvy, int sign, int bipred);
+void orc_inter_chroma(uint8_t *pblock, const uint8_t *ref, int width, int height, int stride, int pstride, int mvx, int mvy, int sign);
+void orc_average_trunc(uint8_t *dst, const uint8_t *a, const uint8_t *b, int n);             /* (a+b)>>1   */
+void orc_block_avg(uint8_t *p, const uint8_t *r0, const uint8_t *r1, int sp, int s0, int s1, int w, int h); /* (a+b+1)>>1 */
+
+/* ---- transforms, quantisation, residual/reconstruct ---- */
+const int16_t *orc_dct_matrix(int size);        /* size 4,8,16,32: row-major size x size */
+const int *orc_zigzag(int qsize);               /* qsize 4,8,16 */
+void orc_transform(const int16_t *block, int16_t *coeff, int size, int fast);
+void orc_inverse_transform(const int16_t *coeff, int16_t *block, int size);
+int  orc_quantize(const int16_t *coeff, int16_t *coeffq, int qp, int size, int coeff_block_type);
+void orc_dequantize(const int16_t *coeff, int16_t *rcoeff, int qp, int size);
+void orc_get_residual(int16_t *block, const uint8_t *pblock, const uint8_t *orig, int size, int orig_stride);
+void orc_reconstruct_block(const int16_t *block, const uint8_t *pblock, uint8_t *rec, int size, int stride);
+
+/* ---- motion-search costs (enc/encode_block.c:497-828) ---- */
+unsigned orc_sad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h);
+unsigned orc_widesad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h, int *x);
+int      orc_ssd(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h);
+unsigned orc_sad_fasthalf(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h, int *x, int *y);
+unsigned orc_sad_fastquarter(const uint8_t *o, const uint8_t *r, int os, int rs, int w, int h, int *x, int *y);
+void     orc_clip_mv(int16_t *mvx, int16_t *mvy, int ypos, int xpos, int fwidth, int fheight, int size, int sign);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,336 @@
+"""Pins oracle/orc_*.c (our C restatement) to the unmodified reference compiled into
+oracle/_ref/libthorref.so, on both of the reference's code paths (use_simd = 1 and 0).
+Skipped when the reference build is absent (it cannot be rebuilt without /root/reference)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from thorref import (BLOCKINFO, Picture, blocky_frame, YuvFrame, load_oracle, load_ref, ptr, random_blockinfo,
+                     set_ref_simd, smooth_frame)
+
+ref = load_ref()
+pytestmark = pytest.mark.skipif(ref is None, reason="oracle/_ref/libthorref.so not built")
+orc = load_oracle()
+orc.orc_dct_matrix.restype = C.c_void_p
+orc.orc_zigzag.restype = C.c_void_p
+
+
+@pytest.fixture(params=[1, 0], ids=["simd", "plainc"])
+def simd(request):
+    set_ref_simd(ref, request.param)
+    return request.param
+
+
+def test_tables():
+    for n, name in ((4, "g1mat_hevc"), (8, "g2mat_hevc"), (16, "g3mat_hevc"), (32, "g4mat_hevc")):
+        want = np.ctypeslib.as_array((C.c_int16 * (n * n)).in_dll(ref, name))
+        got = np.ctypeslib.as_array((C.c_int16 * (n * n)).from_address(orc.orc_dct_matrix(n)))
+        assert np.array_equal(want, got), name
+    for q, name in ((4, "zigzag16"), (8, "zigzag64"), (16, "zigzag256")):
+        want = np.ctypeslib.as_array((C.c_int * (q * q)).in_dll(ref, name))
+        got = np.ctypeslib.as_array((C.c_int * (q * q)).from_address(orc.orc_zigzag(q)))
+        assert np.array_equal(want, got), name
+    cq = np.ctypeslib.as_array((C.c_int * 52).in_dll(ref, "chroma_qp"))
+    assert [orc.orc_chroma_qp(q) for q in range(52)] == list(cq)
+
+
+@pytest.mark.parametrize("wh", [(416, 240), (192, 136)])
+@pytest.mark.parametrize("qp", [0, 20, 32, 51])
+def test_deblock(simd, wh, qp):
+    w, h = wh
+    rng = np.random.default_rng(qp * 7 + w)
+    y, u, v = blocky_frame(w, h, seed=qp + 1)
+    a = Picture(w, h)
+    a.set_visible(y, u, v)
+    b = a.copy()
+    bi = random_blockinfo(w, h, rng)
+    fa = a.as_ref_struct()
+    qpc = orc.orc_chroma_qp(qp)
+    ref.deblock_frame_y(C.byref(fa), ptr(bi), w, h, C.c_uint8(qp))
+    ref.deblock_frame_uv(C.byref(fa), ptr(bi), w, h, C.c_uint8(qpc))
+    orc.orc_deblock_frame_y(C.c_void_p(b.origin_ptr(0)), b.stride_y, ptr(bi), w, h, qp)
+    orc.orc_deblock_frame_uv(C.c_void_p(b.origin_ptr(1)), C.c_void_p(b.origin_ptr(2)), b.stride_c, ptr(bi), w, h, qpc)
+    for i in range(3):
+        assert np.array_equal(a.plane(i), b.plane(i)), f"plane {i}"
+    if qp >= 20:
+        assert not np.array_equal(a.plane(0), y), "filter never fired: weak test"
+
+
+DECISION = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.POINTER(YuvFrame), C.POINTER(YuvFrame), C.c_void_p, C.c_int, C.c_void_p)
+
+
+def _ref_clpf(pic, org, bi, w, h, bits_in, simd):
+    """Drive the reference clpf_frame with a Python decision callback equal to enc/encode_frame.c:50-63
+    (org given) or dec/decode_frame.c:130-133 (bits given).  Returns the per-SB bits."""
+    nsbx = w // 64
+    out = np.full((h // 64) * nsbx, 0xFF, np.uint8)
+    bia = bi.reshape(h // 4, w // 4)
+    detect = ref.detect_clpf_simd if simd else ref.detect_clpf
+
+    def decide(k, l, rec, o, dd, bs, stream):
+        if org is None:
+            on = int(bits_in[k * nsbx + l])
+        else:
+            s0, s1 = C.c_int(0), C.c_int(0)
+            for m in range(8):
+                for n in range(8):
+                    e = bia[k * 16 + m * 2, l * 16 + n * 2]
+                    if e["cbp_y"] and e["mode"] != 3:
+                        detect(C.c_void_p(pic.origin_ptr(0)), C.c_void_p(org.origin_ptr(0)), l * 64 + n * 8, k * 64 + m * 8,
+                               w, h, org.stride_y, pic.stride_y, C.byref(s0), C.byref(s1))
+            on = int(s1.value < s0.value)
+        out[k * nsbx + l] = on
+        return on
+
+    f = pic.as_ref_struct()
+    fo = (org or pic).as_ref_struct()
+    ref.clpf_frame(C.byref(f), C.byref(fo), ptr(bi), None, DECISION(decide))
+    return out
+
+
+@pytest.mark.parametrize("wh", [(416, 240), (256, 192)])
+@pytest.mark.parametrize("enc", [True, False])
+def test_clpf_frame(simd, wh, enc):
+    w, h = wh
+    rng = np.random.default_rng(w + enc)
+    y, u, v = blocky_frame(w, h, seed=3)
+    org = Picture(w, h)
+    org.set_visible(y, u, v)
+    a = Picture(w, h)
+    noisy = [np.clip(p.astype(int) + rng.integers(-3, 4, p.shape), 0, 255).astype(np.uint8) for p in (y, u, v)]
+    a.set_visible(*noisy)
+    b = a.copy()
+    bi = random_blockinfo(w, h, rng)
+    nsb = (w // 64) * (h // 64)
+    bits_in = rng.integers(0, 2, nsb).astype(np.uint8)
+    want_bits = _ref_clpf(a, org if enc else None, bi, w, h, bits_in, simd)
+    got_bits = np.zeros(nsb, np.uint8)
+    orc.orc_clpf_frame(C.c_void_p(b.origin_ptr(0)), C.c_void_p(b.origin_ptr(1)), C.c_void_p(b.origin_ptr(2)),
+                       b.stride_y, b.stride_c, C.c_void_p(org.origin_ptr(0)) if enc else None, org.stride_y,
+                       ptr(bi), w, h, ptr(bits_in), ptr(got_bits))
+    assert np.array_equal(want_bits, got_bits)
+    for i in range(3):
+        assert np.array_equal(a.plane(i), b.plane(i)), f"plane {i}"
+    assert not np.array_equal(a.plane(0), noisy[0])
+
+
+def test_pad_and_reference():
+    w, h = 416, 240
+    rng = np.random.default_rng(5)
+    rec = Picture(w, h, rng=rng)
+    a = Picture(w, h, 96, 48, rng=rng)
+    b = a.copy()
+    fr, fa = rec.as_ref_struct(), a.as_ref_struct()
+    ref.create_reference_frame(C.byref(fa), C.byref(fr))
+    for i in range(3):
+        b.plane(i)[...] = rec.plane(i)
+    orc.orc_pad_plane(C.c_void_p(b.origin_ptr(0)), b.stride_y, w, h, 96, 96)
+    orc.orc_pad_plane(C.c_void_p(b.origin_ptr(1)), b.stride_c, w // 2, h // 2, 48, 48)
+    orc.orc_pad_plane(C.c_void_p(b.origin_ptr(2)), b.stride_c, w // 2, h // 2, 48, 48)
+    assert np.array_equal(a.buf_y, b.buf_y) and np.array_equal(a.buf_u, b.buf_u) and np.array_equal(a.buf_v, b.buf_v)
+
+
+class Mv(C.Structure):
+    _fields_ = [("x", C.c_int16), ("y", C.c_int16)]
+
+
+@pytest.mark.parametrize("bipred", [0, 1])
+def test_inter_luma_all_phases(simd, bipred):
+    rng = np.random.default_rng(11)
+    refp = Picture(128, 128, 96, 48, rng=rng)
+    refp.buf_y[::7, ::5] = 255
+    refp.buf_y[3::11, 1::3] = 0
+    for (w, h) in ((4, 4), (8, 8), (16, 16), (32, 32), (64, 64), (16, 8), (8, 16), (4, 8), (64, 24)):
+        for fy in range(4):
+            for fx in range(4):
+                for sign in (0, 1):
+                    mv = Mv(int(rng.integers(-6, 6)) * 4 + fx, int(rng.integers(-6, 6)) * 4 + fy)
+                    base = refp.origin_ptr(0) + 32 * refp.stride_y + 40
+                    a = np.zeros((h, w), np.uint8)
+                    b = np.zeros((h, w), np.uint8)
+                    ref.get_inter_prediction_luma(ptr(a), C.c_void_p(base), w, h, refp.stride_y, w, C.byref(mv), sign, bipred)
+                    orc.orc_inter_luma(ptr(b), C.c_void_p(base), w, h, refp.stride_y, w, mv.x, mv.y, sign, bipred)
+                    assert np.array_equal(a, b), (w, h, fx, fy, sign)
+
+
+def test_inter_chroma_all_phases(simd):
+    rng = np.random.default_rng(12)
+    refp = Picture(128, 128, 96, 48, rng=rng)
+    refp.buf_u[::3, ::4] = 255
+    refp.buf_u[1::5, 2::7] = 0
+    for (w, h) in ((2, 2), (4, 4), (8, 8), (16, 16), (32, 32), (8, 4), (4, 8), (2, 4), (32, 12)):
+        for fy in range(8):
+            for fx in range(8):
+                sign = (fx + fy) & 1
+                mv = Mv(int(rng.integers(-4, 4)) * 8 + fx, int(rng.integers(-4, 4)) * 8 + fy)
+                base = refp.origin_ptr(1) + 16 * refp.stride_c + 24
+                a = np.zeros((h, w), np.uint8)
+                b = np.zeros((h, w), np.uint8)
+                ref.get_inter_prediction_chroma(ptr(a), C.c_void_p(base), w, h, refp.stride_c, w, C.byref(mv), sign)
+                orc.orc_inter_chroma(ptr(b), C.c_void_p(base), w, h, refp.stride_c, w, mv.x, mv.y, sign)
+                assert np.array_equal(a, b), (w, h, fx, fy, sign)
+
+
+def _residuals(rng, n):
+    yield np.zeros((n, n), np.int16)
+    yield np.full((n, n), 255, np.int16)
+    yield np.full((n, n), -255, np.int16)
+    cb = ((np.add.outer(np.arange(n), np.arange(n)) & 1) * 510 - 255).astype(np.int16)
+    yield cb
+    for s in (2, 20, 120):
+        yield np.clip(rng.normal(0, s, (n, n)).round(), -255, 255).astype(np.int16)
+    yield rng.integers(-255, 256, (n, n)).astype(np.int16)
+
+
+@pytest.mark.parametrize("n", [4, 8, 16, 32, 64])
+def test_transform_quant_chain(simd, n):
+    rng = np.random.default_rng(n)
+    for blk in _residuals(rng, n):
+        for fast in ((0, 1) if n > 16 else (0,)):
+            ca = np.zeros((n, n), np.int16)
+            cb = np.zeros((n, n), np.int16)
+            ref.transform(ptr(blk), ptr(ca), n, fast)
+            orc.orc_transform(ptr(blk), ptr(cb), n, fast)
+            q = min(n, 16)
+            assert np.array_equal(ca[:q, :q], cb[:q, :q]), ("fwd", n, fast)
+            for qp in (0, 13, 26, 32, 45, 51):
+                for cbt in range(4):
+                    qa = np.zeros((n, n), np.int16)
+                    qb = np.zeros((n, n), np.int16)
+                    ra = ref.quantize(ptr(ca), ptr(qa), qp, n, cbt, 0)
+                    rb = orc.orc_quantize(ptr(cb), ptr(qb), qp, n, cbt)
+                    assert ra == rb and np.array_equal(qa, qb), ("quant", n, qp, cbt)
+                da = np.zeros((n, n), np.int16)
+                db = np.zeros((n, n), np.int16)
+                ref.dequantize(ptr(qa), ptr(da), qp, n)
+                orc.orc_dequantize(ptr(qb), ptr(db), qp, n)
+                assert np.array_equal(da, db), ("dequant", n, qp)
+                ia = np.zeros((n, n), np.int16)
+                ib = np.zeros((n, n), np.int16)
+                ref.inverse_transform(ptr(da), ptr(ia), n)
+                orc.orc_inverse_transform(ptr(db), ptr(ib), n)
+                assert np.array_equal(ia, ib), ("inv", n, qp)
+
+
+@pytest.mark.parametrize("n", [4, 8, 16, 32, 64])
+def test_inverse_transform_dense(simd, n):
+    """Dense / large coefficients (exercises the int16 clips and defeats the sparse shortcuts)."""
+    rng = np.random.default_rng(100 + n)
+    q = min(n, 16)
+    for amp in (3, 300, 6000, 32767):
+        for fill in ("dense", "dc", "4x4"):
+            c = np.zeros((n, n), np.int16)
+            if fill == "dense":
+                c[:q, :q] = rng.integers(-amp, amp + 1, (q, q))
+            elif fill == "dc":
+                c[0, 0] = amp
+            else:
+                c[:4, :4] = rng.integers(-amp, amp + 1, (4, 4))
+            ia = np.zeros((n, n), np.int16)
+            ib = np.zeros((n, n), np.int16)
+            ref.inverse_transform(ptr(c), ptr(ia), n)
+            orc.orc_inverse_transform(ptr(c), ptr(ib), n)
+            assert np.array_equal(ia, ib), (n, amp, fill)
+
+
+def test_residual_reconstruct():
+    rng = np.random.default_rng(9)
+    for n in (4, 8, 16, 32, 64):
+        org = rng.integers(0, 256, (n, 80), dtype=np.uint8)
+        pred = rng.integers(0, 256, (n, n), dtype=np.uint8)
+        ra = np.zeros((n, n), np.int16)
+        rb = np.zeros((n, n), np.int16)
+        ref.get_residual(ptr(ra), ptr(pred), ptr(org), n, 80)
+        orc.orc_get_residual(ptr(rb), ptr(pred), ptr(org), n, 80)
+        assert np.array_equal(ra, rb)
+        blk = rng.integers(-600, 600, (n, n)).astype(np.int16)
+        oa = np.zeros((n, 96), np.uint8)
+        ob = np.zeros((n, 96), np.uint8)
+        ref.reconstruct_block(ptr(blk), ptr(pred), ptr(oa), n, 96)
+        orc.orc_reconstruct_block(ptr(blk), ptr(pred), ptr(ob), n, 96)
+        assert np.array_equal(oa, ob)
+
+
+def _aligned(shape, align=16):
+    n = int(np.prod(shape))
+    raw = np.zeros(n + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n].reshape(shape)
+
+
+def test_sad_family(simd):
+    rng = np.random.default_rng(21)
+    refp = Picture(160, 160, 96, 48, rng=rng)
+    y, _, _ = smooth_frame(160 + 192, 160 + 192, seed=4)
+    refp.buf_y[...] = y[:refp.rows_y, :refp.stride_y]
+    for r in (ref, orc):
+        for f in ("sad_calc", "widesad_calc", "sad_calc_fasthalf", "sad_calc_fastquarter", "orc_sad", "orc_widesad",
+                  "orc_sad_fasthalf", "orc_sad_fastquarter"):
+            if hasattr(r, f) or f in ("sad_calc",):
+                try:
+                    getattr(r, f).restype = C.c_uint
+                except AttributeError:
+                    pass
+    for (w, h, cb) in ((8, 8, 8), (16, 16, 16), (32, 32, 32), (64, 64, 64), (16, 8, 16), (8, 16, 16), (4, 8, 8), (4, 4, 8), (32, 16, 32)):
+        for trial in range(6):
+            org = _aligned((cb, cb))
+            oy, ox = int(rng.integers(8, 90)), int(rng.integers(8, 90))
+            src = refp.plane(0)[oy:oy + cb, ox:ox + cb]
+            org[...] = np.clip(src.astype(int) + rng.integers(-9, 10, src.shape), 0, 255)
+            dy, dx = int(rng.integers(-3, 4)), int(rng.integers(-3, 4))
+            bptr = C.c_void_p(refp.origin_ptr(0) + (oy + dy) * refp.stride_y + ox + dx)
+            s = refp.stride_y
+            assert ref.sad_calc(ptr(org), bptr, cb, s, w, h) == orc.orc_sad(ptr(org), bptr, cb, s, w, h)
+            # ssd_calc's SIMD twin needs both operands 16-byte aligned compact blocks (enc/enc_kernels.c:100-122)
+            recb = _aligned((cb, cb))
+            recb[...] = refp.plane(0)[oy + dy:oy + dy + cb, ox + dx:ox + dx + cb]
+            assert ref.ssd_calc(ptr(org), ptr(recb), cb, cb, w, h) == orc.orc_ssd(ptr(org), ptr(recb), cb, cb, w, h)
+            xa, xb = C.c_int(9), C.c_int(9)
+            assert ref.widesad_calc(ptr(org), bptr, cb, s, w, h, C.byref(xa)) == orc.orc_widesad(ptr(org), bptr, cb, s, w, h, C.byref(xb))
+            assert xa.value == xb.value
+            hx, hy, gx, gy = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+            fh = ref.sad_calc_fasthalf_simd if (simd and w > 4) else ref.sad_calc_fasthalf
+            fh.restype = C.c_uint
+            va = fh(ptr(org), bptr, cb, s, w, h, C.byref(hx), C.byref(hy), None)
+            vb = orc.orc_sad_fasthalf(ptr(org), bptr, cb, s, w, h, C.byref(gx), C.byref(gy))
+            assert (va, hx.value, hy.value) == (vb, gx.value, gy.value), ("half", w, h)
+            fq = ref.sad_calc_fastquarter_simd if (simd and w > 4) else ref.sad_calc_fastquarter
+            fq.restype = C.c_uint
+            for (px, py) in ((0, 0), (2, 0), (-2, 0), (0, 2), (0, -2), (2, 2), (-2, 2), (2, -2), (-2, -2)):
+                qx, qy, rx, ry = C.c_int(px), C.c_int(py), C.c_int(px), C.c_int(py)
+                va = fq(ptr(org), bptr, cb, s, w, h, C.byref(qx), C.byref(qy))
+                vb = orc.orc_sad_fastquarter(ptr(org), bptr, cb, s, w, h, C.byref(rx), C.byref(ry))
+                assert (va, qx.value, qy.value) == (vb, rx.value, ry.value), ("quarter", w, h, px, py)
+
+
+def test_clip_mv():
+    rng = np.random.default_rng(2)
+    for _ in range(4000):
+        fw, fh = (416, 240) if rng.random() < 0.5 else (1920, 1080)
+        size = int(rng.choice([8, 16, 32, 64]))
+        ypos, xpos = int(rng.integers(0, fh // 8)) * 8, int(rng.integers(0, fw // 8)) * 8
+        sign = int(rng.integers(0, 2))
+        mx, my = int(rng.integers(-900, 900)), int(rng.integers(-900, 900))
+        if rng.random() < 0.3:
+            mx *= 8
+            my *= 8
+        m = Mv(mx, my)
+        ref.clip_mv(C.byref(m), ypos, xpos, fw, fh, size, sign)
+        ax, ay = C.c_int16(mx), C.c_int16(my)
+        orc.orc_clip_mv(C.byref(ax), C.byref(ay), ypos, xpos, fw, fh, size, sign)
+        assert (m.x, m.y) == (ax.value, ay.value)
+
+
+def test_block_avg(simd):
+    rng = np.random.default_rng(1)
+    for n in (4, 8):
+        a = _aligned((n, 16))
+        b = _aligned((n, 16))
+        a[...] = rng.integers(0, 256, a.shape)
+        b[...] = rng.integers(0, 256, b.shape)
+        pa = _aligned((n, 16))
+        pb = _aligned((n, 16))
+        ref.block_avg_simd(ptr(pa), ptr(a), ptr(b), 16, 16, 16, n, n)
+        orc.orc_block_avg(ptr(pb), ptr(a), ptr(b), 16, 16, 16, n, n)
+        assert np.array_equal(pa[:, :n], pb[:, :n])

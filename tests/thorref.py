@@ -1,0 +1,182 @@
+"""Test-only helpers: ctypes views of the two CPU checkers and synthetic input generators.
+
+* ``oracle/_ref/libthorref.so`` -- the UNMODIFIED reference (awakecoding/thor) compiled by
+  ``oracle/Makefile`` from /root/reference (kind "reference"); may be absent.
+* ``oracle/libthor_oracle.so``  -- our C restatement (kind "port"); always buildable.
+
+Nothing in the product package imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+# reference common/types.h:127-135 (sizeof == 44, probed)
+BLOCKINFO = np.dtype([
+    ("mode", "<i4"), ("cbp_y", "<i4"), ("cbp_u", "<i4"), ("cbp_v", "<i4"),
+    ("size", "u1"), ("tb_split", "u1"), ("_pad", "u1", (2,)), ("pb_part", "<i4"),
+    ("mv0", "<i2", (2,)), ("mv1", "<i2", (2,)),
+    ("ref_idx0", "<u4"), ("ref_idx1", "<u4"), ("bipred_flag", "<u4")], align=False)
+assert BLOCKINFO.itemsize == 44
+
+MODE_SKIP, MODE_INTRA, MODE_INTER, MODE_BIPRED, MODE_MERGE = range(5)
+
+
+class YuvFrame(C.Structure):  # reference common/types.h:41-59
+    _fields_ = [("y", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p)] + [
+        (n, C.c_int) for n in ("width", "height", "stride_y", "stride_c", "offset_y", "offset_c",
+                               "pad_hor_y", "pad_hor_c", "pad_ver_y", "pad_ver_c", "area_y", "area_c",
+                               "frame_num")]
+
+
+def build_oracle():
+    subprocess.run(["make", "-C", ORACLE_DIR, "oracle"], check=True, capture_output=True)
+
+
+_cache = {}
+
+
+def load_oracle():
+    if "orc" not in _cache:
+        p = os.path.join(ORACLE_DIR, "libthor_oracle.so")
+        if not os.path.exists(p):
+            build_oracle()
+        _cache["orc"] = C.CDLL(p)
+    return _cache["orc"]
+
+
+def load_ref():
+    """The compiled reference, or None when oracle/_ref was not built (no /root/reference)."""
+    if "ref" not in _cache:
+        p = os.path.join(ORACLE_DIR, "_ref", "libthorref.so")
+        _cache["ref"] = C.CDLL(p) if os.path.exists(p) else None
+    return _cache["ref"]
+
+
+def set_ref_simd(lib, on):
+    C.c_int.in_dll(lib, "use_simd").value = int(on)
+
+
+def ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Picture:
+    """A padded I420 picture with the reference's geometry (common/common_frame.c:324-351)."""
+
+    def __init__(self, width, height, pad_y=0, pad_c=0, rng=None):
+        self.width, self.height, self.pad_y, self.pad_c = width, height, pad_y, pad_c
+        self.stride_y = (width + 2 * pad_y + 15) & ~15
+        self.stride_c = (width // 2 + 2 * pad_c + 15) & ~15
+        self.rows_y, self.rows_c = height + 2 * pad_y, height // 2 + 2 * pad_c
+        self.buf_y = np.zeros((self.rows_y, self.stride_y), np.uint8)
+        self.buf_u = np.zeros((self.rows_c, self.stride_c), np.uint8)
+        self.buf_v = np.zeros((self.rows_c, self.stride_c), np.uint8)
+        if rng is not None:
+            for b in (self.buf_y, self.buf_u, self.buf_v):
+                b[...] = rng.integers(0, 256, b.shape, dtype=np.uint8)
+
+    def plane(self, i):
+        b, p = ((self.buf_y, self.pad_y), (self.buf_u, self.pad_c), (self.buf_v, self.pad_c))[i]
+        h, w = (self.height, self.width) if i == 0 else (self.height // 2, self.width // 2)
+        return b[p:p + h, p:p + w]
+
+    def origin_ptr(self, i):
+        b, p = ((self.buf_y, self.pad_y), (self.buf_u, self.pad_c), (self.buf_v, self.pad_c))[i]
+        return b.ctypes.data + p * b.shape[1] + p
+
+    def set_visible(self, y, u, v):
+        self.plane(0)[...] = y
+        self.plane(1)[...] = u
+        self.plane(2)[...] = v
+
+    def as_ref_struct(self):
+        f = YuvFrame()
+        f.y, f.u, f.v = self.origin_ptr(0), self.origin_ptr(1), self.origin_ptr(2)
+        f.width, f.height, f.stride_y, f.stride_c = self.width, self.height, self.stride_y, self.stride_c
+        f.pad_hor_y = f.pad_ver_y = self.pad_y
+        f.pad_hor_c = f.pad_ver_c = self.pad_c
+        return f
+
+    def copy(self):
+        q = Picture(self.width, self.height, self.pad_y, self.pad_c)
+        q.buf_y[...], q.buf_u[...], q.buf_v[...] = self.buf_y, self.buf_u, self.buf_v
+        return q
+
+
+def smooth_frame(width, height, seed, shift=(0, 0)):
+    """Seeded synthetic I420 frame: blurred noise texture (SURVEY 8d recipe, simplified)."""
+    rng = np.random.default_rng(seed)
+    big = rng.integers(0, 256, (height + 64, width + 64)).astype(np.float32)
+    k = np.ones(5, np.float32) / 5
+    for ax in (0, 1):
+        big = np.apply_along_axis(lambda m: np.convolve(m, k, mode="same"), ax, big)
+    big = np.clip((big - 128) * 3 + 128, 0, 255)
+    oy, ox = 32 + shift[0], 32 + shift[1]
+    y = big[oy:oy + height, ox:ox + width]
+    y = np.clip(y + rng.normal(0, 2, y.shape), 0, 255).astype(np.uint8)
+    yy, xx = np.mgrid[0:height // 2, 0:width // 2]
+    u = (128 + 60 * np.sin((xx + shift[1]) / 23.0) * np.cos(yy / 29.0)).astype(np.uint8)
+    v = (128 + 60 * np.cos(xx / 27.0) * np.sin((yy + shift[0]) / 25.0)).astype(np.uint8)
+    return y, u, v
+
+
+def random_blockinfo(width, height, rng, p_split=0.55, intra_frac=0.2):
+    """Quad-tree consistent per-4x4 side information with a realistic mode mix."""
+    bw, bh = width // 4, height // 4
+    bi = np.zeros((bh, bw), BLOCKINFO)
+
+    def leaf(y, x, size):
+        r = rng.random()
+        mode = (MODE_SKIP if r < 0.3 else MODE_INTER if r < 0.6 else MODE_BIPRED if r < 0.7 else
+                MODE_MERGE if r < 1.0 - intra_frac else MODE_INTRA)
+        e = np.zeros((), BLOCKINFO)
+        e["mode"] = mode
+        e["size"] = size
+        if mode != MODE_SKIP:
+            e["cbp_y"], e["cbp_u"], e["cbp_v"] = rng.random() < 0.5, rng.random() < 0.4, rng.random() < 0.4
+            e["tb_split"] = rng.random() < 0.15
+        if mode == MODE_INTER:
+            e["pb_part"] = rng.integers(0, 4) if rng.random() < 0.3 else 0
+        if mode != MODE_INTRA:
+            e["mv0"] = np.clip(rng.normal(0, 4, 2).round(), -200, 200).astype(np.int16)
+            if mode == MODE_BIPRED:
+                e["mv1"] = np.clip(rng.normal(0, 4, 2).round(), -200, 200).astype(np.int16)
+                e["bipred_flag"] = 1
+        bi[y // 4:min(y + size, height) // 4, x // 4:min(x + size, width) // 4] = e
+
+    def rec(y, x, size):
+        if y >= height or x >= width:
+            return
+        fits = y + size <= height and x + size <= width
+        if size > 8 and (not fits or rng.random() < p_split):
+            h = size // 2
+            for dy, dx in ((0, 0), (0, h), (h, 0), (h, h)):
+                rec(y + dy, x + dx, h)
+        else:
+            leaf(y, x, size)
+
+    for y in range(0, height, 64):
+        for x in range(0, width, 64):
+            rec(y, x, 64)
+    return bi.reshape(-1)
+
+
+def blocky_frame(width, height, seed):
+    """Smooth gradients + per-8x8 DC steps + mild noise: a decoded-looking picture whose block
+    edges straddle the deblocking activity threshold (so filtered and unfiltered edges both occur)."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for (w, h, b) in ((width, height, 8), (width // 2, height // 2, 4)):
+        yy, xx = np.mgrid[0:h, 0:w]
+        base = 128 + 50 * np.sin(xx / 37.0 + seed) + 40 * np.cos(yy / 23.0)
+        steps = rng.integers(-6, 7, (h // b + 1, w // b + 1))
+        base = base + np.kron(steps, np.ones((b, b)))[:h, :w]
+        tex = rng.random((h // 32 + 1, w // 32 + 1)) < 0.3          # some busy regions (d >= beta)
+        noise = rng.normal(0, 1.2, (h, w)) + np.kron(tex, np.ones((32, 32)))[:h, :w] * rng.normal(0, 12, (h, w))
+        out.append(np.clip(base + noise, 0, 255).astype(np.uint8))
+    return out[0], out[1], out[1][::-1].copy()
