@@ -4,7 +4,8 @@
  * Two groups of entry points:
  *
  *  (1) thorcuda_*   : frame-level / batched calls.  This is the performance path: pictures live in
- *                     HBM, one launch processes a whole frame (or a whole list of blocks).
+ *                     HBM, one launch processes whole frames (of one or many independent streams) or a
+ *                     whole list of blocks.
  *  (2) the reference's own kernel names (thorcuda_compat.h): per-block, synchronous, host pointers.
  *                     Same symbol names and signatures as awakecoding/thor's common_kernels.h,
  *                     enc_kernels.h and transform.h so Thorenc/Thordec link against libthorcuda
@@ -15,6 +16,9 @@
  *
  * All functions that return int return 0 on success, non-zero on error (thorcuda_last_error()).
  * The library is single-context, single-host-thread, like the reference (SURVEY 8b "Threading").
+ * Every call only QUEUES work on the library's stream; host output buffers are valid after
+ * thorcuda_sync().  Host input buffers are consumed (copied to a pinned staging ring) before the
+ * call returns, so the caller may reuse them immediately.
  */
 #ifndef THORCUDA_H
 #define THORCUDA_H
@@ -34,6 +38,14 @@ int         thorcuda_sync(void);                   /* wait for all queued work  
 void       *thorcuda_stream(void);                 /* the cudaStream_t all work is queued on         */
 /* number of kernels this library has launched since init (bench.py "gpu_launches")                 */
 uint64_t    thorcuda_launch_count(void);
+/* CUDA-event timing of everything queued between begin and end, on the library's stream (ms).
+ * Nestable up to 64 open timers: begin returns a timer id, end(id) queues the stop event,
+ * elapsed(id) synchronises on it.                                                                    */
+int         thorcuda_timer_begin(void);
+int         thorcuda_timer_end(int id);
+float       thorcuda_timer_elapsed_ms(int id);
+/* write `bytes` of device scratch (>= L2 size) to evict the L2 between timed iterations             */
+int         thorcuda_flush_l2(size_t bytes);
 
 /* pinned host memory for staging (replaces malloc in create_yuv_frame, common_frame.c:338-339)     */
 void       *thorcuda_host_alloc(size_t bytes);
@@ -45,10 +57,13 @@ void        thorcuda_host_free(void *p);
  * stride_c = (w/2+2*pad_c+15)&~15, (h+2*pad) rows, Y then U then V.  Reference pictures use
  * pad_y=96, pad_c=48 (enc/mainenc.c:165); orig/rec use 0.                                           */
 typedef int thorcuda_pic;                          /* handle >= 0                                    */
+#define THORCUDA_MAX_PICS 4096
 thorcuda_pic thorcuda_pic_create(int width, int height, int pad_y, int pad_c);
 void         thorcuda_pic_destroy(thorcuda_pic p); /* replaces close_yuv_frame (:353-357)             */
 int          thorcuda_pic_stride(thorcuda_pic p, int plane);
-/* copy the visible area host<->device (queued; host rows at the given strides, any alignment)      */
+/* copy the visible area host<->device (queued; host rows at the given strides, any alignment).
+ * The HOST buffer must stay valid until thorcuda_sync() (it is the DMA source/target; use
+ * thorcuda_host_alloc memory for full-speed transfers).                                              */
 int thorcuda_pic_upload(thorcuda_pic p, const uint8_t *y, const uint8_t *u, const uint8_t *v, int stride_y, int stride_c);
 int thorcuda_pic_download(thorcuda_pic p, uint8_t *y, uint8_t *u, uint8_t *v, int stride_y, int stride_c);
 /* whole padded planes (borders included), for tests                                                 */
@@ -56,18 +71,21 @@ int thorcuda_pic_download_padded(thorcuda_pic p, uint8_t *y, uint8_t *u, uint8_t
 int thorcuda_pic_upload_padded(thorcuda_pic p, const uint8_t *y, const uint8_t *u, const uint8_t *v);
 /* raw device pointer to the visible origin of a plane (for callers that own CUDA code / torch)     */
 void *thorcuda_pic_devptr(thorcuda_pic p, int plane);
+/* device-side copy of the visible area src -> dst (same size; paddings may differ)                  */
+int thorcuda_pic_copy(thorcuda_pic dst, thorcuda_pic src);
 
 /* ---------------------------------------------------- in-loop filters, frame tail ---- */
 /* Side information: the reference's deblock_data_t array (common/types.h:127-135, 44 bytes per
- * 4x4 luma unit, (h/4)*(w/4) entries, host memory).  Uploaded and packed to 2 bytes/unit on device. */
-int thorcuda_blockinfo_upload(const void *deblock_data, int width, int height);
+ * 4x4 luma unit, (h/4)*(w/4) entries, host memory).  Uploaded, packed to 2 bytes/unit on the device
+ * and attached to picture `rec` (it describes that picture's blocks).                               */
+int thorcuda_blockinfo_upload(thorcuda_pic rec, const void *deblock_data);
 
 #define THORCUDA_LF_DEBLOCK_Y   1   /* deblock_frame_y   common/common_frame.c:46-241               */
 #define THORCUDA_LF_DEBLOCK_UV  2   /* deblock_frame_uv  common/common_frame.c:243-321              */
 #define THORCUDA_LF_CLPF        4   /* clpf_frame        common/common_frame.c:485-557              */
 #define THORCUDA_LF_MAKE_REF    8   /* create_reference_frame common/common_frame.c:464-483         */
 /* One fused pass over `rec` (unpadded, in-place semantics as in the reference) using the side
- * information of the last thorcuda_blockinfo_upload():
+ * information attached to it:
  *   deblock Y (qp) and UV (chroma_qp[qp]) -> CLPF -> optionally copy+pad into `ref_out`.
  * CLPF decision: org >= 0 (encoder, enc/encode_frame.c:50-63): per-SB bit = SSD(filtered) < SSD(unfiltered)
  * over coded non-bipred 8x8 luma blocks, written to sb_bits_out[] (0xFF = SB signals nothing);
@@ -76,8 +94,29 @@ int thorcuda_blockinfo_upload(const void *deblock_data, int width, int height);
  * sb_bits_* are host pointers; sb_bits_out is valid after thorcuda_sync().                           */
 int thorcuda_loopfilter_frame(thorcuda_pic rec, thorcuda_pic org, thorcuda_pic ref_out, int qp, int stages,
                               const uint8_t *sb_bits_in, uint8_t *sb_bits_out);
+/* The same for n frames of n independent streams in ONE launch (grid.z = frame): this is how a B200
+ * is kept busy, a single 1080p frame is 3 MB.  Pictures may differ in size.                         */
+typedef struct {
+  thorcuda_pic   rec, org, ref_out;      /* org/ref_out: -1 when unused                              */
+  int            qp, stages;
+  const uint8_t *sb_bits_in;             /* host, may be NULL                                        */
+  uint8_t       *sb_bits_out;            /* host, may be NULL                                        */
+} thorcuda_lf_job;
+int thorcuda_loopfilter_frames(int n, const thorcuda_lf_job *jobs);
 /* pad_yuv_frame (common/common_frame.c:405-462) on a padded picture                                 */
 int thorcuda_pad_frame(thorcuda_pic p);
+
+/* ------------------------------------------------------------------ task lists ---- */
+/* Block-level work is submitted as task lists.  A list is validated, expanded and made resident in
+ * HBM once (thorcuda_list_create) and can then be executed any number of times; the *_blocks
+ * convenience calls below create, run and release a list in one go.  Tasks name pictures by INDEX
+ * into the pics[] table given at creation, so one list can span many frames / streams.             */
+typedef int thorcuda_list;
+#define THORCUDA_LIST_PRED 0            /* thorcuda_pred_task                                        */
+#define THORCUDA_LIST_TB   1            /* thorcuda_tb_task                                          */
+#define THORCUDA_LIST_COST 2            /* thorcuda_cost_task                                        */
+thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics, const void *tasks, int ntasks);
+void          thorcuda_list_destroy(thorcuda_list l);
 
 /* ------------------------------------------------------------ inter prediction ---- */
 /* One prediction block.  (x,y) luma position, (w,h) luma size (4..64, multiples of 4; chroma is
@@ -88,20 +127,24 @@ int thorcuda_pad_frame(thorcuda_pic p);
 typedef struct {
   uint16_t x, y;
   uint8_t  w, h;
-  int8_t   ref0, ref1;      /* index into the refs[] array passed to the call                       */
+  int8_t   ref0, ref1;      /* index into pics[]                                                    */
   int16_t  mv0x, mv0y, mv1x, mv1y;
   uint8_t  sign0, sign1;
-  uint16_t reserved;
+  uint8_t  dst;             /* index into pics[]: picture the prediction is written to              */
+  uint8_t  reserved;
 } thorcuda_pred_task;       /* 20 bytes */
 
-/* Predict all tasks from refs[] into picture dst (Y, U and V).  `bipred_filter` selects the luma
- * coefficient set exactly like the reference's `bipred` argument (the encoder CONFIG flag).
- * tasks is a host pointer.  planes: bit0 luma, bit1 chroma.                                         */
-int thorcuda_predict_blocks(thorcuda_pic dst, const thorcuda_pic *refs, int nrefs,
-                            const thorcuda_pred_task *tasks, int ntasks, int bipred_filter, int planes);
+/* Predict all tasks (Y, U and V).  `bipred_filter` selects the luma coefficient set exactly like the
+ * reference's `bipred` argument (the encoder CONFIG flag).  planes: bit0 luma, bit1 chroma.         */
+int thorcuda_predict_list(thorcuda_list l, int bipred_filter, int planes);
+int thorcuda_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_pred_task *tasks, int ntasks,
+                            int bipred_filter, int planes);
 
 /* --------------------------------------- residual / transform / quant / reconstruct ---- */
-/* One transform block of one plane.  size 4..64.  (x,y) in that plane's coordinates.               */
+/* One transform block of one plane.  size 4..64.  (x,y) in that plane's coordinates.
+ * Coefficient pool layout: task t owns q*q int16 entries at coeff_offset, q = min(size,16), row-major
+ * with stride q -- the low-frequency corner, the only part the reference ever produces or reads
+ * (common/transform.c:269,309,320; enc/write_bits.c:114-135).                                       */
 typedef struct {
   uint16_t x, y;
   uint8_t  size;
@@ -109,46 +152,54 @@ typedef struct {
   uint8_t  qp;              /* already chroma-mapped for planes 1,2                                  */
   uint8_t  coeff_type;      /* bit0 chroma, bit1 intra  (quantize(), enc/encode_block.c:75)          */
   uint8_t  fast;            /* transform() `fast` flag (common/transform.c:273)                      */
-  uint8_t  reserved[3];
-  uint32_t coeff_offset;    /* int16 index into the coefficient pool (size*size entries per block)   */
+  uint8_t  org, pred, rec;  /* indices into pics[] (decoder leg ignores org)                         */
+  uint32_t coeff_offset;    /* int16 index into the coefficient pool                                 */
 } thorcuda_tb_task;         /* 16 bytes */
 
 /* Encoder leg (encode_and_reconstruct_block_inter, enc/encode_block.c:1469-1532), per task:
  *   res = org - pred; coeff = transform(res); cbp = quantize(coeff) ; if cbp: rec = clip(pred +
  *   inverse_transform(dequantize(coeffq))) else rec = pred.
  * pred and rec may be the same picture (in place).  Quantised coefficients go to the device pool and
- * are copied to host_coeffq (if non-NULL); cbp flags (one byte per task) to host_cbp; SSD(org,rec)
- * per task (ssd_calc, enc/encode_block.c:782-797) to host_ssd (if non-NULL).                         */
-int thorcuda_encode_blocks(thorcuda_pic org, thorcuda_pic pred, thorcuda_pic rec,
-                           const thorcuda_tb_task *tasks, int ntasks, size_t pool_entries,
+ * are copied to host_coeffq (if non-NULL, pool_entries int16); cbp flags (one byte per task) to
+ * host_cbp; SSD(org,rec) per task (ssd_calc, enc/encode_block.c:782-797) to host_ssd.               */
+int thorcuda_encode_list(thorcuda_list l, int16_t *host_coeffq, uint8_t *host_cbp, uint32_t *host_ssd);
+int thorcuda_encode_blocks(const thorcuda_pic *pics, int npics, const thorcuda_tb_task *tasks, int ntasks,
                            int16_t *host_coeffq, uint8_t *host_cbp, uint32_t *host_ssd);
 /* Decoder leg (decode_and_reconstruct_block_inter, dec/decode_block.c:90-120):
- *   rec = clip(pred + inverse_transform(dequantize(coeffq))) for every task (cbp != 0 blocks only). */
-int thorcuda_reconstruct_blocks(thorcuda_pic pred, thorcuda_pic rec, const thorcuda_tb_task *tasks, int ntasks,
-                                const int16_t *host_coeffq, size_t pool_entries);
+ *   rec = clip(pred + inverse_transform(dequantize(coeffq))) for every task (cbp != 0 blocks only).
+ * host_coeffq == NULL: use the pool contents already on the device (e.g. left by encode_list).      */
+int thorcuda_reconstruct_list(thorcuda_list l, const int16_t *host_coeffq);
+int thorcuda_reconstruct_blocks(const thorcuda_pic *pics, int npics, const thorcuda_tb_task *tasks, int ntasks,
+                                const int16_t *host_coeffq);
+size_t thorcuda_list_pool_entries(thorcuda_list l);   /* int16 entries of a TB list's pool            */
 
 /* -------------------------------------------------------------- motion search ---- */
-/* Whole-frame integer-pel cost table (north_star: "whole-frame per-block cost table").
- * For every 8x8-aligned block of `org` of size bs (8,16,32,64) and every displacement
- * (dx,dy) in [-range,range]^2 around that block's centre (cx,cy) (full-pel; centres[] = int16 pairs
- * per block in raster order, or NULL for (0,0)):  table = SAD(org block, ref at +d)  == sad_calc().
- * Table layout: [block][dy+range][dx+range], uint16 for bs<=16, uint32 for bs>=32.
- * Positions whose reference block would leave the padded picture are written as 0xFFFF/0xFFFFFFFF.
- * The table stays on the device; thorcuda_sad_table_fetch copies a level to the host.              */
-int thorcuda_sad_table_build(thorcuda_pic org, thorcuda_pic ref, int range, const int16_t *centres8);
-int thorcuda_sad_table_fetch(int bs, void *host_dst, size_t bytes);
-size_t thorcuda_sad_table_bytes(int bs);
-void *thorcuda_sad_table_devptr(int bs);
+/* Whole-frame integer-pel cost tables (north_star: "whole-frame per-block cost table").
+ * For every block of `org` of size bs in {8,16,32,64} on the bs-aligned grid (blocks that do not
+ * lie completely inside the frame are omitted: (w/bs) x (h/bs) blocks, raster order) and every
+ * full-pel displacement (dx,dy) in [-range,range]^2 around the superblock's search centre
+ * (centres: int16 (cx,cy) pairs per 64x64 SB in raster order, host pointer, NULL = all (0,0)):
+ *      table[block][dy+range][dx+range] = sad_calc(org block, ref + (cy+dy)*stride + cx+dx)
+ * uint16 for bs <= 16, uint32 for bs >= 32.  Rectangular partitions (HOR/VER/QUAD halves) are sums
+ * of two entries of the next finer level -- SAD is additive -- so the host forms them itself.
+ * Displacements whose reference block would leave the padded picture hold 0xFFFF / 0xFFFFFFFF.
+ * Tables live in HBM in one of THORCUDA_SAD_SLOTS slots; fetch copies one level to the host.
+ * n (org,ref) pairs are processed in ONE launch.                                                     */
+#define THORCUDA_SAD_SLOTS 64
+int    thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, const thorcuda_pic *refs,
+                                int range, const int16_t *const *centres);
+size_t thorcuda_sad_table_bytes(int slot, int bs);
+int    thorcuda_sad_table_fetch(int slot, int bs, void *host_dst, size_t bytes);
+void  *thorcuda_sad_table_devptr(int slot, int bs);
 
 /* Generic batched costs: one task = one (block, candidate) pair.                                    */
 typedef struct {
   uint16_t x, y;            /* luma position of the original block                                   */
   uint8_t  w, h;            /* prediction block size (4..64)                                         */
-  int8_t   ref;             /* index into refs[]                                                     */
-  uint8_t  hx, hy;          /* fastquarter only: incoming half-pel x,y + 2  (0,2,4)                  */
-  uint8_t  reserved;
+  uint8_t  org, ref;        /* indices into pics[]                                                   */
+  int8_t   hx, hy;          /* fastquarter only: incoming half-pel (*x,*y) in {-2,0,2}               */
   int16_t  ix, iy;          /* full-pel displacement of the reference block                          */
-  uint16_t pad;
+  uint16_t reserved;
 } thorcuda_cost_task;       /* 16 bytes */
 typedef struct { uint32_t cost; int16_t x, y; } thorcuda_cost_result;
 
@@ -157,8 +208,9 @@ typedef struct { uint32_t cost; int16_t x, y; } thorcuda_cost_result;
 #define THORCUDA_COST_FASTHALF     2   /* sad_calc_fasthalf   enc/encode_block.c:497-605  (x,y out) */
 #define THORCUDA_COST_FASTQUARTER  3   /* sad_calc_fastquarter enc/encode_block.c:609-738 (x,y out) */
 #define THORCUDA_COST_SSD          4   /* ssd_calc            enc/encode_block.c:782-797            */
-int thorcuda_cost_batch(int kind, thorcuda_pic org, const thorcuda_pic *refs, int nrefs,
-                        const thorcuda_cost_task *tasks, int ntasks, thorcuda_cost_result *host_results);
+int thorcuda_cost_list(thorcuda_list l, int kind, thorcuda_cost_result *host_results);
+int thorcuda_cost_batch(int kind, const thorcuda_pic *pics, int npics, const thorcuda_cost_task *tasks, int ntasks,
+                        thorcuda_cost_result *host_results);
 
 #ifdef __cplusplus
 }

@@ -55,12 +55,12 @@ def test_deblock_stages(tb, wh, qp):
         pytest.skip("full size once")
     orc = load_oracle()
     rng, org, rec, bi = make_case(w, h, seed=qp + w)
-    tb.ops.blockinfo_upload(bi, w, h)
     for stages in (1, 2, 3):
         host = rec.copy()
         oracle_chain(orc, host, None, bi, w, h, qp, stages, None)
         dev = tb.Picture(w, h)
         dev.upload(rec.plane(0), rec.plane(1), rec.plane(2))
+        tb.ops.blockinfo_upload(dev, bi)
         tb.ops.loopfilter_frame(dev, qp, stages)
         got = dev.download()
         dev.close()
@@ -80,9 +80,9 @@ def test_clpf(tb, wh, enc):
     bits_in = rng.integers(0, 2, max(nsb, 1)).astype(np.uint8)
     host = rec.copy()
     want_bits = oracle_chain(orc, host, org if enc else None, bi, w, h, 0, 4, None if enc else bits_in)
-    tb.ops.blockinfo_upload(bi, w, h)
     dev = tb.Picture(w, h)
     dev.upload(rec.plane(0), rec.plane(1), rec.plane(2))
+    tb.ops.blockinfo_upload(dev, bi)
     dorg = None
     if enc:
         dorg = tb.Picture(w, h)
@@ -115,9 +115,9 @@ def test_fused_frame_tail_and_reference(tb, wh):
     orc.orc_pad_plane(C.c_void_p(href.origin_ptr(1)), href.stride_c, w // 2, h // 2, 48, 48)
     orc.orc_pad_plane(C.c_void_p(href.origin_ptr(2)), href.stride_c, w // 2, h // 2, 48, 48)
 
-    tb.ops.blockinfo_upload(bi, w, h)
     dev, dorg, dref = tb.Picture(w, h), tb.Picture(w, h), tb.Picture(w, h, 96, 48)
     dev.upload(rec.plane(0), rec.plane(1), rec.plane(2))
+    tb.ops.blockinfo_upload(dev, bi)
     dorg.upload(org.plane(0), org.plane(1), org.plane(2))
     got_bits = tb.ops.loopfilter_frame(dev, qp, 15, org=dorg, ref_out=dref)
     assert np.array_equal(got_bits, want_bits)
@@ -144,3 +144,42 @@ def test_no_silent_fallback(tb):
     with pytest.raises(tb.ThorCudaError):
         tb.ops.loopfilter_frame(dev, 30, 7)
     dev.close()
+
+
+def test_batched_frames_one_launch(tb):
+    """Four frames of different sizes / qps through ONE thorcuda_loopfilter_frames launch."""
+    orc = load_oracle()
+    cases = [(416, 240, 30), (200, 136, 40), (128, 64, 22), (416, 240, 51)]
+    jobs, want, pics = [], [], []
+    for k, (w, h, qp) in enumerate(cases):
+        rng, org, rec, bi = make_case(w, h, seed=700 + k)
+        host = rec.copy()
+        bits = oracle_chain(orc, host, org, bi, w, h, qp, 7, None)
+        href = HostPic(w, h, 96, 48)
+        for i in range(3):
+            href.plane(i)[...] = host.plane(i)
+        orc.orc_pad_plane(C.c_void_p(href.origin_ptr(0)), href.stride_y, w, h, 96, 96)
+        orc.orc_pad_plane(C.c_void_p(href.origin_ptr(1)), href.stride_c, w // 2, h // 2, 48, 48)
+        orc.orc_pad_plane(C.c_void_p(href.origin_ptr(2)), href.stride_c, w // 2, h // 2, 48, 48)
+        dev, dorg, dref = tb.Picture(w, h), tb.Picture(w, h), tb.Picture(w, h, 96, 48)
+        dev.upload(rec.plane(0), rec.plane(1), rec.plane(2))
+        dorg.upload(org.plane(0), org.plane(1), org.plane(2))
+        tb.ops.blockinfo_upload(dev, bi)
+        jobs.append(dict(rec=dev, qp=qp, stages=15, org=dorg, ref_out=dref))
+        want.append((host, bits, href))
+        pics += [dev, dorg, dref]
+    before = tb.launch_count()
+    got_bits = tb.ops.loopfilter_frames(jobs)
+    assert tb.launch_count() - before == 2          # fused filter kernel + border kernel, for all four frames
+    for j, (host, bits, href), gb in zip(jobs, want, got_bits):
+        assert np.array_equal(gb, bits)
+        got = j["rec"].download()
+        for i in range(3):
+            assert np.array_equal(got[i], host.plane(i))
+        py, pu, pv = j["ref_out"].download_padded()
+        w = host.width
+        assert np.array_equal(py[:, :w + 192], href.buf_y[:, :w + 192])
+        assert np.array_equal(pu[:, :w // 2 + 96], href.buf_u[:, :w // 2 + 96])
+        assert np.array_equal(pv[:, :w // 2 + 96], href.buf_v[:, :w // 2 + 96])
+    for p in pics:
+        p.close()

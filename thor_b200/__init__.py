@@ -5,7 +5,7 @@ package is the thin Python mirror used by the tests and the benchmark; it never 
 itself and has no CPU fallback: if the library is missing, or no sm_100 device is present,
 ``init()`` raises.
 """
-from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, COST_FASTHALF, COST_FASTQUARTER, COST_SAD,  # noqa: F401
-                  COST_SSD, COST_WIDESAD, COST_TASK, COST_RESULT, PRED_TASK, TB_TASK, Picture, ThorCudaError, cdll,
-                  init, launch_count, lib_path, shutdown, sync)
+from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, LIST_COST, LIST_PRED, LIST_TB, COST_FASTHALF,  # noqa: F401
+                  COST_FASTQUARTER, COST_SAD, COST_SSD, COST_WIDESAD, COST_TASK, COST_RESULT, PRED_TASK, TB_TASK, Picture,
+                  ThorCudaError, cdll, init, launch_count, lib_path, shutdown, sync)
 from . import ops  # noqa: F401

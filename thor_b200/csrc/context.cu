@@ -1,4 +1,4 @@
-// libthorcuda: context, error convention, picture pool, host<->device picture copies.
+// libthorcuda: context, error convention, picture pool, staging ring, host<->device picture copies.
 #include <stdarg.h>
 #include <string.h>
 #include "internal.cuh"
@@ -23,8 +23,8 @@ void die(const char *msg) {
 }
 
 void *DevBuf::reserve(size_t bytes) {
-  if (bytes <= cap) return p;
-  if (p) cudaFree(p);
+  if (bytes <= cap && p) return p;
+  if (p) { cudaStreamSynchronize(g_ctx.stream); cudaFree(p); }
   p = nullptr; cap = 0;
   size_t want = bytes + bytes / 4 + 256;
   if (cudaMalloc(&p, want) != cudaSuccess) { p = nullptr; return nullptr; }
@@ -33,7 +33,7 @@ void *DevBuf::reserve(size_t bytes) {
 }
 void DevBuf::release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 void *PinBuf::reserve(size_t bytes) {
-  if (bytes <= cap) return p;
+  if (bytes <= cap && p) return p;
   if (p) cudaFreeHost(p);
   p = nullptr; cap = 0;
   size_t want = bytes + bytes / 4 + 256;
@@ -53,12 +53,76 @@ PicView Pic::view(int which) const {
   v.stride[0] = stride_y; v.stride[1] = v.stride[2] = stride_c;
   v.w = w; v.h = h;
   v.pad[0] = pad_y; v.pad[1] = v.pad[2] = pad_c;
+  v.reserved = 0;
   return v;
 }
 
 Pic *get_pic(thorcuda_pic h) {
-  if (h < 0 || h >= 256 || !g_ctx.pics[h].used) return nullptr;
+  if (h < 0 || h >= THORCUDA_MAX_PICS || !g_ctx.pics[h].used) return nullptr;
   return &g_ctx.pics[h];
+}
+List *get_list(thorcuda_list h) {
+  if (h < 0 || h >= 256 || !g_ctx.lists[h].used) return nullptr;
+  return &g_ctx.lists[h];
+}
+
+static bool is_pinned(const void *p, size_t bytes) {
+  const uintptr_t a = (uintptr_t)p;
+  for (auto &r : g_ctx.pinned) if (a >= r.first && a + bytes <= r.first + r.second) return true;
+  return false;
+}
+
+void *stage_acquire(size_t bytes) {
+  Context &c = g_ctx;
+  StageSlot &s = c.stage[c.stage_next];
+  if (s.pending) { cudaEventSynchronize(s.ev); s.pending = false; }
+  return s.buf.reserve(bytes);
+}
+int stage_commit_copy(void *dst, const void *staged, size_t bytes) {
+  Context &c = g_ctx;
+  StageSlot &s = c.stage[c.stage_next];
+  THOR_CUDA(cudaMemcpyAsync(dst, staged, bytes, cudaMemcpyHostToDevice, c.stream));
+  THOR_CUDA(cudaEventRecord(s.ev, c.stream));
+  s.pending = true;
+  c.stage_next = (c.stage_next + 1) % 8;
+  return 0;
+}
+int h2d(void *dst, const void *src, size_t bytes) {
+  if (!bytes) return 0;
+  if (is_pinned(src, bytes)) {
+    THOR_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, g_ctx.stream));
+    return 0;
+  }
+  void *st = stage_acquire(bytes);
+  if (!st) return fail("pinned staging allocation of %zu bytes failed", bytes);
+  memcpy(st, src, bytes);
+  return stage_commit_copy(dst, st, bytes);
+}
+int d2h(void *dst, const void *src, size_t bytes) {
+  if (!bytes) return 0;
+  THOR_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, g_ctx.stream));
+  return 0;
+}
+int sync_pic_view(thorcuda_pic h) {
+  const PicView v = g_ctx.pics[h].view();
+  return h2d(g_ctx.d_pics + h, &v, sizeof(v));
+}
+
+__global__ void k_fill(uint4 *p, size_t n, uint32_t v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    p[i] = make_uint4(v, v, v, v);
+}
+
+// copy of the visible area of all three planes, 16 bytes per thread (widths are multiples of 8; the
+// chroma tail of an odd multiple of 8 is handled with 4-byte accesses)
+__global__ void k_copy_visible(PicView d, PicView s) {
+  const int pl = blockIdx.z, w = pl ? s.w / 2 : s.w, h = pl ? s.h / 2 : s.h;
+  const int y = blockIdx.y;
+  if (y >= h) return;
+  const uint8_t *sp = s.p[pl] + (size_t)y * s.stride[pl];
+  uint8_t *dp = d.p[pl] + (size_t)y * d.stride[pl];
+  for (int x = (blockIdx.x * blockDim.x + threadIdx.x) * 4; x < w; x += gridDim.x * blockDim.x * 4)
+    *reinterpret_cast<uint32_t *>(dp + x) = *reinterpret_cast<const uint32_t *>(sp + x);
 }
 
 }  // namespace thor
@@ -80,6 +144,17 @@ int thorcuda_init(int device) {
     return fail("libthorcuda: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
   THOR_CUDA(cudaSetDevice(device));
   THOR_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  {  // task lists come from the stream-ordered allocator; keep freed blocks cached instead of returning them to the OS
+    cudaMemPool_t pool;
+    THOR_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t keep = UINT64_MAX;
+    THOR_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  }
+  THOR_CUDA(cudaMalloc((void **)&c.d_pics, sizeof(PicView) * THORCUDA_MAX_PICS));
+  THOR_CUDA(cudaMemsetAsync(c.d_pics, 0, sizeof(PicView) * THORCUDA_MAX_PICS, c.stream));
+  for (auto &s : c.stage) { THOR_CUDA(cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming)); s.pending = false; }
+  for (int i = 0; i < 64; i++) { THOR_CUDA(cudaEventCreate(&c.tm0[i])); THOR_CUDA(cudaEventCreate(&c.tm1[i])); c.tm_used[i] = false; }
+  c.stage_next = 0;
   c.device = device;
   c.sm_count = prop.multiProcessorCount;
   c.launches = 0;
@@ -91,11 +166,17 @@ void thorcuda_shutdown(void) {
   Context &c = ctx();
   if (!c.ready) return;
   cudaStreamSynchronize(c.stream);
-  for (int i = 0; i < 256; i++) if (c.pics[i].used) thorcuda_pic_destroy(i);
-  DevBuf *bufs[] = {&c.blockinfo_raw, &c.blockinfo_packed, &c.sb_bits, &c.tasks, &c.results, &c.pool, &c.cbp, &c.ssd,
-                    &c.refs, &c.sadtab[0], &c.sadtab[1], &c.sadtab[2], &c.sadtab[3], &c.centres};
+  for (int i = 0; i < 256; i++) if (c.lists[i].used) thorcuda_list_destroy(i);
+  for (int i = 0; i < THORCUDA_MAX_PICS; i++) if (c.pics[i].used) thorcuda_pic_destroy(i);
+  DevBuf *bufs[] = {&c.raw_info, &c.scratch, &c.flush, &c.lfjobs, &c.sadjobs, &c.centres};
   for (DevBuf *b : bufs) b->release();
-  c.h_tasks.release(); c.h_misc.release();
+  for (auto &s : c.sad) {
+    for (int l = 0; l < 4; l++) if (s.tab[l]) cudaFree(s.tab[l]);
+    s = SadSlot();
+  }
+  for (auto &s : c.stage) { s.buf.release(); cudaEventDestroy(s.ev); s.ev = nullptr; s.pending = false; }
+  for (int i = 0; i < 64; i++) { cudaEventDestroy(c.tm0[i]); cudaEventDestroy(c.tm1[i]); }
+  cudaFree(c.d_pics); c.d_pics = nullptr;
   cudaStreamDestroy(c.stream);
   c.stream = nullptr;
   c.ready = false;
@@ -112,21 +193,69 @@ int thorcuda_sync(void) {
 void *thorcuda_stream(void) { return (void *)ctx().stream; }
 uint64_t thorcuda_launch_count(void) { return ctx().launches; }
 
+int thorcuda_timer_begin(void) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  for (int i = 0; i < 64; i++)
+    if (!c.tm_used[i]) {
+      c.tm_used[i] = true;
+      if (cudaEventRecord(c.tm0[i], c.stream) != cudaSuccess) return -1;
+      return i;
+    }
+  fail("timer: all 64 timers are open");
+  return -1;
+}
+int thorcuda_timer_end(int id) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (id < 0 || id >= 64 || !c.tm_used[id]) return fail("timer: bad id %d", id);
+  THOR_CUDA(cudaEventRecord(c.tm1[id], c.stream));
+  return 0;
+}
+float thorcuda_timer_elapsed_ms(int id) {
+  Context &c = ctx();
+  if (id < 0 || id >= 64 || !c.tm_used[id]) return -1.f;
+  float ms = -1.f;
+  if (cudaEventSynchronize(c.tm1[id]) != cudaSuccess || cudaEventElapsedTime(&ms, c.tm0[id], c.tm1[id]) != cudaSuccess) ms = -1.f;
+  c.tm_used[id] = false;
+  return ms;
+}
+
+int thorcuda_flush_l2(size_t bytes) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  bytes = (bytes + 15) & ~(size_t)15;
+  void *p = c.flush.reserve(bytes);
+  if (!p) return fail("flush_l2: device allocation of %zu bytes failed", bytes);
+  k_fill<<<c.sm_count * 8, 256, 0, c.stream>>>((uint4 *)p, bytes / 16, 0x5a5a5a5au);
+  THOR_CUDA(cudaGetLastError());   // not counted in launch_count: it is measurement hygiene, not pipeline work
+  return 0;
+}
+
 void *thorcuda_host_alloc(size_t bytes) {
   THOR_NEED_CTX();
   void *p = nullptr;
   if (cudaMallocHost(&p, bytes) != cudaSuccess) die("libthorcuda: pinned host allocation failed");
+  ctx().pinned.push_back({(uintptr_t)p, bytes});
   return p;
 }
-void thorcuda_host_free(void *p) { if (p) cudaFreeHost(p); }
+void thorcuda_host_free(void *p) {
+  if (!p) return;
+  auto &v = ctx().pinned;
+  for (size_t i = 0; i < v.size(); i++) if (v[i].first == (uintptr_t)p) { v.erase(v.begin() + i); break; }
+  cudaStreamSynchronize(ctx().stream);
+  cudaFreeHost(p);
+}
 
 thorcuda_pic thorcuda_pic_create(int width, int height, int pad_y, int pad_c) {
   THOR_NEED_CTX();
   Context &c = ctx();
   if (width <= 0 || height <= 0 || (width & 7) || (height & 7))   // enc/strings.c:437
     return fail("thorcuda_pic_create: width/height must be positive multiples of 8 (got %dx%d)", width, height);
+  if (width > 16384 || height > 16384 || pad_y < 0 || pad_c < 0 || pad_y > 256 || pad_c > 256)
+    return fail("thorcuda_pic_create: unsupported geometry");
   int h = -1;
-  for (int i = 0; i < 256; i++) if (!c.pics[i].used) { h = i; break; }
+  for (int i = 0; i < THORCUDA_MAX_PICS; i++) if (!c.pics[i].used) { h = i; break; }
   if (h < 0) return fail("thorcuda_pic_create: picture pool exhausted");
   Pic &p = c.pics[h];
   p = Pic();
@@ -139,6 +268,7 @@ thorcuda_pic thorcuda_pic_create(int width, int height, int pad_y, int pad_c) {
   if (cudaMalloc((void **)&p.buf[0], p.bytes + 256) != cudaSuccess) return fail("thorcuda_pic_create: cudaMalloc(%zu) failed", p.bytes);
   cudaMemsetAsync(p.buf[0], 0, p.bytes + 256, c.stream);
   p.used = true;
+  if (sync_pic_view(h)) return -1;
   return h;
 }
 
@@ -147,6 +277,7 @@ void thorcuda_pic_destroy(thorcuda_pic h) {
   if (!p) return;
   cudaStreamSynchronize(ctx().stream);
   for (int i = 0; i < 2; i++) if (p->buf[i]) cudaFree(p->buf[i]);
+  if (p->info) cudaFree(p->info);
   *p = Pic();
 }
 
@@ -207,6 +338,17 @@ int thorcuda_pic_download_padded(thorcuda_pic h, uint8_t *y, uint8_t *u, uint8_t
 int thorcuda_pic_upload_padded(thorcuda_pic h, const uint8_t *y, const uint8_t *u, const uint8_t *v) {
   uint8_t *hp[3] = {(uint8_t *)y, (uint8_t *)u, (uint8_t *)v};
   return copy_padded(h, hp, true);
+}
+
+int thorcuda_pic_copy(thorcuda_pic hd, thorcuda_pic hs) {
+  THOR_NEED_CTX();
+  Pic *d = get_pic(hd), *s = get_pic(hs);
+  if (!d || !s) return fail("pic_copy: bad handle");
+  if (d->w != s->w || d->h != s->h) return fail("pic_copy: size mismatch");
+  dim3 grid(4, s->h, 3);
+  k_copy_visible<<<grid, 128, 0, ctx().stream>>>(d->view(), s->view());
+  THOR_LAUNCHED();
+  return 0;
 }
 
 }  // extern "C"

@@ -10,13 +10,10 @@
 // passes need (8 rows above/below, 16 columns left/right so that loads stay 16-byte aligned) is staged
 // in shared memory with 128-bit loads; both edge passes and CLPF run on the staged tile; results leave
 // with 128-bit stores.  Every picture byte is read from HBM once (halo re-reads hit L2) and written once.
+#include <string.h>
 #include "internal.cuh"
 
 namespace thor {
-
-// common/common_block.c:78-83
-static const uint8_t h_chroma_qp[52] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 25,
-                                        26, 27, 28, 29, 29, 30, 31, 32, 33, 33, 34, 34, 35, 35, 36, 36, 37, 37, 38, 39, 40, 41, 42, 43, 44, 45};
 
 // ---- packed side information: 2 bytes per 4x4 luma unit --------------------------------------
 // bits 0-2 mode | 3 cbp.y | 4 cbp.u | 5 cbp.v | 6-7 log2(size)-3 | 8 tb_split | 9-10 pb_part | 11 any |mv comp| >= 4
@@ -25,21 +22,18 @@ __device__ __forceinline__ int bi_mode(unsigned v) { return v & BI_MODE; }
 __device__ __forceinline__ int bi_size(unsigned v) { return 8 << ((v >> 6) & 3); }
 __device__ __forceinline__ int bi_part(unsigned v) { return (v >> 9) & 3; }
 
-// deblock_data_t (common/types.h:127-135) viewed as 11 little-endian 32-bit words
-__global__ void k_pack_blockinfo(const int32_t *__restrict__ raw, uint16_t *__restrict__ out, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int32_t *e = raw + (size_t)i * 11;
+// deblock_data_t (common/types.h:127-135) viewed as 11 little-endian 32-bit words; packed on the host
+// while the record is copied into the pinned staging buffer (22x fewer bytes cross PCIe).
+static inline uint16_t pack_blockinfo(const int32_t *e) {
   const int mode = e[0], cy = e[1], cu = e[2], cv = e[3], sz = e[4] & 0xff, tb = (e[4] >> 8) & 0xff, part = e[5];
-  const int mv0 = e[6], mv1 = e[7];
   auto big = [](int packed) {
     const int x = (int16_t)(packed & 0xffff), y = (int16_t)(packed >> 16);   // NEW_MV_TEST, common_frame.c:119-120
     return abs(x) >= 4 || abs(y) >= 4;
   };
   const int lg = sz >= 64 ? 3 : sz >= 32 ? 2 : sz >= 16 ? 1 : 0;
-  unsigned v = (mode & 7) | (cy ? BI_CBPY : 0) | (cu ? BI_CBPU : 0) | (cv ? BI_CBPV : 0) | (lg << 6) | (tb ? BI_TBSPLIT : 0) |
-               ((part & 3) << 9) | ((big(mv0) || big(mv1)) ? BI_MVLARGE : 0);
-  out[i] = (uint16_t)v;
+  const unsigned v = (mode & 7) | (cy ? BI_CBPY : 0) | (cu ? BI_CBPU : 0) | (cv ? BI_CBPV : 0) | (lg << 6) | (tb ? BI_TBSPLIT : 0) |
+                     ((part & 3) << 9) | ((big(e[6]) || big(e[7])) ? BI_MVLARGE : 0);
+  return (uint16_t)v;
 }
 
 constexpr int LF_THREADS = 256;
@@ -56,9 +50,8 @@ struct LfParams {
   const uint8_t *bits_in;
   uint8_t *bits_out;
   int nsbx_full, nsby_full;         // floor(w/64), floor(h/64): SBs CLPF may touch (common_frame.c:496-497)
+  PicView *self;                    // entry of rec in the device picture table: updated to dstA (the buffers flip)
 };
-
-__device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
 
 // CLPF of 4 packed samples.  x = centre, a/b/c/d = up/left/right/down neighbours (already clamped).
 // delta = (#nbr > x  > 2) - (#nbr < x > 2), per byte (common_block.c:186-194).
@@ -110,7 +103,8 @@ __device__ __forceinline__ uint4 clpf_chunk(const uint8_t *win, int r, int c, in
   return f;
 }
 
-__global__ void __launch_bounds__(LF_THREADS) k_loopfilter(const LfParams P) {
+__global__ void __launch_bounds__(LF_THREADS) k_loopfilter(const LfParams *__restrict__ jobs) {
+  __shared__ LfParams P;
   __shared__ __align__(16) uint8_t sY[LY_ROWS * LY_PITCH];
   __shared__ __align__(16) uint8_t sC[2][LC_ROWS * LC_PITCH];
   __shared__ uint16_t sI[LI_ROWS * LI_COLS];
@@ -119,8 +113,13 @@ __global__ void __launch_bounds__(LF_THREADS) k_loopfilter(const LfParams P) {
   __shared__ int sOn;
 
   const int tid = threadIdx.x;
+  if (tid < (int)(sizeof(LfParams) / 4)) reinterpret_cast<uint32_t *>(&P)[tid] = reinterpret_cast<const uint32_t *>(jobs + blockIdx.z)[tid];
+  __syncthreads();
   const int W = P.src.w, H = P.src.h;
   const int x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
+  if (x0 >= W || y0 >= H) return;                 // frames of a batch may differ in size
+  if (blockIdx.x == 0 && blockIdx.y == 0 && tid < (int)(sizeof(PicView) / 4))
+    reinterpret_cast<uint32_t *>(P.self)[tid] = reinterpret_cast<const uint32_t *>(&P.dstA)[tid];
   const int tx0 = x0 - 16, ty0 = y0 - 8;           // luma tile origin in the frame
   const int cx0 = x0 >> 1, cy0 = y0 >> 1;
   const int tcx0 = cx0 - 16, tcy0 = cy0 - 4;       // chroma tile origin
@@ -335,11 +334,10 @@ __global__ void __launch_bounds__(LF_THREADS) k_loopfilter(const LfParams P) {
 }
 
 // Border replication (pad_yuv_frame, common_frame.c:405-462).  One thread per 4 border bytes.
-// grid.y enumerates rows of the padded plane, grid.z the plane.
-__global__ void k_pad(PicView v) {
-  const int pl = blockIdx.z;
+// grid.y enumerates rows of the padded plane, grid.z = 3*job + plane.
+__device__ __forceinline__ void pad_rows(const PicView &v, int pl, int prow) {
   const int pad = v.pad[pl], w = pl ? v.w / 2 : v.w, h = pl ? v.h / 2 : v.h, stride = v.stride[pl];
-  const int row = (int)blockIdx.y - pad;               // -pad .. h+pad-1
+  const int row = prow - pad;                          // -pad .. h+pad-1
   if (row >= h + pad) return;
   const int srow = min(max(row, 0), h - 1);
   uint8_t *dst = v.p[pl] + (ptrdiff_t)row * stride;
@@ -354,6 +352,12 @@ __global__ void k_pad(PicView v) {
     *reinterpret_cast<uint32_t *>(dst + x) = val;
   }
 }
+__global__ void k_pad(PicView v) { pad_rows(v, blockIdx.z, blockIdx.y); }
+__global__ void k_pad_jobs(const LfParams *__restrict__ jobs) {
+  const LfParams &J = jobs[blockIdx.z / 3];
+  if (!J.dstB.p[0]) return;
+  pad_rows(J.dstB, blockIdx.z % 3, blockIdx.y);
+}
 
 }  // namespace thor
 
@@ -361,27 +365,19 @@ using namespace thor;
 
 extern "C" {
 
-int thorcuda_blockinfo_upload(const void *deblock_data, int width, int height) {
+int thorcuda_blockinfo_upload(thorcuda_pic hrec, const void *deblock_data) {
   THOR_NEED_CTX();
-  Context &c = ctx();
-  const int n = (width / 4) * (height / 4);
-  const size_t raw_bytes = (size_t)n * 44;
-  void *raw = c.blockinfo_raw.reserve(raw_bytes);
-  void *packed = c.blockinfo_packed.reserve((size_t)n * 2);
-  if (!raw || !packed) return fail("blockinfo: device allocation failed");
-  THOR_CUDA(cudaMemcpyAsync(raw, deblock_data, raw_bytes, cudaMemcpyHostToDevice, c.stream));
-  k_pack_blockinfo<<<(n + 255) / 256, 256, 0, c.stream>>>((const int32_t *)raw, (uint16_t *)packed, n);
-  THOR_LAUNCHED();
-  c.bi_w = width; c.bi_h = height;
-  return 0;
-}
-
-static int launch_pad(Pic *p) {
-  Context &c = ctx();
-  if (p->pad_y == 0 && p->pad_c == 0) return 0;
-  dim3 grid(4, p->rows_y, 3);
-  k_pad<<<grid, 128, 0, c.stream>>>(p->view());
-  THOR_LAUNCHED();
+  Pic *rec = get_pic(hrec);
+  if (!rec) return fail("blockinfo: bad picture handle %d", hrec);
+  if (!deblock_data) return fail("blockinfo: NULL side information");
+  const int n = (rec->w / 4) * (rec->h / 4);
+  if (!rec->info) THOR_CUDA(cudaMalloc((void **)&rec->info, (size_t)n * 2));
+  uint16_t *st = (uint16_t *)stage_acquire((size_t)n * 2);
+  if (!st) return fail("blockinfo: staging allocation failed");
+  const int32_t *e = (const int32_t *)deblock_data;
+  for (int i = 0; i < n; i++, e += 11) st[i] = pack_blockinfo(e);
+  if (stage_commit_copy(rec->info, st, (size_t)n * 2)) return -1;
+  rec->info_ok = true;
   return 0;
 }
 
@@ -389,61 +385,111 @@ int thorcuda_pad_frame(thorcuda_pic h) {
   THOR_NEED_CTX();
   Pic *p = get_pic(h);
   if (!p) return fail("bad picture handle %d", h);
-  return launch_pad(p);
+  if (p->pad_y == 0 && p->pad_c == 0) return 0;
+  dim3 grid(4, p->rows_y, 3);
+  k_pad<<<grid, 128, 0, ctx().stream>>>(p->view());
+  THOR_LAUNCHED();
+  return 0;
+}
+
+int thorcuda_loopfilter_frames(int n, const thorcuda_lf_job *jobs) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  static const uint8_t beta[52] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15,
+                                   16, 17, 18, 20, 22, 24, 26, 28, 30, 32, 34, 36, 38, 40, 42, 44, 46, 48, 50, 52, 54, 56, 58, 60, 62, 64};
+  static const uint8_t tc[56] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2,
+                                 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 5, 5, 6, 6, 7, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13, 14, 14};
+  if (n <= 0) return 0;
+  if (n > 16384) return fail("loopfilter: too many frames in one batch");
+  // validate, size the per-SB bit scratch
+  size_t bits_total = 0;
+  int maxw = 0, maxh = 0, max_ref_rows = 0;
+  for (int i = 0; i < n; i++) {
+    const thorcuda_lf_job &j = jobs[i];
+    Pic *rec = get_pic(j.rec), *org = j.org >= 0 ? get_pic(j.org) : nullptr, *ref = j.ref_out >= 0 ? get_pic(j.ref_out) : nullptr;
+    if (!rec) return fail("loopfilter: bad rec handle");
+    if (j.org >= 0 && !org) return fail("loopfilter: bad org handle");
+    if (j.ref_out >= 0 && !ref) return fail("loopfilter: bad ref handle");
+    if (rec->pad_y || rec->pad_c) return fail("loopfilter: rec must be an unpadded picture");
+    if (j.qp < 0 || j.qp > 51) return fail("loopfilter: qp %d out of range", j.qp);
+    if ((j.stages & (THORCUDA_LF_DEBLOCK_Y | THORCUDA_LF_DEBLOCK_UV | THORCUDA_LF_CLPF)) && !rec->info_ok)
+      return fail("loopfilter: no side information uploaded for picture %d", j.rec);
+    if ((org && (org->w != rec->w || org->h != rec->h)) || (ref && (ref->w != rec->w || ref->h != rec->h)))
+      return fail("loopfilter: picture size mismatch");
+    if ((j.stages & THORCUDA_LF_CLPF) && !org && !j.sb_bits_in && (rec->w / 64) * (rec->h / 64) > 0)
+      return fail("loopfilter: decoder-mode CLPF needs sb_bits_in");
+    for (int k = 0; k < i; k++) if (jobs[k].rec == j.rec) return fail("loopfilter: picture %d appears twice in one batch", j.rec);
+    if (!rec->buf[1 - rec->cur]) THOR_CUDA(cudaMalloc((void **)&rec->buf[1 - rec->cur], rec->bytes + 256));
+    bits_total += 2 * (size_t)((rec->w / 64) * (rec->h / 64) + 1);
+    maxw = max(maxw, rec->w); maxh = max(maxh, rec->h);
+    if (ref && (j.stages & THORCUDA_LF_MAKE_REF)) max_ref_rows = max(max_ref_rows, ref->rows_y);
+  }
+  uint8_t *d_bits = (uint8_t *)c.scratch.reserve(bits_total);
+  LfParams *d_jobs = (LfParams *)c.lfjobs.reserve(sizeof(LfParams) * n);
+  uint8_t *st = (uint8_t *)stage_acquire(sizeof(LfParams) * n + bits_total);
+  if (!d_bits || !d_jobs || !st) return fail("loopfilter: allocation failed");
+  LfParams *hj = (LfParams *)st;
+  uint8_t *hbits = st + sizeof(LfParams) * n;
+  size_t off = 0;
+  bool any_bits_in = false;
+  for (int i = 0; i < n; i++) {
+    const thorcuda_lf_job &j = jobs[i];
+    Pic *rec = get_pic(j.rec), *org = j.org >= 0 ? get_pic(j.org) : nullptr, *ref = j.ref_out >= 0 ? get_pic(j.ref_out) : nullptr;
+    const int nsbx = rec->w / 64, nsby = rec->h / 64, nsb = nsbx * nsby;
+    LfParams &P = hj[i];
+    memset(&P, 0, sizeof(P));
+    P.src = rec->view(rec->cur);
+    P.dstA = rec->view(1 - rec->cur);
+    if (ref && (j.stages & THORCUDA_LF_MAKE_REF)) P.dstB = ref->view(); else { P.dstB = P.dstA; P.dstB.p[0] = nullptr; }
+    if (org) P.org = org->view(); else { P.org = P.src; P.org.p[0] = nullptr; }
+    P.info = rec->info;
+    P.bw = rec->w / 4;
+    P.beta = beta[j.qp]; P.tc_y = tc[j.qp]; P.tc_c = tc[h_chroma_qp[j.qp]];
+    P.stages = j.stages;
+    P.nsbx_full = nsbx; P.nsby_full = nsby;
+    P.bits_in = nullptr; P.bits_out = nullptr;
+    P.self = c.d_pics + j.rec;
+    if ((j.stages & THORCUDA_LF_CLPF) && nsb > 0) {
+      if (!org) {
+        memcpy(hbits + off, j.sb_bits_in, nsb);
+        P.bits_in = d_bits + off;
+        any_bits_in = true;
+      }
+      P.bits_out = d_bits + off + nsb + 1;
+    }
+    off += 2 * (size_t)(nsb + 1);
+  }
+  // one staged copy carries the job table and (decoder mode) the signalled bits
+  THOR_CUDA(cudaMemcpyAsync(d_jobs, hj, sizeof(LfParams) * n, cudaMemcpyHostToDevice, c.stream));
+  if (any_bits_in) { if (stage_commit_copy(d_bits, hbits, bits_total)) return -1; }
+  else if (stage_commit_copy(d_jobs, hj, 0)) return -1;
+  dim3 grid((maxw + 63) / 64, (maxh + 63) / 64, n);
+  k_loopfilter<<<grid, LF_THREADS, 0, c.stream>>>(d_jobs);
+  THOR_LAUNCHED();
+  off = 0;
+  for (int i = 0; i < n; i++) {
+    const thorcuda_lf_job &j = jobs[i];
+    Pic *rec = get_pic(j.rec);
+    const int nsb = (rec->w / 64) * (rec->h / 64);
+    rec->cur ^= 1;                                   // the kernel updated the device picture table itself
+    if ((j.stages & THORCUDA_LF_CLPF) && nsb > 0 && j.sb_bits_out)
+      if (d2h(j.sb_bits_out, d_bits + off + nsb + 1, nsb)) return -1;
+    off += 2 * (size_t)(nsb + 1);
+  }
+  if (max_ref_rows) {
+    dim3 pg(4, max_ref_rows, 3 * n);
+    k_pad_jobs<<<pg, 128, 0, c.stream>>>(d_jobs);
+    THOR_LAUNCHED();
+  }
+  return 0;
 }
 
 int thorcuda_loopfilter_frame(thorcuda_pic hrec, thorcuda_pic horg, thorcuda_pic href, int qp, int stages,
                               const uint8_t *sb_bits_in, uint8_t *sb_bits_out) {
-  THOR_NEED_CTX();
-  Context &c = ctx();
-  Pic *rec = get_pic(hrec), *org = horg >= 0 ? get_pic(horg) : nullptr, *ref = href >= 0 ? get_pic(href) : nullptr;
-  if (!rec) return fail("loopfilter: bad rec handle");
-  if (horg >= 0 && !org) return fail("loopfilter: bad org handle");
-  if (href >= 0 && !ref) return fail("loopfilter: bad ref handle");
-  if (rec->pad_y || rec->pad_c) return fail("loopfilter: rec must be an unpadded picture");
-  if (qp < 0 || qp > 51) return fail("loopfilter: qp %d out of range", qp);
-  if (c.bi_w != rec->w || c.bi_h != rec->h) return fail("loopfilter: no side information uploaded for %dx%d", rec->w, rec->h);
-  if ((org && (org->w != rec->w || org->h != rec->h)) || (ref && (ref->w != rec->w || ref->h != rec->h)))
-    return fail("loopfilter: picture size mismatch");
-  if (!rec->buf[1 - rec->cur]) {
-    THOR_CUDA(cudaMalloc((void **)&rec->buf[1 - rec->cur], rec->bytes + 256));
-  }
-  const int nsbx = rec->w / 64, nsby = rec->h / 64, nsb = nsbx * nsby;
-  uint8_t *d_bits = (uint8_t *)c.sb_bits.reserve((size_t)2 * (nsb + 1));
-  if (!d_bits) return fail("loopfilter: device allocation failed");
-  LfParams P;
-  P.src = rec->view(rec->cur);
-  P.dstA = rec->view(1 - rec->cur);
-  if (ref && (stages & THORCUDA_LF_MAKE_REF)) P.dstB = ref->view(); else { P.dstB = P.dstA; P.dstB.p[0] = nullptr; }
-  if (org) P.org = org->view(); else { P.org = P.src; P.org.p[0] = nullptr; }
-  P.info = (const uint16_t *)c.blockinfo_packed.p;
-  P.bw = rec->w / 4;
-  P.beta = 0; P.tc_y = 0; P.tc_c = 0;
-  {
-    static const uint8_t beta[52] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15,
-                                     16, 17, 18, 20, 22, 24, 26, 28, 30, 32, 34, 36, 38, 40, 42, 44, 46, 48, 50, 52, 54, 56, 58, 60, 62, 64};
-    static const uint8_t tc[56] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2,
-                                   2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 5, 5, 6, 6, 7, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13, 14, 14};
-    P.beta = beta[qp]; P.tc_y = tc[qp]; P.tc_c = tc[h_chroma_qp[qp]];
-  }
-  P.stages = stages;
-  P.nsbx_full = nsbx; P.nsby_full = nsby;
-  P.bits_in = nullptr; P.bits_out = nullptr;
-  if ((stages & THORCUDA_LF_CLPF) && nsb > 0) {
-    if (!org) {
-      if (!sb_bits_in) return fail("loopfilter: decoder-mode CLPF needs sb_bits_in");
-      THOR_CUDA(cudaMemcpyAsync(d_bits, sb_bits_in, nsb, cudaMemcpyHostToDevice, c.stream));
-      P.bits_in = d_bits;
-    }
-    P.bits_out = d_bits + nsb + 1;
-  }
-  dim3 grid((rec->w + 63) / 64, (rec->h + 63) / 64, 1);
-  k_loopfilter<<<grid, LF_THREADS, 0, c.stream>>>(P);
-  THOR_LAUNCHED();
-  rec->cur ^= 1;
-  if (P.bits_out && sb_bits_out) THOR_CUDA(cudaMemcpyAsync(sb_bits_out, P.bits_out, nsb, cudaMemcpyDeviceToHost, c.stream));
-  if (ref && (stages & THORCUDA_LF_MAKE_REF)) return launch_pad(ref);
-  return 0;
+  thorcuda_lf_job j;
+  j.rec = hrec; j.org = horg; j.ref_out = href; j.qp = qp; j.stages = stages;
+  j.sb_bits_in = sb_bits_in; j.sb_bits_out = sb_bits_out;
+  return thorcuda_loopfilter_frames(1, &j);
 }
 
 }  // extern "C"

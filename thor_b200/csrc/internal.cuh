@@ -1,9 +1,10 @@
-// libthorcuda internals: context, device pictures, scratch buffers, launch bookkeeping.
+// libthorcuda internals: context, device pictures, staging, task lists, launch bookkeeping.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <vector>
 #include "../../include/thorcuda.h"
 
 namespace thor {
@@ -14,17 +15,9 @@ struct PicView {
   int stride[3];       // bytes per row (U and V share stride_c)
   int w, h;            // luma size
   int pad[3];          // border width of each plane
-};
-
-struct Pic {
-  bool used = false;
-  int w = 0, h = 0, pad_y = 0, pad_c = 0, stride_y = 0, stride_c = 0, rows_y = 0, rows_c = 0;
-  size_t bytes = 0;
-  uint8_t *buf[2] = {nullptr, nullptr};   // buf[cur] holds the picture; the other is the filter target
-  int cur = 0;
-  PicView view(int which) const;
-  PicView view() const { return view(cur); }
-};
+  int reserved;
+};                     // 64 bytes
+static_assert(sizeof(PicView) == 64, "PicView is mirrored in a device table");
 
 struct DevBuf {   // grow-only device scratch
   void *p = nullptr; size_t cap = 0;
@@ -37,6 +30,50 @@ struct PinBuf {   // grow-only pinned host scratch
   void release();
 };
 
+struct Pic {
+  bool used = false;
+  int w = 0, h = 0, pad_y = 0, pad_c = 0, stride_y = 0, stride_c = 0, rows_y = 0, rows_c = 0;
+  size_t bytes = 0;
+  uint8_t *buf[2] = {nullptr, nullptr};   // buf[cur] holds the picture; the other is the filter target
+  int cur = 0;
+  uint16_t *info = nullptr;               // packed side information (2 bytes per 4x4 luma unit)
+  bool info_ok = false;
+  PicView view(int which) const;
+  PicView view() const { return view(cur); }
+};
+
+// A resident task list (thorcuda_list_create).
+struct List {
+  bool used = false;
+  int kind = -1, ntasks = 0, npics = 0, ntiles = 0;
+  std::vector<int> pics;                  // handles
+  uint8_t *blob = nullptr;                // one device allocation: tasks | tiles | map
+  size_t off_tiles = 0, off_map = 0, blob_bytes = 0;
+  // TB lists
+  size_t pool_entries = 0;
+  int16_t *pool = nullptr;                // quantised coefficients
+  uint8_t *cbp = nullptr;
+  uint32_t *ssd = nullptr;
+  int ntb[5] = {0, 0, 0, 0, 0};           // tasks per transform size 4,8,16,32,64 (tasks are sorted by size)
+  int tb_first[5] = {0, 0, 0, 0, 0};
+  uint32_t *order = nullptr;              // device: sorted position -> task index
+  // COST lists
+  thorcuda_cost_result *results = nullptr;
+  const void *tasks() const { return blob; }
+  const void *tiles() const { return blob + off_tiles; }
+  const uint16_t *map() const { return (const uint16_t *)(blob + off_map); }
+};
+
+struct StageSlot { PinBuf buf; cudaEvent_t ev = nullptr; bool pending = false; };
+
+struct SadSlot {
+  bool used = false;
+  int w = 0, h = 0, range = 0;
+  void *tab[4] = {nullptr, nullptr, nullptr, nullptr};   // levels 8,16,32,64
+  size_t bytes[4] = {0, 0, 0, 0};
+  size_t cap[4] = {0, 0, 0, 0};
+};
+
 struct Context {
   bool ready = false;
   int device = -1;
@@ -44,22 +81,33 @@ struct Context {
   cudaStream_t stream = nullptr;
   uint64_t launches = 0;
   char err[512] = {0};
-  Pic pics[256];
-  // side information of the current frame, packed (2 bytes per 4x4 unit)
-  DevBuf blockinfo_raw, blockinfo_packed;
-  int bi_w = 0, bi_h = 0;
-  DevBuf sb_bits, tasks, results, pool, cbp, ssd, refs;
-  PinBuf h_tasks, h_misc;
-  // sad tables: level 0..3 = block size 8,16,32,64
-  DevBuf sadtab[4];
-  size_t sadtab_bytes[4] = {0, 0, 0, 0};
-  int sad_range = 0, sad_w = 0, sad_h = 0;
-  DevBuf centres;
+  Pic pics[THORCUDA_MAX_PICS];
+  PicView *d_pics = nullptr;              // device mirror of view() of every picture, indexed by handle
+  List lists[256];
+  StageSlot stage[8];
+  int stage_next = 0;
+  std::vector<std::pair<uintptr_t, size_t>> pinned;   // thorcuda_host_alloc ranges
+  DevBuf raw_info, scratch, flush, lfjobs, sadjobs, centres;
+  cudaEvent_t tm0[64], tm1[64];
+  bool tm_used[64] = {false};
+  SadSlot sad[THORCUDA_SAD_SLOTS];
 };
 
 Context &ctx();
 int fail(const char *fmt, ...);
 Pic *get_pic(thorcuda_pic h);
+List *get_list(thorcuda_list h);
+[[noreturn]] void die(const char *msg);   // fatalerror() convention: message on stderr, abort()
+
+// Queue a host->device copy of a caller buffer: through the pinned staging ring (the caller may reuse
+// src on return) unless src lies in thorcuda_host_alloc memory (then it is the DMA source itself).
+int h2d(void *dst, const void *src, size_t bytes);
+// Pinned staging memory the caller fills itself, then queues with stage_commit_copy().
+void *stage_acquire(size_t bytes);
+int stage_commit_copy(void *dst, const void *staged, size_t bytes);
+int d2h(void *dst, const void *src, size_t bytes);
+// refresh the device mirror entry of picture h
+int sync_pic_view(thorcuda_pic h);
 
 #define THOR_CUDA(call)                                                                   \
   do {                                                                                    \
@@ -74,8 +122,11 @@ Pic *get_pic(thorcuda_pic h);
 #define THOR_LAUNCHED()                                                                   \
   do { thor::ctx().launches++; THOR_CUDA(cudaGetLastError()); } while (0)
 
-[[noreturn]] void die(const char *msg);   // fatalerror() convention: message on stderr, abort()
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
+__device__ __forceinline__ int clip255(int v) { return min(max(v, 0), 255); }
 
-// reference tables living in constant memory (defined in tables.cu)
-// DCT bases: c_dct4[k*4+n] ... c_dct32[k*32+n]; zig-zag scan positions; deblock thresholds.
+// reference common/common_block.c:78-83
+static const uint8_t h_chroma_qp[52] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 25,
+                                        26, 27, 28, 29, 29, 30, 31, 32, 33, 33, 34, 34, 35, 35, 36, 36, 37, 37, 38, 39, 40, 41, 42, 43, 44, 45};
+
 }  // namespace thor

@@ -9,6 +9,7 @@
 // shared memory with aligned 32-bit loads, the separable filter runs vertical-then-horizontal exactly
 // like the reference (single rounding at the end), results leave as 32-bit words.
 #include "internal.cuh"
+#include "lists.cuh"
 
 namespace thor {
 
@@ -18,24 +19,20 @@ __constant__ int8_t c_luma_uni[4][6] = {{0, 0, 64, 0, 0, 0}, {1, -7, 55, 19, -5,
 __constant__ int8_t c_chroma[8][4] = {{0, 64, 0, 0}, {-2, 58, 10, -2}, {-4, 54, 16, -2}, {-4, 44, 28, -4},
                                       {-4, 36, 36, -4}, {-4, 28, 44, -4}, {-2, 16, 54, -4}, {-2, 10, 58, -2}};
 
-struct PredTile { uint32_t task; uint8_t tx, ty, pad0, pad1; };   // tile offset in units of 16 luma samples
-
 constexpr int PW = 8;                 // warps per CTA
 constexpr int WIN_PITCH = 24;         // bytes per staged window row (21 + up to 3 alignment bytes)
 constexpr int WIN_ROWS = 21;
 constexpr int TMP_PITCH = 22;         // int16 per row of the vertical-pass result
 
 struct PredParams {
-  PicView dst;
-  const PicView *refs;                // device array
+  const PicView *pics;                // device picture table, indexed by handle
+  const uint16_t *map;                // list-local picture index -> handle
   const thorcuda_pred_task *tasks;
   const PredTile *tiles;
   int ntiles;
   int bipred_filter;
   int planes;
 };
-
-__device__ __forceinline__ int clip255(int v) { return min(max(v, 0), 255); }
 
 // Stage rows [0,rows) x bytes [0,cols) starting at src (any alignment) into win (pitch WIN_PITCH);
 // returns the byte offset of src inside the first staged word.
@@ -196,12 +193,15 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
   const int mv0x = t.sign0 ? -t.mv0x : t.mv0x, mv0y = t.sign0 ? -t.mv0y : t.mv0y;
   const int mv1x = t.sign1 ? -t.mv1x : t.mv1x, mv1y = t.sign1 ? -t.mv1y : t.mv1y;
   const bool bi = t.ref1 >= 0;
+  const PicView dst = P.pics[P.map[t.dst]];
+  const PicView r0 = P.pics[P.map[t.ref0]];
+  const PicView r1 = P.pics[P.map[bi ? t.ref1 : t.ref0]];
 
   if (P.planes & 1) {
     uint32_t a[2] = {0, 0}, b[2] = {0, 0};
-    luma_tile(P.refs[t.ref0], x, y, tw, th, mv0x, mv0y, P.bipred_filter, win, tmp, lane, a);
+    luma_tile(r0, x, y, tw, th, mv0x, mv0y, P.bipred_filter, win, tmp, lane, a);
     if (bi) {
-      luma_tile(P.refs[t.ref1], x, y, tw, th, mv1x, mv1y, P.bipred_filter, win, tmp, lane, b);
+      luma_tile(r1, x, y, tw, th, mv1x, mv1y, P.bipred_filter, win, tmp, lane, b);
       a[0] = avg_trunc4(a[0], b[0]);
       a[1] = avg_trunc4(a[1], b[1]);
     }
@@ -210,17 +210,15 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
     for (int k = 0; k < 2; k++) {
       const int g = lane + 32 * k;
       if (g < gpr * th)
-        *reinterpret_cast<uint32_t *>(P.dst.p[0] + (size_t)(y + g / gpr) * P.dst.stride[0] + x + 4 * (g % gpr)) = a[k];
+        *reinterpret_cast<uint32_t *>(dst.p[0] + (size_t)(y + g / gpr) * dst.stride[0] + x + 4 * (g % gpr)) = a[k];
     }
   }
   if (P.planes & 2) {
     const int cx = x >> 1, cy = y >> 1, cw = tw >> 1, ch = th >> 1;
     for (int pl = 1; pl <= 2; pl++) {
       int a[2] = {0, 0}, b[2] = {0, 0};
-      const PicView &r0 = P.refs[t.ref0];
       chroma_tile(r0.p[pl], r0.stride[pl], cx, cy, cw, ch, mv0x, mv0y, win, tmp, lane, a);
       if (bi) {
-        const PicView &r1 = P.refs[t.ref1];
         chroma_tile(r1.p[pl], r1.stride[pl], cx, cy, cw, ch, mv1x, mv1y, win, tmp, lane, b);
         a[0] = (a[0] + b[0]) >> 1;
         a[1] = (a[1] + b[1]) >> 1;
@@ -228,7 +226,7 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
 #pragma unroll
       for (int k = 0; k < 2; k++) {
         const int s = lane + 32 * k;
-        if (s < cw * ch) P.dst.p[pl][(size_t)(cy + s / cw) * P.dst.stride[pl] + cx + (s % cw)] = (uint8_t)a[k];
+        if (s < cw * ch) dst.p[pl][(size_t)(cy + s / cw) * dst.stride[pl] + cx + (s % cw)] = (uint8_t)a[k];
       }
     }
   }
@@ -238,66 +236,34 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
 
 using namespace thor;
 
-extern "C" int thorcuda_predict_blocks(thorcuda_pic hdst, const thorcuda_pic *refs, int nrefs, const thorcuda_pred_task *tasks,
-                                       int ntasks, int bipred_filter, int planes) {
+extern "C" {
+
+int thorcuda_predict_list(thorcuda_list hl, int bipred_filter, int planes) {
   THOR_NEED_CTX();
   Context &c = ctx();
-  Pic *dst = get_pic(hdst);
-  if (!dst) return fail("predict: bad dst handle");
-  if (nrefs <= 0 || nrefs > 64) return fail("predict: nrefs %d out of range", nrefs);
-  if (ntasks <= 0) return 0;
-  PicView rv[64];
-  for (int i = 0; i < nrefs; i++) {
-    Pic *r = get_pic(refs[i]);
-    if (!r) return fail("predict: bad ref handle %d", refs[i]);
-    if (r->w != dst->w || r->h != dst->h) return fail("predict: reference size mismatch");
-    rv[i] = r->view();
-  }
-  // validate tasks and expand into <=16x16 tiles
-  size_t ntiles = 0;
-  for (int i = 0; i < ntasks; i++) ntiles += (size_t)((tasks[i].w + 15) / 16) * ((tasks[i].h + 15) / 16);
-  const size_t task_bytes = (size_t)ntasks * sizeof(thorcuda_pred_task), tile_bytes = ntiles * sizeof(PredTile);
-  const size_t tile_off = (task_bytes + 15) & ~(size_t)15, ref_off = (tile_off + tile_bytes + 15) & ~(size_t)15;
-  const size_t total = ref_off + sizeof(PicView) * nrefs;
-  uint8_t *hbuf = (uint8_t *)c.h_tasks.reserve(total);
-  uint8_t *dbuf = (uint8_t *)c.tasks.reserve(total);
-  if (!hbuf || !dbuf) return fail("predict: staging allocation failed");
-  THOR_CUDA(cudaStreamSynchronize(c.stream));     // the pinned staging buffer may still be in flight
-  memcpy(hbuf, tasks, task_bytes);
-  PredTile *tl = (PredTile *)(hbuf + tile_off);
-  size_t k = 0;
-  for (int i = 0; i < ntasks; i++) {
-    const thorcuda_pred_task &t = tasks[i];
-    if (t.w < 4 || t.h < 4 || t.w > 64 || t.h > 64 || (t.w & 3) || (t.h & 3) || t.x + t.w > dst->w || t.y + t.h > dst->h ||
-        (t.x & 3) || (t.y & 3))
-      return fail("predict: task %d has an invalid block (%d,%d %dx%d)", i, t.x, t.y, t.w, t.h);
-    for (int pass = 0; pass < 2; pass++) {
-      const int rix = pass ? t.ref1 : t.ref0;
-      if (pass && rix < 0) break;
-      if (rix < 0 || rix >= nrefs) return fail("predict: task %d references picture %d of %d", i, rix, nrefs);
-      Pic *r = get_pic(refs[rix]);
-      const int sgn = pass ? t.sign1 : t.sign0;
-      const int mx = sgn ? -(pass ? t.mv1x : t.mv0x) : (pass ? t.mv1x : t.mv0x);
-      const int my = sgn ? -(pass ? t.mv1y : t.mv0y) : (pass ? t.mv1y : t.mv0y);
-      const int lx = t.x + (mx >> 2), ly = t.y + (my >> 2);
-      // filter reach: 2 left/up, 3 right/down (luma); the padded picture must contain the window
-      if (lx - 2 < -r->pad_y || ly - 2 < -r->pad_y || lx + t.w + 3 > r->w + r->pad_y || ly + t.h + 3 > r->h + r->pad_y)
-        return fail("predict: task %d reads outside the padded reference (mv %d,%d)", i, mx, my);
-    }
-    for (int ty = 0; ty < (t.h + 15) / 16; ty++)
-      for (int tx = 0; tx < (t.w + 15) / 16; tx++) tl[k++] = PredTile{(uint32_t)i, (uint8_t)tx, (uint8_t)ty, 0, 0};
-  }
-  memcpy(hbuf + ref_off, rv, sizeof(PicView) * nrefs);
-  THOR_CUDA(cudaMemcpyAsync(dbuf, hbuf, total, cudaMemcpyHostToDevice, c.stream));
+  List *L = get_list(hl);
+  if (!L || L->kind != THORCUDA_LIST_PRED) return fail("predict: not a prediction list");
   PredParams P;
-  P.dst = dst->view();
-  P.refs = (const PicView *)(dbuf + ref_off);
-  P.tasks = (const thorcuda_pred_task *)dbuf;
-  P.tiles = (const PredTile *)(dbuf + tile_off);
-  P.ntiles = (int)ntiles;
+  P.pics = c.d_pics;
+  P.map = L->map();
+  P.tasks = (const thorcuda_pred_task *)L->tasks();
+  P.tiles = (const PredTile *)L->tiles();
+  P.ntiles = L->ntiles;
   P.bipred_filter = bipred_filter;
   P.planes = planes;
-  k_predict<<<(unsigned)((ntiles + PW - 1) / PW), PW * 32, 0, c.stream>>>(P);
+  k_predict<<<(unsigned)((L->ntiles + PW - 1) / PW), PW * 32, 0, c.stream>>>(P);
   THOR_LAUNCHED();
   return 0;
 }
+
+int thorcuda_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_pred_task *tasks, int ntasks,
+                            int bipred_filter, int planes) {
+  if (ntasks <= 0) return 0;
+  const thorcuda_list l = thorcuda_list_create(THORCUDA_LIST_PRED, pics, npics, tasks, ntasks);
+  if (l < 0) return -1;
+  const int rc = thorcuda_predict_list(l, bipred_filter, planes);
+  thorcuda_list_destroy(l);
+  return rc;
+}
+
+}  // extern "C"

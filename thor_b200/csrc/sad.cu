@@ -1,0 +1,432 @@
+// libthorcuda: motion-search costs.
+//
+//  (1) k_sad_table : whole-frame integer-pel SAD tables for the 8/16/32/64 block levels in one pass
+//                    (restates sad_calc, reference enc/encode_block.c:740-755, for every block and every
+//                    displacement of the search window; larger levels are sums of the 8x8 level, which is
+//                    exact because SAD is additive over disjoint sub-blocks).
+//  (2) k_cost_batch: one warp per (block, candidate) task: sad_calc, widesad_calc (:757-780),
+//                    sad_calc_fasthalf (:497-605), sad_calc_fastquarter (:609-738), ssd_calc (:782-797).
+//
+// Bound: integer ALU (VABSDIFF4.U8.ACC = 4 abs-diffs + accumulate per lane per instruction), not HBM.
+#include <string.h>
+#include "internal.cuh"
+
+namespace thor {
+
+struct SadJob {
+  PicView org, ref;
+  const int16_t *centres;       // device, (cx,cy) per SB, or nullptr
+  uint16_t *t8, *t16;
+  uint32_t *t32, *t64;
+};
+
+constexpr int SAD_THREADS = 256;
+
+__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) { return __vsadu4(a, b) + acc; }
+
+// One CTA per 64x64 superblock.  Shared memory: original SB (64x64) | reference window
+// (64+2R rows, pitch bytes) | 32x32-level accumulators [4][n*n] | 64x64-level accumulator [n*n], n = 2R+1.
+// Warp w owns block-row pair p = w & 3 (two rows of 8x8 blocks) and column half ch = w >> 2;
+// lane = (bxl = lane >> 3: block column inside the half, d8 = lane & 7: one of 8 consecutive dx).
+// A thread keeps its two 8x8 original blocks in 32 registers and slides down the window: at each
+// reference row it adds that row's contribution to the 8 displacements dy it belongs to (rotating
+// accumulators, statically indexed because the row loop is unrolled by 8).
+__global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs, int R) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const SadJob &J = jobs[blockIdx.z];
+  const int W = J.org.w, H = J.org.h;
+  const int x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
+  if (x0 >= W || y0 >= H) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n = 2 * R + 1, nn = n * n;
+  const int win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
+  uint8_t *sOrg = smem;
+  uint8_t *sWin = smem + 64 * 64;
+  uint32_t *acc32 = reinterpret_cast<uint32_t *>(sWin + ((win_rows * pitch + 15) & ~15));
+  uint32_t *acc64 = acc32 + 4 * nn;
+
+  int cx = 0, cy = 0;
+  if (J.centres) {
+    const int sb = blockIdx.y * gridDim.x + blockIdx.x;    // host lays centres out with the launch's SB pitch
+    cx = J.centres[2 * sb]; cy = J.centres[2 * sb + 1];
+  }
+  const int wx = x0 + cx - R, wy = y0 + cy - R;
+  const int o = wx & 3, ax = wx - o;
+  {
+    const int pad = J.ref.pad[0], stride = J.ref.stride[0], wpr = pitch >> 2;
+    const uint8_t *rp = J.ref.p[0];
+    for (int i = tid; i < win_rows * wpr; i += SAD_THREADS) {
+      const int r = i / wpr, wd = i - r * wpr;
+      const int gy = clampi(wy + r, -pad, H + pad - 1), gx = clampi(ax + 4 * wd, -pad, W + pad - 4);
+      reinterpret_cast<uint32_t *>(sWin + r * pitch)[wd] = *reinterpret_cast<const uint32_t *>(rp + (ptrdiff_t)gy * stride + gx);
+    }
+    const uint8_t *op = J.org.p[0];
+    const int ostride = J.org.stride[0];
+    for (int i = tid; i < 64 * 16; i += SAD_THREADS) {
+      const int r = i >> 4, wd = i & 15;
+      const int gy = min(y0 + r, H - 1), gx = min(x0 + 4 * wd, W - 4);
+      reinterpret_cast<uint32_t *>(sOrg)[i] = *reinterpret_cast<const uint32_t *>(op + (size_t)gy * ostride + gx);
+    }
+    for (int i = tid; i < 5 * nn; i += SAD_THREADS) acc32[i] = 0;
+  }
+  __syncthreads();
+
+  const int p = warp & 3, ch = warp >> 2, d8 = lane & 7, bxl = lane >> 3, bx = 4 * ch + bxl;
+  uint32_t oT[8][2], oB[8][2];
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const uint32_t *a = reinterpret_cast<const uint32_t *>(sOrg + (16 * p + r) * 64 + bx * 8);
+    const uint32_t *b = reinterpret_cast<const uint32_t *>(sOrg + (16 * p + 8 + r) * 64 + bx * 8);
+    oT[r][0] = a[0]; oT[r][1] = a[1]; oB[r][0] = b[0]; oB[r][1] = b[1];
+  }
+  // which outputs exist (frame edges) and where they go
+  const int gx8 = x0 + bx * 8, gyT = y0 + 16 * p, gyB = gyT + 8;
+  const bool okx8 = gx8 + 8 <= W;
+  const bool okT = okx8 && gyT + 8 <= H, okB = okx8 && gyB + 8 <= H;
+  const bool ok16 = !(bxl & 1) && gx8 + 16 <= W && gyT + 16 <= H;
+  const bool ok32 = bxl == 0;
+  const int bw8 = W >> 3, bw16 = W >> 4;
+  uint16_t *t8T = J.t8 + ((size_t)(gyT >> 3) * bw8 + (gx8 >> 3)) * nn;
+  uint16_t *t8B = J.t8 + ((size_t)(gyB >> 3) * bw8 + (gx8 >> 3)) * nn;
+  uint16_t *t16 = J.t16 + ((size_t)(gyT >> 4) * bw16 + (gx8 >> 4)) * nn;
+  uint32_t *a32 = acc32 + ((p >> 1) * 2 + ch) * nn;
+
+  const int ngroups = (n + 7) >> 3;
+  for (int g = 0; g < ngroups; g++) {
+    const int dxi_raw = g * 8 + d8;
+    const bool act = dxi_raw < n;
+    const int dxi = act ? dxi_raw : n - 1;
+    const int off = bx * 8 + dxi + o;
+    const int sh = (off & 3) * 8;
+    const uint8_t *colT = sWin + (16 * p) * pitch + (off & ~3);
+    uint32_t aT[8], aB[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { aT[k] = 0; aB[k] = 0; }
+    for (int jj = 0; jj < 8 + 2 * R; jj += 8) {
+#pragma unroll
+      for (int s = 0; s < 8; s++) {
+        const int j = jj + s;
+        const uint32_t *rt = reinterpret_cast<const uint32_t *>(colT + j * pitch);
+        const uint32_t *rb = reinterpret_cast<const uint32_t *>(colT + (j + 8) * pitch);
+        const uint32_t t0 = rt[0], t1 = rt[1], t2 = rt[2], b0 = rb[0], b1 = rb[1], b2 = rb[2];
+        const uint32_t wT0 = __funnelshift_r(t0, t1, sh), wT1 = __funnelshift_r(t1, t2, sh);
+        const uint32_t wB0 = __funnelshift_r(b0, b1, sh), wB1 = __funnelshift_r(b1, b2, sh);
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+          const int k = (s - r) & 7;
+          aT[k] = sad4(oT[r][0], wT0, aT[k]); aT[k] = sad4(oT[r][1], wT1, aT[k]);
+          aB[k] = sad4(oB[r][0], wB0, aB[k]); aB[k] = sad4(oB[r][1], wB1, aB[k]);
+        }
+        const int kc = (s + 1) & 7, dyi = j - 7;    // displacement row dyi is complete
+        if (dyi >= 0) {
+          const uint32_t vT = aT[kc], vB = aB[kc];
+          const int e = dyi * n + dxi;
+          if (act && okT) t8T[e] = (uint16_t)vT;
+          if (act && okB) t8B[e] = (uint16_t)vB;
+          uint32_t v = vT + vB;
+          v += __shfl_xor_sync(0xffffffffu, v, 8);
+          if (act && ok16) t16[e] = (uint16_t)v;
+          v += __shfl_xor_sync(0xffffffffu, v, 16);
+          if (act && ok32) { atomicAdd(a32 + e, v); atomicAdd(acc64 + e, v); }
+        }
+        aT[kc] = 0; aB[kc] = 0;
+      }
+    }
+  }
+  __syncthreads();
+  // 32x32 and 64x64 levels: coalesced 32-bit rows
+  const int bw32 = W >> 5, bw64 = W >> 6;
+#pragma unroll 1
+  for (int q = 0; q < 4; q++) {
+    const int gx = x0 + (q & 1) * 32, gy = y0 + (q >> 1) * 32;
+    if (gx + 32 > W || gy + 32 > H) continue;
+    uint32_t *dst = J.t32 + ((size_t)(gy >> 5) * bw32 + (gx >> 5)) * nn;
+    for (int i = tid; i < nn; i += SAD_THREADS) dst[i] = acc32[q * nn + i];
+  }
+  if (x0 + 64 <= W && y0 + 64 <= H) {
+    uint32_t *dst = J.t64 + ((size_t)(y0 >> 6) * bw64 + (x0 >> 6)) * nn;
+    for (int i = tid; i < nn; i += SAD_THREADS) dst[i] = acc64[i];
+  }
+}
+
+// --------------------------------------------------------------------------- cost batch ----
+constexpr int CW = 8;                         // warps per CTA
+constexpr int CPITCH = 76;                    // window row: up to 64 + 3 + 3 samples + 3 alignment bytes
+constexpr int CROWS = 70;
+
+struct CostParams {
+  const PicView *pics;
+  const uint16_t *map;
+  const thorcuda_cost_task *tasks;
+  thorcuda_cost_result *out;
+  int ntasks, kind;
+};
+
+__device__ __forceinline__ int avg_up(int a, int b) { return (a + b + 1) >> 1; }   // v64_avg_u8
+__device__ __forceinline__ int avg_dn(int a, int b) { return (a + b) >> 1; }       // v64_rdavg_u8
+
+// bilinear diagonal half-pel sample between rows (sy-1,sy) and columns (sx-1,sx) of p (reference
+// enc/encode_block.c:527-571: a fixed tree of rounding / truncating averages)
+__device__ __forceinline__ int diag_half(const uint8_t *p, int sy, int sx) {
+  const uint8_t *q = p + (sy - 1) * CPITCH + (sx - 1);
+  const int core = avg_dn(avg_up(q[0], q[1]), avg_up(q[CPITCH], q[CPITCH + 1]));
+  const int vert = avg_dn(avg_up(q[-CPITCH], q[2 * CPITCH]), avg_up(q[-CPITCH + 1], q[2 * CPITCH + 1]));
+  const int hori = avg_dn(avg_up(q[-1], q[2]), avg_up(q[CPITCH - 1], q[CPITCH + 2]));
+  return avg_dn(avg_dn(vert, hori), core);
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+  return v;
+}
+
+__global__ void __launch_bounds__(CW * 32) k_cost_batch(const CostParams P) {
+  __shared__ __align__(16) uint8_t sWin[CW][CROWS * CPITCH];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ti = blockIdx.x * CW + warp;
+  if (ti >= P.ntasks) return;
+  const thorcuda_cost_task t = P.tasks[ti];
+  const PicView org = P.pics[P.map[t.org]], ref = P.pics[P.map[t.ref]];
+  const int w = t.w, h = t.h;
+  // stage reference rows -3..h+2, columns -3..w+2 around the candidate position
+  uint8_t *win = sWin[warp];
+  const uint8_t *src = ref.p[0] + (ptrdiff_t)(t.y + t.iy - 3) * ref.stride[0] + (t.x + t.ix - 3);
+  const int o = (int)((uintptr_t)src & 3);
+  {
+    const uint8_t *base = src - o;
+    const int words = (w + 6 + o + 3) >> 2;
+    for (int i = lane; i < (h + 6) * words; i += 32) {
+      const int r = i / words, wd = i - r * words;
+      reinterpret_cast<uint32_t *>(win + r * CPITCH)[wd] = *reinterpret_cast<const uint32_t *>(base + (ptrdiff_t)r * ref.stride[0] + 4 * wd);
+    }
+  }
+  __syncwarp();
+  const uint8_t *b00 = win + 3 * CPITCH + 3 + o;        // reference sample (0,0) of the candidate block
+  const uint8_t *a00 = org.p[0] + (size_t)t.y * org.stride[0] + t.x;
+  const int npix = w * h;
+  uint32_t s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const int kind = P.kind;
+  const int sel = (t.hx & t.hy) ? 0 : (t.hx ? 1 : (t.hy ? 2 : 3));
+  for (int i = lane; i < npix; i += 32) {
+    const int r = i / w, c = i - r * w;
+    const int A = a00[(size_t)r * org.stride[0] + c];
+    const uint8_t *p = b00 + r * CPITCH + c;
+    if (kind == THORCUDA_COST_SAD) {
+      s[0] += abs(A - p[0]);
+    } else if (kind == THORCUDA_COST_SSD) {
+      const int d = A - p[0];
+      s[0] += d * d;
+    } else if (kind == THORCUDA_COST_WIDESAD) {
+      s[0] += abs(A - p[-3]); s[1] += abs(A - p[-1]); s[2] += abs(A - p[0]); s[3] += abs(A - p[1]); s[4] += abs(A - p[3]);
+    } else if (kind == THORCUDA_COST_FASTHALF) {
+      // order: top down left right tl tr bl br
+      s[0] += abs(A - avg_up(p[0], p[-CPITCH]));
+      s[1] += abs(A - avg_up(p[0], p[CPITCH]));
+      s[2] += abs(A - avg_up(p[-1], p[0]));
+      s[3] += abs(A - avg_up(p[0], p[1]));
+      s[4] += abs(A - diag_half(p, 0, 0));
+      s[5] += abs(A - diag_half(p, 0, 1));
+      s[6] += abs(A - diag_half(p, 1, 0));
+      s[7] += abs(A - diag_half(p, 1, 1));
+    } else {
+      // fastquarter (enc/encode_block.c:609-738): a = here, b = up, c = up-right, d = right, e = down-right,
+      // f = down, g = down-left, hh = left; four formula sets chosen by the incoming half-pel offset
+      const int a = p[0], b = p[-CPITCH], c2 = p[-CPITCH + 1], d = p[1], e = p[CPITCH + 1], f = p[CPITCH], g = p[CPITCH - 1], hh = p[-1];
+      const int ad = avg_up(a, d), de = avg_up(d, e), af = avg_up(a, f), fe = avg_up(f, e), dc = avg_up(d, c2), ab = avg_up(a, b),
+                ah = avg_up(a, hh), gf = avg_up(g, f);
+      int v[8];   // tl top tr left right bl down br
+      if (sel == 0)      { v[0]=avg_dn(ad,af); v[1]=avg_dn(de,a); v[2]=avg_dn(ad,de); v[3]=avg_dn(ad,f); v[4]=avg_dn(ad,e); v[5]=avg_dn(af,fe); v[6]=avg_dn(de,f); v[7]=avg_dn(de,fe); }
+      else if (sel == 1) { v[0]=avg_dn(ad,ab); v[1]=avg_dn(dc,a); v[2]=avg_dn(ad,dc); v[3]=avg_dn(ad,a); v[4]=avg_dn(ad,d); v[5]=avg_dn(ad,af); v[6]=avg_dn(af,d); v[7]=avg_dn(ad,de); }
+      else if (sel == 2) { v[0]=avg_dn(ah,af); v[1]=avg_dn(af,a); v[2]=avg_dn(ad,af); v[3]=avg_dn(gf,a); v[4]=avg_dn(ad,f); v[5]=avg_dn(af,gf); v[6]=avg_dn(af,f); v[7]=avg_dn(af,fe); }
+      else               { v[0]=avg_dn(ah,ab); v[1]=avg_dn(ab,a); v[2]=avg_dn(ad,ab); v[3]=avg_dn(ah,a); v[4]=avg_dn(ad,a); v[5]=avg_dn(ah,af); v[6]=avg_dn(af,a); v[7]=avg_dn(af,ad); }
+#pragma unroll
+      for (int k = 0; k < 8; k++) s[k] += abs(A - v[k]);
+    }
+  }
+  const int nsum = (kind == THORCUDA_COST_SAD || kind == THORCUDA_COST_SSD) ? 1 : (kind == THORCUDA_COST_WIDESAD ? 5 : 8);
+#pragma unroll
+  for (int k = 0; k < 8; k++) if (k < nsum) s[k] = warp_sum(s[k]);
+  if (lane) return;
+  thorcuda_cost_result res;
+  res.cost = s[0]; res.x = 0; res.y = 0;
+  if (kind == THORCUDA_COST_WIDESAD) {
+    // first minimum in the order -3,-1,0,+1,+3 (enc/encode_block.c:764-776; SIMD packs (sad<<3)|idx: same order)
+    const int offx[5] = {-3, -1, 0, 1, 3};
+    uint32_t best = 1u << 31; int bx = 0;
+#pragma unroll
+    for (int k = 0; k < 5; k++) if (s[k] < best) { best = s[k]; bx = offx[k]; }
+    res.cost = best; res.x = (int16_t)bx;
+  } else if (kind == THORCUDA_COST_FASTHALF) {
+    // strict '<' in the order down,right,left,tl,tr,br,bl starting from top = (0,-2)  (:577-603)
+    uint32_t best = s[0]; int bx = 0, by = -2;
+    if (s[1] < best) { best = s[1]; bx = 0;  by = 2; }
+    if (s[3] < best) { best = s[3]; bx = 2;  by = 0; }
+    if (s[2] < best) { best = s[2]; bx = -2; by = 0; }
+    if (s[4] < best) { best = s[4]; bx = -2; by = -2; }
+    if (s[5] < best) { best = s[5]; bx = 2;  by = -2; }
+    if (s[7] < best) { best = s[7]; bx = 2;  by = 2; }
+    if (s[6] < best) { best = s[6]; bx = -2; by = 2; }
+    res.cost = best; res.x = (int16_t)bx; res.y = (int16_t)by;
+  } else if (kind == THORCUDA_COST_FASTQUARTER) {
+    // start from top = (0,-1); order tl,tr,left,right,bl,down,br; tl/tr keep besty  (:703-734)
+    uint32_t best = s[1]; int bx = 0, by = -1;
+    if (s[0] < best) { best = s[0]; bx = -1; }
+    if (s[2] < best) { best = s[2]; bx = 1; }
+    if (s[3] < best) { best = s[3]; bx = -1; by = 0; }
+    if (s[4] < best) { best = s[4]; bx = 1;  by = 0; }
+    if (s[5] < best) { best = s[5]; bx = -1; by = 1; }
+    if (s[6] < best) { best = s[6]; bx = 0;  by = 1; }
+    if (s[7] < best) { best = s[7]; bx = 1;  by = 1; }
+    res.cost = best; res.x = (int16_t)bx; res.y = (int16_t)by;
+  }
+  P.out[ti] = res;
+}
+
+static size_t sad_smem_bytes(int R) {
+  const int n = 2 * R + 1, win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
+  return 64 * 64 + ((size_t)(win_rows * pitch + 15) & ~(size_t)15) + (size_t)5 * n * n * 4;
+}
+
+}  // namespace thor
+
+using namespace thor;
+
+extern "C" {
+
+size_t thorcuda_sad_table_bytes(int slot, int bs) {
+  if (slot < 0 || slot >= THORCUDA_SAD_SLOTS) return 0;
+  const int l = bs == 8 ? 0 : bs == 16 ? 1 : bs == 32 ? 2 : bs == 64 ? 3 : -1;
+  if (l < 0 || !ctx().sad[slot].used) return 0;
+  return ctx().sad[slot].bytes[l];
+}
+
+void *thorcuda_sad_table_devptr(int slot, int bs) {
+  if (slot < 0 || slot >= THORCUDA_SAD_SLOTS) return nullptr;
+  const int l = bs == 8 ? 0 : bs == 16 ? 1 : bs == 32 ? 2 : bs == 64 ? 3 : -1;
+  if (l < 0 || !ctx().sad[slot].used) return nullptr;
+  return ctx().sad[slot].tab[l];
+}
+
+int thorcuda_sad_table_fetch(int slot, int bs, void *host_dst, size_t bytes) {
+  THOR_NEED_CTX();
+  const size_t have = thorcuda_sad_table_bytes(slot, bs);
+  if (!have) return fail("sad_table_fetch: slot %d has no %dx%d table", slot, bs, bs);
+  if (bytes > have) return fail("sad_table_fetch: %zu bytes requested, table has %zu", bytes, have);
+  return d2h(host_dst, thorcuda_sad_table_devptr(slot, bs), bytes);
+}
+
+int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, const thorcuda_pic *refs, int range,
+                             const int16_t *const *centres) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (n <= 0) return 0;
+  if (range < 4 || range > 32 || (range & 3)) return fail("sad_table: range must be 4,8,...,32 (got %d)", range);
+  const int nn = (2 * range + 1) * (2 * range + 1);
+  int maxw = 0, maxh = 0;
+  size_t centre_entries = 0;
+  for (int i = 0; i < n; i++) {
+    Pic *o = get_pic(orgs[i]), *r = get_pic(refs[i]);
+    if (!o || !r) return fail("sad_table: bad picture handle in pair %d", i);
+    if (o->w != r->w || o->h != r->h) return fail("sad_table: pair %d: picture size mismatch", i);
+    if ((r->pad_y & 3) || r->pad_y < range) return fail("sad_table: pair %d: reference padding %d cannot hold range %d", i, r->pad_y, range);
+    if (slots[i] < 0 || slots[i] >= THORCUDA_SAD_SLOTS) return fail("sad_table: slot %d out of range", slots[i]);
+    for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail("sad_table: slot %d used twice in one call", slots[i]);
+    maxw = max(maxw, o->w); maxh = max(maxh, o->h);
+  }
+  const int gx = (maxw + 63) / 64, gy = (maxh + 63) / 64;
+  for (int i = 0; i < n; i++) {
+    if (!centres || !centres[i]) continue;
+    Pic *o = get_pic(orgs[i]), *r = get_pic(refs[i]);
+    const int nsbx = (o->w + 63) / 64, nsby = (o->h + 63) / 64;
+    for (int sy = 0; sy < nsby; sy++)
+      for (int sx = 0; sx < nsbx; sx++) {
+        const int cx = centres[i][2 * (sy * nsbx + sx)], cy = centres[i][2 * (sy * nsbx + sx) + 1];
+        const int x0 = sx * 64, y0 = sy * 64, x1 = min(x0 + 64, o->w), y1 = min(y0 + 64, o->h);
+        if (x0 + cx - range < -r->pad_y || y0 + cy - range < -r->pad_y || x1 + cx + range > o->w + r->pad_y ||
+            y1 + cy + range > o->h + r->pad_y)
+          return fail("sad_table: pair %d SB (%d,%d): centre (%d,%d) +- %d leaves the padded reference", i, sx, sy, cx, cy, range);
+      }
+    centre_entries += (size_t)2 * gx * gy;
+  }
+  // (re)size the slots
+  for (int i = 0; i < n; i++) {
+    Pic *o = get_pic(orgs[i]);
+    SadSlot &s = c.sad[slots[i]];
+    for (int l = 0; l < 4; l++) {
+      const int bs = 8 << l;
+      const size_t bytes = (size_t)(o->w / bs) * (o->h / bs) * nn * (l < 2 ? 2 : 4);
+      if (bytes > s.cap[l]) {
+        if (s.tab[l]) { cudaStreamSynchronize(c.stream); cudaFree(s.tab[l]); s.tab[l] = nullptr; s.cap[l] = 0; }
+        if (bytes && cudaMalloc(&s.tab[l], bytes + 64) != cudaSuccess) return fail("sad_table: device allocation of %zu bytes failed", bytes);
+        s.cap[l] = bytes;
+      }
+      s.bytes[l] = bytes;
+    }
+    s.used = true; s.w = o->w; s.h = o->h; s.range = range;
+  }
+  SadJob *d_jobs = (SadJob *)c.sadjobs.reserve(sizeof(SadJob) * n);
+  int16_t *d_centres = centre_entries ? (int16_t *)c.centres.reserve(centre_entries * 2) : nullptr;
+  const size_t st_bytes = sizeof(SadJob) * n + centre_entries * 2;
+  uint8_t *st = (uint8_t *)stage_acquire(st_bytes);
+  if (!d_jobs || !st || (centre_entries && !d_centres)) return fail("sad_table: allocation failed");
+  SadJob *hj = (SadJob *)st;
+  int16_t *hc = (int16_t *)(st + sizeof(SadJob) * n);
+  size_t coff = 0;
+  for (int i = 0; i < n; i++) {
+    Pic *o = get_pic(orgs[i]), *r = get_pic(refs[i]);
+    SadSlot &s = c.sad[slots[i]];
+    hj[i].org = o->view(); hj[i].ref = r->view();
+    hj[i].t8 = (uint16_t *)s.tab[0]; hj[i].t16 = (uint16_t *)s.tab[1];
+    hj[i].t32 = (uint32_t *)s.tab[2]; hj[i].t64 = (uint32_t *)s.tab[3];
+    hj[i].centres = nullptr;
+    if (centres && centres[i]) {
+      // re-pitch to the launch grid (gx SBs per row) so the kernel can index with gridDim.x
+      const int nsbx = (o->w + 63) / 64, nsby = (o->h + 63) / 64;
+      memset(hc + coff, 0, (size_t)2 * gx * gy * 2);
+      for (int sy = 0; sy < nsby; sy++) memcpy(hc + coff + (size_t)2 * sy * gx, centres[i] + (size_t)2 * sy * nsbx, (size_t)2 * nsbx * 2);
+      hj[i].centres = d_centres + coff;
+      coff += (size_t)2 * gx * gy;
+    }
+  }
+  THOR_CUDA(cudaMemcpyAsync(d_jobs, hj, sizeof(SadJob) * n, cudaMemcpyHostToDevice, c.stream));
+  if (stage_commit_copy(d_centres ? (void *)d_centres : (void *)d_jobs, hc, centre_entries * 2)) return -1;
+  const size_t smem = sad_smem_bytes(range);
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    THOR_CUDA(cudaFuncSetAttribute(k_sad_table, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  dim3 grid(gx, gy, n);
+  k_sad_table<<<grid, SAD_THREADS, smem, c.stream>>>(d_jobs, range);
+  THOR_LAUNCHED();
+  return 0;
+}
+
+int thorcuda_cost_list(thorcuda_list hl, int kind, thorcuda_cost_result *host_results) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  List *L = get_list(hl);
+  if (!L || L->kind != THORCUDA_LIST_COST) return fail("cost: not a cost list");
+  if (kind < 0 || kind > THORCUDA_COST_SSD) return fail("cost: unknown kind %d", kind);
+  CostParams P;
+  P.pics = c.d_pics; P.map = L->map();
+  P.tasks = (const thorcuda_cost_task *)L->tasks();
+  P.out = L->results; P.ntasks = L->ntasks; P.kind = kind;
+  k_cost_batch<<<(L->ntasks + CW - 1) / CW, CW * 32, 0, c.stream>>>(P);
+  THOR_LAUNCHED();
+  if (host_results) return d2h(host_results, L->results, (size_t)L->ntasks * sizeof(thorcuda_cost_result));
+  return 0;
+}
+
+int thorcuda_cost_batch(int kind, const thorcuda_pic *pics, int npics, const thorcuda_cost_task *tasks, int ntasks,
+                        thorcuda_cost_result *host_results) {
+  if (ntasks <= 0) return 0;
+  const thorcuda_list l = thorcuda_list_create(THORCUDA_LIST_COST, pics, npics, tasks, ntasks);
+  if (l < 0) return -1;
+  const int rc = thorcuda_cost_list(l, kind, host_results);
+  thorcuda_list_destroy(l);
+  return rc;
+}
+
+}  // extern "C"

@@ -8,16 +8,17 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _lib = None
 
 LF_DEBLOCK_Y, LF_DEBLOCK_UV, LF_CLPF, LF_MAKE_REF = 1, 2, 4, 8
+LIST_PRED, LIST_TB, LIST_COST = 0, 1, 2
 COST_SAD, COST_WIDESAD, COST_FASTHALF, COST_FASTQUARTER, COST_SSD = range(5)
 
 # struct layouts of include/thorcuda.h
 PRED_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("w", "u1"), ("h", "u1"), ("ref0", "i1"), ("ref1", "i1"),
                       ("mv0x", "<i2"), ("mv0y", "<i2"), ("mv1x", "<i2"), ("mv1y", "<i2"),
-                      ("sign0", "u1"), ("sign1", "u1"), ("reserved", "<u2")])
+                      ("sign0", "u1"), ("sign1", "u1"), ("dst", "u1"), ("reserved", "u1")])
 TB_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("size", "u1"), ("plane", "u1"), ("qp", "u1"), ("coeff_type", "u1"),
-                    ("fast", "u1"), ("reserved", "u1", (3,)), ("coeff_offset", "<u4")])
-COST_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("w", "u1"), ("h", "u1"), ("ref", "i1"), ("hx", "u1"), ("hy", "u1"),
-                      ("reserved", "u1"), ("ix", "<i2"), ("iy", "<i2"), ("pad", "<u2")])
+                    ("fast", "u1"), ("org", "u1"), ("pred", "u1"), ("rec", "u1"), ("coeff_offset", "<u4")])
+COST_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("w", "u1"), ("h", "u1"), ("org", "u1"), ("ref", "u1"), ("hx", "i1"), ("hy", "i1"),
+                      ("ix", "<i2"), ("iy", "<i2"), ("reserved", "<u2")])
 COST_RESULT = np.dtype([("cost", "<u4"), ("x", "<i2"), ("y", "<i2")])
 assert PRED_TASK.itemsize == 20 and TB_TASK.itemsize == 16 and COST_TASK.itemsize == 16 and COST_RESULT.itemsize == 8
 
@@ -40,22 +41,33 @@ def cdll():
         _lib = C.CDLL(p)
         _lib.thorcuda_last_error.restype = C.c_char_p
         _lib.thorcuda_launch_count.restype = C.c_uint64
-        _lib.thorcuda_pic_devptr.restype = C.c_void_p
         _lib.thorcuda_stream.restype = C.c_void_p
         _lib.thorcuda_host_alloc.restype = C.c_void_p
         _lib.thorcuda_host_alloc.argtypes = [C.c_size_t]
         _lib.thorcuda_host_free.argtypes = [C.c_void_p]
+        V, I, Z = C.c_void_p, C.c_int, C.c_size_t
         for name, res, args in (
-                ("thorcuda_sad_table_bytes", C.c_size_t, None),
-                ("thorcuda_sad_table_devptr", C.c_void_p, None),
-                ("thorcuda_sad_table_fetch", C.c_int, [C.c_int, C.c_void_p, C.c_size_t]),
-                ("thorcuda_encode_blocks", C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_size_t, C.c_void_p,
-                                                     C.c_void_p, C.c_void_p]),
-                ("thorcuda_reconstruct_blocks", C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t])):
+                ("thorcuda_init", I, [I]),
+                ("thorcuda_timer_begin", I, []), ("thorcuda_timer_end", I, [I]), ("thorcuda_timer_elapsed_ms", C.c_float, [I]),
+                ("thorcuda_flush_l2", I, [Z]),
+                ("thorcuda_pic_create", I, [I, I, I, I]), ("thorcuda_pic_destroy", None, [I]), ("thorcuda_pic_stride", I, [I, I]),
+                ("thorcuda_pic_upload", I, [I, V, V, V, I, I]), ("thorcuda_pic_download", I, [I, V, V, V, I, I]),
+                ("thorcuda_pic_download_padded", I, [I, V, V, V]), ("thorcuda_pic_upload_padded", I, [I, V, V, V]),
+                ("thorcuda_pic_devptr", V, [I, I]), ("thorcuda_pic_copy", I, [I, I]),
+                ("thorcuda_blockinfo_upload", I, [I, V]),
+                ("thorcuda_loopfilter_frame", I, [I, I, I, I, I, V, V]), ("thorcuda_loopfilter_frames", I, [I, V]),
+                ("thorcuda_pad_frame", I, [I]),
+                ("thorcuda_list_create", I, [I, V, I, V, I]), ("thorcuda_list_destroy", None, [I]),
+                ("thorcuda_list_pool_entries", Z, [I]),
+                ("thorcuda_predict_list", I, [I, I, I]), ("thorcuda_predict_blocks", I, [V, I, V, I, I, I]),
+                ("thorcuda_encode_list", I, [I, V, V, V]), ("thorcuda_encode_blocks", I, [V, I, V, I, V, V, V]),
+                ("thorcuda_reconstruct_list", I, [I, V]), ("thorcuda_reconstruct_blocks", I, [V, I, V, I, V]),
+                ("thorcuda_sad_table_build", I, [I, V, V, V, I, V]), ("thorcuda_sad_table_bytes", Z, [I, I]),
+                ("thorcuda_sad_table_fetch", I, [I, I, V, Z]), ("thorcuda_sad_table_devptr", V, [I, I]),
+                ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):
             fn = getattr(_lib, name)   # AttributeError here means a stale libthorcuda.so: rebuild
             fn.restype = res
-            if args is not None:
-                fn.argtypes = args
+            fn.argtypes = args
     return _lib
 
 

@@ -1,38 +1,63 @@
-"""Host-side mirror of the reference's frame-level operators for the hot path, same names and
-argument meaning, executing on the B200 through libthorcuda (no CPU fallback).
+"""Host-side mirror of the reference's operators for the hot path, same names and argument meaning,
+executing on the B200 through libthorcuda (no CPU fallback).
 
   deblock_frame_y / deblock_frame_uv   reference common/common_frame.c:46-321
   clpf_frame                           reference common/common_frame.c:485-557
   create_reference_frame, pad_yuv_frame reference common/common_frame.c:405-483
-  loopfilter_frame                     the fused frame tail of enc/encode_frame.c:150-177 /
+  loopfilter_frame(s)                  the fused frame tail of enc/encode_frame.c:150-177 /
                                        dec/decode_frame.c:124-147
+  predict_blocks                       get_inter_prediction_luma/chroma + bi-pred average
+                                       (common/inter_prediction.c:72-180, enc/encode_block.c:1534-1588)
+  encode_blocks / reconstruct_blocks   encode_and_reconstruct_block_inter (enc/encode_block.c:1469-1532),
+                                       decode_and_reconstruct_block_inter (dec/decode_block.c:90-120)
+  sad_table / cost_batch               sad_calc, widesad_calc, sad_calc_fasthalf/fastquarter, ssd_calc
+                                       (enc/encode_block.c:497-797)
 """
 import ctypes as C
 
 import numpy as np
 
-from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, COST_RESULT, COST_TASK, PRED_TASK, TB_TASK, _p, cdll,
-                  check, sync)
+from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, LIST_COST, LIST_PRED, LIST_TB, COST_RESULT, COST_TASK,
+                  PRED_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
 
 
-def blockinfo_upload(deblock_data, width, height):
-    """deblock_data: numpy array of the reference's deblock_data_t (44-byte records), raster order."""
+class LfJob(C.Structure):  # thorcuda_lf_job
+    _fields_ = [("rec", C.c_int), ("org", C.c_int), ("ref_out", C.c_int), ("qp", C.c_int), ("stages", C.c_int),
+                ("sb_bits_in", C.c_void_p), ("sb_bits_out", C.c_void_p)]
+
+
+def blockinfo_upload(rec, deblock_data):
+    """deblock_data: numpy array of the reference's deblock_data_t (44-byte records), raster order;
+    it describes picture `rec`."""
     a = np.ascontiguousarray(deblock_data)
-    assert a.dtype.itemsize == 44 and a.size == (width // 4) * (height // 4)
-    check(cdll().thorcuda_blockinfo_upload(_p(a), width, height))
-    sync()
+    assert a.dtype.itemsize == 44 and a.size == (rec.width // 4) * (rec.height // 4)
+    check(cdll().thorcuda_blockinfo_upload(rec.handle, _p(a)))
+
+
+def loopfilter_frames(jobs, wait=True):
+    """jobs: list of dicts(rec, qp, stages, org=None, ref_out=None, sb_bits_in=None).  One launch for all
+    frames.  Returns the per-SB CLPF bits of every frame (0xFF: not signalled)."""
+    arr = (LfJob * len(jobs))()
+    outs, keep = [], []
+    for i, j in enumerate(jobs):
+        rec = j["rec"]
+        nsb = (rec.width // 64) * (rec.height // 64)
+        out = np.full(max(nsb, 1), 0xFF, np.uint8)
+        bin_ = None if j.get("sb_bits_in") is None else np.ascontiguousarray(j["sb_bits_in"], np.uint8)
+        keep.append(bin_)
+        outs.append((out, nsb))
+        org, ref = j.get("org"), j.get("ref_out")
+        arr[i] = LfJob(rec.handle, -1 if org is None else org.handle, -1 if ref is None else ref.handle, int(j["qp"]),
+                       int(j["stages"]), None if bin_ is None else bin_.ctypes.data, out.ctypes.data)
+    check(cdll().thorcuda_loopfilter_frames(len(jobs), C.byref(arr)))
+    if wait:
+        sync()
+    return [o[:n] for o, n in outs]
 
 
 def loopfilter_frame(rec, qp, stages, org=None, ref_out=None, sb_bits_in=None):
     """Fused deblock -> CLPF -> reference creation.  Returns the per-SB CLPF bits (0xFF: not signalled)."""
-    nsb = (rec.width // 64) * (rec.height // 64)
-    bits_out = np.full(max(nsb, 1), 0xFF, np.uint8)
-    bin_ = None if sb_bits_in is None else np.ascontiguousarray(sb_bits_in, np.uint8)
-    check(cdll().thorcuda_loopfilter_frame(rec.handle, -1 if org is None else org.handle,
-                                           -1 if ref_out is None else ref_out.handle, int(qp), int(stages),
-                                           _p(bin_), _p(bits_out)))
-    sync()
-    return bits_out[:nsb]
+    return loopfilter_frames([dict(rec=rec, qp=qp, stages=stages, org=org, ref_out=ref_out, sb_bits_in=sb_bits_in)])[0]
 
 
 def deblock_frame_y(rec, qp):
@@ -61,58 +86,119 @@ def _handles(pics):
     return (C.c_int * len(pics))(*[p.handle for p in pics])
 
 
-def predict_blocks(dst, refs, tasks, bipred_filter, planes=3):
-    """tasks: numpy array of PRED_TASK.  get_inter_prediction_luma/chroma (+ bi-pred average) for a
-    whole block list (reference common/inter_prediction.c:72-180, enc/encode_block.c:1534-1588)."""
+class TaskList:
+    """A task list resident in HBM (thorcuda_list_create)."""
+    _dtypes = {LIST_PRED: PRED_TASK, LIST_TB: TB_TASK, LIST_COST: COST_TASK}
+
+    def __init__(self, kind, pics, tasks):
+        t = np.ascontiguousarray(tasks, self._dtypes[kind])
+        self.kind, self.ntasks = kind, t.size
+        self.handle = cdll().thorcuda_list_create(kind, _handles(pics), len(pics), _p(t), t.size)
+        if self.handle < 0:
+            raise ThorCudaError(cdll().thorcuda_last_error().decode())
+        self.pool_entries = cdll().thorcuda_list_pool_entries(self.handle) if kind == LIST_TB else 0
+
+    def close(self):
+        if self.handle >= 0:
+            cdll().thorcuda_list_destroy(self.handle)
+            self.handle = -1
+
+    # -- execution -----------------------------------------------------------------------------
+    def predict(self, bipred_filter, planes=3):
+        check(cdll().thorcuda_predict_list(self.handle, int(bipred_filter), int(planes)))
+
+    def encode(self, coeffq=None, cbp=None, ssd=None):
+        check(cdll().thorcuda_encode_list(self.handle, _p(coeffq), _p(cbp), _p(ssd)))
+
+    def reconstruct(self, coeffq=None):
+        check(cdll().thorcuda_reconstruct_list(self.handle, _p(coeffq)))
+
+    def cost(self, kind, results=None):
+        check(cdll().thorcuda_cost_list(self.handle, int(kind), _p(results)))
+
+
+def predict_blocks(pics, tasks, bipred_filter, planes=3):
+    """tasks: numpy array of PRED_TASK whose dst/ref0/ref1 index into pics."""
     t = np.ascontiguousarray(tasks, PRED_TASK)
-    check(cdll().thorcuda_predict_blocks(dst.handle, _handles(refs), len(refs), _p(t), t.size, int(bipred_filter), int(planes)))
+    check(cdll().thorcuda_predict_blocks(_handles(pics), len(pics), _p(t), t.size, int(bipred_filter), int(planes)))
     sync()
 
 
-def encode_blocks(org, pred, rec, tasks, pool_entries, want_ssd=True):
-    """Batched encode_and_reconstruct_block_inter (reference enc/encode_block.c:1469-1532).
-    Returns (coeffq pool int16, cbp flags uint8, ssd uint32 or None)."""
-    t = np.ascontiguousarray(tasks, TB_TASK)
-    coeffq = np.zeros(pool_entries, np.int16)
-    cbp = np.zeros(t.size, np.uint8)
-    ssd = np.zeros(t.size, np.uint32) if want_ssd else None
-    check(cdll().thorcuda_encode_blocks(org.handle, pred.handle, rec.handle, _p(t), t.size, pool_entries, _p(coeffq),
-                                        _p(cbp), _p(ssd)))
+def pool_layout(tasks):
+    """Assign coeff_offset to every TB task (q*q entries each, 8-entry aligned).  Returns total entries."""
+    off = 0
+    for t in tasks:
+        q = min(int(t["size"]), 16)
+        t["coeff_offset"] = off
+        off += (q * q + 7) & ~7
+    return off
+
+
+def encode_blocks(pics, tasks, want_ssd=True):
+    """Batched encode_and_reconstruct_block_inter.  Returns (coeffq pool int16, cbp uint8, ssd uint32)."""
+    lst = TaskList(LIST_TB, pics, tasks)
+    coeffq = np.zeros(lst.pool_entries, np.int16)
+    cbp = np.zeros(lst.ntasks, np.uint8)
+    ssd = np.zeros(lst.ntasks, np.uint32) if want_ssd else None
+    lst.encode(coeffq, cbp, ssd)
     sync()
+    lst.close()
     return coeffq, cbp, ssd
 
 
-def reconstruct_blocks(pred, rec, tasks, coeffq):
-    """Batched decode_and_reconstruct_block_inter (reference dec/decode_block.c:90-120)."""
-    t = np.ascontiguousarray(tasks, TB_TASK)
-    cq = np.ascontiguousarray(coeffq, np.int16)
-    check(cdll().thorcuda_reconstruct_blocks(pred.handle, rec.handle, _p(t), t.size, _p(cq), cq.size))
+def reconstruct_blocks(pics, tasks, coeffq):
+    """Batched decode_and_reconstruct_block_inter."""
+    lst = TaskList(LIST_TB, pics, tasks)
+    cq = np.zeros(lst.pool_entries, np.int16)
+    cq[:min(cq.size, coeffq.size)] = coeffq[:cq.size]
+    lst.reconstruct(cq)
     sync()
+    lst.close()
 
 
-def cost_batch(kind, org, refs, tasks):
-    """Batched sad_calc / widesad_calc / sad_calc_fasthalf / sad_calc_fastquarter / ssd_calc
-    (reference enc/encode_block.c:497-797).  Returns a COST_RESULT array."""
+def cost_batch(kind, pics, tasks):
+    """Batched sad_calc / widesad_calc / sad_calc_fasthalf / sad_calc_fastquarter / ssd_calc.
+    Returns a COST_RESULT array."""
     t = np.ascontiguousarray(tasks, COST_TASK)
     out = np.zeros(t.size, COST_RESULT)
-    check(cdll().thorcuda_cost_batch(int(kind), org.handle, _handles(refs), len(refs), _p(t), t.size, _p(out)))
+    check(cdll().thorcuda_cost_batch(int(kind), _handles(pics), len(pics), _p(t), t.size, _p(out)))
     sync()
     return out
 
 
-def sad_table(org, ref, search_range, centres=None):
-    """Whole-frame integer-pel SAD tables for block sizes 8,16,32,64 (dict size -> ndarray
-    [blocks_y, blocks_x, 2R+1, 2R+1])."""
-    c = None if centres is None else np.ascontiguousarray(centres, np.int16)
-    check(cdll().thorcuda_sad_table_build(org.handle, ref.handle, int(search_range), _p(c)))
+def sad_table_build(slots, orgs, refs, search_range, centres=None):
+    """Queue the table build for n (org, ref) pairs (one launch)."""
+    n = len(slots)
+    sl = (C.c_int * n)(*slots)
+    cptr, keep = None, []
+    if centres is not None:
+        arr = (C.c_void_p * n)()
+        for i, c in enumerate(centres):
+            if c is None:
+                arr[i] = None
+            else:
+                a = np.ascontiguousarray(c, np.int16)
+                keep.append(a)
+                arr[i] = a.ctypes.data
+        cptr = C.cast(arr, C.c_void_p)
+    check(cdll().thorcuda_sad_table_build(n, sl, _handles(orgs), _handles(refs), int(search_range), cptr))
+
+
+def sad_table_fetch(slot, width, height, search_range, sizes=(8, 16, 32, 64)):
+    """dict size -> ndarray [blocks_y, blocks_x, 2R+1, 2R+1] (uint16 for 8/16, uint32 for 32/64)."""
     out = {}
     n = 2 * search_range + 1
-    for bs in (8, 16, 32, 64):
-        nbytes = cdll().thorcuda_sad_table_bytes(bs)
+    for bs in sizes:
+        nbytes = cdll().thorcuda_sad_table_bytes(slot, bs)
         dt = np.uint16 if bs <= 16 else np.uint32
         a = np.empty(nbytes // np.dtype(dt).itemsize, dt)
-        check(cdll().thorcuda_sad_table_fetch(bs, _p(a), nbytes))
+        if nbytes:
+            check(cdll().thorcuda_sad_table_fetch(slot, bs, _p(a), nbytes))
         sync()
-        by, bx = (org.height - bs) // 8 + 1, (org.width - bs) // 8 + 1
-        out[bs] = a.reshape(by, bx, n, n)
+        out[bs] = a.reshape(height // bs, width // bs, n, n)
     return out
+
+
+def sad_table(org, ref, search_range, centres=None, slot=0):
+    sad_table_build([slot], [org], [ref], search_range, None if centres is None else [centres])
+    return sad_table_fetch(slot, org.width, org.height, search_range)
