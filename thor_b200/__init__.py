@@ -7,5 +7,5 @@ itself and has no CPU fallback: if the library is missing, or no sm_100 device i
 """
 from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, LIST_COST, LIST_PRED, LIST_TB, COST_FASTHALF,  # noqa: F401
                   COST_FASTQUARTER, COST_SAD, COST_SSD, COST_WIDESAD, COST_TASK, COST_RESULT, PRED_TASK, TB_TASK, Picture,
-                  ThorCudaError, cdll, init, launch_count, lib_path, shutdown, sync)
+                  ThorCudaError, cdll, check, init, launch_count, lib_path, shutdown, sync)
 from . import ops  # noqa: F401
