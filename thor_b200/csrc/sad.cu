@@ -22,28 +22,123 @@ struct SadJob {
 
 constexpr int SAD_THREADS = 256;
 
-__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) { return __vsadu4(a, b) + acc; }
+// acc + sum of |a.b[i] - b.b[i]| over the four bytes: ONE VABSDIFF4.U8.ACC (the intrinsic form
+// __vsadu4(a,b)+acc is split by the compiler into VABSDIFF4 + IADD3, doubling the ALU-pipe work)
+__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) {
+  uint32_t r;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(acc));
+  return r;
+}
+
+struct SadCtx {
+  const uint8_t *sOrg, *sWin;
+  uint32_t *part;               // [8 warps-worth of strips: p*2+ch][n*n] sums over 32x16 strips
+  uint16_t *t8, *t16;
+  int W, H, x0, y0, o;
+};
+
+// One "pass": this lane owns the two vertically adjacent 8x8 blocks (block column bx, block rows 2p and
+// 2p+1 of the SB) at ONE horizontal displacement index dxi and slides over all 2R+1 vertical ones.
+// m16 / m32: lane-xor distances that pair block columns (bx^1) and pair the pairs (bx^2) in this pass's
+// lane layout.  The 8 reference rows that start / end the slide touch fewer displacement rows than the
+// middle ones; FIRST / LAST blocks skip those (row r of the block only meets displacement rows j-r in
+// [0, 2R]), so no abs-diff is computed that is not part of an output.
+enum { BLK_FIRST = 0, BLK_MID = 1, BLK_LAST = 2 };
+
+template <int MODE, int R>
+__device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint32_t (&oB)[8][2], uint32_t (&aT)[8], uint32_t (&aB)[8],
+                                          const uint8_t *col, int sh, bool okT, bool okB, bool ok16, bool ok32, int m16, int m32,
+                                          uint16_t *t8T, uint16_t *t8B, uint16_t *t16, uint32_t *part) {
+  constexpr int n = 2 * R + 1, pitch = (64 + 2 * R + 7) & ~3;
+  // col / t8T / t8B / t16 / part already point at this block's first reference row / first output row
+#pragma unroll
+  for (int s = 0; s < 8; s++) {
+    const uint32_t *rt = reinterpret_cast<const uint32_t *>(col + s * pitch);
+    const uint32_t *rb = reinterpret_cast<const uint32_t *>(col + (s + 8) * pitch);
+    const uint32_t t0 = rt[0], t1 = rt[1], t2 = rt[2], b0 = rb[0], b1 = rb[1], b2 = rb[2];
+    const uint32_t wT0 = __funnelshift_r(t0, t1, sh), wT1 = __funnelshift_r(t1, t2, sh);
+    const uint32_t wB0 = __funnelshift_r(b0, b1, sh), wB1 = __funnelshift_r(b1, b2, sh);
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+      if (MODE == BLK_FIRST && r > s) continue;      // displacement row j - r < 0
+      if (MODE == BLK_LAST && r < s) continue;       // displacement row j - r > 2R
+      const int k = (s - r) & 7;
+      aT[k] = sad4(oT[r][0], wT0, aT[k]); aT[k] = sad4(oT[r][1], wT1, aT[k]);
+      aB[k] = sad4(oB[r][0], wB0, aB[k]); aB[k] = sad4(oB[r][1], wB1, aB[k]);
+    }
+    if (MODE != BLK_FIRST || s == 7) {               // displacement row (s - 7) relative to this block is complete
+      const int kc = (s + 1) & 7;
+      const uint32_t vT = aT[kc], vB = aB[kc];
+      const int e = (s - 7) * n;
+      if (okT) t8T[e] = (uint16_t)vT;
+      if (okB) t8B[e] = (uint16_t)vB;
+      uint32_t v = vT + vB;
+      v += __shfl_xor_sync(0xffffffffu, v, m16);
+      if (ok16) t16[e] = (uint16_t)v;
+      v += __shfl_xor_sync(0xffffffffu, v, m32);
+      if (ok32) part[e] = v;
+      aT[kc] = 0; aB[kc] = 0;
+    }
+  }
+}
+
+template <int R>
+__device__ __forceinline__ void sad_pass(const SadCtx &C, int p, int bx, int dxi, int m16, int m32) {
+  constexpr int n = 2 * R + 1, nn = n * n, pitch = (64 + 2 * R + 7) & ~3;
+  uint32_t oT[8][2], oB[8][2];
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const uint32_t *a = reinterpret_cast<const uint32_t *>(C.sOrg + (16 * p + r) * 64 + bx * 8);
+    const uint32_t *b = reinterpret_cast<const uint32_t *>(C.sOrg + (16 * p + 8 + r) * 64 + bx * 8);
+    oT[r][0] = a[0]; oT[r][1] = a[1]; oB[r][0] = b[0]; oB[r][1] = b[1];
+  }
+  // which outputs exist (frame edges) and where they go
+  const int gx8 = C.x0 + bx * 8, gyT = C.y0 + 16 * p, gyB = gyT + 8;
+  const bool okx8 = gx8 + 8 <= C.W;
+  const bool okT = okx8 && gyT + 8 <= C.H, okB = okx8 && gyB + 8 <= C.H;
+  const bool ok16 = !(bx & 1) && gx8 + 16 <= C.W && gyT + 16 <= C.H;
+  const bool ok32 = !(bx & 3);
+  const int bw8 = C.W >> 3, bw16 = C.W >> 4;
+  uint16_t *t8T = C.t8 + ((size_t)(gyT >> 3) * bw8 + (gx8 >> 3)) * nn + dxi;
+  uint16_t *t8B = C.t8 + ((size_t)(gyB >> 3) * bw8 + (gx8 >> 3)) * nn + dxi;
+  uint16_t *t16 = C.t16 + ((size_t)(gyT >> 4) * bw16 + (gx8 >> 4)) * nn + dxi;
+  uint32_t *part = C.part + (p * 2 + (bx >> 2)) * nn + dxi;
+  const int off = bx * 8 + dxi + C.o;
+  const int sh = (off & 3) * 8;
+  const uint8_t *col = C.sWin + (16 * p) * pitch + (off & ~3);
+  uint32_t aT[8], aB[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) { aT[k] = 0; aB[k] = 0; }
+  sad_block<BLK_FIRST, R>(oT, oB, aT, aB, col, sh, okT, okB, ok16, ok32, m16, m32, t8T, t8B, t16, part);
+#pragma unroll 1
+  for (int jj = 8; jj < 2 * R; jj += 8) {
+    col += 8 * pitch; t8T += 8 * n; t8B += 8 * n; t16 += 8 * n; part += 8 * n;
+    sad_block<BLK_MID, R>(oT, oB, aT, aB, col, sh, okT, okB, ok16, ok32, m16, m32, t8T, t8B, t16, part);
+  }
+  col += 8 * pitch; t8T += 8 * n; t8B += 8 * n; t16 += 8 * n; part += 8 * n;
+  sad_block<BLK_LAST, R>(oT, oB, aT, aB, col, sh, okT, okB, ok16, ok32, m16, m32, t8T, t8B, t16, part);
+}
 
 // One CTA per 64x64 superblock.  Shared memory: original SB (64x64) | reference window
-// (64+2R rows, pitch bytes) | 32x32-level accumulators [4][n*n] | 64x64-level accumulator [n*n], n = 2R+1.
-// Warp w owns block-row pair p = w & 3 (two rows of 8x8 blocks) and column half ch = w >> 2;
-// lane = (bxl = lane >> 3: block column inside the half, d8 = lane & 7: one of 8 consecutive dx).
-// A thread keeps its two 8x8 original blocks in 32 registers and slides down the window: at each
-// reference row it adds that row's contribution to the 8 displacements dy it belongs to (rotating
-// accumulators, statically indexed because the row loop is unrolled by 8).
-__global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs, int R) {
+// (64+2R rows, pitch bytes) | 32x16-strip partial sums [8][n*n], n = 2R+1 (two of them make a 32x32
+// block, all eight the 64x64 block).
+// Main passes: warp w owns block-row pair p = w & 3 and column half ch = w >> 2; lane = (bxl = lane >> 3:
+// block column inside the half, d8 = lane & 7: one of 8 consecutive dx); 2R/8 groups cover dx index
+// 0..2R-1 with every lane busy.  Tail pass (warp 0): the last column dx = +R for the whole SB, lane =
+// (bx = lane & 7, p = lane >> 3).
+template <int R>
+__global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs) {
   extern __shared__ __align__(16) uint8_t smem[];
   const SadJob &J = jobs[blockIdx.z];
   const int W = J.org.w, H = J.org.h;
   const int x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
   if (x0 >= W || y0 >= H) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n = 2 * R + 1, nn = n * n;
-  const int win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
+  constexpr int n = 2 * R + 1, nn = n * n;
+  constexpr int win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
   uint8_t *sOrg = smem;
   uint8_t *sWin = smem + 64 * 64;
-  uint32_t *acc32 = reinterpret_cast<uint32_t *>(sWin + ((win_rows * pitch + 15) & ~15));
-  uint32_t *acc64 = acc32 + 4 * nn;
+  uint32_t *part = reinterpret_cast<uint32_t *>(sWin + ((win_rows * pitch + 15) & ~15));
 
   int cx = 0, cy = 0;
   if (J.centres) {
@@ -53,7 +148,8 @@ __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__re
   const int wx = x0 + cx - R, wy = y0 + cy - R;
   const int o = wx & 3, ax = wx - o;
   {
-    const int pad = J.ref.pad[0], stride = J.ref.stride[0], wpr = pitch >> 2;
+    const int pad = J.ref.pad[0], stride = J.ref.stride[0];
+    constexpr int wpr = pitch >> 2;
     const uint8_t *rp = J.ref.p[0];
     for (int i = tid; i < win_rows * wpr; i += SAD_THREADS) {
       const int r = i / wpr, wd = i - r * wpr;
@@ -67,85 +163,41 @@ __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__re
       const int gy = min(y0 + r, H - 1), gx = min(x0 + 4 * wd, W - 4);
       reinterpret_cast<uint32_t *>(sOrg)[i] = *reinterpret_cast<const uint32_t *>(op + (size_t)gy * ostride + gx);
     }
-    for (int i = tid; i < 5 * nn; i += SAD_THREADS) acc32[i] = 0;
   }
   __syncthreads();
 
-  const int p = warp & 3, ch = warp >> 2, d8 = lane & 7, bxl = lane >> 3, bx = 4 * ch + bxl;
-  uint32_t oT[8][2], oB[8][2];
-#pragma unroll
-  for (int r = 0; r < 8; r++) {
-    const uint32_t *a = reinterpret_cast<const uint32_t *>(sOrg + (16 * p + r) * 64 + bx * 8);
-    const uint32_t *b = reinterpret_cast<const uint32_t *>(sOrg + (16 * p + 8 + r) * 64 + bx * 8);
-    oT[r][0] = a[0]; oT[r][1] = a[1]; oB[r][0] = b[0]; oB[r][1] = b[1];
-  }
-  // which outputs exist (frame edges) and where they go
-  const int gx8 = x0 + bx * 8, gyT = y0 + 16 * p, gyB = gyT + 8;
-  const bool okx8 = gx8 + 8 <= W;
-  const bool okT = okx8 && gyT + 8 <= H, okB = okx8 && gyB + 8 <= H;
-  const bool ok16 = !(bxl & 1) && gx8 + 16 <= W && gyT + 16 <= H;
-  const bool ok32 = bxl == 0;
-  const int bw8 = W >> 3, bw16 = W >> 4;
-  uint16_t *t8T = J.t8 + ((size_t)(gyT >> 3) * bw8 + (gx8 >> 3)) * nn;
-  uint16_t *t8B = J.t8 + ((size_t)(gyB >> 3) * bw8 + (gx8 >> 3)) * nn;
-  uint16_t *t16 = J.t16 + ((size_t)(gyT >> 4) * bw16 + (gx8 >> 4)) * nn;
-  uint32_t *a32 = acc32 + ((p >> 1) * 2 + ch) * nn;
-
-  const int ngroups = (n + 7) >> 3;
-  for (int g = 0; g < ngroups; g++) {
-    const int dxi_raw = g * 8 + d8;
-    const bool act = dxi_raw < n;
-    const int dxi = act ? dxi_raw : n - 1;
-    const int off = bx * 8 + dxi + o;
-    const int sh = (off & 3) * 8;
-    const uint8_t *colT = sWin + (16 * p) * pitch + (off & ~3);
-    uint32_t aT[8], aB[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) { aT[k] = 0; aB[k] = 0; }
-    for (int jj = 0; jj < 8 + 2 * R; jj += 8) {
-#pragma unroll
-      for (int s = 0; s < 8; s++) {
-        const int j = jj + s;
-        const uint32_t *rt = reinterpret_cast<const uint32_t *>(colT + j * pitch);
-        const uint32_t *rb = reinterpret_cast<const uint32_t *>(colT + (j + 8) * pitch);
-        const uint32_t t0 = rt[0], t1 = rt[1], t2 = rt[2], b0 = rb[0], b1 = rb[1], b2 = rb[2];
-        const uint32_t wT0 = __funnelshift_r(t0, t1, sh), wT1 = __funnelshift_r(t1, t2, sh);
-        const uint32_t wB0 = __funnelshift_r(b0, b1, sh), wB1 = __funnelshift_r(b1, b2, sh);
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-          const int k = (s - r) & 7;
-          aT[k] = sad4(oT[r][0], wT0, aT[k]); aT[k] = sad4(oT[r][1], wT1, aT[k]);
-          aB[k] = sad4(oB[r][0], wB0, aB[k]); aB[k] = sad4(oB[r][1], wB1, aB[k]);
-        }
-        const int kc = (s + 1) & 7, dyi = j - 7;    // displacement row dyi is complete
-        if (dyi >= 0) {
-          const uint32_t vT = aT[kc], vB = aB[kc];
-          const int e = dyi * n + dxi;
-          if (act && okT) t8T[e] = (uint16_t)vT;
-          if (act && okB) t8B[e] = (uint16_t)vB;
-          uint32_t v = vT + vB;
-          v += __shfl_xor_sync(0xffffffffu, v, 8);
-          if (act && ok16) t16[e] = (uint16_t)v;
-          v += __shfl_xor_sync(0xffffffffu, v, 16);
-          if (act && ok32) { atomicAdd(a32 + e, v); atomicAdd(acc64 + e, v); }
-        }
-        aT[kc] = 0; aB[kc] = 0;
-      }
-    }
-  }
-  __syncthreads();
-  // 32x32 and 64x64 levels: coalesced 32-bit rows
-  const int bw32 = W >> 5, bw64 = W >> 6;
+  SadCtx C;
+  C.sOrg = sOrg; C.sWin = sWin; C.part = part; C.t8 = J.t8; C.t16 = J.t16;
+  C.W = W; C.H = H; C.x0 = x0; C.y0 = y0; C.o = o;
+  {
+    const int p = warp & 3, bx = 4 * (warp >> 2) + (lane >> 3), d8 = lane & 7;
 #pragma unroll 1
+    for (int g = 0; g < (2 * R) >> 3; g++) sad_pass<R>(C, p, bx, g * 8 + d8, 8, 16);
+  }
+  if (warp == 0) sad_pass<R>(C, lane >> 3, lane & 7, 2 * R, 1, 2);
+  __syncthreads();
+  // 32x32 and 64x64 levels from the strip sums: coalesced 32-bit rows
+  const int bw32 = W >> 5, bw64 = W >> 6;
+  const bool ok64 = x0 + 64 <= W && y0 + 64 <= H;
+  uint32_t *d64 = J.t64 + ((size_t)(y0 >> 6) * bw64 + (x0 >> 6)) * nn;
+  uint32_t *d32[4];
+  bool ok32[4];
+#pragma unroll
   for (int q = 0; q < 4; q++) {
     const int gx = x0 + (q & 1) * 32, gy = y0 + (q >> 1) * 32;
-    if (gx + 32 > W || gy + 32 > H) continue;
-    uint32_t *dst = J.t32 + ((size_t)(gy >> 5) * bw32 + (gx >> 5)) * nn;
-    for (int i = tid; i < nn; i += SAD_THREADS) dst[i] = acc32[q * nn + i];
+    ok32[q] = gx + 32 <= W && gy + 32 <= H;
+    d32[q] = J.t32 + ((size_t)(gy >> 5) * bw32 + (gx >> 5)) * nn;
   }
-  if (x0 + 64 <= W && y0 + 64 <= H) {
-    uint32_t *dst = J.t64 + ((size_t)(y0 >> 6) * bw64 + (x0 >> 6)) * nn;
-    for (int i = tid; i < nn; i += SAD_THREADS) dst[i] = acc64[i];
+  for (int i = tid; i < nn; i += SAD_THREADS) {
+    uint32_t tot = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {   // 32x32 block q = (qy, qx): strips p = 2qy, 2qy+1 of column half qx
+      const int qy = q >> 1, qx = q & 1;
+      const uint32_t v = part[((2 * qy) * 2 + qx) * nn + i] + part[((2 * qy + 1) * 2 + qx) * nn + i];
+      if (ok32[q]) d32[q][i] = v;
+      tot += v;
+    }
+    if (ok64) d64[i] = tot;
   }
 }
 
@@ -285,7 +337,19 @@ __global__ void __launch_bounds__(CW * 32) k_cost_batch(const CostParams P) {
 
 static size_t sad_smem_bytes(int R) {
   const int n = 2 * R + 1, win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
-  return 64 * 64 + ((size_t)(win_rows * pitch + 15) & ~(size_t)15) + (size_t)5 * n * n * 4;
+  return 64 * 64 + ((size_t)(win_rows * pitch + 15) & ~(size_t)15) + (size_t)8 * n * n * 4;
+}
+
+template <int R>
+static int launch_sad(dim3 grid, size_t smem, const SadJob *d_jobs) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    THOR_CUDA(cudaFuncSetAttribute(k_sad_table<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  k_sad_table<R><<<grid, SAD_THREADS, smem, ctx().stream>>>(d_jobs);
+  THOR_LAUNCHED();
+  return 0;
 }
 
 }  // namespace thor
@@ -392,15 +456,17 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
   THOR_CUDA(cudaMemcpyAsync(d_jobs, hj, sizeof(SadJob) * n, cudaMemcpyHostToDevice, c.stream));
   if (stage_commit_copy(d_centres ? (void *)d_centres : (void *)d_jobs, hc, centre_entries * 2)) return -1;
   const size_t smem = sad_smem_bytes(range);
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    THOR_CUDA(cudaFuncSetAttribute(k_sad_table, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
-  }
   dim3 grid(gx, gy, n);
-  k_sad_table<<<grid, SAD_THREADS, smem, c.stream>>>(d_jobs, range);
-  THOR_LAUNCHED();
-  return 0;
+  switch (range) {
+    case 4: return launch_sad<4>(grid, smem, d_jobs);
+    case 8: return launch_sad<8>(grid, smem, d_jobs);
+    case 12: return launch_sad<12>(grid, smem, d_jobs);
+    case 16: return launch_sad<16>(grid, smem, d_jobs);
+    case 20: return launch_sad<20>(grid, smem, d_jobs);
+    case 24: return launch_sad<24>(grid, smem, d_jobs);
+    case 28: return launch_sad<28>(grid, smem, d_jobs);
+    default: return launch_sad<32>(grid, smem, d_jobs);
+  }
 }
 
 int thorcuda_cost_list(thorcuda_list hl, int kind, thorcuda_cost_result *host_results) {
