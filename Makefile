@@ -14,7 +14,7 @@ build/%.o: $(CSRC)/%.cu $(CSRC)/internal.cuh $(CSRC)/lists.cuh include/thorcuda.
 	$(NVCC) $(NVCCFLAGS) -c -o $@ $< 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; false)
 
 $(LIB): $(OBJS)
-	$(NVCC) -shared -o $@ $^ -lcudart
+	$(NVCC) -shared -cudart static -o $@ $^
 
 build:
 	mkdir -p build

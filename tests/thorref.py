@@ -180,3 +180,55 @@ def blocky_frame(width, height, seed):
         noise = rng.normal(0, 1.2, (h, w)) + np.kron(tex, np.ones((32, 32)))[:h, :w] * rng.normal(0, 12, (h, w))
         out.append(np.clip(base + noise, 0, 255).astype(np.uint8))
     return out[0], out[1], out[1][::-1].copy()
+
+
+# ------------------------------------------------------------------------------------------------
+# End-to-end helpers: the reference binaries built by oracle/Makefile, its shipped operating points as
+# command-line flags (values of /root/reference/config_*.txt, which does not exist on the GPU box), and a
+# seeded synthetic clip.
+REF_DIR = os.path.join(ORACLE_DIR, "_ref")
+
+_LD = ["-HQperiod", "12", "-mqpP", "1.2", "-dqpI", "-2", "-lambda_coeffI", "0.8", "-lambda_coeffP", "1.2", "-max_num_ref", "2",
+       "-use_block_contexts", "1"]
+_RA = ["-HQperiod", "1", "-num_reorder_pics", "7", "-interp_ref", "1", "-intra_period", "64", "-dqpI", "-2", "-dqpB0", "3", "-dqpB1", "1",
+       "-dqpB2", "0", "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.1", "-mqpB1", "1.2", "-mqpB2", "1.3", "-lambda_coeffI", "0.8",
+       "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2",
+       "-use_block_contexts", "1"]
+THOR_CONFIGS = {
+    "LDB_low_complexity": _LD + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
+                                 "-enable_bipred", "0", "-encoder_speed", "2"],
+    "LDB_medium_complexity": _LD + ["-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "0.8",
+                                    "-enable_bipred", "1", "-encoder_speed", "1"],
+    "RA_high_efficiency": _RA + ["-intra_rdo", "1", "-enable_tb_split", "1", "-enable_pb_split", "1", "-early_skip_thr", "0.3",
+                                 "-max_num_ref", "4", "-enable_bipred", "1", "-encoder_speed", "0", "-max_delta_qp", "1"],
+}
+
+
+def write_clip(path, width, height, frames, seed):
+    """Seeded I420 clip: a textured background translating by (1,2) px per frame plus noise."""
+    with open(path, "wb") as f:
+        for n in range(frames):
+            y, u, v = smooth_frame(width, height, seed, shift=(n, 2 * n))
+            for p in (y, u, v):
+                f.write(np.ascontiguousarray(p).tobytes())
+
+
+def run_thorenc(exe, cfg, yuv, width, height, frames, qp, out_prefix, timeout=600):
+    """Run a Thorenc binary of oracle/_ref; returns (bitstream bytes, reconstruction bytes, seconds)."""
+    import time
+    bit, rec = out_prefix + ".bit", out_prefix + "_rec.yuv"
+    cmd = [os.path.join(REF_DIR, exe), "-if", yuv, "-of", bit, "-rf", rec, "-stat", out_prefix + "_stat.txt", "-width", str(width),
+           "-height", str(height), "-n", str(frames), "-f", "30", "-qp", str(qp)] + THOR_CONFIGS[cfg]
+    t0 = time.perf_counter()
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    dt = time.perf_counter() - t0
+    if r.returncode != 0:
+        raise RuntimeError(f"{exe} failed ({r.returncode}):\n{r.stdout[-2000:]}\n{r.stderr[-2000:]}")
+    return open(bit, "rb").read(), open(rec, "rb").read(), dt
+
+
+def run_thordec(exe, bit, out_yuv, timeout=600):
+    r = subprocess.run([os.path.join(REF_DIR, exe), bit, out_yuv], capture_output=True, text=True, timeout=timeout)
+    if r.returncode != 0:
+        raise RuntimeError(f"{exe} failed ({r.returncode}):\n{r.stdout[-2000:]}\n{r.stderr[-2000:]}")
+    return open(out_yuv, "rb").read()

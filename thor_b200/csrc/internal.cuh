@@ -108,6 +108,9 @@ int stage_commit_copy(void *dst, const void *staged, size_t bytes);
 int d2h(void *dst, const void *src, size_t bytes);
 // refresh the device mirror entry of picture h
 int sync_pic_view(thorcuda_pic h);
+// one stand-alone forward / inverse transform on device buffers (transform.cu), queued on the stream
+int tb_raw(int size, int fast, int inverse, const int16_t *d_in, int16_t *d_out);
+void compat_reset();   // compat.cu: drop the per-block API's scratch pictures (thorcuda_shutdown)
 
 #define THOR_CUDA(call)                                                                   \
   do {                                                                                    \

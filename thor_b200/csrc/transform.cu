@@ -80,6 +80,55 @@ struct WarpScratch {
 __device__ __forceinline__ int clip16(int v) { return min(max(v, -32768), 32767); }
 __device__ __forceinline__ int warp_or(int v) { return __any_sync(0xffffffffu, v); }
 
+// forward passes on the n x n block in S.in (n = 4..32; row k of the n-point basis = row k << msk of the
+// 32-point one): S.coef[v*Q + k], v,k < min(n,16)
+template <int Q>
+__device__ __forceinline__ void fwd_passes(WarpScratch &S, const int16_t *sM, int n, int msk, int sh1, int sh2, int lane) {
+  // ---- forward pass 1: mid[k][r] = (sum_c M[k][c] in[r][c] + rnd) >> sh1, k < keep ----
+  const int keep = n < 16 ? n : 16;
+  for (int i = lane; i < keep * n; i += 32) {
+    const int k = i / n, r = i - k * n;
+    const int16_t *m = sM + ((k << msk) << 5), *x = S.in + r * IN_PITCH;
+    int acc = 0;
+    for (int c = 0; c < n; c++) acc += m[c] * x[c];
+    S.mid[k * IN_PITCH + r] = (int16_t)((acc + (1 << (sh1 - 1))) >> sh1);
+  }
+  __syncwarp();
+  // ---- forward pass 2: coef[v][k] = (sum_r M[v][r] mid[k][r] + rnd) >> sh2 ----
+  for (int i = lane; i < keep * keep; i += 32) {
+    const int v = i / keep, k = i - v * keep;
+    const int16_t *m = sM + ((v << msk) << 5), *x = S.mid + k * IN_PITCH;
+    int acc = 0;
+    for (int r = 0; r < n; r++) acc += m[r] * x[r];
+    S.coef[v * Q + k] = (int16_t)((acc + (1 << (sh2 - 1))) >> sh2);
+  }
+  __syncwarp();
+}
+
+// inverse passes: S.coef (Q x Q, low-frequency corner) -> S.in (NI x NI)
+template <int NI, int Q>
+__device__ __forceinline__ void inv_passes(WarpScratch &S, const int16_t *sM, int lane) {
+  constexpr int MSK = NI == 4 ? 3 : NI == 8 ? 2 : NI == 16 ? 1 : 0;
+  // ---- inverse pass 1: mid[k][r] = clip16((sum_v M[v][r] c[v][k] + 64) >> 7) ----
+  for (int i = lane; i < Q * NI; i += 32) {
+    const int k = i / NI, r = i - k * NI;
+    int acc = 0;
+#pragma unroll 4
+    for (int v = 0; v < Q; v++) acc += sM[((v << MSK) << 5) + r] * S.coef[v * Q + k];
+    S.mid[k * IN_PITCH + r] = (int16_t)clip16((acc + 64) >> 7);
+  }
+  __syncwarp();
+  // ---- inverse pass 2: block[r][c] = clip16((sum_k M[k][c] mid[k][r] + 2048) >> 12) ----
+  for (int i = lane; i < NI * NI; i += 32) {
+    const int r = i / NI, c = i - r * NI;
+    int acc = 0;
+#pragma unroll 4
+    for (int k = 0; k < Q; k++) acc += sM[((k << MSK) << 5) + c] * S.mid[k * IN_PITCH + r];
+    S.in[r * IN_PITCH + c] = (int16_t)clip16((acc + 2048) >> 12);
+  }
+  __syncwarp();
+}
+
 template <int N>
 __global__ void __launch_bounds__(TW * 32) k_tb(const TbParams P) {
   __shared__ __align__(16) int16_t sM[32 * 32];
@@ -137,25 +186,7 @@ __global__ void __launch_bounds__(TW * 32) k_tb(const TbParams P) {
       }
     }
     __syncwarp();
-    // ---- forward pass 1: mid[k][r] = (sum_c M[k][c] in[r][c] + rnd) >> sh1, k < keep ----
-    const int keep = n < 16 ? n : 16;
-    for (int i = lane; i < keep * n; i += 32) {
-      const int k = i / n, r = i - k * n;
-      const int16_t *m = sM + ((k << msk) << 5), *x = S.in + r * IN_PITCH;
-      int acc = 0;
-      for (int c = 0; c < n; c++) acc += m[c] * x[c];
-      S.mid[k * IN_PITCH + r] = (int16_t)((acc + (1 << (sh1 - 1))) >> sh1);
-    }
-    __syncwarp();
-    // ---- forward pass 2: coef[v][k] = (sum_r M[v][r] mid[k][r] + rnd) >> sh2 ----
-    for (int i = lane; i < keep * keep; i += 32) {
-      const int v = i / keep, k = i - v * keep;
-      const int16_t *m = sM + ((v << msk) << 5), *x = S.mid + k * IN_PITCH;
-      int acc = 0;
-      for (int r = 0; r < n; r++) acc += m[r] * x[r];
-      S.coef[v * Q + k] = (int16_t)((acc + (1 << (sh2 - 1))) >> sh2);
-    }
-    __syncwarp();
+    fwd_passes<Q>(S, sM, n, msk, sh1, sh2, lane);
     // ---- quantise (enc/encode_block.c:75-178, rdoq == 0) ----
     const uint8_t *scan = sZ + (Q == 4 ? 0 : Q == 8 ? 16 : 80);
     const int intra = (t.coeff_type >> 1) & 1, chroma = t.coeff_type & 1;
@@ -229,25 +260,7 @@ __global__ void __launch_bounds__(TW * 32) k_tb(const TbParams P) {
     const int dq = c_dqscale[qrem], rshift = LG - 1, add = 1 << (rshift - 1);
     for (int i = lane; i < Q * Q; i += 32) S.coef[i] = (int16_t)((((int)S.coef[i] * dq << qper) + add) >> rshift);
     __syncwarp();
-    // ---- inverse pass 1: mid[k][r] = clip16((sum_v M[v][r] c[v][k] + 64) >> 7) ----
-    constexpr int MSK = NI == 4 ? 3 : NI == 8 ? 2 : NI == 16 ? 1 : 0;
-    for (int i = lane; i < Q * NI; i += 32) {
-      const int k = i / NI, r = i - k * NI;
-      int acc = 0;
-#pragma unroll 4
-      for (int v = 0; v < Q; v++) acc += sM[((v << MSK) << 5) + r] * S.coef[v * Q + k];
-      S.mid[k * IN_PITCH + r] = (int16_t)clip16((acc + 64) >> 7);
-    }
-    __syncwarp();
-    // ---- inverse pass 2: block[r][c] = clip16((sum_k M[k][c] mid[k][r] + 2048) >> 12) ----
-    for (int i = lane; i < NI * NI; i += 32) {
-      const int r = i / NI, c = i - r * NI;
-      int acc = 0;
-#pragma unroll 4
-      for (int k = 0; k < Q; k++) acc += sM[((k << MSK) << 5) + c] * S.mid[k * IN_PITCH + r];
-      S.in[r * IN_PITCH + c] = (int16_t)clip16((acc + 2048) >> 12);
-    }
-    __syncwarp();
+    inv_passes<NI, Q>(S, sM, lane);
   }
   // ---- reconstruct (common_block.c:148-156; 64: 2x nearest-neighbour up-sampling, transform.c:507-514) + SSD ----
   const uint8_t *org = nullptr;
@@ -286,6 +299,61 @@ __global__ void __launch_bounds__(TW * 32) k_tb(const TbParams P) {
     for (int m = 16; m > 0; m >>= 1) ssd += __shfl_xor_sync(0xffffffffu, ssd, m);
     if (lane == 0) P.ssd[ti] = ssd;
   }
+}
+
+// Stand-alone transform of ONE int16 block (the reference's transform()/inverse_transform() signatures,
+// common/transform.h:36-37): forward N x N (stride N) -> low Q x Q corner written at stride N; inverse reads
+// that corner at stride N -> N x N block.  One warp.  Used by the per-block compatibility entry points.
+template <int N>
+__global__ void __launch_bounds__(32) k_tb_raw(const int16_t *__restrict__ in, int16_t *__restrict__ out, int fastflag, int inverse) {
+  __shared__ __align__(16) int16_t sM[32 * 32];
+  __shared__ __align__(16) WarpScratch S;
+  const int lane = threadIdx.x;
+  for (int i = lane; i < 32 * 32 / 2; i += 32) reinterpret_cast<uint32_t *>(sM)[i] = reinterpret_cast<const uint32_t *>(c_m32)[i];
+  __syncwarp();
+  constexpr int LG = N == 4 ? 2 : N == 8 ? 3 : N == 16 ? 4 : N == 32 ? 5 : 6;
+  constexpr int Q = N < 16 ? N : 16;
+  constexpr int NI = N == 64 ? 32 : N;
+  if (!inverse) {
+    const bool fast = N > 16 && fastflag;
+    const int f = fast ? N / 16 : (N == 64 ? 2 : 1);
+    const int n = N / f;
+    const int sh1 = fast ? (N == 64 ? 8 : 6) : (N == 64 ? 7 : LG), sh2 = fast ? 9 : (N == 64 ? 10 : LG + 5);
+    const int msk = 5 - (31 - __clz(n));
+    for (int i = lane; i < n * n; i += 32) {
+      const int r = i / n, c = i - r * n;
+      int s = 0;
+      for (int a = 0; a < f; a++)
+        for (int b = 0; b < f; b++) s += in[(r * f + a) * N + c * f + b];
+      S.in[r * IN_PITCH + c] = (int16_t)s;
+    }
+    __syncwarp();
+    fwd_passes<Q>(S, sM, n, msk, sh1, sh2, lane);
+    for (int i = lane; i < Q * Q; i += 32) out[(i / Q) * N + (i % Q)] = S.coef[i];
+  } else {
+    for (int i = lane; i < Q * Q; i += 32) S.coef[i] = in[(i / Q) * N + (i % Q)];
+    __syncwarp();
+    inv_passes<NI, Q>(S, sM, lane);
+    for (int i = lane; i < N * N; i += 32) {
+      const int r = i / N, c = i - r * N;
+      out[i] = N == 64 ? S.in[(r >> 1) * IN_PITCH + (c >> 1)] : S.in[r * IN_PITCH + c];
+    }
+  }
+}
+
+int tb_raw(int size, int fast, int inverse, const int16_t *d_in, int16_t *d_out) {
+  Context &c = ctx();
+  if (upload_tables()) return -1;
+  switch (size) {
+    case 4: k_tb_raw<4><<<1, 32, 0, c.stream>>>(d_in, d_out, fast, inverse); break;
+    case 8: k_tb_raw<8><<<1, 32, 0, c.stream>>>(d_in, d_out, fast, inverse); break;
+    case 16: k_tb_raw<16><<<1, 32, 0, c.stream>>>(d_in, d_out, fast, inverse); break;
+    case 32: k_tb_raw<32><<<1, 32, 0, c.stream>>>(d_in, d_out, fast, inverse); break;
+    case 64: k_tb_raw<64><<<1, 32, 0, c.stream>>>(d_in, d_out, fast, inverse); break;
+    default: return fail("transform: size %d", size);
+  }
+  THOR_LAUNCHED();
+  return 0;
 }
 
 static int run_tb(List *L, int decode, bool want_ssd) {
