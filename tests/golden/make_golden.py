@@ -1,0 +1,200 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.  Run in the BUILD container, where /root/reference is mounted and
+`make -C oracle ref` has compiled the unmodified reference into oracle/_ref/ :
+
+    python tests/golden/make_golden.py
+
+The reference (awakecoding/thor) ships no tests, known-answer vectors or fixtures of its own, so the
+golden data are outputs of the reference itself on seeded inputs:
+
+  kernels.npz   inputs AND reference outputs of every hot-path function, produced by
+                oracle/_ref/libthorref.so with its SIMD dispatch on (the plain-C path is checked equal here);
+  streams.json  md5 of the bitstream and of the reconstruction that oracle/_ref/Thorenc writes for three shipped
+                operating points on seeded synthetic clips (+ that Thordec reproduces the reconstruction).
+
+tests/test_golden.py checks the oracle port (CPU) and libthorcuda (GPU) against these files; nothing there needs
+/root/reference.
+"""
+import ctypes as C
+import hashlib
+import json
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+from thorref import (BLOCKINFO, THOR_CONFIGS, Picture, blocky_frame, load_ref, ptr, random_blockinfo, run_thordec, run_thorenc,  # noqa: E402
+                     set_ref_simd, smooth_frame, write_clip)
+
+
+class Mv(C.Structure):
+    _fields_ = [("x", C.c_int16), ("y", C.c_int16)]
+
+
+def aligned(a):
+    raw = np.zeros(a.nbytes + 64, np.uint8)
+    off = (-raw.ctypes.data) % 64
+    out = raw[off:off + a.nbytes].view(a.dtype).reshape(a.shape)
+    out[...] = a
+    return out
+
+
+def residuals(rng, n):
+    cb = ((np.add.outer(np.arange(n), np.arange(n)) & 1) * 510 - 255).astype(np.int16)
+    return [np.full((n, n), 255, np.int16), np.full((n, n), -255, np.int16), cb,
+            np.clip(rng.normal(0, 20, (n, n)).round(), -255, 255).astype(np.int16),
+            rng.integers(-255, 256, (n, n)).astype(np.int16)]
+
+
+def kernels(ref):
+    out = {}
+    rng = np.random.default_rng(20261104)
+    # ---- transforms / quantisation (a10-a13) ----
+    for n in (4, 8, 16, 32, 64):
+        q = min(n, 16)
+        blocks = np.stack(residuals(rng, n))
+        out[f"tr{n}_in"] = blocks
+        fw, qq, cbp, rec = [], [], [], []
+        for blk in blocks:
+            blk = aligned(blk)
+            for fast in ((0, 1) if n > 16 else (0,)):
+                co = aligned(np.zeros((n, n), np.int16))
+                ref.transform(ptr(blk), ptr(co), n, fast)
+                fw.append(co[:q, :q].copy())
+                for qp in (0, 20, 32, 51):
+                    for cbt in (0, 1, 2, 3):
+                        cq = aligned(np.zeros((n, n), np.int16))
+                        cbp.append(ref.quantize(ptr(co), ptr(cq), qp, n, cbt, 0))
+                        qq.append(cq[:q, :q].copy())
+                    dq = aligned(np.zeros((n, n), np.int16))
+                    ref.dequantize(ptr(cq), ptr(dq), qp, n)
+                    ib = aligned(np.zeros((n, n), np.int16))
+                    ref.inverse_transform(ptr(dq), ptr(ib), n)
+                    rec.append(ib.copy())
+        out[f"tr{n}_fwd"], out[f"tr{n}_q"], out[f"tr{n}_cbp"], out[f"tr{n}_rec"] = np.stack(fw), np.stack(qq), np.array(cbp, np.int32), np.stack(rec)
+    # ---- inter prediction (a6-a8') ----
+    src = rng.integers(0, 256, (48, 48), dtype=np.uint8)
+    src[::7, ::5] = 255
+    src[3::11, 1::3] = 0
+    out["pred_src"] = src
+    src = aligned(src)
+    base = src.ctypes.data + 16 * 48 + 16
+    luma = np.zeros((2, 4, 4, 16, 16), np.uint8)
+    for bip in (0, 1):
+        for fy in range(4):
+            for fx in range(4):
+                mv = Mv(fx - 8, fy + 4)          # integer part (-2, +1)
+                o = aligned(np.zeros((16, 16), np.uint8))
+                ref.get_inter_prediction_luma(ptr(o), C.c_void_p(base), 16, 16, 48, 16, C.byref(mv), 0, bip)
+                luma[bip, fy, fx] = o
+    out["pred_luma"] = luma
+    chroma = np.zeros((8, 8, 8, 8), np.uint8)
+    for fy in range(8):
+        for fx in range(8):
+            mv = Mv(fx + 8, fy - 16)             # integer part (+1, -2)
+            o = aligned(np.zeros((8, 8), np.uint8))
+            ref.get_inter_prediction_chroma(ptr(o), C.c_void_p(base), 8, 8, 48, 8, C.byref(mv), 0)
+            chroma[fy, fx] = o
+    out["pred_chroma"] = chroma
+    # ---- SAD family (a1-a5) ----
+    win = smooth_frame(64, 64, seed=4)[0]
+    out["sad_ref"] = win
+    win = aligned(win)
+    res = []
+    orgs = []
+    for k, (w, h) in enumerate(((8, 8), (16, 16), (32, 32), (16, 8), (8, 16))):
+        oy, ox = 12 + k, 14 + 2 * k
+        org = aligned(np.clip(win[oy:oy + h, ox:ox + w].astype(int) + rng.integers(-9, 10, (h, w)), 0, 255).astype(np.uint8))
+        padded = np.zeros((32, 32), np.uint8)
+        padded[:h, :w] = org
+        orgs.append(padded)
+        b = C.c_void_p(win.ctypes.data + (oy + 1) * 64 + ox - 1)
+        for f in ("sad_calc", "widesad_calc", "sad_calc_fasthalf", "sad_calc_fastquarter"):
+            getattr(ref, f).restype = C.c_uint
+        row = [w, h, oy + 1, ox - 1, ref.sad_calc(ptr(org), b, w, 64, w, h)]
+        x = C.c_int(0)
+        row += [ref.widesad_calc(ptr(org), b, w, 64, w, h, C.byref(x)), x.value]
+        x, y = C.c_int(0), C.c_int(0)
+        row += [ref.sad_calc_fasthalf(ptr(org), b, w, 64, w, h, C.byref(x), C.byref(y)), x.value, y.value]
+        for (px, py) in ((0, 0), (2, 0), (0, 2), (2, 2)):
+            x, y = C.c_int(px), C.c_int(py)
+            row += [ref.sad_calc_fastquarter(ptr(org), b, w, 64, w, h, C.byref(x), C.byref(y)), x.value, y.value]
+        rb = aligned(win[oy + 1:oy + 1 + h, ox - 1:ox - 1 + w].copy())
+        row.append(ref.ssd_calc(ptr(org), ptr(rb), w, w, w, h))
+        res.append(row)
+    out["sad_org"] = np.stack(orgs)
+    out["sad_res"] = np.array(res, np.int64)
+    # ---- clip_mv (a20) ----
+    cm = []
+    for _ in range(64):
+        fw_, fh_ = (416, 240) if rng.random() < 0.5 else (1920, 1080)
+        size = int(rng.choice([8, 16, 32, 64]))
+        ypos, xpos = int(rng.integers(0, fh_ // 8)) * 8, int(rng.integers(0, fw_ // 8)) * 8
+        sign = int(rng.integers(0, 2))
+        mx, my = int(rng.integers(-2000, 2000)), int(rng.integers(-2000, 2000))
+        m = Mv(mx, my)
+        ref.clip_mv(C.byref(m), ypos, xpos, fw_, fh_, size, sign)
+        cm.append([mx, my, ypos, xpos, fw_, fh_, size, sign, m.x, m.y])
+    out["clip_mv"] = np.array(cm, np.int32)
+    # ---- frame tail: deblock Y/UV, reference creation (a14, a15, a17) on a 192x136 frame (partial SB row/col) ----
+    w, h, qp = 192, 136, 32
+    y, u, v = blocky_frame(w, h, seed=33)
+    bi = random_blockinfo(w, h, np.random.default_rng(7))
+    pic = Picture(w, h)
+    pic.set_visible(y, u, v)
+    f = pic.as_ref_struct()
+    chroma_qp = (C.c_int * 52).in_dll(ref, "chroma_qp")
+    ref.deblock_frame_y(C.byref(f), ptr(bi), w, h, C.c_uint8(qp))
+    ref.deblock_frame_uv(C.byref(f), ptr(bi), w, h, C.c_uint8(chroma_qp[qp]))
+    out["lf_in_y"], out["lf_in_u"], out["lf_in_v"] = y, u, v
+    out["lf_blockinfo"] = bi.view(np.uint8).reshape(-1, BLOCKINFO.itemsize)
+    out["lf_qp"] = np.array([qp, chroma_qp[qp]], np.int32)
+    out["lf_out_y"], out["lf_out_u"], out["lf_out_v"] = pic.plane(0).copy(), pic.plane(1).copy(), pic.plane(2).copy()
+    refpic = Picture(w, h, 96, 48)
+    fr = refpic.as_ref_struct()
+    ref.create_reference_frame(C.byref(fr), C.byref(f))
+    out["ref_md5"] = np.frombuffer(hashlib.md5(refpic.buf_y[:, :w + 192].tobytes() + refpic.buf_u[:, :w // 2 + 96].tobytes() +
+                                               refpic.buf_v[:, :w // 2 + 96].tobytes()).digest(), np.uint8)
+    return out
+
+
+def streams():
+    res = {}
+    with tempfile.TemporaryDirectory() as d:
+        for cfg, w, h, n, qp, seed in (("LDB_low_complexity", 416, 240, 10, 32, 1234), ("LDB_medium_complexity", 192, 136, 6, 30, 7),
+                                       ("RA_high_efficiency", 128, 64, 9, 34, 7), ("LDB_low_complexity", 64, 64, 3, 32, 1234),
+                                       ("LDB_medium_complexity", 72, 64, 3, 28, 1234), ("RA_high_efficiency", 64, 64, 3, 34, 1234)):
+            yuv = os.path.join(d, "clip.yuv")
+            write_clip(yuv, w, h, n, seed)
+            bit, rec, _ = run_thorenc("Thorenc", cfg, yuv, w, h, n, qp, os.path.join(d, "o"))
+            dec = run_thordec("Thordec", os.path.join(d, "o.bit"), os.path.join(d, "dec.yuv"))
+            assert dec == rec, "reference decoder does not reproduce the encoder's reconstruction"
+            res[f"{cfg}_{w}x{h}x{n}_qp{qp}_seed{seed}"] = {
+                "config": cfg, "width": w, "height": h, "frames": n, "qp": qp, "seed": seed,
+                "clip_md5": hashlib.md5(open(yuv, "rb").read()).hexdigest(),
+                "bit_bytes": len(bit), "bit_md5": hashlib.md5(bit).hexdigest(), "rec_md5": hashlib.md5(rec).hexdigest()}
+    return res
+
+
+def main():
+    ref = load_ref()
+    if ref is None:
+        raise SystemExit("oracle/_ref/libthorref.so missing: run `make -C oracle ref` where /root/reference is mounted")
+    set_ref_simd(ref, 1)
+    a = kernels(ref)
+    set_ref_simd(ref, 0)
+    b = kernels(ref)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), f"reference SIMD and plain-C paths disagree on {k}"
+    set_ref_simd(ref, 1)
+    np.savez_compressed(os.path.join(HERE, "kernels.npz"), **a)
+    json.dump(streams(), open(os.path.join(HERE, "streams.json"), "w"), indent=1, sort_keys=True)
+    print("wrote", os.path.join(HERE, "kernels.npz"), os.path.getsize(os.path.join(HERE, "kernels.npz")), "bytes;",
+          os.path.join(HERE, "streams.json"))
+
+
+if __name__ == "__main__":
+    main()

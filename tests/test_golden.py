@@ -1,0 +1,278 @@
+"""Golden vectors (tests/golden/, produced by the unmodified reference through tests/golden/make_golden.py):
+the oracle port is pinned against them on the CPU, libthorcuda on the GPU.  Needs neither /root/reference nor
+oracle/_ref at run time."""
+import ctypes as C
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from thorref import (BLOCKINFO, REF_DIR, Picture, load_oracle, ptr, run_thordec, run_thorenc, write_clip)
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def g():
+    return np.load(os.path.join(GOLD, "kernels.npz"))
+
+
+@pytest.fixture(scope="module")
+def orc():
+    o = load_oracle()
+    for f in ("orc_sad", "orc_widesad", "orc_sad_fasthalf", "orc_sad_fastquarter"):
+        getattr(o, f).restype = C.c_uint
+    return o
+
+
+def _z(n, dt=np.int16):
+    return np.zeros((n, n), dt)
+
+
+# ------------------------------------------------------------------------------ oracle port (CPU) ----
+@pytest.mark.parametrize("n", [4, 8, 16, 32, 64])
+def test_port_transform_chain(g, orc, n):
+    q = min(n, 16)
+    i_f = i_q = i_r = 0
+    for blk in g[f"tr{n}_in"]:
+        blk = np.ascontiguousarray(blk)
+        for fast in ((0, 1) if n > 16 else (0,)):
+            co = _z(n)
+            orc.orc_transform(ptr(blk), ptr(co), n, fast)
+            assert np.array_equal(co[:q, :q], g[f"tr{n}_fwd"][i_f]), ("fwd", n, fast)
+            full = _z(n)
+            full[:q, :q] = g[f"tr{n}_fwd"][i_f]
+            i_f += 1
+            for qp in (0, 20, 32, 51):
+                for cbt in range(4):
+                    cq = _z(n)
+                    cbp = orc.orc_quantize(ptr(full), ptr(cq), qp, n, cbt)
+                    assert cbp == g[f"tr{n}_cbp"][i_q] and np.array_equal(cq[:q, :q], g[f"tr{n}_q"][i_q]), ("quant", n, qp, cbt)
+                    i_q += 1
+                dq, ib = _z(n), _z(n)
+                orc.orc_dequantize(ptr(cq), ptr(dq), qp, n)
+                orc.orc_inverse_transform(ptr(dq), ptr(ib), n)
+                assert np.array_equal(ib, g[f"tr{n}_rec"][i_r]), ("inverse", n, qp)
+                i_r += 1
+
+
+def test_port_inter_prediction(g, orc):
+    src = np.ascontiguousarray(g["pred_src"])
+    base = C.c_void_p(src.ctypes.data + 16 * 48 + 16)
+    for bip in (0, 1):
+        for fy in range(4):
+            for fx in range(4):
+                o = _z(16, np.uint8)
+                orc.orc_inter_luma(ptr(o), base, 16, 16, 48, 16, fx - 8, fy + 4, 0, bip)
+                assert np.array_equal(o, g["pred_luma"][bip, fy, fx]), (bip, fy, fx)
+    for fy in range(8):
+        for fx in range(8):
+            o = _z(8, np.uint8)
+            orc.orc_inter_chroma(ptr(o), base, 8, 8, 48, 8, fx + 8, fy - 16, 0)
+            assert np.array_equal(o, g["pred_chroma"][fy, fx]), (fy, fx)
+
+
+def test_port_sad_family(g, orc):
+    win = np.ascontiguousarray(g["sad_ref"])
+    for row, padded in zip(g["sad_res"], g["sad_org"]):
+        w, h, by, bx = (int(v) for v in row[:4])
+        org = np.ascontiguousarray(padded[:h, :w])
+        b = C.c_void_p(win.ctypes.data + by * 64 + bx)
+        got = [orc.orc_sad(ptr(org), b, w, 64, w, h)]
+        x, y = C.c_int(0), C.c_int(0)
+        got += [orc.orc_widesad(ptr(org), b, w, 64, w, h, C.byref(x)), x.value]
+        got += [orc.orc_sad_fasthalf(ptr(org), b, w, 64, w, h, C.byref(x), C.byref(y)), x.value, y.value]
+        for (px, py) in ((0, 0), (2, 0), (0, 2), (2, 2)):
+            x, y = C.c_int(px), C.c_int(py)
+            got += [orc.orc_sad_fastquarter(ptr(org), b, w, 64, w, h, C.byref(x), C.byref(y)), x.value, y.value]
+        got.append(orc.orc_ssd(ptr(org), b, w, 64, w, h))
+        assert got == [int(v) for v in row[4:]], (w, h)
+
+
+def test_port_clip_mv(g, orc):
+    for mx, my, ypos, xpos, fw, fh, size, sign, ox, oy in g["clip_mv"]:
+        ax, ay = C.c_int16(mx), C.c_int16(my)
+        orc.orc_clip_mv(C.byref(ax), C.byref(ay), int(ypos), int(xpos), int(fw), int(fh), int(size), int(sign))
+        assert (ax.value, ay.value) == (ox, oy)
+
+
+def _lf_inputs(g):
+    y, u, v = (np.ascontiguousarray(g[k]) for k in ("lf_in_y", "lf_in_u", "lf_in_v"))
+    bi = np.ascontiguousarray(g["lf_blockinfo"]).view(BLOCKINFO).reshape(-1)
+    return y, u, v, bi, int(g["lf_qp"][0]), int(g["lf_qp"][1])
+
+
+def test_port_frame_tail(g, orc):
+    y, u, v, bi, qp, qpc = _lf_inputs(g)
+    h, w = y.shape
+    assert orc.orc_chroma_qp(qp) == qpc
+    pic = Picture(w, h)
+    pic.set_visible(y, u, v)
+    orc.orc_deblock_frame_y(C.c_void_p(pic.origin_ptr(0)), pic.stride_y, ptr(bi), w, h, qp)
+    orc.orc_deblock_frame_uv(C.c_void_p(pic.origin_ptr(1)), C.c_void_p(pic.origin_ptr(2)), pic.stride_c, ptr(bi), w, h, qpc)
+    for i, k in enumerate(("lf_out_y", "lf_out_u", "lf_out_v")):
+        assert np.array_equal(pic.plane(i), g[k]), k
+    r = Picture(w, h, 96, 48)
+    for i in range(3):
+        r.plane(i)[...] = pic.plane(i)
+    orc.orc_pad_plane(C.c_void_p(r.origin_ptr(0)), r.stride_y, w, h, 96, 96)
+    orc.orc_pad_plane(C.c_void_p(r.origin_ptr(1)), r.stride_c, w // 2, h // 2, 48, 48)
+    orc.orc_pad_plane(C.c_void_p(r.origin_ptr(2)), r.stride_c, w // 2, h // 2, 48, 48)
+    md5 = hashlib.md5(r.buf_y[:, :w + 192].tobytes() + r.buf_u[:, :w // 2 + 96].tobytes() + r.buf_v[:, :w // 2 + 96].tobytes()).digest()
+    assert md5 == bytes(g["ref_md5"])
+
+
+def _streams():
+    return json.load(open(os.path.join(GOLD, "streams.json")))
+
+
+@pytest.mark.parametrize("key", sorted(_streams()))
+def test_reference_binaries_reproduce_golden_streams(tmp_path, key):
+    """The stock reference build (when it travelled with the repo) still produces the committed hashes: guards
+    the end-to-end oracle against a changed compiler / numpy (the clip's own md5 is checked first)."""
+    if not os.path.exists(os.path.join(REF_DIR, "Thorenc")):
+        pytest.skip("oracle/_ref/Thorenc not built")
+    e = _streams()[key]
+    yuv = str(tmp_path / "clip.yuv")
+    write_clip(yuv, e["width"], e["height"], e["frames"], e["seed"])
+    if hashlib.md5(open(yuv, "rb").read()).hexdigest() != e["clip_md5"]:
+        pytest.skip("synthetic clip differs on this numpy build; regenerate tests/golden")
+    bit, rec, _ = run_thorenc("Thorenc", e["config"], yuv, e["width"], e["height"], e["frames"], e["qp"], str(tmp_path / "o"))
+    assert (len(bit), hashlib.md5(bit).hexdigest(), hashlib.md5(rec).hexdigest()) == (e["bit_bytes"], e["bit_md5"], e["rec_md5"])
+    assert run_thordec("Thordec", str(tmp_path / "o.bit"), str(tmp_path / "d.yuv")) == rec
+
+
+# ------------------------------------------------------------------------------ libthorcuda (GPU) ----
+@pytest.fixture(scope="module")
+def tb():
+    import thor_b200 as t
+    t.init(0)
+    yield t
+    t.shutdown()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [4, 8, 16, 32, 64])
+def test_gpu_transform_chain(g, tb, n):
+    """forward transform through the per-block API; quantise + reconstruct through the batched encoder leg with
+    org = max(r,0), pred = max(-r,0) so that org - pred is the golden residual."""
+    lib = tb.cdll()
+    q = min(n, 16)
+    blocks = g[f"tr{n}_in"]
+    fasts = (0, 1) if n > 16 else (0,)
+    i_f = 0
+    for blk in blocks:
+        blk = np.ascontiguousarray(blk)
+        for fast in fasts:
+            co = _z(n)
+            lib.transform(ptr(blk), ptr(co), n, fast)
+            assert np.array_equal(co[:q, :q], g[f"tr{n}_fwd"][i_f]), ("fwd", n, fast)
+            i_f += 1
+    # one picture row of blocks per (block, fast, qp, cbt)
+    combos = [(b, f, qp, cbt) for b in range(len(blocks)) for f in fasts for qp in (0, 20, 32, 51) for cbt in range(4)]
+    cols = 8
+    W, H = cols * 64, ((len(combos) + cols - 1) // cols) * 64
+    oy, py = np.zeros((H, W), np.uint8), np.zeros((H, W), np.uint8)
+    tasks = np.zeros(len(combos), tb.TB_TASK)
+    for i, (b, f, qp, cbt) in enumerate(combos):
+        x, y = (i % cols) * 64, (i // cols) * 64
+        r = blocks[b].astype(np.int32)
+        oy[y:y + n, x:x + n] = np.maximum(r, 0)
+        py[y:y + n, x:x + n] = np.maximum(-r, 0)
+        tasks[i] = (x, y, n, 0, qp, cbt, f, 0, 1, 2, 0)
+    zc = np.zeros((H // 2, W // 2), np.uint8)
+    porg, ppred, prec = tb.Picture(W, H), tb.Picture(W, H), tb.Picture(W, H)
+    porg.upload(oy, zc, zc)
+    ppred.upload(py, zc, zc)
+    tb.ops.pool_layout(tasks)
+    coeffq, cbp, _ = tb.ops.encode_blocks([porg, ppred, prec], tasks)
+    ry = prec.download()[0]
+    for i, (b, f, qp, cbt) in enumerate(combos):
+        off = int(tasks[i]["coeff_offset"])
+        assert cbp[i] == (g[f"tr{n}_cbp"][i] != 0), ("cbp", n, combos[i])
+        assert np.array_equal(coeffq[off:off + q * q].reshape(q, q), g[f"tr{n}_q"][i]), ("quant", n, combos[i])
+        if cbt == 3:
+            x, y = (i % cols) * 64, (i // cols) * 64
+            want = py[y:y + n, x:x + n].astype(np.int32)
+            if cbp[i]:
+                want = np.clip(want + g[f"tr{n}_rec"][i // 4], 0, 255)
+            assert np.array_equal(ry[y:y + n, x:x + n], want), ("rec", n, combos[i])
+    for p in (porg, ppred, prec):
+        p.close()
+
+
+@pytest.mark.gpu
+def test_gpu_inter_prediction(g, tb):
+    src = g["pred_src"]
+    # a 16x16 picture whose padded planes ARE the 48x48 golden source: block origin (16,16) of the source = visible (0,0)
+    ref = tb.Picture(16, 16, 16, 16)
+    dst = tb.Picture(16, 16)
+    assert ref.stride_y == 48 and ref.stride_c == 48
+    cpl = np.zeros((8 + 32, 48), np.uint8)
+    cpl[:, :] = src[:40, :]                      # chroma plane: origin (16,16) as well
+    ref.upload_padded(src, cpl, cpl)
+    for bip in (0, 1):
+        tasks = np.zeros(16, tb.PRED_TASK)
+        for fy in range(4):
+            for fx in range(4):
+                tasks[0] = (0, 0, 16, 16, 0, -1, fx - 8, fy + 4, 0, 0, 0, 0, 1, 0)
+                tb.ops.predict_blocks([ref, dst], tasks[:1], bip, planes=1)
+                assert np.array_equal(dst.download()[0], g["pred_luma"][bip, fy, fx]), (bip, fy, fx)
+    for fy in range(8):
+        for fx in range(8):
+            t = np.zeros(1, tb.PRED_TASK)
+            t[0] = (0, 0, 16, 16, 0, -1, fx + 8, fy - 16, 0, 0, 0, 0, 1, 0)
+            tb.ops.predict_blocks([ref, dst], t, 0, planes=2)
+            assert np.array_equal(dst.download()[1], g["pred_chroma"][fy, fx]), (fy, fx)
+    ref.close()
+    dst.close()
+
+
+@pytest.mark.gpu
+def test_gpu_sad_family(g, tb):
+    win = g["sad_ref"]
+    ref = tb.Picture(32, 32, 16, 8)              # padded luma plane 64x64 = the golden window, visible origin (16,16)
+    assert ref.stride_y == 64
+    ref.upload_padded(win, np.zeros((24, 32), np.uint8), np.zeros((24, 32), np.uint8))
+    org = tb.Picture(32, 32)
+    zc = np.zeros((16, 16), np.uint8)
+    for row, padded in zip(g["sad_res"], g["sad_org"]):
+        w, h, by, bx = (int(v) for v in row[:4])
+        org.upload(np.ascontiguousarray(padded), zc, zc)
+        want = [int(v) for v in row[4:]]
+        t = np.zeros(1, tb.COST_TASK)
+        t[0] = (0, 0, w, h, 0, 1, 0, 0, bx - 16, by - 16, 0)
+        got = [int(tb.ops.cost_batch(tb.COST_SAD, [org, ref], t)[0]["cost"])]
+        r = tb.ops.cost_batch(tb.COST_WIDESAD, [org, ref], t)[0]
+        got += [int(r["cost"]), int(r["x"])]
+        r = tb.ops.cost_batch(tb.COST_FASTHALF, [org, ref], t)[0]
+        got += [int(r["cost"]), int(r["x"]), int(r["y"])]
+        for (px, py) in ((0, 0), (2, 0), (0, 2), (2, 2)):
+            t[0]["hx"], t[0]["hy"] = px, py
+            r = tb.ops.cost_batch(tb.COST_FASTQUARTER, [org, ref], t)[0]
+            got += [int(r["cost"]), int(r["x"]), int(r["y"])]
+        t[0]["hx"], t[0]["hy"] = 0, 0
+        got.append(int(tb.ops.cost_batch(tb.COST_SSD, [org, ref], t)[0]["cost"]))
+        assert got == want, (w, h)
+    ref.close()
+    org.close()
+
+
+@pytest.mark.gpu
+def test_gpu_frame_tail(g, tb):
+    y, u, v, bi, qp, _ = _lf_inputs(g)
+    h, w = y.shape
+    rec, newref = tb.Picture(w, h), tb.Picture(w, h, 96, 48)
+    rec.upload(y, u, v)
+    tb.ops.blockinfo_upload(rec, bi)
+    tb.ops.loopfilter_frame(rec, qp, tb.LF_DEBLOCK_Y | tb.LF_DEBLOCK_UV | tb.LF_MAKE_REF, ref_out=newref)
+    got = rec.download()
+    for i, k in enumerate(("lf_out_y", "lf_out_u", "lf_out_v")):
+        assert np.array_equal(got[i], g[k]), k
+    ny, nu, nv = newref.download_padded()
+    md5 = hashlib.md5(ny[:, :w + 192].tobytes() + nu[:, :w // 2 + 96].tobytes() + nv[:, :w // 2 + 96].tobytes()).digest()
+    assert md5 == bytes(g["ref_md5"])
+    rec.close()
+    newref.close()

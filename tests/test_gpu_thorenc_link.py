@@ -8,6 +8,8 @@ decoder's output must be byte-identical to the stock CPU binaries'.
 
 The per-block API is synchronous (one PCIe round trip per call), so the clips are tiny; the point is
 bit-exactness of the whole encode/decode with the CUDA kernels in the loop, not speed."""
+import hashlib
+import json
 import os
 
 import pytest
@@ -35,6 +37,11 @@ def test_thorenc_thordec_linked_against_libthorcuda(tmp_path, cfg, w, h, frames,
     bit_cpu, rec_cpu, t_cpu = run_thorenc("Thorenc", cfg, yuv, w, h, frames, qp, str(tmp_path / "cpu"))
     bit_gpu, rec_gpu, t_gpu = run_thorenc("Thorenc_cuda", cfg, yuv, w, h, frames, qp, str(tmp_path / "gpu"), timeout=900)
     print(f"{cfg}: {len(bit_cpu)} bytes; stock {t_cpu:.2f} s, linked against libthorcuda {t_gpu:.2f} s")
+    # the committed golden hashes of the same clip (tests/golden/streams.json), when numpy reproduces the clip
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "streams.json")))
+    e = gold.get(f"{cfg}_{w}x{h}x{frames}_qp{qp}_seed1234")
+    if e and hashlib.md5(open(yuv, "rb").read()).hexdigest() == e["clip_md5"]:
+        assert (hashlib.md5(bit_gpu).hexdigest(), hashlib.md5(rec_gpu).hexdigest()) == (e["bit_md5"], e["rec_md5"]), "golden hash differs"
     assert bit_gpu == bit_cpu, "bitstream differs"
     assert rec_gpu == rec_cpu, "encoder reconstruction differs"
     dec_cpu = run_thordec("Thordec", str(tmp_path / "cpu.bit"), str(tmp_path / "dec_cpu.yuv"))
