@@ -235,7 +235,8 @@ def test_gpu_sad_family(g, tb):
     win = g["sad_ref"]
     ref = tb.Picture(32, 32, 16, 8)              # padded luma plane 64x64 = the golden window, visible origin (16,16)
     assert ref.stride_y == 64
-    ref.upload_padded(win, np.zeros((24, 32), np.uint8), np.zeros((24, 32), np.uint8))
+    zpad = np.zeros(ref.padded_shapes()[1], np.uint8)
+    ref.upload_padded(win, zpad, zpad)
     org = tb.Picture(32, 32)
     zc = np.zeros((16, 16), np.uint8)
     for row, padded in zip(g["sad_res"], g["sad_org"]):
