@@ -30,27 +30,82 @@ __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) {
   return r;
 }
 
-struct SadCtx {
-  const uint8_t *sOrg, *sWin;
-  uint32_t *part;               // [8 warps-worth of strips: p*2+ch][n*n] sums over 32x16 strips
-  uint16_t *t8, *t16;
-  int W, H, x0, y0, o;
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// Geometry of one launch configuration (search range R, a multiple of 4).
+//   n x n displacements per block.  A warp pass covers UPW block columns x DXL consecutive horizontal
+//   displacements (lane = u * DXL + d), so that a store instruction writes DXL consecutive table entries of a
+//   block (64 contiguous bytes for R = 16 / 32).  The last displacement column (index 2R) is the tail pass.
+template <int R>
+struct SadCfg {
+  static constexpr int n = 2 * R + 1, nn = n * n;
+  // 32 lanes per block column only for R = 16: at R = 32 the pending-half-sum rows would not fit in shared memory
+  static constexpr int DXL = R == 16 ? 32 : (2 * R) % 16 == 0 ? 16 : 8;
+  static constexpr int UPW = 32 / DXL;          // block columns per warp pass
+  static constexpr int NB = 4 / UPW;            // column passes that cover a warp's 4 block columns
+  static constexpr int NCH = 2 * R / DXL;       // displacement chunks
+  static constexpr int win_rows = 64 + 2 * R;
+  static constexpr int pitch = (64 + 2 * R + 15 + 15) & ~15;   // window rows start 16-byte aligned in global memory
+  static constexpr int buf_bytes = 64 * 64 + win_rows * pitch; // one stage: original SB | reference window
+  static constexpr int part_off = 2 * buf_bytes;               // uint32 [8 strips][nn]
+  static constexpr int pair_off = part_off + 8 * nn * 4;       // uint16 [8 warps][nn] (UPW == 1 only)
+  static constexpr int smem_bytes = pair_off + (UPW == 1 ? ((8 * nn * 2 + 15) & ~15) : 0);
 };
 
-// One "pass": this lane owns the two vertically adjacent 8x8 blocks (block column bx, block rows 2p and
-// 2p+1 of the SB) at ONE horizontal displacement index dxi and slides over all 2R+1 vertical ones.
-// m16 / m32: lane-xor distances that pair block columns (bx^1) and pair the pairs (bx^2) in this pass's
-// lane layout.  The 8 reference rows that start / end the slide touch fewer displacement rows than the
-// middle ones; FIRST / LAST blocks skip those (row r of the block only meets displacement rows j-r in
-// [0, 2R]), so no abs-diff is computed that is not part of an output.
+// where one pass's results go
+struct SadOut {
+  uint16_t *t8T, *t8B, *t16;    // already offset to this lane's horizontal displacement
+  uint32_t *part;               // this warp's 32x16 strip sums (+ displacement)
+  uint16_t *pair;               // this warp's pending 16x16 half sums (+ displacement)
+  bool okT, okB, ok16, lead;
+  int b;                        // column pass index inside the warp's 4 block columns
+};
+
+// combine the 8x16 column sum v of this lane's block column into the 16x16 and 32x16 levels.
+//   UPW 4 / 2: partner columns sit in other lanes of the same pass (shuffle);  UPW 1: they are other passes of
+//   the SAME lane, so the running sums live in this warp's shared-memory rows (no synchronisation needed);
+//   UPW 8 marks the tail pass (lane = 8 * p + bx).
+template <int UPW>
+__device__ __forceinline__ void sad_reduce(uint32_t v, int e, const SadOut &O) {
+  if (UPW == 8) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    if (O.ok16) O.t16[e] = (uint16_t)v;
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    if (O.lead) O.part[e] = v;
+  } else if (UPW == 4) {
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    if (O.ok16) O.t16[e] = (uint16_t)v;
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    if (O.lead) O.part[e] = v;
+  } else if (UPW == 2) {
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    if (O.ok16) O.t16[e] = (uint16_t)v;
+    if (O.lead) O.part[e] = O.b ? O.part[e] + v : v;
+  } else {
+    if (!(O.b & 1)) {
+      O.pair[e] = (uint16_t)v;
+    } else {
+      v += O.pair[e];
+      if (O.ok16) O.t16[e] = (uint16_t)v;
+      O.part[e] = O.b == 1 ? v : O.part[e] + v;
+    }
+  }
+}
+
+// One "pass": a lane owns the two vertically adjacent 8x8 blocks (block column bx, block rows 2p and 2p+1 of
+// the SB) at ONE horizontal displacement and slides over all 2R+1 vertical ones with 2 x 8 rotating
+// accumulators.  The 8 reference rows that start / end the slide touch fewer displacement rows than the middle
+// ones; FIRST / LAST skip those, so no abs-diff is computed that is not part of an output.
 enum { BLK_FIRST = 0, BLK_MID = 1, BLK_LAST = 2 };
 
-template <int MODE, int R>
+template <int MODE, int R, int UPW>
 __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint32_t (&oB)[8][2], uint32_t (&aT)[8], uint32_t (&aB)[8],
-                                          const uint8_t *col, int sh, bool okT, bool okB, bool ok16, bool ok32, int m16, int m32,
-                                          uint16_t *t8T, uint16_t *t8B, uint16_t *t16, uint32_t *part) {
-  constexpr int n = 2 * R + 1, pitch = (64 + 2 * R + 7) & ~3;
-  // col / t8T / t8B / t16 / part already point at this block's first reference row / first output row
+                                          const uint8_t *col, int sh, const SadOut &O, int e0) {
+  constexpr int n = SadCfg<R>::n, pitch = SadCfg<R>::pitch;
 #pragma unroll
   for (int s = 0; s < 8; s++) {
     const uint32_t *rt = reinterpret_cast<const uint32_t *>(col + s * pitch);
@@ -69,135 +124,178 @@ __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint
     if (MODE != BLK_FIRST || s == 7) {               // displacement row (s - 7) relative to this block is complete
       const int kc = (s + 1) & 7;
       const uint32_t vT = aT[kc], vB = aB[kc];
-      const int e = (s - 7) * n;
-      if (okT) t8T[e] = (uint16_t)vT;
-      if (okB) t8B[e] = (uint16_t)vB;
-      uint32_t v = vT + vB;
-      v += __shfl_xor_sync(0xffffffffu, v, m16);
-      if (ok16) t16[e] = (uint16_t)v;
-      v += __shfl_xor_sync(0xffffffffu, v, m32);
-      if (ok32) part[e] = v;
+      const int e = e0 + (s - 7) * n;
+      if (O.okT) O.t8T[e] = (uint16_t)vT;
+      if (O.okB) O.t8B[e] = (uint16_t)vB;
+      sad_reduce<UPW>(vT + vB, e, O);
       aT[kc] = 0; aB[kc] = 0;
     }
   }
 }
 
-template <int R>
-__device__ __forceinline__ void sad_pass(const SadCtx &C, int p, int bx, int dxi, int m16, int m32) {
-  constexpr int n = 2 * R + 1, nn = n * n, pitch = (64 + 2 * R + 7) & ~3;
+struct SadTile {
+  const uint8_t *sOrg, *sWin;
+  uint32_t *part;
+  uint16_t *pair;
+  uint16_t *t8, *t16;
+  int W, H, x0, y0, o;
+};
+
+template <int R, int UPW>
+__device__ __forceinline__ void sad_pass(const SadTile &C, int p, int bx, int dxi, int b, int warp, bool lead) {
+  constexpr int n = SadCfg<R>::n, nn = SadCfg<R>::nn, pitch = SadCfg<R>::pitch;
   uint32_t oT[8][2], oB[8][2];
 #pragma unroll
   for (int r = 0; r < 8; r++) {
     const uint32_t *a = reinterpret_cast<const uint32_t *>(C.sOrg + (16 * p + r) * 64 + bx * 8);
-    const uint32_t *b = reinterpret_cast<const uint32_t *>(C.sOrg + (16 * p + 8 + r) * 64 + bx * 8);
-    oT[r][0] = a[0]; oT[r][1] = a[1]; oB[r][0] = b[0]; oB[r][1] = b[1];
+    const uint32_t *bb = reinterpret_cast<const uint32_t *>(C.sOrg + (16 * p + 8 + r) * 64 + bx * 8);
+    oT[r][0] = a[0]; oT[r][1] = a[1]; oB[r][0] = bb[0]; oB[r][1] = bb[1];
   }
   // which outputs exist (frame edges) and where they go
-  const int gx8 = C.x0 + bx * 8, gyT = C.y0 + 16 * p, gyB = gyT + 8;
+  const int gx8 = C.x0 + bx * 8, gx16 = C.x0 + (bx & ~1) * 8, gyT = C.y0 + 16 * p, gyB = gyT + 8;
   const bool okx8 = gx8 + 8 <= C.W;
-  const bool okT = okx8 && gyT + 8 <= C.H, okB = okx8 && gyB + 8 <= C.H;
-  const bool ok16 = !(bx & 1) && gx8 + 16 <= C.W && gyT + 16 <= C.H;
-  const bool ok32 = !(bx & 3);
   const int bw8 = C.W >> 3, bw16 = C.W >> 4;
-  uint16_t *t8T = C.t8 + ((size_t)(gyT >> 3) * bw8 + (gx8 >> 3)) * nn + dxi;
-  uint16_t *t8B = C.t8 + ((size_t)(gyB >> 3) * bw8 + (gx8 >> 3)) * nn + dxi;
-  uint16_t *t16 = C.t16 + ((size_t)(gyT >> 4) * bw16 + (gx8 >> 4)) * nn + dxi;
-  uint32_t *part = C.part + (p * 2 + (bx >> 2)) * nn + dxi;
+  SadOut O;
+  O.okT = okx8 && gyT + 8 <= C.H; O.okB = okx8 && gyB + 8 <= C.H;
+  // the lane that completes a 16x16 sum: the odd column when partners are other passes (UPW 1), the even one else
+  O.ok16 = (UPW == 1 ? (bx & 1) : !(bx & 1)) && gx16 + 16 <= C.W && gyT + 16 <= C.H;
+  O.lead = lead; O.b = b;
+  O.t8T = C.t8 + ((size_t)(gyT >> 3) * bw8 + (gx8 >> 3)) * nn + dxi;
+  O.t8B = C.t8 + ((size_t)(gyB >> 3) * bw8 + (gx8 >> 3)) * nn + dxi;
+  O.t16 = C.t16 + ((size_t)(gyT >> 4) * bw16 + (gx16 >> 4)) * nn + dxi;
+  O.part = C.part + (p * 2 + (bx >> 2)) * nn + dxi;
+  O.pair = C.pair + warp * nn + dxi;
   const int off = bx * 8 + dxi + C.o;
   const int sh = (off & 3) * 8;
   const uint8_t *col = C.sWin + (16 * p) * pitch + (off & ~3);
   uint32_t aT[8], aB[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) { aT[k] = 0; aB[k] = 0; }
-  sad_block<BLK_FIRST, R>(oT, oB, aT, aB, col, sh, okT, okB, ok16, ok32, m16, m32, t8T, t8B, t16, part);
+  sad_block<BLK_FIRST, R, UPW>(oT, oB, aT, aB, col, sh, O, 0);
+  int e0 = 0;
 #pragma unroll 1
   for (int jj = 8; jj < 2 * R; jj += 8) {
-    col += 8 * pitch; t8T += 8 * n; t8B += 8 * n; t16 += 8 * n; part += 8 * n;
-    sad_block<BLK_MID, R>(oT, oB, aT, aB, col, sh, okT, okB, ok16, ok32, m16, m32, t8T, t8B, t16, part);
+    col += 8 * pitch; e0 += 8 * n;
+    sad_block<BLK_MID, R, UPW>(oT, oB, aT, aB, col, sh, O, e0);
   }
-  col += 8 * pitch; t8T += 8 * n; t8B += 8 * n; t16 += 8 * n; part += 8 * n;
-  sad_block<BLK_LAST, R>(oT, oB, aT, aB, col, sh, okT, okB, ok16, ok32, m16, m32, t8T, t8B, t16, part);
+  col += 8 * pitch; e0 += 8 * n;
+  sad_block<BLK_LAST, R, UPW>(oT, oB, aT, aB, col, sh, O, e0);
 }
 
-// One CTA per 64x64 superblock.  Shared memory: original SB (64x64) | reference window
-// (64+2R rows, pitch bytes) | 32x16-strip partial sums [8][n*n], n = 2R+1 (two of them make a 32x32
-// block, all eight the 64x64 block).
-// Main passes: warp w owns block-row pair p = w & 3 and column half ch = w >> 2; lane = (bxl = lane >> 3:
-// block column inside the half, d8 = lane & 7: one of 8 consecutive dx); 2R/8 groups cover dx index
-// 0..2R-1 with every lane busy.  Tail pass (warp 0): the last column dx = +R for the whole SB, lane =
-// (bx = lane & 7, p = lane >> 3).
+// Persistent kernel: gridDim.x CTAs walk the (job, SB row, SB column) tiles of the launch with a stride of
+// gridDim.x.  Shared memory: two stages of {original SB 64x64 | reference window (64+2R rows)} filled by
+// cp.async (the next tile's loads are in flight while the current tile is searched) | 32x16-strip sums
+// [8][n*n] | pending 16x16 half sums [8 warps][n*n].
+// Main passes: warp w owns block-row pair p = w & 3 and column half ch = w >> 2 (block columns 4ch..4ch+3).
+// Tail pass (warp 0): the last displacement column dx = +R for the whole SB, lane = 8 * p + bx.
 template <int R>
-__global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs) {
+__global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs, int gx, int gy, int njobs) {
+  using Cfg = SadCfg<R>;
+  constexpr int n = Cfg::n, nn = Cfg::nn, pitch = Cfg::pitch, win_rows = Cfg::win_rows;
   extern __shared__ __align__(16) uint8_t smem[];
-  const SadJob &J = jobs[blockIdx.z];
-  const int W = J.org.w, H = J.org.h;
-  const int x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
-  if (x0 >= W || y0 >= H) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  constexpr int n = 2 * R + 1, nn = n * n;
-  constexpr int win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
-  uint8_t *sOrg = smem;
-  uint8_t *sWin = smem + 64 * 64;
-  uint32_t *part = reinterpret_cast<uint32_t *>(sWin + ((win_rows * pitch + 15) & ~15));
+  uint32_t *part = reinterpret_cast<uint32_t *>(smem + Cfg::part_off);
+  uint16_t *pair = reinterpret_cast<uint16_t *>(smem + Cfg::pair_off);
+  const int per_job = gx * gy, total = per_job * njobs;
 
-  int cx = 0, cy = 0;
-  if (J.centres) {
-    const int sb = blockIdx.y * gridDim.x + blockIdx.x;    // host lays centres out with the launch's SB pitch
-    cx = J.centres[2 * sb]; cy = J.centres[2 * sb + 1];
-  }
-  const int wx = x0 + cx - R, wy = y0 + cy - R;
-  const int o = wx & 3, ax = wx - o;
-  {
+  struct Tile { int z, x0, y0, o, W, H; };
+  // first valid tile at or after linear index L (frames of a batch may differ in size)
+  auto find = [&](int L, Tile &t) -> int {
+    for (; L < total; L += gridDim.x) {
+      t.z = L / per_job;
+      const int rem = L - t.z * per_job, sy = rem / gx, sx = rem - sy * gx;
+      t.x0 = sx * 64; t.y0 = sy * 64;
+      t.W = jobs[t.z].org.w; t.H = jobs[t.z].org.h;
+      if (t.x0 < t.W && t.y0 < t.H) return L;
+    }
+    return total;
+  };
+  // queue the loads of a tile into stage `st`; returns the window's byte offset of displacement (-R) inside a row
+  auto issue = [&](Tile &t, int st) {
+    const SadJob &J = jobs[t.z];
+    uint8_t *sOrg = smem + st * Cfg::buf_bytes, *sWin = sOrg + 64 * 64;
+    int cx = 0, cy = 0;
+    if (J.centres) {
+      const int sb = (t.y0 >> 6) * gx + (t.x0 >> 6);       // host lays centres out with the launch's SB pitch
+      cx = J.centres[2 * sb]; cy = J.centres[2 * sb + 1];
+    }
+    const int wx = t.x0 + cx - R, wy = t.y0 + cy - R;
+    const int ax = wx & ~15;
+    t.o = wx - ax;
     const int pad = J.ref.pad[0], stride = J.ref.stride[0];
-    constexpr int wpr = pitch >> 2;
     const uint8_t *rp = J.ref.p[0];
-    for (int i = tid; i < win_rows * wpr; i += SAD_THREADS) {
-      const int r = i / wpr, wd = i - r * wpr;
-      const int gy = clampi(wy + r, -pad, H + pad - 1), gx = clampi(ax + 4 * wd, -pad, W + pad - 4);
-      reinterpret_cast<uint32_t *>(sWin + r * pitch)[wd] = *reinterpret_cast<const uint32_t *>(rp + (ptrdiff_t)gy * stride + gx);
+    // rows / 16-byte chunks outside the padded picture only feed blocks that are not output; clamp them to legal addresses
+    const int xlo = -(pad & ~15), xhi = (t.W + pad - 1) & ~15;
+    constexpr int cpr = pitch >> 4;
+    for (int i = tid; i < win_rows * cpr; i += SAD_THREADS) {
+      const int r = i / cpr, c = i - r * cpr;
+      const int gyy = clampi(wy + r, -pad, t.H + pad - 1), gxx = clampi(ax + 16 * c, xlo, xhi);
+      cp_async16(sWin + r * pitch + 16 * c, rp + (ptrdiff_t)gyy * stride + gxx);
     }
     const uint8_t *op = J.org.p[0];
-    const int ostride = J.org.stride[0];
-    for (int i = tid; i < 64 * 16; i += SAD_THREADS) {
-      const int r = i >> 4, wd = i & 15;
-      const int gy = min(y0 + r, H - 1), gx = min(x0 + 4 * wd, W - 4);
-      reinterpret_cast<uint32_t *>(sOrg)[i] = *reinterpret_cast<const uint32_t *>(op + (size_t)gy * ostride + gx);
+    const int ostride = J.org.stride[0], oxhi = (t.W - 1) & ~15;
+    for (int i = tid; i < 64 * 4; i += SAD_THREADS) {
+      const int r = i >> 2, c = i & 3;
+      const int gyy = min(t.y0 + r, t.H - 1), gxx = min(t.x0 + 16 * c, oxhi);
+      cp_async16(sOrg + r * 64 + 16 * c, op + (size_t)gyy * ostride + gxx);
     }
-  }
-  __syncthreads();
+  };
 
-  SadCtx C;
-  C.sOrg = sOrg; C.sWin = sWin; C.part = part; C.t8 = J.t8; C.t16 = J.t16;
-  C.W = W; C.H = H; C.x0 = x0; C.y0 = y0; C.o = o;
-  {
-    const int p = warp & 3, bx = 4 * (warp >> 2) + (lane >> 3), d8 = lane & 7;
+  Tile cur, nxt;
+  int L = find(blockIdx.x, cur);
+  int st = 0;
+  if (L < total) issue(cur, 0);
+  cp_async_commit();
+  while (L < total) {
+    const int Ln = find(L + gridDim.x, nxt);
+    if (Ln < total) issue(nxt, st ^ 1);
+    cp_async_commit();
+    cp_async_wait1();                 // everything but the group just committed has landed
+    __syncthreads();
+
+    const SadJob &J = jobs[cur.z];
+    SadTile C;
+    C.sOrg = smem + st * Cfg::buf_bytes; C.sWin = C.sOrg + 64 * 64;
+    C.part = part; C.pair = pair; C.t8 = J.t8; C.t16 = J.t16;
+    C.W = cur.W; C.H = cur.H; C.x0 = cur.x0; C.y0 = cur.y0; C.o = cur.o;
+    {
+      const int p = warp & 3, ch = warp >> 2, u = lane / Cfg::DXL, d = lane % Cfg::DXL;
 #pragma unroll 1
-    for (int g = 0; g < (2 * R) >> 3; g++) sad_pass<R>(C, p, bx, g * 8 + d8, 8, 16);
-  }
-  if (warp == 0) sad_pass<R>(C, lane >> 3, lane & 7, 2 * R, 1, 2);
-  __syncthreads();
-  // 32x32 and 64x64 levels from the strip sums: coalesced 32-bit rows
-  const int bw32 = W >> 5, bw64 = W >> 6;
-  const bool ok64 = x0 + 64 <= W && y0 + 64 <= H;
-  uint32_t *d64 = J.t64 + ((size_t)(y0 >> 6) * bw64 + (x0 >> 6)) * nn;
-  uint32_t *d32[4];
-  bool ok32[4];
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-    const int gx = x0 + (q & 1) * 32, gy = y0 + (q >> 1) * 32;
-    ok32[q] = gx + 32 <= W && gy + 32 <= H;
-    d32[q] = J.t32 + ((size_t)(gy >> 5) * bw32 + (gx >> 5)) * nn;
-  }
-  for (int i = tid; i < nn; i += SAD_THREADS) {
-    uint32_t tot = 0;
-#pragma unroll
-    for (int q = 0; q < 4; q++) {   // 32x32 block q = (qy, qx): strips p = 2qy, 2qy+1 of column half qx
-      const int qy = q >> 1, qx = q & 1;
-      const uint32_t v = part[((2 * qy) * 2 + qx) * nn + i] + part[((2 * qy + 1) * 2 + qx) * nn + i];
-      if (ok32[q]) d32[q][i] = v;
-      tot += v;
+      for (int c = 0; c < Cfg::NCH; c++)
+#pragma unroll 1
+        for (int b = 0; b < Cfg::NB; b++)
+          sad_pass<R, Cfg::UPW>(C, p, 4 * ch + b * Cfg::UPW + u, c * Cfg::DXL + d, b, warp, u == 0);
     }
-    if (ok64) d64[i] = tot;
+    if (warp == 0) sad_pass<R, 8>(C, lane >> 3, lane & 7, 2 * R, 0, 0, (lane & 3) == 0);
+    __syncthreads();
+    // 32x32 and 64x64 levels from the strip sums: coalesced 32-bit rows
+    {
+      const int W = cur.W, H = cur.H, x0 = cur.x0, y0 = cur.y0;
+      const int bw32 = W >> 5, bw64 = W >> 6;
+      const bool ok64 = x0 + 64 <= W && y0 + 64 <= H;
+      uint32_t *d64 = J.t64 + ((size_t)(y0 >> 6) * bw64 + (x0 >> 6)) * nn;
+      uint32_t *d32[4];
+      bool ok32[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int gxx = x0 + (q & 1) * 32, gyy = y0 + (q >> 1) * 32;
+        ok32[q] = gxx + 32 <= W && gyy + 32 <= H;
+        d32[q] = J.t32 + ((size_t)(gyy >> 5) * bw32 + (gxx >> 5)) * nn;
+      }
+      for (int i = tid; i < nn; i += SAD_THREADS) {
+        uint32_t tot = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {   // 32x32 block q = (qy, qx): strips p = 2qy, 2qy+1 of column half qx
+          const int qy = q >> 1, qx = q & 1;
+          const uint32_t v = part[((2 * qy) * 2 + qx) * nn + i] + part[((2 * qy + 1) * 2 + qx) * nn + i];
+          if (ok32[q]) d32[q][i] = v;
+          tot += v;
+        }
+        if (ok64) d64[i] = tot;
+      }
+    }
+    cur = nxt; L = Ln; st ^= 1;
+    __syncthreads();                  // `part` and stage st are free again: the next iteration refills / rewrites them
   }
 }
 
@@ -335,19 +433,19 @@ __global__ void __launch_bounds__(CW * 32) k_cost_batch(const CostParams P) {
   P.out[ti] = res;
 }
 
-static size_t sad_smem_bytes(int R) {
-  const int n = 2 * R + 1, win_rows = 64 + 2 * R, pitch = (64 + 2 * R + 7) & ~3;
-  return 64 * 64 + ((size_t)(win_rows * pitch + 15) & ~(size_t)15) + (size_t)8 * n * n * 4;
-}
-
 template <int R>
-static int launch_sad(dim3 grid, size_t smem, const SadJob *d_jobs) {
-  static bool attr_set = false;
-  if (!attr_set) {
+static int launch_sad(int gx, int gy, int n, const SadJob *d_jobs) {
+  static int ctas_per_sm = 0;
+  constexpr size_t smem = SadCfg<R>::smem_bytes;
+  if (!ctas_per_sm) {
     THOR_CUDA(cudaFuncSetAttribute(k_sad_table<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+    THOR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k_sad_table<R>, SAD_THREADS, smem));
+    if (ctas_per_sm < 1) return fail("sad_table: kernel for range %d does not fit on an SM", R);
   }
-  k_sad_table<R><<<grid, SAD_THREADS, smem, ctx().stream>>>(d_jobs);
+  // persistent: as many CTAs as are resident at once (2 per SM up to R = 24) walk the tiles
+  const int total = gx * gy * n;
+  const int grid = total < ctas_per_sm * ctx().sm_count ? total : ctas_per_sm * ctx().sm_count;
+  k_sad_table<R><<<grid, SAD_THREADS, smem, ctx().stream>>>(d_jobs, gx, gy, n);
   THOR_LAUNCHED();
   return 0;
 }
@@ -393,7 +491,7 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
     Pic *o = get_pic(orgs[i]), *r = get_pic(refs[i]);
     if (!o || !r) return fail("sad_table: bad picture handle in pair %d", i);
     if (o->w != r->w || o->h != r->h) return fail("sad_table: pair %d: picture size mismatch", i);
-    if ((r->pad_y & 3) || r->pad_y < range) return fail("sad_table: pair %d: reference padding %d cannot hold range %d", i, r->pad_y, range);
+    if ((r->pad_y & 15) || r->pad_y < range) return fail("sad_table: pair %d: reference padding %d cannot hold range %d", i, r->pad_y, range);
     if (slots[i] < 0 || slots[i] >= THORCUDA_SAD_SLOTS) return fail("sad_table: slot %d out of range", slots[i]);
     for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail("sad_table: slot %d used twice in one call", slots[i]);
     maxw = max(maxw, o->w); maxh = max(maxh, o->h);
@@ -455,17 +553,15 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
   }
   THOR_CUDA(cudaMemcpyAsync(d_jobs, hj, sizeof(SadJob) * n, cudaMemcpyHostToDevice, c.stream));
   if (stage_commit_copy(d_centres ? (void *)d_centres : (void *)d_jobs, hc, centre_entries * 2)) return -1;
-  const size_t smem = sad_smem_bytes(range);
-  dim3 grid(gx, gy, n);
   switch (range) {
-    case 4: return launch_sad<4>(grid, smem, d_jobs);
-    case 8: return launch_sad<8>(grid, smem, d_jobs);
-    case 12: return launch_sad<12>(grid, smem, d_jobs);
-    case 16: return launch_sad<16>(grid, smem, d_jobs);
-    case 20: return launch_sad<20>(grid, smem, d_jobs);
-    case 24: return launch_sad<24>(grid, smem, d_jobs);
-    case 28: return launch_sad<28>(grid, smem, d_jobs);
-    default: return launch_sad<32>(grid, smem, d_jobs);
+    case 4: return launch_sad<4>(gx, gy, n, d_jobs);
+    case 8: return launch_sad<8>(gx, gy, n, d_jobs);
+    case 12: return launch_sad<12>(gx, gy, n, d_jobs);
+    case 16: return launch_sad<16>(gx, gy, n, d_jobs);
+    case 20: return launch_sad<20>(gx, gy, n, d_jobs);
+    case 24: return launch_sad<24>(gx, gy, n, d_jobs);
+    case 28: return launch_sad<28>(gx, gy, n, d_jobs);
+    default: return launch_sad<32>(gx, gy, n, d_jobs);
   }
 }
 
