@@ -66,7 +66,7 @@ class CpuFrame:
         from thor_b200.lib import COST_RESULT
         self.job, self.lib, self.threads = job, lib, threads
         w, h, R = job["width"], job["height"], job["range"]
-        n2 = (2 * R + 1) ** 2
+        n2 = (2 * R) ** 2
         self.rec = HostPicture(w, h)
         self.newref = HostPicture(w, h, PAD_Y, PAD_C)
         self.tab = [{bs: aligned_zeros(((w // bs) * (h // bs) * n2,), np.uint16 if bs <= 16 else np.uint32) for bs in (8, 16, 32, 64)}
@@ -403,7 +403,7 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
     from thor_b200.lib import COST_RESULT
     B = len(streams)
     R = args.range
-    n2 = (2 * R + 1) ** 2
+    n2 = (2 * R) ** 2
     w, h = args.width, args.height
 
     def pinned(nbytes, dtype=np.uint8):

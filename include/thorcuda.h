@@ -177,12 +177,14 @@ size_t thorcuda_list_pool_entries(thorcuda_list l);   /* int16 entries of a TB l
 /* Whole-frame integer-pel cost tables (north_star: "whole-frame per-block cost table").
  * For every block of `org` of size bs in {8,16,32,64} on the bs-aligned grid (blocks that do not
  * lie completely inside the frame are omitted: (w/bs) x (h/bs) blocks, raster order) and every
- * full-pel displacement (dx,dy) in [-range,range]^2 around the superblock's search centre
+ * full-pel displacement (dx,dy) in [-range, range-1]^2 (a 2*range x 2*range window, range a multiple of 4,
+ * 4..32) around the superblock's search centre
  * (centres: int16 (cx,cy) pairs per 64x64 SB in raster order, host pointer, NULL = all (0,0)):
  *      table[block][dy+range][dx+range] = sad_calc(org block, ref + (cy+dy)*stride + cx+dx)
+ * (rows of 2*range entries: for range 16 a block's table is 2 KiB and every row one 64-byte line).
  * uint16 for bs <= 16, uint32 for bs >= 32.  Rectangular partitions (HOR/VER/QUAD halves) are sums
  * of two entries of the next finer level -- SAD is additive -- so the host forms them itself.
- * Displacements whose reference block would leave the padded picture hold 0xFFFF / 0xFFFFFFFF.
+ * The call fails if a window of an existing block would leave the padded reference picture.
  * Tables live in HBM in one of THORCUDA_SAD_SLOTS slots; fetch copies one level to the host.
  * n (org,ref) pairs are processed in ONE launch.                                                     */
 #define THORCUDA_SAD_SLOTS 64

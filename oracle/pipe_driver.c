@@ -102,7 +102,7 @@ static void CHROMA(uint8_t *p, const uint8_t *ref, int w, int h, int stride, int
 
 /* ---- stage 1: whole-frame SAD tables, one sad_calc per (block, displacement), as the reference's search would ---- */
 static void stage_sad(const pipe_job *j) {
-  const int R = j->range, n = 2 * R + 1, W = j->w, H = j->h;
+  const int R = j->range, n = 2 * R, W = j->w, H = j->h;   /* displacements -R .. R-1 (include/thorcuda.h) */
   for (int r = 0; r < 2; r++) {
     const uint8_t *ref = j->ref[r][0];
     const int rs = j->ref_stride_y;
@@ -114,8 +114,8 @@ static void stage_sad(const pipe_job *j) {
           const uint8_t *a = j->org[0] + (size_t)by * bs * W + bx * bs;
           const uint8_t *b0 = ref + (ptrdiff_t)by * bs * rs + bx * bs;
           const size_t base = ((size_t)by * nbx + bx) * n * n;
-          for (int dy = -R; dy <= R; dy++)
-            for (int dx = -R; dx <= R; dx++) {
+          for (int dy = -R; dy < R; dy++)
+            for (int dx = -R; dx < R; dx++) {
               const unsigned s = SAD(a, b0 + (ptrdiff_t)dy * rs + dx, W, rs, bs, bs);
               const size_t e = base + (size_t)(dy + R) * n + dx + R;
               if (lv == 0) j->t8[r][e] = (uint16_t)s;

@@ -347,7 +347,7 @@ def test_reconstruct_dense_coefficients(tb, orc):
 def numpy_sad_tables(org_y, ref_pic, R, centres):
     """All four levels by brute force.  ref_pic: host Picture (padded)."""
     h, w = org_y.shape
-    n = 2 * R + 1
+    n = 2 * R                                     # displacements -R .. R-1
     pad = ref_pic.pad_y
     full = ref_pic.buf_y.astype(np.int16)
     out = {bs: np.zeros((h // bs, w // bs, n, n), np.uint16 if bs <= 16 else np.uint32) for bs in (8, 16, 32, 64)}
@@ -358,7 +358,7 @@ def numpy_sad_tables(org_y, ref_pic, R, centres):
             cx, cy = (0, 0) if centres is None else (int(centres[2 * sb]), int(centres[2 * sb + 1]))
             bh, bw = min(64, h - y0), min(64, w - x0)
             o = org_y[y0:y0 + bh, x0:x0 + bw].astype(np.int16)
-            win = full[pad + y0 + cy - R:pad + y0 + cy + R + bh, pad + x0 + cx - R:pad + x0 + cx + R + bw]
+            win = full[pad + y0 + cy - R:pad + y0 + cy + R - 1 + bh, pad + x0 + cx - R:pad + x0 + cx + R - 1 + bw]
             sw = np.lib.stride_tricks.sliding_window_view(win, (bh, bw))           # [n, n, bh, bw]
             ad = np.abs(sw - o[None, None]).astype(np.uint32)
             s8 = ad.reshape(n, n, bh // 8, 8, bw // 8, 8).sum(axis=(3, 5))           # [n, n, bh/8, bw/8]
@@ -391,11 +391,11 @@ def test_sad_table(tb, orc, wh, R, with_centres):
     got = tb.ops.sad_table(dorg, dref, R, centres)
     if w >= 1920:
         # full size: spot-check against sad_calc of the oracle + the additivity property between levels
-        n = 2 * R + 1
+        n = 2 * R
         for _ in range(300):
             bs = int(rng.choice([8, 16, 32, 64]))
             by, bx = int(rng.integers(0, h // bs)), int(rng.integers(0, w // bs))
-            dy, dx = int(rng.integers(-R, R + 1)), int(rng.integers(-R, R + 1))
+            dy, dx = int(rng.integers(-R, R)), int(rng.integers(-R, R))
             a = np.ascontiguousarray(oy[by * bs:(by + 1) * bs, bx * bs:(bx + 1) * bs])
             b = C.c_void_p(href.origin_ptr(0) + (by * bs + dy) * href.stride_y + bx * bs + dx)
             assert got[bs][by, bx, dy + R, dx + R] == orc.orc_sad(ptr(a), b, bs, href.stride_y, bs, bs)
@@ -411,7 +411,7 @@ def test_sad_table(tb, orc, wh, R, with_centres):
         for _ in range(20):
             bs = int(rng.choice([8, 16]))
             by, bx = int(rng.integers(0, h // bs)), int(rng.integers(0, w // bs))
-            dy, dx = int(rng.integers(-R, R + 1)), int(rng.integers(-R, R + 1))
+            dy, dx = int(rng.integers(-R, R)), int(rng.integers(-R, R))
             sb = (by * bs // 64) * ((w + 63) // 64) + bx * bs // 64
             cx, cy = (0, 0) if centres is None else (int(centres[2 * sb]), int(centres[2 * sb + 1]))
             a = np.ascontiguousarray(oy[by * bs:(by + 1) * bs, bx * bs:(bx + 1) * bs])

@@ -39,10 +39,10 @@ __device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_g
 // Geometry of one launch configuration (search range R, a multiple of 4).
 //   n x n displacements per block.  A warp pass covers UPW block columns x DXL consecutive horizontal
 //   displacements (lane = u * DXL + d), so that a store instruction writes DXL consecutive table entries of a
-//   block (64 contiguous bytes for R = 16 / 32).  The last displacement column (index 2R) is the tail pass.
+//   block (one aligned 64-byte row for R = 16).
 template <int R>
 struct SadCfg {
-  static constexpr int n = 2 * R + 1, nn = n * n;
+  static constexpr int n = 2 * R, nn = n * n;   // displacements -R .. R-1 in both directions
   // 32 lanes per block column only for R = 16: at R = 32 the pending-half-sum rows would not fit in shared memory
   static constexpr int DXL = R == 16 ? 32 : (2 * R) % 16 == 0 ? 16 : 8;
   static constexpr int UPW = 32 / DXL;          // block columns per warp pass
@@ -67,16 +67,10 @@ struct SadOut {
 
 // combine the 8x16 column sum v of this lane's block column into the 16x16 and 32x16 levels.
 //   UPW 4 / 2: partner columns sit in other lanes of the same pass (shuffle);  UPW 1: they are other passes of
-//   the SAME lane, so the running sums live in this warp's shared-memory rows (no synchronisation needed);
-//   UPW 8 marks the tail pass (lane = 8 * p + bx).
+//   the SAME lane, so the running sums live in this warp's shared-memory rows (no synchronisation needed).
 template <int UPW>
 __device__ __forceinline__ void sad_reduce(uint32_t v, int e, const SadOut &O) {
-  if (UPW == 8) {
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    if (O.ok16) O.t16[e] = (uint16_t)v;
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    if (O.lead) O.part[e] = v;
-  } else if (UPW == 4) {
+  if (UPW == 4) {
     v += __shfl_xor_sync(0xffffffffu, v, 8);
     if (O.ok16) O.t16[e] = (uint16_t)v;
     v += __shfl_xor_sync(0xffffffffu, v, 16);
@@ -97,7 +91,7 @@ __device__ __forceinline__ void sad_reduce(uint32_t v, int e, const SadOut &O) {
 }
 
 // One "pass": a lane owns the two vertically adjacent 8x8 blocks (block column bx, block rows 2p and 2p+1 of
-// the SB) at ONE horizontal displacement and slides over all 2R+1 vertical ones with 2 x 8 rotating
+// the SB) at ONE horizontal displacement and slides over all 2R vertical ones with 2 x 8 rotating
 // accumulators.  The 8 reference rows that start / end the slide touch fewer displacement rows than the middle
 // ones; FIRST / LAST skip those, so no abs-diff is computed that is not part of an output.
 enum { BLK_FIRST = 0, BLK_MID = 1, BLK_LAST = 2 };
@@ -107,7 +101,7 @@ __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint
                                           const uint8_t *col, int sh, const SadOut &O, int e0) {
   constexpr int n = SadCfg<R>::n, pitch = SadCfg<R>::pitch;
 #pragma unroll
-  for (int s = 0; s < 8; s++) {
+  for (int s = 0; s < (MODE == BLK_LAST ? 7 : 8); s++) {     // the last block: reference rows 2R .. 2R+6
     const uint32_t *rt = reinterpret_cast<const uint32_t *>(col + s * pitch);
     const uint32_t *rb = reinterpret_cast<const uint32_t *>(col + (s + 8) * pitch);
     const uint32_t t0 = rt[0], t1 = rt[1], t2 = rt[2], b0 = rb[0], b1 = rb[1], b2 = rb[2];
@@ -116,7 +110,7 @@ __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint
 #pragma unroll
     for (int r = 0; r < 8; r++) {
       if (MODE == BLK_FIRST && r > s) continue;      // displacement row j - r < 0
-      if (MODE == BLK_LAST && r < s) continue;       // displacement row j - r > 2R
+      if (MODE == BLK_LAST && r <= s) continue;      // displacement row j - r > 2R - 1
       const int k = (s - r) & 7;
       aT[k] = sad4(oT[r][0], wT0, aT[k]); aT[k] = sad4(oT[r][1], wT1, aT[k]);
       aB[k] = sad4(oB[r][0], wB0, aB[k]); aB[k] = sad4(oB[r][1], wB1, aB[k]);
@@ -186,8 +180,8 @@ __device__ __forceinline__ void sad_pass(const SadTile &C, int p, int bx, int dx
 // gridDim.x.  Shared memory: two stages of {original SB 64x64 | reference window (64+2R rows)} filled by
 // cp.async (the next tile's loads are in flight while the current tile is searched) | 32x16-strip sums
 // [8][n*n] | pending 16x16 half sums [8 warps][n*n].
-// Main passes: warp w owns block-row pair p = w & 3 and column half ch = w >> 2 (block columns 4ch..4ch+3).
-// Tail pass (warp 0): the last displacement column dx = +R for the whole SB, lane = 8 * p + bx.
+// Warp w owns block-row pair p = w & 3 and column half ch = w >> 2 (block columns 4ch..4ch+3): 32 equal passes
+// per tile, 4 per warp.
 template <int R>
 __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs, int gx, int gy, int njobs) {
   using Cfg = SadCfg<R>;
@@ -266,7 +260,6 @@ __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__re
         for (int b = 0; b < Cfg::NB; b++)
           sad_pass<R, Cfg::UPW>(C, p, 4 * ch + b * Cfg::UPW + u, c * Cfg::DXL + d, b, warp, u == 0);
     }
-    if (warp == 0) sad_pass<R, 8>(C, lane >> 3, lane & 7, 2 * R, 0, 0, (lane & 3) == 0);
     __syncthreads();
     // 32x32 and 64x64 levels from the strip sums: coalesced 32-bit rows
     {
@@ -484,7 +477,7 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
   Context &c = ctx();
   if (n <= 0) return 0;
   if (range < 4 || range > 32 || (range & 3)) return fail("sad_table: range must be 4,8,...,32 (got %d)", range);
-  const int nn = (2 * range + 1) * (2 * range + 1);
+  const int nn = (2 * range) * (2 * range);
   int maxw = 0, maxh = 0;
   size_t centre_entries = 0;
   for (int i = 0; i < n; i++) {
@@ -505,8 +498,8 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
       for (int sx = 0; sx < nsbx; sx++) {
         const int cx = centres[i][2 * (sy * nsbx + sx)], cy = centres[i][2 * (sy * nsbx + sx) + 1];
         const int x0 = sx * 64, y0 = sy * 64, x1 = min(x0 + 64, o->w), y1 = min(y0 + 64, o->h);
-        if (x0 + cx - range < -r->pad_y || y0 + cy - range < -r->pad_y || x1 + cx + range > o->w + r->pad_y ||
-            y1 + cy + range > o->h + r->pad_y)
+        if (x0 + cx - range < -r->pad_y || y0 + cy - range < -r->pad_y || x1 + cx + range - 1 > o->w + r->pad_y ||
+            y1 + cy + range - 1 > o->h + r->pad_y)
           return fail("sad_table: pair %d SB (%d,%d): centre (%d,%d) +- %d leaves the padded reference", i, sx, sy, cx, cy, range);
       }
     centre_entries += (size_t)2 * gx * gy;

@@ -185,9 +185,9 @@ def sad_table_build(slots, orgs, refs, search_range, centres=None):
 
 
 def sad_table_fetch(slot, width, height, search_range, sizes=(8, 16, 32, 64)):
-    """dict size -> ndarray [blocks_y, blocks_x, 2R+1, 2R+1] (uint16 for 8/16, uint32 for 32/64)."""
+    """dict size -> ndarray [blocks_y, blocks_x, 2R, 2R] (displacements -R..R-1; uint16 for 8/16, uint32 for 32/64)."""
     out = {}
-    n = 2 * search_range + 1
+    n = 2 * search_range
     for bs in sizes:
         nbytes = cdll().thorcuda_sad_table_bytes(slot, bs)
         dt = np.uint16 if bs <= 16 else np.uint32

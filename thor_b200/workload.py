@@ -210,7 +210,7 @@ def algorithmic_bytes(job):
     """Per-frame algorithmic HBM traffic of each stage."""
     w, h, R = job["width"], job["height"], job["range"]
     F = w * h * 3 // 2
-    n2 = (2 * R + 1) ** 2
+    n2 = (2 * R) ** 2
     padded = lambda hp: hp.rows_y * hp.stride_y + 2 * hp.rows_c * hp.stride_c   # noqa: E731
     table = sum((w // bs) * (h // bs) * n2 * (2 if bs <= 16 else 4) for bs in (8, 16, 32, 64))
     ref_luma = (w + 2 * R) * (h + 2 * R)
