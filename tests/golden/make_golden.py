@@ -179,6 +179,32 @@ def streams():
     return res
 
 
+def coding_orders():
+    """(frame_num, type) per coded frame as printed by the reference's Thorenc, for thor_b200/segments.py"""
+    import subprocess
+    from thorref import REF_DIR
+    res = {}
+    with tempfile.TemporaryDirectory() as d:
+        yuv = os.path.join(d, "clip.yuv")
+        write_clip(yuv, 64, 64, 70, 3)
+        for name, cfg, n, extra in (("RA_n20", "RA_high_efficiency", 20, []), ("RA_p16_n53", "RA_high_efficiency", 53, ["-intra_period", "16"]),
+                                    ("RA_n70", "RA_high_efficiency", 70, []), ("LDB_n6", "LDB_low_complexity", 6, []),
+                                    ("RA_p16_n48", "RA_high_efficiency", 48, ["-intra_period", "16"])):
+            flags = THOR_CONFIGS[cfg]
+            cmd = [os.path.join(REF_DIR, "Thorenc"), "-if", yuv, "-of", os.path.join(d, "o.bit"), "-stat", os.path.join(d, "s.txt"),
+                   "-width", "64", "-height", "64", "-n", str(n), "-f", "30", "-qp", "40"] + flags + extra
+            out = subprocess.run(cmd, capture_output=True, text=True, check=True).stdout
+            frames = []
+            for ln in out.splitlines():
+                f = ln.split()
+                if len(f) > 3 and f[0].isdigit() and f[1] in ("I", "P", "B"):
+                    frames.append([int(f[0]), f[1]])
+            reorder = int(flags[flags.index("-num_reorder_pics") + 1]) if "-num_reorder_pics" in flags else 0
+            ip = int((flags + extra)[len(flags + extra) - 1 - (flags + extra)[::-1].index("-intra_period") + 1]) if "-intra_period" in flags + extra else 0
+            res[name] = {"num_frames": n, "num_reorder_pics": reorder, "intra_period": ip, "frames": frames}
+    return res
+
+
 def main():
     ref = load_ref()
     if ref is None:
@@ -192,6 +218,7 @@ def main():
     set_ref_simd(ref, 1)
     np.savez_compressed(os.path.join(HERE, "kernels.npz"), **a)
     json.dump(streams(), open(os.path.join(HERE, "streams.json"), "w"), indent=1, sort_keys=True)
+    json.dump(coding_orders(), open(os.path.join(HERE, "coding_order.json"), "w"), sort_keys=True)
     print("wrote", os.path.join(HERE, "kernels.npz"), os.path.getsize(os.path.join(HERE, "kernels.npz")), "bytes;",
           os.path.join(HERE, "streams.json"))
 

@@ -208,7 +208,7 @@ def write_clip(path, width, height, frames, seed):
     """Seeded I420 clip: a textured background translating by (1,2) px per frame plus noise."""
     with open(path, "wb") as f:
         for n in range(frames):
-            y, u, v = smooth_frame(width, height, seed, shift=(n, 2 * n))
+            y, u, v = smooth_frame(width, height, seed, shift=(n % 16, (2 * n) % 32))   # stays inside the texture margin
             for p in (y, u, v):
                 f.write(np.ascontiguousarray(p).tobytes())
 
