@@ -57,6 +57,7 @@ static int check_tb(const Pic *const *P, int npics, const thorcuda_tb_task *task
       return fail("tb: task %d block (%d,%d size %d) is misaligned or outside plane %d", i, t.x, t.y, t.size, t.plane);
     if (P[t.org]->w != r->w || P[t.org]->h != r->h || P[t.pred]->w != r->w || P[t.pred]->h != r->h)
       return fail("tb: task %d: picture size mismatch", i);
+    if (t.size >= 8 && ((t.x | t.y) & 7)) return fail("tb: task %d: blocks of size >= 8 must lie on the 8-sample grid (%d,%d)", i, t.x, t.y);
     const int q = t.size < 16 ? t.size : 16;
     if ((t.coeff_offset & 7) && t.size > 4) return fail("tb: task %d: coeff_offset must be a multiple of 8 entries", i);
     if (t.coeff_offset & 3) return fail("tb: task %d: coeff_offset must be a multiple of 4 entries", i);
