@@ -4,10 +4,13 @@
 // Restates reference common/inter_prediction.c:72-180 (get_inter_prediction_chroma/_luma) and the
 // truncating bi-pred average of enc/encode_block.c:1569-1588 / dec/decode_block.c:272-283.
 //
-// Work decomposition: the host splits every prediction block into tiles of at most 16x16 luma samples;
-// one warp owns one tile (luma + both chroma planes).  The reference window of the tile is staged in
-// shared memory with aligned 32-bit loads, the separable filter runs vertical-then-horizontal exactly
-// like the reference (single rounding at the end), results leave as 32-bit words.
+// Work decomposition: the host splits every prediction block into tiles of at most 16x16 luma samples; one warp
+// owns one tile (luma + both chroma planes).  All reference windows of the tile (up to 2 luma + 4 chroma) are
+// fetched first, shifted so that the leftmost tap sits at byte 0 of a shared-memory row.  The separable filter
+// runs HORIZONTAL first on packed bytes -- DP4A of a 4-byte window with the int8 taps -- into a transposed int16
+// intermediate, then VERTICAL with DP2A on pairs of rows; because the reference keeps full precision between
+// its two passes and rounds once at the end ((sum + 2048) >> 12), the order of the passes does not change the
+// result.  A lane produces 2 rows x 4 samples and stores 32-bit words.
 #include "internal.cuh"
 #include "lists.cuh"
 
@@ -20,9 +23,11 @@ __constant__ int8_t c_chroma[8][4] = {{0, 64, 0, 0}, {-2, 58, 10, -2}, {-4, 54, 
                                       {-4, 36, 36, -4}, {-4, 28, 44, -4}, {-2, 16, 54, -4}, {-2, 10, 58, -2}};
 
 constexpr int PW = 8;                 // warps per CTA
-constexpr int WIN_PITCH = 24;         // bytes per staged window row (21 + up to 3 alignment bytes)
-constexpr int WIN_ROWS = 21;
-constexpr int TMP_PITCH = 22;         // int16 per row of the vertical-pass result
+constexpr int LW_PITCH = 24;          // luma window row: 16 + 5 samples, taps start at byte 0
+constexpr int LW_ROWS = 21;
+constexpr int CW_PITCH = 12;          // chroma window row: 8 + 3 samples
+constexpr int CW_ROWS = 11;
+constexpr int PT = 22;                // int16 per column of the transposed intermediate (rows 0..th+4, +1 slack)
 
 struct PredParams {
   const PicView *pics;                // device picture table, indexed by handle
@@ -34,142 +39,138 @@ struct PredParams {
   int planes;
 };
 
-// Stage rows [0,rows) x bytes [0,cols) starting at src (any alignment) into win (pitch WIN_PITCH);
-// returns the byte offset of src inside the first staged word.
-__device__ __forceinline__ int stage_window(uint8_t *win, const uint8_t *src, int stride, int rows, int cols, int lane) {
+struct WarpSmem {
+  uint32_t lwin[2][LW_ROWS * LW_PITCH / 4 + 2];     // luma windows of ref0 / ref1
+  uint32_t cwin[4][CW_ROWS * CW_PITCH / 4 + 2];     // chroma windows U0, V0, U1, V1
+  int16_t tmpT[16 * PT + 2];                        // transposed horizontal-pass output [column][row]
+};
+
+// 4 unsigned bytes (samples) x 4 signed bytes (taps) + c
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t pack2(int lo, int hi) { return ((uint32_t)lo & 0xffu) | (((uint32_t)hi & 0xffu) << 8); }
+__device__ __forceinline__ uint32_t taps4(int a, int b, int c, int d) {
+  return ((uint32_t)a & 0xffu) | (((uint32_t)b & 0xffu) << 8) | (((uint32_t)c & 0xffu) << 16) | (((uint32_t)d & 0xffu) << 24);
+}
+
+// Fetch rows x bytes starting at src (any alignment) into win (row pitch `pitch` bytes, byte 0 = src[0]).
+// wpr = words per staged row.
+__device__ __forceinline__ void stage_window(uint32_t *win, const uint8_t *src, int stride, int rows, int wpr, int pitch, int lane) {
   const int o = (int)((uintptr_t)src & 3);
   const uint8_t *base = src - o;
-  const int words = (cols + o + 3) >> 2;          // <= 6
-  for (int i = lane; i < rows * words; i += 32) {
-    const int r = i / words, wd = i - r * words;
-    reinterpret_cast<uint32_t *>(win + r * WIN_PITCH)[wd] = *reinterpret_cast<const uint32_t *>(base + (size_t)r * stride + 4 * wd);
+  const int sh = o * 8;
+  for (int i = lane; i < rows * wpr; i += 32) {
+    const int r = i / wpr, wd = i - r * wpr;
+    const uint32_t *g = reinterpret_cast<const uint32_t *>(base + (size_t)r * stride) + wd;
+    const uint32_t lo = g[0], hi = o ? g[1] : 0u;
+    win[r * (pitch >> 2) + wd] = __funnelshift_r(lo, hi, sh);
   }
-  return o;
 }
 
-// One luma tile from one reference.  out[2]: each lane owns up to two groups of 4 horizontally adjacent
-// samples (group g = lane + 32*k, row = g / (tw/4), col = 4*(g % (tw/4))).
-__device__ __forceinline__ void luma_tile(const PicView &ref, int x, int y, int tw, int th, int mvx, int mvy, int bipred,
-                                          uint8_t *win, int16_t *tmp, int lane, uint32_t out[2]) {
-  const int fx = mvx & 3, fy = mvy & 3;
-  const uint8_t *src = ref.p[0] + (ptrdiff_t)(y + (mvy >> 2)) * ref.stride[0] + (x + (mvx >> 2));
-  const int gpr = tw >> 2, ngroups = gpr * th;
-  if (!fx && !fy) {
-    // integer position: straight copy (memcpy in the reference)
-    const int o = stage_window(win, src, ref.stride[0], th, tw, lane);
-    __syncwarp();
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-      const int g = lane + 32 * k;
-      if (g < ngroups) {
-        const uint8_t *p = win + (g / gpr) * WIN_PITCH + o + 4 * (g % gpr);
-        out[k] = p[0] | (p[1] << 8) | (p[2] << 16) | (p[3] << 24);
-      }
-    }
-    __syncwarp();
-    return;
-  }
-  // window rows -2..th+2, cols -2..tw+2
-  const int o = stage_window(win, src - 2 * ref.stride[0] - 2, ref.stride[0], th + 5, tw + 5, lane);
-  __syncwarp();
+// ---- luma: one tile from one staged window -> out[2] (rows 2*rp, 2*rp+1; samples 4*xq .. 4*xq+3) ----
+__device__ __forceinline__ void luma_tile(const uint32_t *win, int16_t *tmpT, int tw, int th, int fx, int fy, int bipred, int lane,
+                                          uint32_t out[2]) {
+  const int qpr = tw >> 2;                       // quads per row
+  const int xq = lane % qpr, rp = lane / qpr;    // this lane's output quad / row pair
+  const bool act = rp < (th >> 1);
   if (fx == 2 && fy == 2) {
     // centre position: [0 1 1 0; 1 2 2 1; 1 2 2 1; 0 1 1 0], (sum+8)>>4   (inter_prediction.c:146-157)
+    // window byte 0 = sample x-2, window row 0 = sample row y-2; taps cover columns x-1..x+2, rows y-1..y+2
+    if (act) {
 #pragma unroll
-    for (int k = 0; k < 2; k++) {
-      const int g = lane + 32 * k;
-      if (g < ngroups) {
-        const int r = g / gpr, c = 4 * (g % gpr);
-        uint32_t w = 0;
+      for (int k = 0; k < 2; k++) {
+        const int r = 2 * rp + k;
+        int s[4] = {0, 0, 0, 0};
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-          const uint8_t *p = win + (r + 1) * WIN_PITCH + o + c + j + 1;      // sample (r-1, c+j-1) of the block
-          const int s = p[1] + p[2] + p[WIN_PITCH] + 2 * p[WIN_PITCH + 1] + 2 * p[WIN_PITCH + 2] + p[WIN_PITCH + 3] +
-                        p[2 * WIN_PITCH] + 2 * p[2 * WIN_PITCH + 1] + 2 * p[2 * WIN_PITCH + 2] + p[2 * WIN_PITCH + 3] +
-                        p[3 * WIN_PITCH + 1] + p[3 * WIN_PITCH + 2];
-          w |= (uint32_t)clip255((s + 8) >> 4) << (8 * j);
+          const uint32_t *w = win + (r + 1 + j) * (LW_PITCH / 4) + xq;
+          const uint32_t a0 = w[0], a1 = w[1];
+          const uint32_t t = (j == 0 || j == 3) ? 0x00010100u : 0x01020201u;
+          s[0] = dp4a_us(__funnelshift_r(a0, a1, 8), t, s[0]);
+          s[1] = dp4a_us(__funnelshift_r(a0, a1, 16), t, s[1]);
+          s[2] = dp4a_us(__funnelshift_r(a0, a1, 24), t, s[2]);
+          s[3] = dp4a_us(a1, t, s[3]);
         }
-        out[k] = w;
+        out[k] = taps4(clip255((s[0] + 8) >> 4), clip255((s[1] + 8) >> 4), clip255((s[2] + 8) >> 4), clip255((s[3] + 8) >> 4));
       }
     }
-    __syncwarp();
     return;
   }
-  const int8_t *kv = bipred ? c_luma_bi[fy] : c_luma_uni[fy];
   const int8_t *kh = bipred ? c_luma_bi[fx] : c_luma_uni[fx];
-  const int v0 = kv[0], v1 = kv[1], v2 = kv[2], v3 = kv[3], v4 = kv[4], v5 = kv[5];
-  const int h0 = kh[0], h1 = kh[1], h2 = kh[2], h3 = kh[3], h4 = kh[4], h5 = kh[5];
-  // vertical pass: item = (column c in 0..tw+4, group of 4 rows); |sum| <= 94*255 fits int16
-  const int ncols = tw + 5, rgroups = th >> 2;
-  for (int i = lane; i < ncols * rgroups; i += 32) {
-    const int c = i % ncols, r0 = (i / ncols) * 4;
-    const uint8_t *p = win + r0 * WIN_PITCH + o + c;
-    int a0 = p[0], a1 = p[WIN_PITCH], a2 = p[2 * WIN_PITCH], a3 = p[3 * WIN_PITCH], a4 = p[4 * WIN_PITCH];
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int a5 = p[(j + 5) * WIN_PITCH];
-      tmp[(r0 + j) * TMP_PITCH + c] = (int16_t)(v0 * a0 + v1 * a1 + v2 * a2 + v3 * a3 + v4 * a4 + v5 * a5);
-      a0 = a1; a1 = a2; a2 = a3; a3 = a4; a4 = a5;
+  const int8_t *kv = bipred ? c_luma_bi[fy] : c_luma_uni[fy];
+  // ---- horizontal pass: rows 0..th+4 of the window, 4 outputs per item, into tmpT[column][row] ----
+  {
+    const uint32_t hA = taps4(kh[0], kh[1], kh[2], kh[3]), hB = taps4(kh[4], kh[5], 0, 0);
+    const int items = (th + 5) * qpr;
+    for (int i = lane; i < items; i += 32) {
+      const int r = i / qpr, q = i - r * qpr;
+      const uint32_t *w = win + r * (LW_PITCH / 4) + q;
+      const uint32_t a0 = w[0], a1 = w[1], a2 = w[2];
+      const int s0 = dp4a_us(a1, hB, dp4a_us(a0, hA, 0));
+      const int s1 = dp4a_us(__funnelshift_r(a1, a2, 8), hB, dp4a_us(__funnelshift_r(a0, a1, 8), hA, 0));
+      const int s2 = dp4a_us(__funnelshift_r(a1, a2, 16), hB, dp4a_us(__funnelshift_r(a0, a1, 16), hA, 0));
+      const int s3 = dp4a_us(__funnelshift_r(a1, a2, 24), hB, dp4a_us(__funnelshift_r(a0, a1, 24), hA, 0));
+      int16_t *t = tmpT + (4 * q) * PT + r;
+      t[0] = (int16_t)s0; t[PT] = (int16_t)s1; t[2 * PT] = (int16_t)s2; t[3 * PT] = (int16_t)s3;
     }
   }
   __syncwarp();
-  // horizontal pass
+  // ---- vertical pass: rows r = 2rp (even) and r+1; intermediate rows r .. r+7 are words 0..3 of the column ----
+  if (act) {
+    const uint32_t e0 = pack2(kv[0], kv[1]), e1 = pack2(kv[2], kv[3]), e2 = pack2(kv[4], kv[5]);
+    const uint32_t o0 = pack2(0, kv[0]), o1 = pack2(kv[1], kv[2]), o2 = pack2(kv[3], kv[4]), o3 = pack2(kv[5], 0);
+    int ve[4], vo[4];
 #pragma unroll
-  for (int k = 0; k < 2; k++) {
-    const int g = lane + 32 * k;
-    if (g < ngroups) {
-      const int r = g / gpr, c = 4 * (g % gpr);
-      const int16_t *t = tmp + r * TMP_PITCH + c;
-      int a0 = t[0], a1 = t[1], a2 = t[2], a3 = t[3], a4 = t[4];
-      uint32_t w = 0;
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const int a5 = t[j + 5];
-        const int s = h0 * a0 + h1 * a1 + h2 * a2 + h3 * a3 + h4 * a4 + h5 * a5;
-        w |= (uint32_t)clip255((s + 2048) >> 12) << (8 * j);
-        a0 = a1; a1 = a2; a2 = a3; a3 = a4; a4 = a5;
-      }
-      out[k] = w;
+    for (int j = 0; j < 4; j++) {
+      const uint32_t *c = reinterpret_cast<const uint32_t *>(tmpT + (4 * xq + j) * PT) + rp;
+      const uint32_t w0 = c[0], w1 = c[1], w2 = c[2], w3 = c[3];
+      ve[j] = __dp2a_lo((int)w2, (int)e2, __dp2a_lo((int)w1, (int)e1, __dp2a_lo((int)w0, (int)e0, 0)));
+      vo[j] = __dp2a_lo((int)w3, (int)o3, __dp2a_lo((int)w2, (int)o2, __dp2a_lo((int)w1, (int)o1, __dp2a_lo((int)w0, (int)o0, 0))));
     }
+    out[0] = taps4(clip255((ve[0] + 2048) >> 12), clip255((ve[1] + 2048) >> 12), clip255((ve[2] + 2048) >> 12), clip255((ve[3] + 2048) >> 12));
+    out[1] = taps4(clip255((vo[0] + 2048) >> 12), clip255((vo[1] + 2048) >> 12), clip255((vo[2] + 2048) >> 12), clip255((vo[3] + 2048) >> 12));
   }
   __syncwarp();
 }
 
-// One chroma tile (cw x ch <= 8x8) of one plane from one reference; each lane owns up to 2 samples
-// (sample s = lane + 32*k, row = s / cw, col = s % cw).
-__device__ __forceinline__ void chroma_tile(const uint8_t *plane, int stride, int cx, int cy, int cw, int ch, int mvx, int mvy,
-                                            uint8_t *win, int16_t *tmp, int lane, int out[2]) {
-  const int fx = mvx & 7, fy = mvy & 7;
-  const uint8_t *src = plane + (ptrdiff_t)(cy + (mvy >> 3)) * stride + (cx + (mvx >> 3));
-  const int n = cw * ch;
-  if (!fx && !fy) {
-    const int o = stage_window(win, src, stride, ch, cw, lane);
-    __syncwarp();
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-      const int s = lane + 32 * k;
-      if (s < n) out[k] = win[(s / cw) * WIN_PITCH + o + (s % cw)];
-    }
-    __syncwarp();
-    return;
-  }
-  const int o = stage_window(win, src - stride - 1, stride, ch + 3, cw + 3, lane);
-  __syncwarp();
+// ---- chroma: one tile (cw x ch <= 8x8) of one plane -> out[2] as for luma (rows 2rp, 2rp+1; samples 4xq..4xq+3) ----
+__device__ __forceinline__ void chroma_tile(const uint32_t *win, int16_t *tmpT, int cw, int ch, int fx, int fy, int lane, uint32_t out[2]) {
+  const int qpr = (cw + 3) >> 2;
+  const int xq = lane % qpr, rp = lane / qpr;
+  const bool act = rp < (ch >> 1);
   const int8_t *kh = c_chroma[fx], *kv = c_chroma[fy];
-  // horizontal pass over rows -1..ch+1 (inter_prediction.c:97-106); |sum| <= 72*255 fits int16
-  for (int i = lane; i < (ch + 3) * cw; i += 32) {
-    const int r = i / cw, c = i % cw;
-    const uint8_t *p = win + r * WIN_PITCH + o + c;
-    tmp[r * TMP_PITCH + c] = (int16_t)(kh[0] * p[0] + kh[1] * p[1] + kh[2] * p[2] + kh[3] * p[3]);
+  // horizontal pass over window rows 0..ch+2 (sample rows -1..ch+1); window byte 0 = sample x-1  (inter_prediction.c:97-106)
+  {
+    const uint32_t hA = taps4(kh[0], kh[1], kh[2], kh[3]);
+    const int items = (ch + 3) * qpr;
+    for (int i = lane; i < items; i += 32) {
+      const int r = i / qpr, q = i - r * qpr;
+      const uint32_t *w = win + r * (CW_PITCH / 4) + q;
+      const uint32_t a0 = w[0], a1 = w[1];
+      int16_t *t = tmpT + (4 * q) * PT + r;
+      t[0] = (int16_t)dp4a_us(a0, hA, 0);
+      t[PT] = (int16_t)dp4a_us(__funnelshift_r(a0, a1, 8), hA, 0);
+      t[2 * PT] = (int16_t)dp4a_us(__funnelshift_r(a0, a1, 16), hA, 0);
+      t[3 * PT] = (int16_t)dp4a_us(__funnelshift_r(a0, a1, 24), hA, 0);
+    }
   }
   __syncwarp();
+  if (act) {
+    const uint32_t e0 = pack2(kv[0], kv[1]), e1 = pack2(kv[2], kv[3]);
+    const uint32_t o0 = pack2(0, kv[0]), o1 = pack2(kv[1], kv[2]), o2 = pack2(kv[3], 0);
+    int ve[4], vo[4];
 #pragma unroll
-  for (int k = 0; k < 2; k++) {
-    const int s = lane + 32 * k;
-    if (s < n) {
-      const int16_t *t = tmp + (s / cw) * TMP_PITCH + (s % cw);
-      const int acc = kv[0] * t[0] + kv[1] * t[TMP_PITCH] + kv[2] * t[2 * TMP_PITCH] + kv[3] * t[3 * TMP_PITCH];
-      out[k] = clip255((acc + 2048) >> 12);
+    for (int j = 0; j < 4; j++) {
+      const uint32_t *c = reinterpret_cast<const uint32_t *>(tmpT + (4 * xq + j) * PT) + rp;
+      const uint32_t w0 = c[0], w1 = c[1], w2 = c[2];
+      ve[j] = __dp2a_lo((int)w1, (int)e1, __dp2a_lo((int)w0, (int)e0, 0));
+      vo[j] = __dp2a_lo((int)w2, (int)o2, __dp2a_lo((int)w1, (int)o1, __dp2a_lo((int)w0, (int)o0, 0)));
     }
+    out[0] = taps4(clip255((ve[0] + 2048) >> 12), clip255((ve[1] + 2048) >> 12), clip255((ve[2] + 2048) >> 12), clip255((ve[3] + 2048) >> 12));
+    out[1] = taps4(clip255((vo[0] + 2048) >> 12), clip255((vo[1] + 2048) >> 12), clip255((vo[2] + 2048) >> 12), clip255((vo[3] + 2048) >> 12));
   }
   __syncwarp();
 }
@@ -179,54 +180,75 @@ __device__ __forceinline__ uint32_t avg_trunc4(uint32_t a, uint32_t b) {   // pe
 }
 
 __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
-  __shared__ __align__(16) uint8_t sWin[PW][WIN_ROWS * WIN_PITCH];
-  __shared__ __align__(16) int16_t sTmp[PW][16 * TMP_PITCH];
+  __shared__ __align__(16) WarpSmem sm[PW];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tile = blockIdx.x * PW + warp;
   if (tile >= P.ntiles) return;
+  WarpSmem &S = sm[warp];
   const PredTile tl = P.tiles[tile];
   const thorcuda_pred_task t = P.tasks[tl.task];
   const int x = t.x + 16 * tl.tx, y = t.y + 16 * tl.ty;
   const int tw = min(16, t.w - 16 * tl.tx), th = min(16, t.h - 16 * tl.ty);
-  uint8_t *win = sWin[warp];
-  int16_t *tmp = sTmp[warp];
-  const int mv0x = t.sign0 ? -t.mv0x : t.mv0x, mv0y = t.sign0 ? -t.mv0y : t.mv0y;
-  const int mv1x = t.sign1 ? -t.mv1x : t.mv1x, mv1y = t.sign1 ? -t.mv1y : t.mv1y;
-  const bool bi = t.ref1 >= 0;
+  const int mvx[2] = {t.sign0 ? -t.mv0x : t.mv0x, t.sign1 ? -t.mv1x : t.mv1x};
+  const int mvy[2] = {t.sign0 ? -t.mv0y : t.mv0y, t.sign1 ? -t.mv1y : t.mv1y};
+  const int nref = t.ref1 >= 0 ? 2 : 1;
   const PicView dst = P.pics[P.map[t.dst]];
-  const PicView r0 = P.pics[P.map[t.ref0]];
-  const PicView r1 = P.pics[P.map[bi ? t.ref1 : t.ref0]];
+  const int cx = x >> 1, cy = y >> 1, cw = tw >> 1, ch = th >> 1;
+
+  // ---- fetch every window of the tile first (independent loads: their latencies overlap) ----
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    if (k >= nref) break;
+    const PicView &r = P.pics[P.map[k ? t.ref1 : t.ref0]];
+    if (P.planes & 1) {
+      const uint8_t *src = r.p[0] + (ptrdiff_t)(y + (mvy[k] >> 2) - 2) * r.stride[0] + (x + (mvx[k] >> 2) - 2);
+      stage_window(S.lwin[k], src, r.stride[0], th + 5, (tw + 5 + 3) >> 2, LW_PITCH, lane);
+    }
+    if (P.planes & 2) {
+#pragma unroll
+      for (int pl = 1; pl <= 2; pl++) {
+        const uint8_t *src = r.p[pl] + (ptrdiff_t)(cy + (mvy[k] >> 3) - 1) * r.stride[pl] + (cx + (mvx[k] >> 3) - 1);
+        stage_window(S.cwin[2 * k + pl - 1], src, r.stride[pl], ch + 3, (cw + 3 + 3) >> 2, CW_PITCH, lane);
+      }
+    }
+  }
+  __syncwarp();
 
   if (P.planes & 1) {
     uint32_t a[2] = {0, 0}, b[2] = {0, 0};
-    luma_tile(r0, x, y, tw, th, mv0x, mv0y, P.bipred_filter, win, tmp, lane, a);
-    if (bi) {
-      luma_tile(r1, x, y, tw, th, mv1x, mv1y, P.bipred_filter, win, tmp, lane, b);
+    luma_tile(S.lwin[0], S.tmpT, tw, th, mvx[0] & 3, mvy[0] & 3, P.bipred_filter, lane, a);
+    if (nref == 2) {
+      luma_tile(S.lwin[1], S.tmpT, tw, th, mvx[1] & 3, mvy[1] & 3, P.bipred_filter, lane, b);
       a[0] = avg_trunc4(a[0], b[0]);
       a[1] = avg_trunc4(a[1], b[1]);
     }
-    const int gpr = tw >> 2;
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-      const int g = lane + 32 * k;
-      if (g < gpr * th)
-        *reinterpret_cast<uint32_t *>(dst.p[0] + (size_t)(y + g / gpr) * dst.stride[0] + x + 4 * (g % gpr)) = a[k];
+    const int qpr = tw >> 2, xq = lane % qpr, rp = lane / qpr;
+    if (rp < (th >> 1)) {
+      uint8_t *d = dst.p[0] + (size_t)(y + 2 * rp) * dst.stride[0] + x + 4 * xq;
+      *reinterpret_cast<uint32_t *>(d) = a[0];
+      *reinterpret_cast<uint32_t *>(d + dst.stride[0]) = a[1];
     }
   }
   if (P.planes & 2) {
-    const int cx = x >> 1, cy = y >> 1, cw = tw >> 1, ch = th >> 1;
-    for (int pl = 1; pl <= 2; pl++) {
-      int a[2] = {0, 0}, b[2] = {0, 0};
-      chroma_tile(r0.p[pl], r0.stride[pl], cx, cy, cw, ch, mv0x, mv0y, win, tmp, lane, a);
-      if (bi) {
-        chroma_tile(r1.p[pl], r1.stride[pl], cx, cy, cw, ch, mv1x, mv1y, win, tmp, lane, b);
-        a[0] = (a[0] + b[0]) >> 1;
-        a[1] = (a[1] + b[1]) >> 1;
-      }
+    const int qpr = (cw + 3) >> 2, xq = lane % qpr, rp = lane / qpr;
 #pragma unroll
-      for (int k = 0; k < 2; k++) {
-        const int s = lane + 32 * k;
-        if (s < cw * ch) dst.p[pl][(size_t)(cy + s / cw) * dst.stride[pl] + cx + (s % cw)] = (uint8_t)a[k];
+    for (int pl = 1; pl <= 2; pl++) {
+      uint32_t a[2] = {0, 0}, b[2] = {0, 0};
+      chroma_tile(S.cwin[pl - 1], S.tmpT, cw, ch, mvx[0] & 7, mvy[0] & 7, lane, a);
+      if (nref == 2) {
+        chroma_tile(S.cwin[2 + pl - 1], S.tmpT, cw, ch, mvx[1] & 7, mvy[1] & 7, lane, b);
+        a[0] = avg_trunc4(a[0], b[0]);
+        a[1] = avg_trunc4(a[1], b[1]);
+      }
+      if (rp < (ch >> 1)) {
+        uint8_t *d = dst.p[pl] + (size_t)(cy + 2 * rp) * dst.stride[pl] + cx + 4 * xq;
+        // chroma x is only 2-aligned and chroma widths are multiples of 2 (the last quad may be half): 16-bit stores
+        *reinterpret_cast<uint16_t *>(d) = (uint16_t)a[0];
+        *reinterpret_cast<uint16_t *>(d + dst.stride[pl]) = (uint16_t)a[1];
+        if (4 * xq + 4 <= cw) {
+          *reinterpret_cast<uint16_t *>(d + 2) = (uint16_t)(a[0] >> 16);
+          *reinterpret_cast<uint16_t *>(d + dst.stride[pl] + 2) = (uint16_t)(a[1] >> 16);
+        }
       }
     }
   }
