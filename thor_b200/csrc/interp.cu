@@ -58,12 +58,15 @@ __device__ __forceinline__ uint32_t taps4(int a, int b, int c, int d) {
 
 // Fetch rows x bytes starting at src (any alignment) into win (row pitch `pitch` bytes, byte 0 = src[0]).
 // wpr = words per staged row.
+// LW = log2 of the lane columns used per row (8 for luma: wpr <= 6; 4 for chroma: wpr <= 3).
+template <int LW>
 __device__ __forceinline__ void stage_window(uint32_t *win, const uint8_t *src, int stride, int rows, int wpr, int pitch, int lane) {
   const int o = (int)((uintptr_t)src & 3);
   const uint8_t *base = src - o;
   const int sh = o * 8;
-  for (int i = lane; i < rows * wpr; i += 32) {
-    const int r = i / wpr, wd = i - r * wpr;
+  const int wd = lane & ((1 << LW) - 1);
+  if (wd >= wpr) return;
+  for (int r = lane >> LW; r < rows; r += 32 >> LW) {
     const uint32_t *g = reinterpret_cast<const uint32_t *>(base + (size_t)r * stride) + wd;
     const uint32_t lo = g[0], hi = o ? g[1] : 0u;
     win[r * (pitch >> 2) + wd] = __funnelshift_r(lo, hi, sh);
@@ -74,8 +77,8 @@ __device__ __forceinline__ void stage_window(uint32_t *win, const uint8_t *src, 
 __device__ __forceinline__ void luma_tile(const uint32_t *win, int16_t *tmpT, int tw, int th, int fx, int fy, int bipred, int lane,
                                           uint32_t out[2]) {
   const int qpr = tw >> 2;                       // quads per row
-  const int xq = lane % qpr, rp = lane / qpr;    // this lane's output quad / row pair
-  const bool act = rp < (th >> 1);
+  const int xq = lane & 3, rp = lane >> 2;       // this lane's output quad / row pair
+  const bool act = xq < qpr && rp < (th >> 1);
   if (fx == 2 && fy == 2) {
     // centre position: [0 1 1 0; 1 2 2 1; 1 2 2 1; 0 1 1 0], (sum+8)>>4   (inter_prediction.c:146-157)
     // window byte 0 = sample x-2, window row 0 = sample row y-2; taps cover columns x-1..x+2, rows y-1..y+2
@@ -104,9 +107,8 @@ __device__ __forceinline__ void luma_tile(const uint32_t *win, int16_t *tmpT, in
   // ---- horizontal pass: rows 0..th+4 of the window, 4 outputs per item, into tmpT[column][row] ----
   {
     const uint32_t hA = taps4(kh[0], kh[1], kh[2], kh[3]), hB = taps4(kh[4], kh[5], 0, 0);
-    const int items = (th + 5) * qpr;
-    for (int i = lane; i < items; i += 32) {
-      const int r = i / qpr, q = i - r * qpr;
+    const int q = lane & 3;
+    for (int r = lane >> 2; r < th + 5 && q < qpr; r += 8) {
       const uint32_t *w = win + r * (LW_PITCH / 4) + q;
       const uint32_t a0 = w[0], a1 = w[1], a2 = w[2];
       const int s0 = dp4a_us(a1, hB, dp4a_us(a0, hA, 0));
@@ -138,16 +140,15 @@ __device__ __forceinline__ void luma_tile(const uint32_t *win, int16_t *tmpT, in
 
 // ---- chroma: one tile (cw x ch <= 8x8) of one plane -> out[2] as for luma (rows 2rp, 2rp+1; samples 4xq..4xq+3) ----
 __device__ __forceinline__ void chroma_tile(const uint32_t *win, int16_t *tmpT, int cw, int ch, int fx, int fy, int lane, uint32_t out[2]) {
-  const int qpr = (cw + 3) >> 2;
-  const int xq = lane % qpr, rp = lane / qpr;
-  const bool act = rp < (ch >> 1);
+  const int qpr = (cw + 3) >> 2;                 // 1 or 2
+  const int xq = lane & 1, rp = lane >> 1;
+  const bool act = xq < qpr && rp < (ch >> 1);
   const int8_t *kh = c_chroma[fx], *kv = c_chroma[fy];
   // horizontal pass over window rows 0..ch+2 (sample rows -1..ch+1); window byte 0 = sample x-1  (inter_prediction.c:97-106)
   {
     const uint32_t hA = taps4(kh[0], kh[1], kh[2], kh[3]);
-    const int items = (ch + 3) * qpr;
-    for (int i = lane; i < items; i += 32) {
-      const int r = i / qpr, q = i - r * qpr;
+    const int q = lane & 1;
+    for (int r = lane >> 1; r < ch + 3 && q < qpr; r += 16) {
       const uint32_t *w = win + r * (CW_PITCH / 4) + q;
       const uint32_t a0 = w[0], a1 = w[1];
       int16_t *t = tmpT + (4 * q) * PT + r;
@@ -185,30 +186,32 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
   const int tile = blockIdx.x * PW + warp;
   if (tile >= P.ntiles) return;
   WarpSmem &S = sm[warp];
-  const PredTile tl = P.tiles[tile];
-  const thorcuda_pred_task t = P.tasks[tl.task];
-  const int x = t.x + 16 * tl.tx, y = t.y + 16 * tl.ty;
-  const int tw = min(16, t.w - 16 * tl.tx), th = min(16, t.h - 16 * tl.ty);
-  const int mvx[2] = {t.sign0 ? -t.mv0x : t.mv0x, t.sign1 ? -t.mv1x : t.mv1x};
-  const int mvy[2] = {t.sign0 ? -t.mv0y : t.mv0y, t.sign1 ? -t.mv1y : t.mv1y};
-  const int nref = t.ref1 >= 0 ? 2 : 1;
-  const PicView dst = P.pics[P.map[t.dst]];
+  const uint4 *tp = reinterpret_cast<const uint4 *>(P.tiles + tile);
+  const uint4 q0 = tp[0], q1 = tp[1];
+  PredTile t;
+  *reinterpret_cast<uint4 *>(&t) = q0;
+  *(reinterpret_cast<uint4 *>(&t) + 1) = q1;
+  const int x = t.x, y = t.y, tw = t.tw, th = t.th;
+  const int mvx[2] = {t.mv0x, t.mv1x};
+  const int mvy[2] = {t.mv0y, t.mv1y};
+  const int nref = t.ref1 != 0xFFFF ? 2 : 1;
+  const PicView dst = P.pics[t.dst];
   const int cx = x >> 1, cy = y >> 1, cw = tw >> 1, ch = th >> 1;
 
   // ---- fetch every window of the tile first (independent loads: their latencies overlap) ----
 #pragma unroll
   for (int k = 0; k < 2; k++) {
     if (k >= nref) break;
-    const PicView &r = P.pics[P.map[k ? t.ref1 : t.ref0]];
+    const PicView &r = P.pics[k ? t.ref1 : t.ref0];
     if (P.planes & 1) {
       const uint8_t *src = r.p[0] + (ptrdiff_t)(y + (mvy[k] >> 2) - 2) * r.stride[0] + (x + (mvx[k] >> 2) - 2);
-      stage_window(S.lwin[k], src, r.stride[0], th + 5, (tw + 5 + 3) >> 2, LW_PITCH, lane);
+      stage_window<3>(S.lwin[k], src, r.stride[0], th + 5, (tw + 5 + 3) >> 2, LW_PITCH, lane);
     }
     if (P.planes & 2) {
 #pragma unroll
       for (int pl = 1; pl <= 2; pl++) {
         const uint8_t *src = r.p[pl] + (ptrdiff_t)(cy + (mvy[k] >> 3) - 1) * r.stride[pl] + (cx + (mvx[k] >> 3) - 1);
-        stage_window(S.cwin[2 * k + pl - 1], src, r.stride[pl], ch + 3, (cw + 3 + 3) >> 2, CW_PITCH, lane);
+        stage_window<2>(S.cwin[2 * k + pl - 1], src, r.stride[pl], ch + 3, (cw + 3 + 3) >> 2, CW_PITCH, lane);
       }
     }
   }
@@ -222,15 +225,15 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
       a[0] = avg_trunc4(a[0], b[0]);
       a[1] = avg_trunc4(a[1], b[1]);
     }
-    const int qpr = tw >> 2, xq = lane % qpr, rp = lane / qpr;
-    if (rp < (th >> 1)) {
+    const int qpr = tw >> 2, xq = lane & 3, rp = lane >> 2;
+    if (xq < qpr && rp < (th >> 1)) {
       uint8_t *d = dst.p[0] + (size_t)(y + 2 * rp) * dst.stride[0] + x + 4 * xq;
       *reinterpret_cast<uint32_t *>(d) = a[0];
       *reinterpret_cast<uint32_t *>(d + dst.stride[0]) = a[1];
     }
   }
   if (P.planes & 2) {
-    const int qpr = (cw + 3) >> 2, xq = lane % qpr, rp = lane / qpr;
+    const int qpr = (cw + 3) >> 2, xq = lane & 1, rp = lane >> 1;
 #pragma unroll
     for (int pl = 1; pl <= 2; pl++) {
       uint32_t a[2] = {0, 0}, b[2] = {0, 0};
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(PW * 32) k_predict(const PredParams P) {
         a[0] = avg_trunc4(a[0], b[0]);
         a[1] = avg_trunc4(a[1], b[1]);
       }
-      if (rp < (ch >> 1)) {
+      if (xq < qpr && rp < (ch >> 1)) {
         uint8_t *d = dst.p[pl] + (size_t)(cy + 2 * rp) * dst.stride[pl] + cx + 4 * xq;
         // chroma x is only 2-aligned and chroma widths are multiples of 2 (the last quad may be half): 16-bit stores
         *reinterpret_cast<uint16_t *>(d) = (uint16_t)a[0];

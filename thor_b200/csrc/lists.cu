@@ -10,7 +10,7 @@ namespace thor {
 
 static int log2size(int s) { return s == 4 ? 0 : s == 8 ? 1 : s == 16 ? 2 : s == 32 ? 3 : s == 64 ? 4 : -1; }
 
-static int check_pred(const Pic *const *P, int npics, const thorcuda_pred_task *tasks, int ntasks, std::vector<PredTile> &tiles) {
+static int check_pred(const Pic *const *P, const thorcuda_pic *handles, int npics, const thorcuda_pred_task *tasks, int ntasks, std::vector<PredTile> &tiles) {
   for (int i = 0; i < ntasks; i++) {
     const thorcuda_pred_task &t = tasks[i];
     if (t.dst >= npics) return fail("predict: task %d writes picture %d of %d", i, t.dst, npics);
@@ -37,7 +37,17 @@ static int check_pred(const Pic *const *P, int npics, const thorcuda_pred_task *
         return fail("predict: task %d reads outside the padded chroma reference (mv %d,%d)", i, mx, my);
     }
     for (int ty = 0; ty < (t.h + 15) / 16; ty++)
-      for (int tx = 0; tx < (t.w + 15) / 16; tx++) tiles.push_back(PredTile{(uint32_t)i, (uint8_t)tx, (uint8_t)ty, 0, 0});
+      for (int tx = 0; tx < (t.w + 15) / 16; tx++) {
+        PredTile q;
+        memset(&q, 0, sizeof(q));
+        q.x = (uint16_t)(t.x + 16 * tx); q.y = (uint16_t)(t.y + 16 * ty);
+        q.tw = (uint8_t)std::min(16, t.w - 16 * tx); q.th = (uint8_t)std::min(16, t.h - 16 * ty);
+        q.dst = (uint16_t)handles[t.dst]; q.ref0 = (uint16_t)handles[t.ref0]; q.ref1 = t.ref1 >= 0 ? (uint16_t)handles[t.ref1] : (uint16_t)0xFFFF;
+        q.mv0x = (int16_t)(t.sign0 ? -t.mv0x : t.mv0x); q.mv0y = (int16_t)(t.sign0 ? -t.mv0y : t.mv0y);
+        q.mv1x = (int16_t)(t.sign1 ? -t.mv1x : t.mv1x); q.mv1y = (int16_t)(t.sign1 ? -t.mv1y : t.mv1y);
+        q.task = (uint32_t)i;
+        tiles.push_back(q);
+      }
   }
   return 0;
 }
@@ -120,7 +130,7 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
   const void *second = nullptr;
   size_t second_bytes = 0;
   if (kind == THORCUDA_LIST_PRED) {
-    if (check_pred(P, npics, (const thorcuda_pred_task *)tasks, ntasks, tiles)) return -1;
+    if (check_pred(P, pics, npics, (const thorcuda_pred_task *)tasks, ntasks, tiles)) return -1;
     task_size = sizeof(thorcuda_pred_task);
     L.ntiles = (int)tiles.size();
     second = tiles.data(); second_bytes = tiles.size() * sizeof(PredTile);
