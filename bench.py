@@ -301,7 +301,9 @@ def run_gpu_arm(args, rank, world, local_rank):
     slots = [s for st in streams for s in st.slots]
     orgs = [st.org for st in streams for _ in range(2)]
     refs = [r for st in streams for r in st.refs]
-    lf_jobs = [dict(rec=st.work, qp=st.job["qp"], stages=15, org=st.org, ref_out=st.newref) for st in streams]
+    # resident run: the CLPF bits stay in HBM (sb_bits_out = NULL); the e2e leg below fetches them
+    lf_jobs = (tb.ops.LfJob * B)(*[tb.ops.LfJob(st.work.handle, st.org.handle, st.newref.handle, st.job["qp"], 15, None, None)
+                                   for st in streams])
 
     def stage_sad():
         tb.ops.sad_table_build(slots, orgs, refs, args.range)
@@ -317,7 +319,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         l_tb.encode()
 
     def stage_filter():
-        tb.ops.loopfilter_frames(lf_jobs, wait=False)
+        tb.check(lib.thorcuda_loopfilter_frames(B, C.byref(lf_jobs)))
 
     stages = [("sad_table", stage_sad), ("subpel", stage_subpel), ("predict", stage_pred), ("transform", stage_tb),
               ("loopfilter", stage_filter)]

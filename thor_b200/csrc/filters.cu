@@ -333,30 +333,38 @@ __global__ void __launch_bounds__(LF_THREADS) k_loopfilter(const LfParams *__res
   }
 }
 
-// Border replication (pad_yuv_frame, common_frame.c:405-462).  One thread per 4 border bytes.
-// grid.y enumerates rows of the padded plane, grid.z = 3*job + plane.
-__device__ __forceinline__ void pad_rows(const PicView &v, int pl, int prow) {
+// Border replication (pad_yuv_frame, common_frame.c:405-462).  One thread per 4 border bytes; only border bytes
+// are enumerated: item < nA -> the top / bottom bands (2*pad full padded rows), else the left / right bands of
+// the h picture rows.  grid.y = plane, grid.z = job; grid.x covers the largest plane of the batch.
+__device__ __forceinline__ void pad_items(const PicView &v, int pl) {
   const int pad = v.pad[pl], w = pl ? v.w / 2 : v.w, h = pl ? v.h / 2 : v.h, stride = v.stride[pl];
-  const int row = prow - pad;                          // -pad .. h+pad-1
-  if (row >= h + pad) return;
-  const int srow = min(max(row, 0), h - 1);
-  uint8_t *dst = v.p[pl] + (ptrdiff_t)row * stride;
-  const uint8_t *src = v.p[pl] + (ptrdiff_t)srow * stride;
-  const int total = w + 2 * pad;                       // bytes in this padded row (multiple of 4)
-  for (int x = (blockIdx.x * blockDim.x + threadIdx.x) * 4 - pad; x < total - pad; x += gridDim.x * blockDim.x * 4) {
-    if (row >= 0 && row < h && x >= 0 && x < w) continue;   // interior: already written
+  if (!pad) return;
+  const int tw4 = (w + 2 * pad) >> 2, pw4 = pad >> 2;  // words per padded row / per side band (w, pad: multiples of 4)
+  const int nA = 2 * pad * tw4, nB = h * 2 * pw4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nA + nB; i += gridDim.x * blockDim.x) {
+    int row, x;
+    if (i < nA) {
+      const int r = i / tw4;
+      x = (i - r * tw4) * 4 - pad;
+      row = r < pad ? r - pad : h + (r - pad);
+    } else {
+      const int j = i - nA, r = j / (2 * pw4), c = j - r * 2 * pw4;
+      row = r;
+      x = c < pw4 ? c * 4 - pad : w + (c - pw4) * 4;
+    }
+    const uint8_t *src = v.p[pl] + (ptrdiff_t)min(max(row, 0), h - 1) * stride;
     uint32_t val;
     if (x < 0) val = src[0] * 0x01010101u;
     else if (x >= w) val = src[w - 1] * 0x01010101u;
     else val = *reinterpret_cast<const uint32_t *>(src + x);
-    *reinterpret_cast<uint32_t *>(dst + x) = val;
+    *reinterpret_cast<uint32_t *>(v.p[pl] + (ptrdiff_t)row * stride + x) = val;
   }
 }
-__global__ void k_pad(PicView v) { pad_rows(v, blockIdx.z, blockIdx.y); }
-__global__ void k_pad_jobs(const LfParams *__restrict__ jobs) {
-  const LfParams &J = jobs[blockIdx.z / 3];
+__global__ void __launch_bounds__(256) k_pad(PicView v) { pad_items(v, blockIdx.y); }
+__global__ void __launch_bounds__(256) k_pad_jobs(const LfParams *__restrict__ jobs) {
+  const LfParams &J = jobs[blockIdx.z];
   if (!J.dstB.p[0]) return;
-  pad_rows(J.dstB, blockIdx.z % 3, blockIdx.y);
+  pad_items(J.dstB, blockIdx.y);
 }
 
 }  // namespace thor
@@ -386,8 +394,9 @@ int thorcuda_pad_frame(thorcuda_pic h) {
   Pic *p = get_pic(h);
   if (!p) return fail("bad picture handle %d", h);
   if (p->pad_y == 0 && p->pad_c == 0) return 0;
-  dim3 grid(4, p->rows_y, 3);
-  k_pad<<<grid, 128, 0, ctx().stream>>>(p->view());
+  const int items = (2 * p->pad_y * (p->w + 2 * p->pad_y) + p->h * 2 * p->pad_y) / 4;
+  dim3 grid((items + 255) / 256, 3, 1);
+  k_pad<<<grid, 256, 0, ctx().stream>>>(p->view());
   THOR_LAUNCHED();
   return 0;
 }
@@ -403,7 +412,7 @@ int thorcuda_loopfilter_frames(int n, const thorcuda_lf_job *jobs) {
   if (n > 16384) return fail("loopfilter: too many frames in one batch");
   // validate, size the per-SB bit scratch
   size_t bits_total = 0;
-  int maxw = 0, maxh = 0, max_ref_rows = 0;
+  int maxw = 0, maxh = 0, max_ref_rows = 0, max_pad_items = 0;
   for (int i = 0; i < n; i++) {
     const thorcuda_lf_job &j = jobs[i];
     Pic *rec = get_pic(j.rec), *org = j.org >= 0 ? get_pic(j.org) : nullptr, *ref = j.ref_out >= 0 ? get_pic(j.ref_out) : nullptr;
@@ -422,7 +431,10 @@ int thorcuda_loopfilter_frames(int n, const thorcuda_lf_job *jobs) {
     if (!rec->buf[1 - rec->cur]) THOR_CUDA(cudaMalloc((void **)&rec->buf[1 - rec->cur], rec->bytes + 256));
     bits_total += 2 * (size_t)((rec->w / 64) * (rec->h / 64) + 1);
     maxw = max(maxw, rec->w); maxh = max(maxh, rec->h);
-    if (ref && (j.stages & THORCUDA_LF_MAKE_REF)) max_ref_rows = max(max_ref_rows, ref->rows_y);
+    if (ref && (j.stages & THORCUDA_LF_MAKE_REF)) {
+      max_ref_rows = max(max_ref_rows, ref->rows_y);
+      max_pad_items = max(max_pad_items, (2 * ref->pad_y * (ref->w + 2 * ref->pad_y) + ref->h * 2 * ref->pad_y) / 4);
+    }
   }
   uint8_t *d_bits = (uint8_t *)c.scratch.reserve(bits_total);
   LfParams *d_jobs = (LfParams *)c.lfjobs.reserve(sizeof(LfParams) * n);
@@ -477,8 +489,8 @@ int thorcuda_loopfilter_frames(int n, const thorcuda_lf_job *jobs) {
     off += 2 * (size_t)(nsb + 1);
   }
   if (max_ref_rows) {
-    dim3 pg(4, max_ref_rows, 3 * n);
-    k_pad_jobs<<<pg, 128, 0, c.stream>>>(d_jobs);
+    dim3 pg((max_pad_items + 255) / 256, 3, n);
+    k_pad_jobs<<<pg, 256, 0, c.stream>>>(d_jobs);
     THOR_LAUNCHED();
   }
   return 0;
