@@ -92,10 +92,12 @@ static int check_cost(const Pic *const *P, int npics, const thorcuda_cost_task *
     if (o->w != r->w || o->h != r->h) return fail("cost: task %d: picture size mismatch", i);
     if (t.w < 4 || t.h < 4 || t.w > 64 || t.h > 64 || (t.w & 3) || (t.h & 3) || t.x + t.w > o->w || t.y + t.h > o->h)
       return fail("cost: task %d has an invalid block (%d,%d %dx%d)", i, t.x, t.y, t.w, t.h);
+    if (t.x & 3) return fail("cost: task %d: block x %d is not on the 4-sample grid", i, t.x);
     if (t.hx < -2 || t.hx > 2 || t.hy < -2 || t.hy > 2 || (t.hx & 1) || (t.hy & 1)) return fail("cost: task %d: half-pel offset (%d,%d)", i, t.hx, t.hy);
-    // widest reach of any kind: 3 columns (widesad), 2 rows/columns (fasthalf)
+    // widest reach of any kind: 3 columns (widesad), 2 rows/columns (fasthalf); the kernel stages whole words, i.e.
+    // columns -4 .. w+3, so that is what must lie inside the padded picture
     const int lx = t.x + t.ix, ly = t.y + t.iy;
-    if (lx - 3 < -r->pad_y || ly - 3 < -r->pad_y || lx + t.w + 3 > r->w + r->pad_y || ly + t.h + 3 > r->h + r->pad_y)
+    if (lx - 4 < -r->pad_y || ly - 3 < -r->pad_y || lx + t.w + 4 > r->w + r->pad_y || ly + t.h + 3 > r->h + r->pad_y)
       return fail("cost: task %d reads outside the padded reference (%d,%d)", i, t.ix, t.iy);
   }
   return 0;

@@ -293,8 +293,13 @@ __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__re
 }
 
 // --------------------------------------------------------------------------- cost batch ----
+// One warp per (block, candidate) task.  The reference window (rows -3..h+2, columns -4..w+3 around the candidate
+// position, so that the block's columns are word aligned) is staged in shared memory; a lane then works on 4
+// horizontally adjacent samples at a time with byte-SIMD words: VAVG (rounding average = v64_avg_u8), VHADD
+// (truncating average = v64_rdavg_u8) and VABSDIFF4 with accumulate, exactly the operations of the reference's
+// SIMD kernels (enc/enc_kernels.c:162-648).
 constexpr int CW = 8;                         // warps per CTA
-constexpr int CPITCH = 76;                    // window row: up to 64 + 3 + 3 samples + 3 alignment bytes
+constexpr int CPW = 19;                       // window row pitch in words: up to 4 + 64 + 4 samples
 constexpr int CROWS = 70;
 
 struct CostParams {
@@ -305,17 +310,27 @@ struct CostParams {
   int ntasks, kind;
 };
 
-__device__ __forceinline__ int avg_up(int a, int b) { return (a + b + 1) >> 1; }   // v64_avg_u8
-__device__ __forceinline__ int avg_dn(int a, int b) { return (a + b) >> 1; }       // v64_rdavg_u8
+__device__ __forceinline__ uint32_t up4(uint32_t a, uint32_t b) { return __vavgu4(a, b); }    // (a+b+1)>>1 per byte
+__device__ __forceinline__ uint32_t dn4(uint32_t a, uint32_t b) { return __vhaddu4(a, b); }   // (a+b)>>1 per byte
 
-// bilinear diagonal half-pel sample between rows (sy-1,sy) and columns (sx-1,sx) of p (reference
-// enc/encode_block.c:527-571: a fixed tree of rounding / truncating averages)
-__device__ __forceinline__ int diag_half(const uint8_t *p, int sy, int sx) {
-  const uint8_t *q = p + (sy - 1) * CPITCH + (sx - 1);
-  const int core = avg_dn(avg_up(q[0], q[1]), avg_up(q[CPITCH], q[CPITCH + 1]));
-  const int vert = avg_dn(avg_up(q[-CPITCH], q[2 * CPITCH]), avg_up(q[-CPITCH + 1], q[2 * CPITCH + 1]));
-  const int hori = avg_dn(avg_up(q[-1], q[2]), avg_up(q[CPITCH - 1], q[CPITCH + 2]));
-  return avg_dn(avg_dn(vert, hori), core);
+// the 4 samples starting K columns right of the quad, from the three window words around it
+struct Row3 { uint32_t w0, w1, w2; };
+template <int K>
+__device__ __forceinline__ uint32_t col(const Row3 &r) {
+  if (K < 0) return __funnelshift_r(r.w0, r.w1, 8 * (4 + K));
+  if (K == 0) return r.w1;
+  return __funnelshift_r(r.w1, r.w2, 8 * K);
+}
+__device__ __forceinline__ Row3 load_row(const uint32_t *p) { Row3 r; r.w0 = p[0]; r.w1 = p[1]; r.w2 = p[2]; return r; }
+
+// bilinear diagonal half-pel samples (reference enc/encode_block.c:527-571: a fixed tree of rounding / truncating
+// averages); R[0..4] = rows -2..+2; (QY,QX) = top-left sample of the 2x2 core relative to the quad
+template <int QY, int QX>
+__device__ __forceinline__ uint32_t diag_half(const Row3 (&R)[5]) {
+  const uint32_t core = dn4(up4(col<QX>(R[QY + 2]), col<QX + 1>(R[QY + 2])), up4(col<QX>(R[QY + 3]), col<QX + 1>(R[QY + 3])));
+  const uint32_t vert = dn4(up4(col<QX>(R[QY + 1]), col<QX>(R[QY + 4])), up4(col<QX + 1>(R[QY + 1]), col<QX + 1>(R[QY + 4])));
+  const uint32_t hori = dn4(up4(col<QX - 1>(R[QY + 2]), col<QX + 2>(R[QY + 2])), up4(col<QX - 1>(R[QY + 3]), col<QX + 2>(R[QY + 3])));
+  return dn4(dn4(vert, hori), core);
 }
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
@@ -325,66 +340,74 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 }
 
 __global__ void __launch_bounds__(CW * 32) k_cost_batch(const CostParams P) {
-  __shared__ __align__(16) uint8_t sWin[CW][CROWS * CPITCH];
+  __shared__ __align__(16) uint32_t sWin[CW][CROWS * CPW];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ti = blockIdx.x * CW + warp;
   if (ti >= P.ntasks) return;
   const thorcuda_cost_task t = P.tasks[ti];
   const PicView org = P.pics[P.map[t.org]], ref = P.pics[P.map[t.ref]];
   const int w = t.w, h = t.h;
-  // stage reference rows -3..h+2, columns -3..w+2 around the candidate position
-  uint8_t *win = sWin[warp];
-  const uint8_t *src = ref.p[0] + (ptrdiff_t)(t.y + t.iy - 3) * ref.stride[0] + (t.x + t.ix - 3);
-  const int o = (int)((uintptr_t)src & 3);
+  // stage reference rows -3..h+2, columns -4..w+3 around the candidate position; byte 0 of a row = column -4
+  uint32_t *win = sWin[warp];
   {
+    const uint8_t *src = ref.p[0] + (ptrdiff_t)(t.y + t.iy - 3) * ref.stride[0] + (t.x + t.ix - 4);
+    const int o = (int)((uintptr_t)src & 3), sh = 8 * o;
     const uint8_t *base = src - o;
-    const int words = (w + 6 + o + 3) >> 2;
+    const int words = (w + 8) >> 2;
     for (int i = lane; i < (h + 6) * words; i += 32) {
       const int r = i / words, wd = i - r * words;
-      reinterpret_cast<uint32_t *>(win + r * CPITCH)[wd] = *reinterpret_cast<const uint32_t *>(base + (ptrdiff_t)r * ref.stride[0] + 4 * wd);
+      const uint32_t *g = reinterpret_cast<const uint32_t *>(base + (ptrdiff_t)r * ref.stride[0]) + wd;
+      const uint32_t lo = g[0], hi = o ? g[1] : 0u;
+      win[r * CPW + wd] = __funnelshift_r(lo, hi, sh);
     }
   }
   __syncwarp();
-  const uint8_t *b00 = win + 3 * CPITCH + 3 + o;        // reference sample (0,0) of the candidate block
   const uint8_t *a00 = org.p[0] + (size_t)t.y * org.stride[0] + t.x;
-  const int npix = w * h;
+  const int wq = w >> 2, nquads = wq * h;
   uint32_t s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int kind = P.kind;
   const int sel = (t.hx & t.hy) ? 0 : (t.hx ? 1 : (t.hy ? 2 : 3));
-  for (int i = lane; i < npix; i += 32) {
-    const int r = i / w, c = i - r * w;
-    const int A = a00[(size_t)r * org.stride[0] + c];
-    const uint8_t *p = b00 + r * CPITCH + c;
+  for (int i = lane; i < nquads; i += 32) {
+    const int r = i / wq, c4 = i - r * wq;
+    const uint32_t A = *reinterpret_cast<const uint32_t *>(a00 + (size_t)r * org.stride[0] + 4 * c4);
+    const uint32_t *p0 = win + (r + 3) * CPW + c4;       // words around the quad in its own row
     if (kind == THORCUDA_COST_SAD) {
-      s[0] += abs(A - p[0]);
+      s[0] = sad4(A, p0[1], s[0]);
     } else if (kind == THORCUDA_COST_SSD) {
-      const int d = A - p[0];
-      s[0] += d * d;
+      const uint32_t d = __vabsdiffu4(A, p0[1]);
+      s[0] = __dp4a(d, d, s[0]);
     } else if (kind == THORCUDA_COST_WIDESAD) {
-      s[0] += abs(A - p[-3]); s[1] += abs(A - p[-1]); s[2] += abs(A - p[0]); s[3] += abs(A - p[1]); s[4] += abs(A - p[3]);
+      const Row3 R = load_row(p0);
+      s[0] = sad4(A, col<-3>(R), s[0]); s[1] = sad4(A, col<-1>(R), s[1]); s[2] = sad4(A, col<0>(R), s[2]);
+      s[3] = sad4(A, col<1>(R), s[3]); s[4] = sad4(A, col<3>(R), s[4]);
     } else if (kind == THORCUDA_COST_FASTHALF) {
+      Row3 R[5];
+#pragma unroll
+      for (int y = 0; y < 5; y++) R[y] = load_row(p0 + (y - 2) * CPW);
+      const uint32_t X = R[2].w1;
       // order: top down left right tl tr bl br
-      s[0] += abs(A - avg_up(p[0], p[-CPITCH]));
-      s[1] += abs(A - avg_up(p[0], p[CPITCH]));
-      s[2] += abs(A - avg_up(p[-1], p[0]));
-      s[3] += abs(A - avg_up(p[0], p[1]));
-      s[4] += abs(A - diag_half(p, 0, 0));
-      s[5] += abs(A - diag_half(p, 0, 1));
-      s[6] += abs(A - diag_half(p, 1, 0));
-      s[7] += abs(A - diag_half(p, 1, 1));
+      s[0] = sad4(A, up4(X, R[1].w1), s[0]);
+      s[1] = sad4(A, up4(X, R[3].w1), s[1]);
+      s[2] = sad4(A, up4(col<-1>(R[2]), X), s[2]);
+      s[3] = sad4(A, up4(X, col<1>(R[2])), s[3]);
+      s[4] = sad4(A, diag_half<-1, -1>(R), s[4]);
+      s[5] = sad4(A, diag_half<-1, 0>(R), s[5]);
+      s[6] = sad4(A, diag_half<0, -1>(R), s[6]);
+      s[7] = sad4(A, diag_half<0, 0>(R), s[7]);
     } else {
       // fastquarter (enc/encode_block.c:609-738): a = here, b = up, c = up-right, d = right, e = down-right,
       // f = down, g = down-left, hh = left; four formula sets chosen by the incoming half-pel offset
-      const int a = p[0], b = p[-CPITCH], c2 = p[-CPITCH + 1], d = p[1], e = p[CPITCH + 1], f = p[CPITCH], g = p[CPITCH - 1], hh = p[-1];
-      const int ad = avg_up(a, d), de = avg_up(d, e), af = avg_up(a, f), fe = avg_up(f, e), dc = avg_up(d, c2), ab = avg_up(a, b),
-                ah = avg_up(a, hh), gf = avg_up(g, f);
-      int v[8];   // tl top tr left right bl down br
-      if (sel == 0)      { v[0]=avg_dn(ad,af); v[1]=avg_dn(de,a); v[2]=avg_dn(ad,de); v[3]=avg_dn(ad,f); v[4]=avg_dn(ad,e); v[5]=avg_dn(af,fe); v[6]=avg_dn(de,f); v[7]=avg_dn(de,fe); }
-      else if (sel == 1) { v[0]=avg_dn(ad,ab); v[1]=avg_dn(dc,a); v[2]=avg_dn(ad,dc); v[3]=avg_dn(ad,a); v[4]=avg_dn(ad,d); v[5]=avg_dn(ad,af); v[6]=avg_dn(af,d); v[7]=avg_dn(ad,de); }
-      else if (sel == 2) { v[0]=avg_dn(ah,af); v[1]=avg_dn(af,a); v[2]=avg_dn(ad,af); v[3]=avg_dn(gf,a); v[4]=avg_dn(ad,f); v[5]=avg_dn(af,gf); v[6]=avg_dn(af,f); v[7]=avg_dn(af,fe); }
-      else               { v[0]=avg_dn(ah,ab); v[1]=avg_dn(ab,a); v[2]=avg_dn(ad,ab); v[3]=avg_dn(ah,a); v[4]=avg_dn(ad,a); v[5]=avg_dn(ah,af); v[6]=avg_dn(af,a); v[7]=avg_dn(af,ad); }
+      const Row3 Ru = load_row(p0 - CPW), R0 = load_row(p0), Rd = load_row(p0 + CPW);
+      const uint32_t a = R0.w1, b = Ru.w1, c2 = col<1>(Ru), d = col<1>(R0), e = col<1>(Rd), f = Rd.w1, g = col<-1>(Rd), hh = col<-1>(R0);
+      const uint32_t ad = up4(a, d), de = up4(d, e), af = up4(a, f), fe = up4(f, e), dc = up4(d, c2), ab = up4(a, b),
+                     ah = up4(a, hh), gf = up4(g, f);
+      uint32_t v[8];   // tl top tr left right bl down br
+      if (sel == 0)      { v[0]=dn4(ad,af); v[1]=dn4(de,a); v[2]=dn4(ad,de); v[3]=dn4(ad,f); v[4]=dn4(ad,e); v[5]=dn4(af,fe); v[6]=dn4(de,f); v[7]=dn4(de,fe); }
+      else if (sel == 1) { v[0]=dn4(ad,ab); v[1]=dn4(dc,a); v[2]=dn4(ad,dc); v[3]=dn4(ad,a); v[4]=dn4(ad,d); v[5]=dn4(ad,af); v[6]=dn4(af,d); v[7]=dn4(ad,de); }
+      else if (sel == 2) { v[0]=dn4(ah,af); v[1]=dn4(af,a); v[2]=dn4(ad,af); v[3]=dn4(gf,a); v[4]=dn4(ad,f); v[5]=dn4(af,gf); v[6]=dn4(af,f); v[7]=dn4(af,fe); }
+      else               { v[0]=dn4(ah,ab); v[1]=dn4(ab,a); v[2]=dn4(ad,ab); v[3]=dn4(ah,a); v[4]=dn4(ad,a); v[5]=dn4(ah,af); v[6]=dn4(af,a); v[7]=dn4(af,ad); }
 #pragma unroll
-      for (int k = 0; k < 8; k++) s[k] += abs(A - v[k]);
+      for (int k = 0; k < 8; k++) s[k] = sad4(A, v[k], s[k]);
     }
   }
   const int nsum = (kind == THORCUDA_COST_SAD || kind == THORCUDA_COST_SSD) ? 1 : (kind == THORCUDA_COST_WIDESAD ? 5 : 8);
