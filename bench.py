@@ -188,6 +188,17 @@ def workload_config(args, streams):
             "parallelism": "independent streams, one process per GPU, no collective"}
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed `ncu --set full`
+# capture of this very command line (profiles/); only quoted when the workload is the one that was captured.
+NCU_TRAFFIC = {("sad_table", 1920, 1080, 16, 16): {"bytes": 140921088 + 2917634000, "source": "profiles/r1_ncu_sad_table_final.txt",
+                                                  "alu_pipe_pct": 79.0}}
+
+
+def ncu_traffic(kernel, job, B):
+    t = NCU_TRAFFIC.get((kernel, job["width"], job["height"], job["range"], B))
+    return t["bytes"] if t else None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -345,7 +356,6 @@ def run_gpu_arm(args, rank, world, local_rank):
     lib.thorcuda_timer_end(tid)
     ms = lib.thorcuda_timer_elapsed_ms(tid)
     launches = tb.launch_count() - launches0
-    clocks = sampler.stop()
     if dist is not None:
         import torch
         t = torch.tensor([ms], device="cuda")
@@ -362,6 +372,7 @@ def run_gpu_arm(args, rank, world, local_rank):
             f()
         lib.thorcuda_timer_end(tid)
         stage_ms[name] = lib.thorcuda_timer_elapsed_ms(tid) / args.steps
+    clocks = sampler.stop()          # sampled over the timed steps and the per-stage timed passes (all under load)
 
     # ---- e2e: host buffers in, host buffers out, every step ----
     e2e = measure_e2e(args, tb, lib, streams[:min(B, args.e2e_streams)], barrier, dist, world)
@@ -386,7 +397,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                 "e2e": e2e,
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                             "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                             "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": ncu_traffic(dom, jobs[0], B),
                              "launch_ms": round(stage_ms[dom] / n_launch, 4), "algorithmic_bytes_per_launch": int(B * ab[dom] / n_launch)},
                 "stages": per_stage}
         if world == 1 and not args.no_cpu:
@@ -545,7 +556,7 @@ def cpu_baseline_and_parity(args, tb, stream):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="thorcuda", choices=["thorcuda", "reference"])
     ap.add_argument("--streams", type=int, default=16, help="independent 1080p streams per GPU = frames per step")

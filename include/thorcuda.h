@@ -173,6 +173,29 @@ int thorcuda_reconstruct_blocks(const thorcuda_pic *pics, int npics, const thorc
                                 const int16_t *host_coeffq);
 size_t thorcuda_list_pool_entries(thorcuda_list l);   /* int16 entries of a TB list's pool            */
 
+/* ------------------------------------------------------------ early-skip test ---- */
+/* Significance test of a skip candidate (check_early_skip_block, enc/encode_block.c:2612-2741) for one
+ * size x size luma sub-block (size = min(block size, 16): 16 or 8) and its two chroma sub-blocks, given the
+ * candidate's prediction already formed in picture `pred` (thorcuda_predict_*):
+ *   luma   (check_early_skip_sub_block  :2507-2543): residual -> 2x2 mean (sum+2)>>2 -> transform(size/2, fast=0)
+ *          -> any |coefficient| > thr_y
+ *   chroma (check_early_skip_sub_blockC :2545-2610): column sums of the residual (8 wide: each column, compared as
+ *          int16 like the reference's SIMD; 4 wide: pairs of columns) > thr_c -- positive excursions only.
+ * The thresholds are the reference's only floating-point step; thorcuda_early_skip_thresholds() evaluates them
+ * on the HOST in double exactly as the reference does ((int)(rel * (double)(1<<shift2)/(double)scale)), with
+ * rel = 0.5*early_skip_thr for luma, early_skip_thr for chroma at qp chroma_qp[qp_y] and log2 size fixed to 5.
+ * flags[i]: bit0 luma significant, bit1 U, bit2 V (the block is skippable iff all sub-blocks return 0).       */
+typedef struct {
+  uint16_t x, y;            /* luma position of the sub-block                                        */
+  uint8_t  size;            /* 8 or 16                                                               */
+  uint8_t  org, pred;       /* indices into pics[]                                                   */
+  uint8_t  reserved;
+  int32_t  thr_y, thr_c;
+} thorcuda_skip_task;       /* 16 bytes */
+void thorcuda_early_skip_thresholds(int qp_y, int size, float early_skip_thr, int *thr_y, int *thr_c);
+int  thorcuda_early_skip_batch(const thorcuda_pic *pics, int npics, const thorcuda_skip_task *tasks, int ntasks,
+                               uint8_t *host_flags);
+
 /* -------------------------------------------------------------- motion search ---- */
 /* Whole-frame integer-pel cost tables (north_star: "whole-frame per-block cost table").
  * For every block of `org` of size bs in {8,16,32,64} on the bs-aligned grid (blocks that do not

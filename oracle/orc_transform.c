@@ -171,3 +171,60 @@ void orc_reconstruct_block(const int16_t *block, const uint8_t *pblock, uint8_t 
   for (int r = 0; r < size; r++)
     for (int c = 0; c < size; c++) rec[r * stride + c] = (uint8_t)clampi(block[r * size + c] + pblock[r * size + c], 0, 255);
 }
+
+/* ---- early-skip significance test (reference enc/encode_block.c:2481-2610) ---- */
+
+/* check_early_skip_transform_coeff :2481-2505 -- the threshold is the only floating-point step (double) */
+int orc_early_skip_threshold(int qp, int size, double relative_threshold) {
+  static const uint16_t QSCALE[6] = { 26214, 23302, 20560, 18396, 16384, 14564 };
+  const int shift2 = 21 - ilog2(size) + qp / 6;
+  const double first_quantizer_level = (double)(1 << shift2) / (double)QSCALE[qp % 6];
+  return (int)(relative_threshold * first_quantizer_level);
+}
+
+/* check_early_skip_sub_block :2507-2543: residual -> 2x2 mean -> (N/2)-point transform -> any |coef| > threshold */
+int orc_early_skip_luma(const uint8_t *orig, int orig_stride, int size, int qp, const uint8_t *pblock, float early_skip_threshold) {
+  int16_t block[16 * 16], tmp[8 * 8], coeff[16 * 16];
+  orc_get_residual(block, pblock, orig, size, orig_stride);
+  int n = size, thr;
+  if (size > 4) {
+    n = size / 2;
+    for (int i = 0; i < n; i++)
+      for (int j = 0; j < n; j++)
+        tmp[i * n + j] = (int16_t)((block[(2 * i) * size + 2 * j] + block[(2 * i) * size + 2 * j + 1] + block[(2 * i + 1) * size + 2 * j] +
+                                    block[(2 * i + 1) * size + 2 * j + 1] + 2) >> 2);
+    orc_transform(tmp, coeff, n, 0);
+    thr = orc_early_skip_threshold(qp, n, 0.5 * early_skip_threshold);
+  } else {
+    orc_transform(block, coeff, n, 0);
+    thr = orc_early_skip_threshold(qp, n, early_skip_threshold);
+  }
+  for (int i = 0; i < n * n; i++)
+    if (abs(coeff[i]) > thr) return 1;
+  return 0;
+}
+
+/* check_early_skip_sub_blockC :2545-2610: column sums of the residual (8 wide: every column; 4 wide: pairs of
+ * columns) against a threshold derived with a FIXED log2 size of 5; only positive excursions count */
+int orc_early_skip_chroma(const uint8_t *orig, int orig_stride, int size, int qp, const uint8_t *pblock, float early_skip_threshold) {
+  static const uint16_t QSCALE[6] = { 26214, 23302, 20560, 18396, 16384, 14564 };
+  const int shift2 = 21 - 5 + qp / 6;
+  const double first_quantizer_level = (double)(1 << shift2) / (double)QSCALE[qp % 6];
+  const int threshold = (int)(early_skip_threshold * first_quantizer_level);
+  int16_t block[8 * 8];
+  orc_get_residual(block, pblock, orig, size, orig_stride);
+  if (size == 8) {
+    for (int j = 0; j < 8; j++) {
+      int sum = 0;
+      for (int i = 0; i < 8; i++) sum += block[i * 8 + j];
+      if ((int16_t)sum > (int16_t)threshold) return 1;      /* v128_cmpgt_s16 against v128_dup_16(threshold) */
+    }
+    return 0;
+  }
+  for (int j = 0; j < 4; j += 2) {
+    int sum = 0;
+    for (int i = 0; i < 4; i++) sum += block[i * 4 + j] + block[i * 4 + j + 1];
+    if (sum > threshold) return 1;
+  }
+  return 0;
+}

@@ -64,6 +64,11 @@ void orc_dequantize(const int16_t *coeff, int16_t *rcoeff, int qp, int size);
 void orc_get_residual(int16_t *block, const uint8_t *pblock, const uint8_t *orig, int size, int orig_stride);
 void orc_reconstruct_block(const int16_t *block, const uint8_t *pblock, uint8_t *rec, int size, int stride);
 
+/* ---- early-skip significance test (enc/encode_block.c:2481-2610) ---- */
+int orc_early_skip_threshold(int qp, int size, double relative_threshold);
+int orc_early_skip_luma(const uint8_t *orig, int orig_stride, int size, int qp, const uint8_t *pblock, float early_skip_threshold);
+int orc_early_skip_chroma(const uint8_t *orig, int orig_stride, int size, int qp, const uint8_t *pblock, float early_skip_threshold);
+
 /* ---- motion-search costs (enc/encode_block.c:497-828) ---- */
 unsigned orc_sad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h);
 unsigned orc_widesad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h, int *x);

@@ -519,3 +519,44 @@ def test_resident_list_reuse(tb, orc):
     lst.close()
     dorg.close()
     dref.close()
+
+
+# ------------------------------------------------------------------- early-skip test (a19) ----
+@pytest.mark.parametrize("wh,qp,thr,noise", [((256, 192), 32, 1.0, 3), ((416, 240), 24, 0.8, 2), ((1920, 1080), 37, 1.3, 6)])
+def test_early_skip_batch(tb, orc, wh, qp, thr, noise):
+    """check_early_skip_sub_block / _sub_blockC (enc/encode_block.c:2507-2610) for every 16x16 and 8x8 sub-block
+    of a frame; thresholds from the library's host helper against the oracle's (the reference's double arithmetic)."""
+    from thor_b200.lib import SKIP_TASK
+    from thor_b200.ops import early_skip_batch, early_skip_thresholds
+    w, h = wh
+    opl, ppl, org, pred = tb_pictures(tb, w, h, 90 + qp, noise=noise)
+    orc.orc_early_skip_threshold.argtypes = [C.c_int, C.c_int, C.c_double]
+    for f in (orc.orc_early_skip_luma, orc.orc_early_skip_chroma):
+        f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float]
+    thr32 = float(np.float32(thr))
+    tasks = []
+    for size in (16, 8):
+        ty, tc = early_skip_thresholds(qp, size, thr32)
+        assert ty == orc.orc_early_skip_threshold(qp, size // 2, 0.5 * thr32)
+        for y in range(0, h - size + 1, size):
+            for x in range(0, w - size + 1, size):
+                tasks.append((x, y, size, 0, 1, 0, ty, tc))
+    if w * h > 500000:                                     # oracle loop in Python: bound the big frame
+        sel = np.random.default_rng(1).choice(len(tasks), 6000, replace=False)
+        tasks = [tasks[i] for i in sorted(sel)]
+    t = np.array(tasks, SKIP_TASK)
+    got = early_skip_batch([org, pred], t)
+    qpc = orc.orc_chroma_qp(qp)
+    want = np.zeros(len(tasks), np.uint8)
+    for i, (x, y, size, *_r) in enumerate(tasks):
+        pb = np.ascontiguousarray(ppl[0][y:y + size, x:x + size])
+        f = orc.orc_early_skip_luma(ptr(opl[0][y:, x:]), opl[0].strides[0], size, qp, ptr(pb), thr32)
+        cs, cx, cy = size // 2, x // 2, y // 2
+        for pl in (1, 2):
+            pc = np.ascontiguousarray(ppl[pl][cy:cy + cs, cx:cx + cs])
+            f |= orc.orc_early_skip_chroma(ptr(opl[pl][cy:, cx:]), opl[pl].strides[0], cs, qpc, ptr(pc), thr32) << pl
+        want[i] = f
+    assert np.array_equal(got, want)
+    for bit in (1, 2, 4):                                    # both outcomes occur for every plane
+        assert 0 < np.count_nonzero(want & bit) < len(want)
+    org.close(); pred.close()

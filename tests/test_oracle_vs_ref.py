@@ -334,3 +334,31 @@ def test_block_avg(simd):
         ref.block_avg_simd(ptr(pa), ptr(a), ptr(b), 16, 16, 16, n, n)
         orc.orc_block_avg(ptr(pb), ptr(a), ptr(b), 16, 16, 16, n, n)
         assert np.array_equal(pa[:, :n], pb[:, :n])
+
+
+def test_early_skip(simd):
+    """a19: check_early_skip_sub_block / _sub_blockC (enc/encode_block.c:2507-2610), both outcomes exercised."""
+    rng = np.random.default_rng(77)
+    for f in (ref.check_early_skip_sub_block, ref.check_early_skip_sub_blockC):
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float]
+    for f in (orc.orc_early_skip_luma, orc.orc_early_skip_chroma):
+        f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float]
+    seen = set()
+    for trial in range(400):
+        chroma = trial & 1
+        size = int(rng.choice([4, 8])) if chroma else int(rng.choice([8, 16]))
+        qp = int(rng.integers(18, 46))
+        thr = float(rng.choice([0.3, 0.8, 1.0, 1.3]))
+        orig = rng.integers(0, 256, (size, 64), dtype=np.uint8)
+        amp = int(rng.choice([1, 2, 4, 8, 16]))
+        pb = _aligned((size, size))
+        pb[...] = np.clip(orig[:, :size].astype(int) + rng.integers(-amp, amp + 1, (size, size)) + int(rng.integers(-amp, amp + 1)), 0, 255)
+        if chroma:
+            a = ref.check_early_skip_sub_blockC(None, ptr(orig), 64, size, qp, ptr(pb), thr)
+            b = orc.orc_early_skip_chroma(ptr(orig), 64, size, qp, ptr(pb), thr)
+        else:
+            a = ref.check_early_skip_sub_block(None, ptr(orig), 64, size, qp, ptr(pb), thr)
+            b = orc.orc_early_skip_luma(ptr(orig), 64, size, qp, ptr(pb), thr)
+        assert a == b, (chroma, size, qp, thr, amp)
+        seen.add((chroma, a))
+    assert seen == {(0, 0), (0, 1), (1, 0), (1, 1)}, "both outcomes must occur for luma and chroma"

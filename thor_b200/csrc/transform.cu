@@ -486,6 +486,70 @@ int tb_raw(int size, int fast, int inverse, const int16_t *d_in, int16_t *d_out)
   return 0;
 }
 
+// ---- early-skip significance test (enc/encode_block.c:2507-2610): one warp per sub-block ----
+struct SkipParams {
+  PicView pics[8];                     // the batch's pictures (by value: no resident list needed)
+  const thorcuda_skip_task *tasks;
+  uint8_t *flags;
+  int ntasks;
+};
+
+template <int n>   // n = size / 2: length of the transform applied to the 2x2-averaged residual
+__device__ __forceinline__ bool skip_luma(const PicView &vo, const PicView &vp, const thorcuda_skip_task &t, int16_t *S, const int8_t *sFw, int lane) {
+  using L = TbLayout<8>;
+  constexpr int PI = L::PI, PQ = L::PQ, LG = n == 4 ? 2 : 3;
+  int16_t *in = S + L::in_off, *mid = S + L::mid_off, *coef = S + L::coef_off;
+  const uint8_t *org = vo.p[0] + (size_t)t.y * vo.stride[0] + t.x, *pred = vp.p[0] + (size_t)t.y * vp.stride[0] + t.x;
+  for (int i = lane; i < n * n; i += 32) {
+    const int r = i / n, c = i - r * n;
+    int s = 2;
+#pragma unroll
+    for (int a = 0; a < 2; a++) {
+      const uint8_t *po = org + (size_t)(2 * r + a) * vo.stride[0] + 2 * c, *pp = pred + (size_t)(2 * r + a) * vp.stride[0] + 2 * c;
+      s += (int)po[0] + (int)po[1] - (int)pp[0] - (int)pp[1];
+    }
+    in[r * PI + c] = (int16_t)(s >> 2);
+  }
+  __syncwarp();
+  fwd_passes<32, n, PI, PQ>(in, mid, coef, sFw, LG, LG + 5, lane);
+  bool sig = false;
+  for (int i = lane; i < n * n; i += 32) sig |= abs((int)coef[(i / n) * PQ + (i % n)]) > t.thr_y;
+  return __any_sync(0xffffffffu, sig);
+}
+
+__device__ __forceinline__ bool skip_chroma(const PicView &vo, const PicView &vp, const thorcuda_skip_task &t, int pl, int lane) {
+  const int cs = t.size >> 1, cx = t.x >> 1, cy = t.y >> 1;
+  const uint8_t *org = vo.p[pl] + (size_t)cy * vo.stride[pl] + cx, *pred = vp.p[pl] + (size_t)cy * vp.stride[pl] + cx;
+  bool sig = false;
+  if (lane < cs) {
+    int sum = 0;
+    for (int i = 0; i < cs; i++) sum += (int)org[(size_t)i * vo.stride[pl] + lane] - (int)pred[(size_t)i * vp.stride[pl] + lane];
+    if (cs == 8) {
+      sig = (int16_t)sum > (int16_t)t.thr_c;            // v128_cmpgt_s16 against v128_dup_16(threshold)
+    } else {
+      sum += __shfl_xor_sync(0x0000000fu, sum, 1);     // pairs of columns
+      sig = sum > t.thr_c;
+    }
+  }
+  return __any_sync(0xffffffffu, sig);
+}
+
+__global__ void __launch_bounds__(TW * 32) k_skip_test(const SkipParams P) {
+  __shared__ __align__(16) int8_t sFw[FW_BYTES];
+  __shared__ __align__(16) int16_t sScratch[TW * TbLayout<8>::total];
+  for (int i = threadIdx.x; i < FW_BYTES / 4; i += TW * 32) reinterpret_cast<uint32_t *>(sFw)[i] = reinterpret_cast<const uint32_t *>(c_fw)[i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ti = blockIdx.x * TW + warp;
+  if (ti >= P.ntasks) return;
+  const thorcuda_skip_task t = P.tasks[ti];
+  const PicView &vo = P.pics[t.org], &vp = P.pics[t.pred];
+  int16_t *S = sScratch + warp * TbLayout<8>::total;
+  const bool y = t.size == 16 ? skip_luma<8>(vo, vp, t, S, sFw, lane) : skip_luma<4>(vo, vp, t, S, sFw, lane);
+  const bool u = skip_chroma(vo, vp, t, 1, lane), v = skip_chroma(vo, vp, t, 2, lane);
+  if (lane == 0) P.flags[ti] = (uint8_t)((y ? 1 : 0) | (u ? 2 : 0) | (v ? 4 : 0));
+}
+
 static int run_tb(List *L, int decode, bool want_ssd) {
   Context &c = ctx();
   if (upload_tables()) return -1;
@@ -535,6 +599,52 @@ int thorcuda_reconstruct_list(thorcuda_list hl, const int16_t *host_coeffq) {
   if (!L || L->kind != THORCUDA_LIST_TB) return fail("reconstruct: not a transform-block list");
   if (host_coeffq && h2d(L->pool, host_coeffq, L->pool_entries * sizeof(int16_t))) return -1;
   return run_tb(L, 1, false);
+}
+
+void thorcuda_early_skip_thresholds(int qp_y, int size, float early_skip_thr, int *thr_y, int *thr_c) {
+  static const int scale[6] = {26214, 23302, 20560, 18396, 16384, 14564};     // gquant_table, common/common_block.c:97
+  const int n = size > 4 ? size / 2 : size;                                    // transform length after the 2x2 mean
+  const int lg = n == 4 ? 2 : n == 8 ? 3 : n == 16 ? 4 : 5;
+  // check_early_skip_sub_block passes 0.5*early_skip_threshold (double) for size > 4 (enc/encode_block.c:2533)
+  const double rel = size > 4 ? 0.5 * early_skip_thr : (double)early_skip_thr;
+  const double fql_y = (double)(1 << (21 - lg + qp_y / 6)) / (double)scale[qp_y % 6];
+  *thr_y = (int)(rel * fql_y);
+  const int qpc = h_chroma_qp[qp_y < 0 ? 0 : qp_y > 51 ? 51 : qp_y];
+  const double fql_c = (double)(1 << (21 - 5 + qpc / 6)) / (double)scale[qpc % 6];
+  *thr_c = (int)(early_skip_thr * fql_c);
+}
+
+int thorcuda_early_skip_batch(const thorcuda_pic *pics, int npics, const thorcuda_skip_task *tasks, int ntasks, uint8_t *host_flags) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (ntasks <= 0) return 0;
+  if (npics <= 0 || npics > 8) return fail("early_skip: npics %d out of range (1..8)", npics);
+  if (upload_tables()) return -1;
+  SkipParams P;
+  memset(&P, 0, sizeof(P));
+  for (int i = 0; i < npics; i++) {
+    Pic *p = get_pic(pics[i]);
+    if (!p) return fail("early_skip: bad picture handle %d", pics[i]);
+    P.pics[i] = p->view();
+  }
+  for (int i = 0; i < ntasks; i++) {
+    const thorcuda_skip_task &t = tasks[i];
+    if (t.org >= npics || t.pred >= npics) return fail("early_skip: task %d names a picture outside pics[%d]", i, npics);
+    const Pic *o = get_pic(pics[t.org]), *p = get_pic(pics[t.pred]);
+    if ((t.size != 8 && t.size != 16) || (t.x & 3) || (t.y & 3) || t.x + t.size > o->w || t.y + t.size > o->h || o->w != p->w || o->h != p->h)
+      return fail("early_skip: task %d has an invalid sub-block (%d,%d size %d)", i, t.x, t.y, t.size);
+  }
+  const size_t tbytes = (size_t)ntasks * sizeof(thorcuda_skip_task);
+  uint8_t *d = (uint8_t *)c.scratch.reserve(tbytes + ntasks + 64);
+  if (!d) return fail("early_skip: device allocation failed");
+  if (h2d(d, tasks, tbytes)) return -1;
+  P.tasks = (const thorcuda_skip_task *)d;
+  P.flags = d + tbytes;
+  P.ntasks = ntasks;
+  k_skip_test<<<(ntasks + TW - 1) / TW, TW * 32, 0, c.stream>>>(P);
+  THOR_LAUNCHED();
+  if (host_flags) return d2h(host_flags, P.flags, ntasks);
+  return 0;
 }
 
 int thorcuda_encode_blocks(const thorcuda_pic *pics, int npics, const thorcuda_tb_task *tasks, int ntasks,

@@ -20,6 +20,9 @@ TB_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("size", "u1"), ("plane", "u1"),
 COST_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("w", "u1"), ("h", "u1"), ("org", "u1"), ("ref", "u1"), ("hx", "i1"), ("hy", "i1"),
                       ("ix", "<i2"), ("iy", "<i2"), ("reserved", "<u2")])
 COST_RESULT = np.dtype([("cost", "<u4"), ("x", "<i2"), ("y", "<i2")])
+SKIP_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("size", "u1"), ("org", "u1"), ("pred", "u1"), ("reserved", "u1"),
+                      ("thr_y", "<i4"), ("thr_c", "<i4")])
+assert SKIP_TASK.itemsize == 16
 assert PRED_TASK.itemsize == 20 and TB_TASK.itemsize == 16 and COST_TASK.itemsize == 16 and COST_RESULT.itemsize == 8
 
 
@@ -64,6 +67,8 @@ def cdll():
                 ("thorcuda_reconstruct_list", I, [I, V]), ("thorcuda_reconstruct_blocks", I, [V, I, V, I, V]),
                 ("thorcuda_sad_table_build", I, [I, V, V, V, I, V]), ("thorcuda_sad_table_bytes", Z, [I, I]),
                 ("thorcuda_sad_table_fetch", I, [I, I, V, Z]), ("thorcuda_sad_table_devptr", V, [I, I]),
+                ("thorcuda_early_skip_thresholds", None, [I, I, C.c_float, V, V]),
+                ("thorcuda_early_skip_batch", I, [V, I, V, I, V]),
                 ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):
             fn = getattr(_lib, name)   # AttributeError here means a stale libthorcuda.so: rebuild
             fn.restype = res

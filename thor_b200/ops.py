@@ -10,6 +10,7 @@ executing on the B200 through libthorcuda (no CPU fallback).
                                        (common/inter_prediction.c:72-180, enc/encode_block.c:1534-1588)
   encode_blocks / reconstruct_blocks   encode_and_reconstruct_block_inter (enc/encode_block.c:1469-1532),
                                        decode_and_reconstruct_block_inter (dec/decode_block.c:90-120)
+  early_skip_thresholds / early_skip_batch  check_early_skip_sub_block(C) (enc/encode_block.c:2507-2610)
   sad_table / cost_batch               sad_calc, widesad_calc, sad_calc_fasthalf/fastquarter, ssd_calc
                                        (enc/encode_block.c:497-797)
 """
@@ -18,7 +19,7 @@ import ctypes as C
 import numpy as np
 
 from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, LIST_COST, LIST_PRED, LIST_TB, COST_RESULT, COST_TASK,
-                  PRED_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
+                  PRED_TASK, SKIP_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
 
 
 class LfJob(C.Structure):  # thorcuda_lf_job
@@ -162,6 +163,22 @@ def cost_batch(kind, pics, tasks):
     t = np.ascontiguousarray(tasks, COST_TASK)
     out = np.zeros(t.size, COST_RESULT)
     check(cdll().thorcuda_cost_batch(int(kind), _handles(pics), len(pics), _p(t), t.size, _p(out)))
+    sync()
+    return out
+
+
+def early_skip_thresholds(qp, size, early_skip_thr):
+    """(thr_y, thr_c) of check_early_skip_sub_block / _sub_blockC for a size x size luma sub-block at frame qp."""
+    ty, tc = C.c_int(), C.c_int()
+    cdll().thorcuda_early_skip_thresholds(int(qp), int(size), float(early_skip_thr), C.byref(ty), C.byref(tc))
+    return ty.value, tc.value
+
+
+def early_skip_batch(pics, tasks):
+    """Significance flags (bit0 Y, bit1 U, bit2 V) of each sub-block; 0 = the skip candidate stands."""
+    t = np.ascontiguousarray(tasks, SKIP_TASK)
+    out = np.zeros(t.size, np.uint8)
+    check(cdll().thorcuda_early_skip_batch(_handles(pics), len(pics), _p(t), t.size, _p(out)))
     sync()
     return out
 
