@@ -363,15 +363,21 @@ def run_gpu_arm(args, rank, world, local_rank):
         ms = float(t.item())
     value = B * world * args.steps / (ms / 1e3)
 
-    # per-stage device time (CUDA events on the library's stream), separate pass so the main loop is undisturbed
-    stage_ms = {}
-    for name, f in stages:
-        tb.sync()
-        tid = lib.thorcuda_timer_begin()
-        for _ in range(args.steps):
+    # per-stage device time (CUDA events on the library's stream), separate pass so the main loop is undisturbed;
+    # each stage is timed IN SITU, between its neighbours in full steps: a stage repeated back to back would see its own
+    # output as input (the transform stage would find an already reconstructed picture: all-zero residuals)
+    stage_ms = {name: 0.0 for name, _ in stages}
+    reps = max(1, min(args.steps, 50))
+    for _ in range(reps):
+        ids = []
+        for name, f in stages:
+            tid = lib.thorcuda_timer_begin()
             f()
-        lib.thorcuda_timer_end(tid)
-        stage_ms[name] = lib.thorcuda_timer_elapsed_ms(tid) / args.steps
+            lib.thorcuda_timer_end(tid)
+            ids.append((name, tid))
+        tb.sync()
+        for name, tid in ids:
+            stage_ms[name] += lib.thorcuda_timer_elapsed_ms(tid) / reps
     clocks = sampler.stop()          # sampled over the timed steps and the per-stage timed passes (all under load)
 
     # ---- e2e: host buffers in, host buffers out, every step ----

@@ -211,6 +211,16 @@ int  thorcuda_early_skip_batch(const thorcuda_pic *pics, int npics, const thorcu
  * Tables live in HBM in one of THORCUDA_SAD_SLOTS slots; fetch copies one level to the host.
  * n (org,ref) pairs are processed in ONE launch.                                                     */
 #define THORCUDA_SAD_SLOTS 64
+/* Host helpers for forming table indices (pure host code, usable before thorcuda_init):
+ *  thorcuda_clip_mv        = clip_mv (enc/encode_block.c:816-828): keeps the block within 80 px of the frame; the
+ *                            right-edge test omits "+ size" and "/ 4" truncates toward zero, exactly as there.
+ *                            mv[0] = x, mv[1] = y in quarter-pel (mv_t, common/types.h:105-109).
+ *  thorcuda_sad_table_index: entry index inside one level for the integer-pel probe that motion_estimate makes
+ *                            at mv (already clipped; the search walks ref + s*(mv>>2), s = sign ? -1 : 1), or -1 if
+ *                            the probe lies outside the block's window (then use thorcuda_cost_batch).          */
+void    thorcuda_clip_mv(int16_t mv[2], int ypos, int xpos, int fwidth, int fheight, int size, int sign);
+int64_t thorcuda_sad_table_index(int fwidth, int bs, int xpos, int ypos, const int16_t mv[2], int sign,
+                                 int centre_x, int centre_y, int range);
 int    thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, const thorcuda_pic *refs,
                                 int range, const int16_t *const *centres);
 size_t thorcuda_sad_table_bytes(int slot, int bs);

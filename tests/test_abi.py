@@ -53,20 +53,20 @@ def test_every_declared_symbol_is_exported(lib, header):
 def test_struct_sizes_match_header():
     """compile a C probe against the header and compare with the numpy mirrors in thor_b200/lib.py"""
     sys.path.insert(0, ROOT)
-    from thor_b200.lib import COST_RESULT, COST_TASK, PRED_TASK, TB_TASK
+    from thor_b200.lib import COST_RESULT, COST_TASK, PRED_TASK, SKIP_TASK, TB_TASK
     from thor_b200.ops import LfJob
     probe = r'''
 #include <stdio.h>
 #include "thorcuda.h"
 #include "thorcuda_compat.h"
-int main(void){printf("%zu %zu %zu %zu %zu\n",sizeof(thorcuda_pred_task),sizeof(thorcuda_tb_task),sizeof(thorcuda_cost_task),
-sizeof(thorcuda_cost_result),sizeof(thorcuda_lf_job));return 0;}
+int main(void){printf("%zu %zu %zu %zu %zu %zu\n",sizeof(thorcuda_pred_task),sizeof(thorcuda_tb_task),sizeof(thorcuda_cost_task),
+sizeof(thorcuda_cost_result),sizeof(thorcuda_lf_job),sizeof(thorcuda_skip_task));return 0;}
 '''
     exe = os.path.join(ROOT, "build", "abi_probe")
     os.makedirs(os.path.dirname(exe), exist_ok=True)
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", INC, "-x", "c", "-", "-o", exe], input=probe.encode(), check=True)
     out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout.split()
-    assert [int(x) for x in out] == [PRED_TASK.itemsize, TB_TASK.itemsize, COST_TASK.itemsize, COST_RESULT.itemsize, C.sizeof(LfJob)]
+    assert [int(x) for x in out] == [PRED_TASK.itemsize, TB_TASK.itemsize, COST_TASK.itemsize, COST_RESULT.itemsize, C.sizeof(LfJob), SKIP_TASK.itemsize]
 
 
 def test_no_cpu_fallback_without_gpu(lib):
@@ -96,3 +96,46 @@ def test_product_does_not_reference_the_oracle():
                     if re.search(r"oracle/|thor_oracle|libthorref|libthorpipe", txt):
                         bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def test_host_helpers_against_oracle(lib):
+    """a20 and a19's floating-point step are pure host code in the library: clip_mv, the table index of a probe and
+    the early-skip thresholds, checked against the oracle (itself pinned to the reference in test_oracle_vs_ref)."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from thorref import load_oracle
+    sys.path.insert(0, ROOT)
+    from thor_b200.ops import clip_mv, early_skip_thresholds, sad_table_index
+    orc = load_oracle()
+    orc.orc_early_skip_threshold.argtypes = [C.c_int, C.c_int, C.c_double]
+    rng = np.random.default_rng(3)
+    hit = 0
+    for _ in range(3000):
+        fw, fh = (416, 240) if rng.random() < 0.5 else (1920, 1080)
+        size = int(rng.choice([8, 16, 32, 64]))
+        ypos, xpos = int(rng.integers(0, fh // size)) * size, int(rng.integers(0, fw // size)) * size
+        sign = int(rng.integers(0, 2))
+        scale = 8 if rng.random() < 0.3 else 1
+        mx, my = int(rng.integers(-900, 900)) * scale, int(rng.integers(-900, 900)) * scale
+        ax, ay = C.c_int16(mx), C.c_int16(my)
+        orc.orc_clip_mv(C.byref(ax), C.byref(ay), ypos, xpos, fw, fh, size, sign)
+        assert clip_mv((mx, my), ypos, xpos, fw, fh, size, sign) == (ax.value, ay.value)
+        # table index: the probe address the reference forms is ref + s*(mv.y>>2)*stride + s*(mv.x>>2)
+        mv = (int(rng.integers(-90, 90)), int(rng.integers(-90, 90)))
+        c = (int(rng.integers(-4, 5)), int(rng.integers(-4, 5)))
+        s = -1 if sign else 1
+        dx, dy = s * (mv[0] >> 2) - c[0], s * (mv[1] >> 2) - c[1]
+        want = -1
+        if -16 <= dx < 16 and -16 <= dy < 16 and xpos + size <= fw:
+            want = (((ypos // size) * (fw // size) + xpos // size) * 32 + dy + 16) * 32 + dx + 16
+            hit += 1
+        assert sad_table_index(fw, size, xpos, ypos, mv, sign, c, 16) == want
+    assert hit > 500
+    for qp in range(0, 52):
+        for size in (8, 16):
+            for thr in (0.3, 0.8, 1.0, float(np.float32(1.3) * np.float32(0.8))):
+                t32 = float(np.float32(thr))
+                ty, tc = early_skip_thresholds(qp, size, t32)
+                assert ty == orc.orc_early_skip_threshold(qp, size // 2, 0.5 * t32)
+                qpc = orc.orc_chroma_qp(qp)
+                assert tc == int(t32 * (float(1 << (16 + qpc // 6)) / [26214, 23302, 20560, 18396, 16384, 14564][qpc % 6]))

@@ -530,6 +530,12 @@ def test_early_skip_batch(tb, orc, wh, qp, thr, noise):
     from thor_b200.ops import early_skip_batch, early_skip_thresholds
     w, h = wh
     opl, ppl, org, pred = tb_pictures(tb, w, h, 90 + qp, noise=noise)
+    rng = np.random.default_rng(qp)
+    for i, p in enumerate(ppl):            # region-wise DC errors so that the (one-sided) chroma test fires in places
+        gy, gx = (p.shape[0] + 15) // 16, (p.shape[1] + 15) // 16
+        dc = np.kron(rng.integers(-3 * noise, 3 * noise + 1, (gy, gx)) * (rng.random((gy, gx)) < 0.3), np.ones((16, 16), int))
+        ppl[i] = np.clip(p.astype(int) + dc[:p.shape[0], :p.shape[1]], 0, 255).astype(np.uint8)
+    pred.upload(*ppl)
     orc.orc_early_skip_threshold.argtypes = [C.c_int, C.c_int, C.c_double]
     for f in (orc.orc_early_skip_luma, orc.orc_early_skip_chroma):
         f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float]

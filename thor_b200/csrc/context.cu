@@ -162,6 +162,29 @@ int thorcuda_init(int device) {
   return 0;
 }
 
+// ---- host helpers for table indexing (no device work) ----
+void thorcuda_clip_mv(int16_t mv[2], int ypos, int xpos, int fwidth, int fheight, int size, int sign) {
+  const int reach = 80;                        // PADDING_Y - 16 full pixels beyond each frame edge
+  const int s = sign ? -1 : 1;
+  int v[2] = {s * mv[0], s * mv[1]};           // x, y as the search applies them
+  // the four tests run in the reference's order on the running value; C division truncates toward zero
+  if (ypos + v[1] / 4 < -reach) v[1] = 4 * (-reach - ypos);
+  if (ypos + v[1] / 4 + size > fheight + reach) v[1] = 4 * (fheight + reach - ypos - size);
+  if (xpos + v[0] / 4 < -reach) v[0] = 4 * (-reach - xpos);
+  if (xpos + v[0] / 4 > fwidth + reach) v[0] = 4 * (fwidth + reach - xpos - size);      // sic: the test has no "+ size"
+  mv[0] = (int16_t)(s * v[0]);
+  mv[1] = (int16_t)(s * v[1]);
+}
+
+int64_t thorcuda_sad_table_index(int fwidth, int bs, int xpos, int ypos, const int16_t mv[2], int sign, int centre_x, int centre_y, int range) {
+  if (bs <= 0 || (xpos % bs) || (ypos % bs) || xpos + bs > fwidth) return -1;
+  const int s = sign ? -1 : 1;
+  const int dx = s * (mv[0] >> 2) - centre_x, dy = s * (mv[1] >> 2) - centre_y;   // the search reads ref + s*(mv.y>>2)*stride + s*(mv.x>>2)
+  if (dx < -range || dx >= range || dy < -range || dy >= range) return -1;
+  const int64_t block = (int64_t)(ypos / bs) * (fwidth / bs) + xpos / bs;
+  return (block * 2 * range + (dy + range)) * 2 * range + (dx + range);
+}
+
 void thorcuda_shutdown(void) {
   Context &c = ctx();
   if (!c.ready) return;

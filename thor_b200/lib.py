@@ -67,6 +67,8 @@ def cdll():
                 ("thorcuda_reconstruct_list", I, [I, V]), ("thorcuda_reconstruct_blocks", I, [V, I, V, I, V]),
                 ("thorcuda_sad_table_build", I, [I, V, V, V, I, V]), ("thorcuda_sad_table_bytes", Z, [I, I]),
                 ("thorcuda_sad_table_fetch", I, [I, I, V, Z]), ("thorcuda_sad_table_devptr", V, [I, I]),
+                ("thorcuda_clip_mv", None, [V, I, I, I, I, I, I]),
+                ("thorcuda_sad_table_index", C.c_int64, [I, I, I, I, V, I, I, I, I]),
                 ("thorcuda_early_skip_thresholds", None, [I, I, C.c_float, V, V]),
                 ("thorcuda_early_skip_batch", I, [V, I, V, I, V]),
                 ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):

@@ -167,6 +167,19 @@ def cost_batch(kind, pics, tasks):
     return out
 
 
+def clip_mv(mv, ypos, xpos, fwidth, fheight, size, sign):
+    """clip_mv (enc/encode_block.c:816-828) on (x, y) quarter-pel; returns the clipped (x, y).  Host only."""
+    m = (C.c_int16 * 2)(int(mv[0]), int(mv[1]))
+    cdll().thorcuda_clip_mv(m, ypos, xpos, fwidth, fheight, size, int(sign))
+    return m[0], m[1]
+
+
+def sad_table_index(fwidth, bs, xpos, ypos, mv, sign=0, centre=(0, 0), search_range=16):
+    """Index of motion_estimate's integer-pel probe at mv inside one table level, or -1 (outside the window)."""
+    m = (C.c_int16 * 2)(int(mv[0]), int(mv[1]))
+    return int(cdll().thorcuda_sad_table_index(fwidth, bs, xpos, ypos, m, int(sign), int(centre[0]), int(centre[1]), search_range))
+
+
 def early_skip_thresholds(qp, size, early_skip_thr):
     """(thr_y, thr_c) of check_early_skip_sub_block / _sub_blockC for a size x size luma sub-block at frame qp."""
     ty, tc = C.c_int(), C.c_int()
