@@ -45,7 +45,7 @@ struct Pic {
 // A resident task list (thorcuda_list_create).
 struct List {
   bool used = false;
-  int kind = -1, ntasks = 0, npics = 0, ntiles = 0;
+  int kind = -1, ntasks = 0, npics = 0, ntiles = 0, nbig = 0;
   std::vector<int> pics;                  // handles
   uint8_t *blob = nullptr;                // one device allocation: tasks | tiles | map
   size_t off_tiles = 0, off_map = 0, blob_bytes = 0;

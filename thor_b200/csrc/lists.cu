@@ -134,7 +134,10 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
   if (kind == THORCUDA_LIST_PRED) {
     if (check_pred(P, pics, npics, (const thorcuda_pred_task *)tasks, ntasks, tiles)) return -1;
     task_size = sizeof(thorcuda_pred_task);
+    // tiles larger than 8x8 (one warp each) first, then the small ones (four to a warp); stable: neighbours stay together
+    std::stable_partition(tiles.begin(), tiles.end(), [](const PredTile &q) { return q.tw > 8 || q.th > 8; });
     L.ntiles = (int)tiles.size();
+    L.nbig = (int)std::count_if(tiles.begin(), tiles.end(), [](const PredTile &q) { return q.tw > 8 || q.th > 8; });
     second = tiles.data(); second_bytes = tiles.size() * sizeof(PredTile);
   } else if (kind == THORCUDA_LIST_TB) {
     if (check_tb(P, npics, (const thorcuda_tb_task *)tasks, ntasks, L, order)) return -1;

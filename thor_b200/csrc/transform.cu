@@ -193,14 +193,13 @@ __device__ __forceinline__ unsigned group_ballot(bool pred, int gbase) {
 // One transform block of size class N, processed by the G lanes gl = 0..G-1 of a group (all groups of a warp run
 // this in lock step; `valid` only gates the global stores).  S: the unit's scratch (TbLayout<N>).
 template <int N>
-__device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, bool valid, int16_t *S, const int8_t *sFw, const int8_t *sIv,
-                                        const uint8_t *sZ, int gl, int gbase) {
+__device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, const thorcuda_tb_task &t, bool valid, int16_t *S, const int8_t *sFw,
+                                        const int8_t *sIv, const uint8_t *sZ, int gl, int gbase) {
   using L = TbLayout<N>;
   constexpr int G = L::G, NI = L::NI, Q = L::Q, PI = L::PI, PQ = L::PQ;
   constexpr int LG = N == 4 ? 2 : N == 8 ? 3 : N == 16 ? 4 : N == 32 ? 5 : 6;
   int16_t *in = S + L::in_off, *mid = S + L::mid_off, *coef = S + L::coef_off, *lin = S + L::lin_off, *lev = S + L::lev_off;
-  const thorcuda_tb_task t = P.tasks[ti];
-  const PicView vp = P.pics[P.map[t.pred]], vr = P.pics[P.map[t.rec]];
+  const PicView &vp = P.pics[P.map[t.pred]], &vr = P.pics[P.map[t.rec]];
   const int pl = t.plane;
   const uint8_t *pred = vp.p[pl] + (size_t)t.y * vp.stride[pl] + t.x;
   uint8_t *rec = vr.p[pl] + (size_t)t.y * vr.stride[pl] + t.x;
@@ -210,7 +209,7 @@ __device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, bool val
   int any = 0;
 
   if (!P.decode) {
-    const PicView vo = P.pics[P.map[t.org]];
+    const PicView &vo = P.pics[P.map[t.org]];
     const uint8_t *org = vo.p[pl] + (size_t)t.y * vo.stride[pl] + t.x;
     const int ostride = vo.stride[pl];
     // ---- residual, box-summed where the reference does so (transform.c:273-307) ----
@@ -270,11 +269,10 @@ __device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, bool val
     for (int m = G / 2; m > 0; m >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, m));
     const int off_small = (intra ? 102 : 51) << (shift - 8), off_big = (intra ? 115 : 90) << (shift - 8);
     constexpr int NW = (Q * Q + 31) / 32;
-    unsigned big_mask[NW];                             // positions with |level| > 1 (bit p % 32 of word p / 32)
+    constexpr int NIT = Q * Q / G;
+    int lv[NIT];                                       // this lane's levels (magnitudes)
 #pragma unroll
-    for (int w = 0; w < NW; w++) big_mask[w] = 0;
-#pragma unroll
-    for (int it = 0; it < Q * Q / G; it++) {           // uniform trip count: every lane reaches the ballot
+    for (int it = 0; it < NIT; it++) {
       const int p = it * G + gl;
       int l = 0;
       if (p <= last) {
@@ -284,18 +282,30 @@ __device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, bool val
         lev[p] = (int16_t)(c < 0 ? -l : l);
       }
       any |= (l != 0);
-      big_mask[(it * G) / 32] |= group_ballot<G>(l > 1, gbase) << ((it * G) & 31);
+      lv[it] = l;
     }
     any = group_ballot<G>(any != 0, gbase) != 0;
     __syncwarp();
+    // "RDOQ light" (:135-168): a level > 1 that follows two zeros is traded for +-1s.  The pass only ever writes
+    // +-1 (onto the level itself or onto one of the two zeros before it), so neither "|level| > 1" nor the two
+    // zeros of a LATER position can come into being during the pass: the positions that can fire are known up
+    // front -- found here in parallel -- and only those are walked in order (the walk re-tests everything on the
+    // current values, as the conditions on positions p-3 / p-4 do depend on earlier outcomes).
+    unsigned trig_mask[NW];
+#pragma unroll
+    for (int w = 0; w < NW; w++) trig_mask[w] = 0;
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {                 // uniform trip count: every lane reaches the ballot
+      const int p = it * G + gl;
+      const bool trig = lv[it] > 1 && p >= 2 && lev[p - 1] == 0 && lev[p - 2] == 0;
+      trig_mask[(it * G) / 32] |= group_ballot<G>(trig, gbase) << ((it * G) & 31);
+    }
     if (any && gl == 0) {
-      // "RDOQ light" (:135-168): an isolated level > 1 after two zeros is traded for +-1s.  Only positions
-      // that hold |level| > 1 can trigger, and the pass never creates new ones, so walk that bit set.
       const int NN = chroma ? last + 1 : Q * Q;
       const int thr = (73 * (int)c_dqscale[qrem] << qper) >> (4 + LG);
 #pragma unroll
       for (int w = 0; w < NW; w++) {
-        unsigned m = big_mask[w];
+        unsigned m = trig_mask[w];
         while (m) {
           const int p = w * 32 + __ffs(m) - 1;
           m &= m - 1;
@@ -344,7 +354,7 @@ __device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, bool val
   const uint8_t *org = nullptr;
   int ostride = 0;
   if (!P.decode && P.ssd) {
-    const PicView vo = P.pics[P.map[t.org]];
+    const PicView &vo = P.pics[P.map[t.org]];
     org = vo.p[pl] + (size_t)t.y * vo.stride[pl] + t.x;
     ostride = vo.stride[pl];
   }
@@ -380,6 +390,21 @@ __device__ __forceinline__ void tb_unit(const TbParams &P, uint32_t ti, bool val
   __syncwarp();
 }
 
+// Pull the pixel rows of a unit (org and pred) towards the SM ahead of their use.
+template <int N>
+__device__ __forceinline__ void tb_prefetch(const TbParams &P, const thorcuda_tb_task &t, int gl) {
+  constexpr int G = TbLayout<N>::G;
+  const int pl = t.plane;
+  const PicView &vp = P.pics[P.map[t.pred]];
+  const uint8_t *pred = vp.p[pl] + (size_t)t.y * vp.stride[pl] + t.x;
+  for (int r = gl; r < N; r += G) asm volatile("prefetch.global.L1 [%0];" ::"l"(pred + (size_t)r * vp.stride[pl]));
+  if (!P.decode) {
+    const PicView &vo = P.pics[P.map[t.org]];
+    const uint8_t *org = vo.p[pl] + (size_t)t.y * vo.stride[pl] + t.x;
+    for (int r = gl; r < N; r += G) asm volatile("prefetch.global.L1 [%0];" ::"l"(org + (size_t)r * vo.stride[pl]));
+  }
+}
+
 constexpr int cmax(int a, int b) { return a > b ? a : b; }
 // scratch of one warp: the largest of the five classes
 constexpr int TB_SCRATCH = cmax(cmax(cmax(TbLayout<64>::total * TbLayout<64>::UPW, TbLayout<32>::total * TbLayout<32>::UPW),
@@ -396,18 +421,30 @@ __device__ __forceinline__ void tb_class(const TbParams &P, int cls, int16_t *sS
   const int count = P.count[cls];
   // unit index: iteration-major inside the CTA so that the groups of a warp work on neighbouring tasks
   const int per_iter = TW * L::UPW;
+  const int slot0 = cta * TB_ITERS * per_iter + warp * L::UPW + grp;
+  if (cta * TB_ITERS * per_iter >= count) return;
+  uint32_t ti = P.order[P.first[cls] + min(slot0, count - 1)];
+  thorcuda_tb_task t = P.tasks[ti];
 #pragma unroll 1
   for (int it = 0; it < TB_ITERS; it++) {
     const int base = (cta * TB_ITERS + it) * per_iter;
     if (base >= count) break;                              // uniform over the CTA
     const int slot = base + warp * L::UPW + grp;
-    const bool valid = slot < count;
-    const uint32_t ti = P.order[P.first[cls] + (valid ? slot : count - 1)];
-    tb_unit<N>(P, ti, valid, S, sFw, sIv, sZ, gl, gbase);
+    // the next unit's task record is fetched, and its pixel rows are pulled towards the SM, while this one is worked on
+    uint32_t ti_n = ti;
+    thorcuda_tb_task t_n = t;
+    if (it + 1 < TB_ITERS && base + per_iter < count) {
+      ti_n = P.order[P.first[cls] + min(slot + per_iter, count - 1)];
+      t_n = P.tasks[ti_n];
+      tb_prefetch<N>(P, t_n, gl);
+    }
+    tb_unit<N>(P, ti, t, slot < count, S, sFw, sIv, sZ, gl, gbase);
+    ti = ti_n;
+    t = t_n;
   }
 }
 
-__global__ void __launch_bounds__(TW * 32) k_tb(const TbParams P) {
+__global__ void __launch_bounds__(TW * 32, 6) k_tb(const TbParams P) {
   __shared__ __align__(16) int8_t sFw[FW_BYTES];
   __shared__ __align__(16) int8_t sIv[IV_BYTES];
   __shared__ __align__(16) uint8_t sZ[16 + 64 + 256];
@@ -571,6 +608,11 @@ static int run_tb(List *L, int decode, bool want_ssd) {
   }
   P.cta_first[5] = cta;
   if (!cta) return 0;
+  static bool carveout_set = false;
+  if (!carveout_set) {   // 6 CTAs x 22 KB per SM: ask for the large shared-memory split
+    cudaFuncSetAttribute(k_tb, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    carveout_set = true;
+  }
   k_tb<<<(unsigned)cta, TW * 32, 0, c.stream>>>(P);
   THOR_LAUNCHED();
   return 0;
