@@ -46,6 +46,7 @@ struct Pic {
 struct List {
   bool used = false;
   int kind = -1, ntasks = 0, npics = 0, ntiles = 0, nbig = 0;
+  int cost_w = 0, cost_h = 0;      // cost lists: the largest block (sizes the kernel's window buffer)
   std::vector<int> pics;                  // handles
   uint8_t *blob = nullptr;                // one device allocation: tasks | tiles | map
   size_t off_tiles = 0, off_map = 0, blob_bytes = 0;

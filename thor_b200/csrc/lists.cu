@@ -146,6 +146,11 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
   } else {
     if (check_cost(P, npics, (const thorcuda_cost_task *)tasks, ntasks)) return -1;
     task_size = sizeof(thorcuda_cost_task);
+    for (int i = 0; i < ntasks; i++) {
+      const thorcuda_cost_task &t = ((const thorcuda_cost_task *)tasks)[i];
+      L.cost_w = std::max(L.cost_w, (int)t.w);
+      L.cost_h = std::max(L.cost_h, (int)t.h);
+    }
   }
   const size_t task_bytes = (size_t)ntasks * task_size;
   L.off_tiles = (task_bytes + 15) & ~(size_t)15;

@@ -297,17 +297,18 @@ __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__re
 // position, so that the block's columns are word aligned) is staged in shared memory; a lane then works on 4
 // horizontally adjacent samples at a time with byte-SIMD words: VAVG (rounding average = v64_avg_u8), VHADD
 // (truncating average = v64_rdavg_u8) and VABSDIFF4 with accumulate, exactly the operations of the reference's
-// SIMD kernels (enc/enc_kernels.c:162-648).
+// SIMD kernels (enc/enc_kernels.c:162-648).  The kernel is compiled once per kind; the window buffer is sized by
+// the largest block of the list (dynamic shared memory), so lists of small blocks run at full occupancy.
 constexpr int CW = 8;                         // warps per CTA
-constexpr int CPW = 19;                       // window row pitch in words: up to 4 + 64 + 4 samples
-constexpr int CROWS = 70;
 
 struct CostParams {
   const PicView *pics;
   const uint16_t *map;
   const thorcuda_cost_task *tasks;
   thorcuda_cost_result *out;
-  int ntasks, kind;
+  int ntasks;
+  int pitch;                                  // window row pitch in words: (max w + 8) / 4
+  int warp_words;                             // window words per warp: (max h + 6) * pitch
 };
 
 __device__ __forceinline__ uint32_t up4(uint32_t a, uint32_t b) { return __vavgu4(a, b); }    // (a+b+1)>>1 per byte
@@ -339,48 +340,88 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
   return v;
 }
 
-__global__ void __launch_bounds__(CW * 32) k_cost_batch(const CostParams P) {
-  __shared__ __align__(16) uint32_t sWin[CW][CROWS * CPW];
+// Sum each of s[0..7] over the warp with 9 shuffles instead of 40: every exchange halves the number of sums a lane
+// still carries.  Afterwards lane l holds the warp total of s[k], k = 4 * bit4(l) + 2 * bit3(l) + bit2(l).
+__device__ __forceinline__ uint32_t warp_sum8(const uint32_t (&s)[8], int lane) {
+  uint32_t t[4], u[2];
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+#pragma unroll
+  for (int k = 0; k < 4; k++) t[k] = (b4 ? s[k + 4] : s[k]) + __shfl_xor_sync(0xffffffffu, b4 ? s[k] : s[k + 4], 16);
+#pragma unroll
+  for (int k = 0; k < 2; k++) u[k] = (b3 ? t[k + 2] : t[k]) + __shfl_xor_sync(0xffffffffu, b3 ? t[k] : t[k + 2], 8);
+  uint32_t v = (b2 ? u[1] : u[0]) + __shfl_xor_sync(0xffffffffu, b2 ? u[0] : u[1], 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+
+// Stage rows x (4 * words) bytes starting at src (any alignment) into win, byte 0 of a row = src[0].  LPR lanes
+// share a row (LPR > words: the lane after the last output word fetches the word the shift spills into); the loads
+// of 8 row groups are issued before the first is used.
+template <int LPR>
+__device__ __forceinline__ void cost_stage(uint32_t *win, int pitch, const uint8_t *src, int stride, int rows, int words, int lane) {
+  constexpr int RPP = 32 / LPR;                       // rows per pass
+  const int o = (int)((uintptr_t)src & 3), sh = 8 * o;
+  const uint8_t *base = src - o;
+  const int wd = lane % LPR, r0 = lane / LPR;
+  const bool fetch = 4 * wd < o + 4 * words;          // raw words that hold wanted bytes
+  for (int rb = 0; rb < rows; rb += 8 * RPP) {
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int r = rb + k * RPP + r0;
+      v[k] = (fetch && r < rows) ? *reinterpret_cast<const uint32_t *>(base + (ptrdiff_t)r * stride + 4 * wd) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int r = rb + k * RPP + r0;
+      const uint32_t hi = __shfl_down_sync(0xffffffffu, v[k], 1);
+      if (wd < words && r < rows) win[r * pitch + wd] = __funnelshift_r(v[k], hi, sh);
+    }
+  }
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(CW * 32, 4) k_cost_batch(const CostParams P) {
+  extern __shared__ __align__(16) uint32_t sWin[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ti = blockIdx.x * CW + warp;
   if (ti >= P.ntasks) return;
   const thorcuda_cost_task t = P.tasks[ti];
-  const PicView org = P.pics[P.map[t.org]], ref = P.pics[P.map[t.ref]];
+  const PicView &org = P.pics[P.map[t.org]], &ref = P.pics[P.map[t.ref]];
   const int w = t.w, h = t.h;
+  const int CPW = P.pitch;
   // stage reference rows -3..h+2, columns -4..w+3 around the candidate position; byte 0 of a row = column -4
-  uint32_t *win = sWin[warp];
+  uint32_t *win = sWin + warp * P.warp_words;
   {
-    const uint8_t *src = ref.p[0] + (ptrdiff_t)(t.y + t.iy - 3) * ref.stride[0] + (t.x + t.ix - 4);
-    const int o = (int)((uintptr_t)src & 3), sh = 8 * o;
-    const uint8_t *base = src - o;
+    const int rstride = ref.stride[0];
+    const uint8_t *src = ref.p[0] + (ptrdiff_t)(t.y + t.iy - 3) * rstride + (t.x + t.ix - 4);
     const int words = (w + 8) >> 2;
-    for (int i = lane; i < (h + 6) * words; i += 32) {
-      const int r = i / words, wd = i - r * words;
-      const uint32_t *g = reinterpret_cast<const uint32_t *>(base + (ptrdiff_t)r * ref.stride[0]) + wd;
-      const uint32_t lo = g[0], hi = o ? g[1] : 0u;
-      win[r * CPW + wd] = __funnelshift_r(lo, hi, sh);
-    }
+    if (words < 8) cost_stage<8>(win, CPW, src, rstride, h + 6, words, lane);
+    else if (words < 16) cost_stage<16>(win, CPW, src, rstride, h + 6, words, lane);
+    else cost_stage<32>(win, CPW, src, rstride, h + 6, words, lane);
   }
   __syncwarp();
-  const uint8_t *a00 = org.p[0] + (size_t)t.y * org.stride[0] + t.x;
+  const int ostride = org.stride[0];
+  const uint8_t *a00 = org.p[0] + (size_t)t.y * ostride + t.x;
   const int wq = w >> 2, nquads = wq * h;
+  const int wq_inv = (65536 + wq - 1) / wq;              // i / wq == (i * wq_inv) >> 16 for i < 64 * 16
   uint32_t s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const int kind = P.kind;
   const int sel = (t.hx & t.hy) ? 0 : (t.hx ? 1 : (t.hy ? 2 : 3));
   for (int i = lane; i < nquads; i += 32) {
-    const int r = i / wq, c4 = i - r * wq;
-    const uint32_t A = *reinterpret_cast<const uint32_t *>(a00 + (size_t)r * org.stride[0] + 4 * c4);
+    const int r = (i * wq_inv) >> 16, c4 = i - r * wq;
+    const uint32_t A = *reinterpret_cast<const uint32_t *>(a00 + (size_t)r * ostride + 4 * c4);
     const uint32_t *p0 = win + (r + 3) * CPW + c4;       // words around the quad in its own row
-    if (kind == THORCUDA_COST_SAD) {
+    if (KIND == THORCUDA_COST_SAD) {
       s[0] = sad4(A, p0[1], s[0]);
-    } else if (kind == THORCUDA_COST_SSD) {
+    } else if (KIND == THORCUDA_COST_SSD) {
       const uint32_t d = __vabsdiffu4(A, p0[1]);
       s[0] = __dp4a(d, d, s[0]);
-    } else if (kind == THORCUDA_COST_WIDESAD) {
+    } else if (KIND == THORCUDA_COST_WIDESAD) {
       const Row3 R = load_row(p0);
       s[0] = sad4(A, col<-3>(R), s[0]); s[1] = sad4(A, col<-1>(R), s[1]); s[2] = sad4(A, col<0>(R), s[2]);
       s[3] = sad4(A, col<1>(R), s[3]); s[4] = sad4(A, col<3>(R), s[4]);
-    } else if (kind == THORCUDA_COST_FASTHALF) {
+    } else if (KIND == THORCUDA_COST_FASTHALF) {
       Row3 R[5];
 #pragma unroll
       for (int y = 0; y < 5; y++) R[y] = load_row(p0 + (y - 2) * CPW);
@@ -410,43 +451,39 @@ __global__ void __launch_bounds__(CW * 32) k_cost_batch(const CostParams P) {
       for (int k = 0; k < 8; k++) s[k] = sad4(A, v[k], s[k]);
     }
   }
-  const int nsum = (kind == THORCUDA_COST_SAD || kind == THORCUDA_COST_SSD) ? 1 : (kind == THORCUDA_COST_WIDESAD ? 5 : 8);
-#pragma unroll
-  for (int k = 0; k < 8; k++) if (k < nsum) s[k] = warp_sum(s[k]);
-  if (lane) return;
   thorcuda_cost_result res;
-  res.cost = s[0]; res.x = 0; res.y = 0;
-  if (kind == THORCUDA_COST_WIDESAD) {
-    // first minimum in the order -3,-1,0,+1,+3 (enc/encode_block.c:764-776; SIMD packs (sad<<3)|idx: same order)
-    const int offx[5] = {-3, -1, 0, 1, 3};
-    uint32_t best = 1u << 31; int bx = 0;
-#pragma unroll
-    for (int k = 0; k < 5; k++) if (s[k] < best) { best = s[k]; bx = offx[k]; }
-    res.cost = best; res.x = (int16_t)bx;
-  } else if (kind == THORCUDA_COST_FASTHALF) {
-    // strict '<' in the order down,right,left,tl,tr,br,bl starting from top = (0,-2)  (:577-603)
-    uint32_t best = s[0]; int bx = 0, by = -2;
-    if (s[1] < best) { best = s[1]; bx = 0;  by = 2; }
-    if (s[3] < best) { best = s[3]; bx = 2;  by = 0; }
-    if (s[2] < best) { best = s[2]; bx = -2; by = 0; }
-    if (s[4] < best) { best = s[4]; bx = -2; by = -2; }
-    if (s[5] < best) { best = s[5]; bx = 2;  by = -2; }
-    if (s[7] < best) { best = s[7]; bx = 2;  by = 2; }
-    if (s[6] < best) { best = s[6]; bx = -2; by = 2; }
-    res.cost = best; res.x = (int16_t)bx; res.y = (int16_t)by;
-  } else if (kind == THORCUDA_COST_FASTQUARTER) {
-    // start from top = (0,-1); order tl,tr,left,right,bl,down,br; tl/tr keep besty  (:703-734)
-    uint32_t best = s[1]; int bx = 0, by = -1;
-    if (s[0] < best) { best = s[0]; bx = -1; }
-    if (s[2] < best) { best = s[2]; bx = 1; }
-    if (s[3] < best) { best = s[3]; bx = -1; by = 0; }
-    if (s[4] < best) { best = s[4]; bx = 1;  by = 0; }
-    if (s[5] < best) { best = s[5]; bx = -1; by = 1; }
-    if (s[6] < best) { best = s[6]; bx = 0;  by = 1; }
-    if (s[7] < best) { best = s[7]; bx = 1;  by = 1; }
-    res.cost = best; res.x = (int16_t)bx; res.y = (int16_t)by;
+  res.x = 0; res.y = 0;
+  if (KIND == THORCUDA_COST_SAD || KIND == THORCUDA_COST_SSD) {
+    res.cost = warp_sum(s[0]);
+  } else {
+    // Every candidate position gets a rank = its place in the reference's comparison order; the reference keeps the
+    // first strict minimum in that order, which is the minimum of (cost << 3 | rank) -- the packing its own SIMD
+    // widesad uses (enc_kernels.c:93-97).  Costs stay below 2^21 (64 * 64 * 255).
+    //   widesad     (:764-776)  order -3,-1,0,+1,+3
+    //   fasthalf    (:577-603)  start top, then down,right,left,tl,tr,br,bl;  s = top down left right tl tr bl br
+    //   fastquarter (:703-734)  start top, then tl,tr,left,right,bl,down,br;  s = tl top tr left right bl down br
+    const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    if (KIND == THORCUDA_COST_WIDESAD) s[5] = s[6] = s[7] = 0x0fffffffu >> 5;    // never the minimum (summed over 32 lanes)
+    const uint32_t total = warp_sum8(s, lane);
+    const uint32_t rank_of = KIND == THORCUDA_COST_WIDESAD ? 0x76543210u : KIND == THORCUDA_COST_FASTHALF ? 0x67542310u : 0x76543201u;
+    uint32_t key = (total << 3) | ((rank_of >> (4 * k)) & 7u);
+    key = min(key, __shfl_xor_sync(0xffffffffu, key, 16));
+    key = min(key, __shfl_xor_sync(0xffffffffu, key, 8));
+    key = min(key, __shfl_xor_sync(0xffffffffu, key, 4));
+    res.cost = key >> 3;
+    const int rank = key & 7;
+    // (x, y) of each rank, packed as 4-bit fields biased by 3
+    if (KIND == THORCUDA_COST_WIDESAD) {
+      res.x = (int16_t)((int)((0x64320u >> (4 * rank)) & 15u) - 3);                       // -3,-1,0,1,3
+    } else if (KIND == THORCUDA_COST_FASTHALF) {
+      res.x = (int16_t)((int)((0x15511533u >> (4 * rank)) & 15u) - 3);                    // 0,0,2,-2,-2,2,2,-2
+      res.y = (int16_t)((int)((0x55113351u >> (4 * rank)) & 15u) - 3);                    // -2,2,0,0,-2,-2,2,2
+    } else {
+      res.x = (int16_t)((int)((0x43242423u >> (4 * rank)) & 15u) - 3);                    // 0,-1,1,-1,1,-1,0,1
+      res.y = (int16_t)((int)((0x44433222u >> (4 * rank)) & 15u) - 3);                    // -1,-1,-1,0,0,1,1,1
+    }
   }
-  P.out[ti] = res;
+  if (lane == 0) P.out[ti] = res;
 }
 
 template <int R>
@@ -590,8 +627,18 @@ int thorcuda_cost_list(thorcuda_list hl, int kind, thorcuda_cost_result *host_re
   CostParams P;
   P.pics = c.d_pics; P.map = L->map();
   P.tasks = (const thorcuda_cost_task *)L->tasks();
-  P.out = L->results; P.ntasks = L->ntasks; P.kind = kind;
-  k_cost_batch<<<(L->ntasks + CW - 1) / CW, CW * 32, 0, c.stream>>>(P);
+  P.out = L->results; P.ntasks = L->ntasks;
+  P.pitch = (L->cost_w + 8) / 4;
+  P.warp_words = (L->cost_h + 6) * P.pitch;
+  const size_t smem = (size_t)CW * P.warp_words * 4;      // at most 8 x 70 x 18 words = 40 KB
+  const unsigned grid = (unsigned)((L->ntasks + CW - 1) / CW);
+  switch (kind) {
+    case THORCUDA_COST_SAD: k_cost_batch<THORCUDA_COST_SAD><<<grid, CW * 32, smem, c.stream>>>(P); break;
+    case THORCUDA_COST_WIDESAD: k_cost_batch<THORCUDA_COST_WIDESAD><<<grid, CW * 32, smem, c.stream>>>(P); break;
+    case THORCUDA_COST_FASTHALF: k_cost_batch<THORCUDA_COST_FASTHALF><<<grid, CW * 32, smem, c.stream>>>(P); break;
+    case THORCUDA_COST_FASTQUARTER: k_cost_batch<THORCUDA_COST_FASTQUARTER><<<grid, CW * 32, smem, c.stream>>>(P); break;
+    default: k_cost_batch<THORCUDA_COST_SSD><<<grid, CW * 32, smem, c.stream>>>(P); break;
+  }
   THOR_LAUNCHED();
   if (host_results) return d2h(host_results, L->results, (size_t)L->ntasks * sizeof(thorcuda_cost_result));
   return 0;
