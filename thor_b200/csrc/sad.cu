@@ -53,7 +53,15 @@ struct SadCfg {
   static constexpr int buf_bytes = 64 * 64 + win_rows * pitch; // one stage: original SB | reference window
   static constexpr int part_off = 2 * buf_bytes;               // uint32 [8 strips][nn]
   static constexpr int pair_off = part_off + 8 * nn * 4;       // uint16 [8 warps][nn] (UPW == 1 only)
-  static constexpr int smem_bytes = pair_off + (UPW == 1 ? ((8 * nn * 2 + 15) & ~15) : 0);
+  // Byte-phase copies of the window (R <= 16, where they fit beside two resident CTAs): copy k = the window shifted
+  // left by k bytes, so that a lane finds the 4 samples at ANY column as one aligned word of copy (column & 3) and the
+  // inner loop needs no funnel shifts (copy 0 is the staged window itself).  Copy k starts 32k bytes past a
+  // 128-byte boundary: the 32 lanes of a pass (consecutive columns) then hit 32 different banks.
+  static constexpr bool PH = R <= 16;
+  static constexpr int win_bytes = (win_rows * pitch + 127) & ~127;
+  static constexpr int ph_off = (pair_off + (UPW == 1 ? 8 * nn * 2 : 0) + 127) & ~127;
+  static constexpr int smem_bytes = PH ? ph_off + 3 * win_bytes + 128 : ((ph_off + 15) & ~15);
+  static_assert(buf_bytes % 128 == 0, "both stages must have the bank alignment the phase copies are laid out against");
 };
 
 // where one pass's results go
@@ -96,7 +104,7 @@ __device__ __forceinline__ void sad_reduce(uint32_t v, int e, const SadOut &O) {
 // ones; FIRST / LAST skip those, so no abs-diff is computed that is not part of an output.
 enum { BLK_FIRST = 0, BLK_MID = 1, BLK_LAST = 2 };
 
-template <int MODE, int R, int UPW>
+template <int MODE, int R, int UPW, bool PH>
 __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint32_t (&oB)[8][2], uint32_t (&aT)[8], uint32_t (&aB)[8],
                                           const uint8_t *col, int sh, const SadOut &O, int e0) {
   constexpr int n = SadCfg<R>::n, pitch = SadCfg<R>::pitch;
@@ -104,9 +112,14 @@ __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint
   for (int s = 0; s < (MODE == BLK_LAST ? 7 : 8); s++) {     // the last block: reference rows 2R .. 2R+6
     const uint32_t *rt = reinterpret_cast<const uint32_t *>(col + s * pitch);
     const uint32_t *rb = reinterpret_cast<const uint32_t *>(col + (s + 8) * pitch);
-    const uint32_t t0 = rt[0], t1 = rt[1], t2 = rt[2], b0 = rb[0], b1 = rb[1], b2 = rb[2];
-    const uint32_t wT0 = __funnelshift_r(t0, t1, sh), wT1 = __funnelshift_r(t1, t2, sh);
-    const uint32_t wB0 = __funnelshift_r(b0, b1, sh), wB1 = __funnelshift_r(b1, b2, sh);
+    uint32_t wT0, wT1, wB0, wB1;
+    if (PH) {                                         // `col` points into the copy of this lane's byte phase
+      wT0 = rt[0]; wT1 = rt[1]; wB0 = rb[0]; wB1 = rb[1];
+    } else {
+      const uint32_t t0 = rt[0], t1 = rt[1], t2 = rt[2], b0 = rb[0], b1 = rb[1], b2 = rb[2];
+      wT0 = __funnelshift_r(t0, t1, sh); wT1 = __funnelshift_r(t1, t2, sh);
+      wB0 = __funnelshift_r(b0, b1, sh); wB1 = __funnelshift_r(b1, b2, sh);
+    }
 #pragma unroll
     for (int r = 0; r < 8; r++) {
       if (MODE == BLK_FIRST && r > s) continue;      // displacement row j - r < 0
@@ -128,7 +141,7 @@ __device__ __forceinline__ void sad_block(const uint32_t (&oT)[8][2], const uint
 }
 
 struct SadTile {
-  const uint8_t *sOrg, *sWin;
+  const uint8_t *sOrg, *sWin, *sPh;
   uint32_t *part;
   uint16_t *pair;
   uint16_t *t8, *t16;
@@ -161,19 +174,21 @@ __device__ __forceinline__ void sad_pass(const SadTile &C, int p, int bx, int dx
   O.pair = C.pair + warp * nn + dxi;
   const int off = bx * 8 + dxi + C.o;
   const int sh = (off & 3) * 8;
-  const uint8_t *col = C.sWin + (16 * p) * pitch + (off & ~3);
+  const uint8_t *wbase = C.sWin;
+  if (SadCfg<R>::PH && (off & 3)) wbase = C.sPh + (off & 3) * 32 + ((off & 3) - 1) * SadCfg<R>::win_bytes;
+  const uint8_t *col = wbase + (16 * p) * pitch + (off & ~3);
   uint32_t aT[8], aB[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) { aT[k] = 0; aB[k] = 0; }
-  sad_block<BLK_FIRST, R, UPW>(oT, oB, aT, aB, col, sh, O, 0);
+  sad_block<BLK_FIRST, R, UPW, SadCfg<R>::PH>(oT, oB, aT, aB, col, sh, O, 0);
   int e0 = 0;
 #pragma unroll 1
   for (int jj = 8; jj < 2 * R; jj += 8) {
     col += 8 * pitch; e0 += 8 * n;
-    sad_block<BLK_MID, R, UPW>(oT, oB, aT, aB, col, sh, O, e0);
+    sad_block<BLK_MID, R, UPW, SadCfg<R>::PH>(oT, oB, aT, aB, col, sh, O, e0);
   }
   col += 8 * pitch; e0 += 8 * n;
-  sad_block<BLK_LAST, R, UPW>(oT, oB, aT, aB, col, sh, O, e0);
+  sad_block<BLK_LAST, R, UPW, SadCfg<R>::PH>(oT, oB, aT, aB, col, sh, O, e0);
 }
 
 // Persistent kernel: gridDim.x CTAs walk the (job, SB row, SB column) tiles of the launch with a stride of
@@ -186,7 +201,7 @@ template <int R>
 __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__restrict__ jobs, int gx, int gy, int njobs) {
   using Cfg = SadCfg<R>;
   constexpr int n = Cfg::n, nn = Cfg::nn, pitch = Cfg::pitch, win_rows = Cfg::win_rows;
-  extern __shared__ __align__(16) uint8_t smem[];
+  extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   uint32_t *part = reinterpret_cast<uint32_t *>(smem + Cfg::part_off);
   uint16_t *pair = reinterpret_cast<uint16_t *>(smem + Cfg::pair_off);
@@ -249,7 +264,26 @@ __global__ void __launch_bounds__(SAD_THREADS, 2) k_sad_table(const SadJob *__re
 
     const SadJob &J = jobs[cur.z];
     SadTile C;
-    C.sOrg = smem + st * Cfg::buf_bytes; C.sWin = C.sOrg + 64 * 64;
+    C.sOrg = smem + st * Cfg::buf_bytes; C.sWin = C.sOrg + 64 * 64; C.sPh = smem + Cfg::ph_off;
+    if (Cfg::PH) {
+      // the three shifted copies of the window: 16 bytes in, 3 x 16 bytes out per item
+      constexpr int cpr = pitch >> 4;
+      uint8_t *sPh = smem + Cfg::ph_off;
+      for (int i = tid; i < win_rows * cpr; i += SAD_THREADS) {
+        const int r = i / cpr, c = i - r * cpr;
+        const uint8_t *src = C.sWin + r * pitch + 16 * c;
+        const uint4 v = *reinterpret_cast<const uint4 *>(src);
+        const uint32_t nx = c + 1 < cpr ? *reinterpret_cast<const uint32_t *>(src + 16) : 0u;
+#pragma unroll
+        for (int k = 1; k < 4; k++) {
+          uint4 o;
+          o.x = __funnelshift_r(v.x, v.y, 8 * k); o.y = __funnelshift_r(v.y, v.z, 8 * k);
+          o.z = __funnelshift_r(v.z, v.w, 8 * k); o.w = __funnelshift_r(v.w, nx, 8 * k);
+          *reinterpret_cast<uint4 *>(sPh + 32 * k + (k - 1) * Cfg::win_bytes + r * pitch + 16 * c) = o;
+        }
+      }
+      __syncthreads();
+    }
     C.part = part; C.pair = pair; C.t8 = J.t8; C.t16 = J.t16;
     C.W = cur.W; C.H = cur.H; C.x0 = cur.x0; C.y0 = cur.y0; C.o = cur.o;
     {
