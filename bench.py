@@ -190,8 +190,8 @@ def workload_config(args, streams):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed `ncu --set full`
 # capture of this very command line (profiles/); only quoted when the workload is the one that was captured.
-NCU_TRAFFIC = {("sad_table", 1920, 1080, 16, 16): {"bytes": 140921088 + 2917634000, "source": "profiles/r1_ncu_sad_table_final.txt",
-                                                  "alu_pipe_pct": 79.0}}
+NCU_TRAFFIC = {("sad_table", 1920, 1080, 16, 16): {"bytes": 140482560 + 2917670000, "source": "profiles/r1_ncu_sad_table_v4.txt",
+                                                  "alu_pipe_pct": 79.9}}
 
 
 def ncu_traffic(kernel, job, B):
