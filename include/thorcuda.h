@@ -173,6 +173,32 @@ int thorcuda_reconstruct_blocks(const thorcuda_pic *pics, int npics, const thorc
                                 const int16_t *host_coeffq);
 size_t thorcuda_list_pool_entries(thorcuda_list l);   /* int16 entries of a TB list's pool            */
 
+/* ----------------------------------------------------------- intra prediction ---- */
+/* make_top_and_left + get_intra_prediction (common/intra_prediction.c:57-143, :363-389) for a list of blocks.
+ * Neighbours are read from picture `src` around the block -- row above, column left, corner; 128 where the block
+ * touches the top / left picture edge; one extra sample beyond `size` when flagged available, the last one then
+ * repeated up to 2*size -- and the size x size prediction is written into picture `dst` at the block position.
+ * x, y are the position of the predicted block in ITS plane: under tb_split each of the four sub-blocks is a task
+ * with the availability the reference derives for it (:106-110):
+ *     upright  = (j == 0 || (i == 0 && cb_upright_available)),  downleft = (j == 0 && (i == 0 || cb_downleft_available))
+ * (a flag set on a block in the first row / column is legal and unused: those neighbours are 128).
+ * cb_x is the plane x of the CODING block: the reference takes the corner sample only if that is > 0 (:83,:116 test
+ * xpos, not xpos + j) and top[0] otherwise.  The decoder predicts chroma with the luma mode and the CB's flags
+ * (dec/decode_block.c:234-239).
+ * Tasks of ONE call must be independent: the caller batches by wavefront (a block may enter a call once the blocks
+ * owning its neighbour samples are reconstructed -- thorcuda_reconstruct_blocks on the same picture).  Neighbours are
+ * read before anything is written, so src == dst is allowed.                                                     */
+typedef struct {
+  uint16_t x, y;            /* position of the block in its plane                                    */
+  uint16_t cb_x;            /* plane x of the coding block (= x unless tb_split)                     */
+  uint8_t  size;            /* 4, 8, 16, 32, 64                                                      */
+  uint8_t  plane;           /* 0 = Y, 1 = U, 2 = V                                                   */
+  uint8_t  mode;            /* intra_mode_t (common/types.h:137-149); other values predict DC (:387) */
+  uint8_t  flags;           /* bit0 up-right sample available, bit1 down-left sample available       */
+  uint8_t  src, dst;        /* indices into pics[]                                                   */
+} thorcuda_intra_task;      /* 12 bytes */
+int thorcuda_intra_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, int ntasks);
+
 /* ------------------------------------------------------------ early-skip test ---- */
 /* Significance test of a skip candidate (check_early_skip_block, enc/encode_block.c:2612-2741) for one
  * size x size luma sub-block (size = min(block size, 16): 16 or 8) and its two chroma sub-blocks, given the

@@ -69,6 +69,13 @@ int orc_early_skip_threshold(int qp, int size, double relative_threshold);
 int orc_early_skip_luma(const uint8_t *orig, int orig_stride, int size, int qp, const uint8_t *pblock, float early_skip_threshold);
 int orc_early_skip_chroma(const uint8_t *orig, int orig_stride, int size, int qp, const uint8_t *pblock, float early_skip_threshold);
 
+/* ---- intra prediction (orc_intra.c; reference common/intra_prediction.c:39-389, common/common_block.c:110-128) ---- */
+void orc_intra_neighbours(const uint8_t *rec, int stride, int x, int y, int cb_x, int size, int upright, int downleft,
+                          uint8_t *left, uint8_t *top, uint8_t *top_left);
+void orc_intra_predict(const uint8_t *left, const uint8_t *top, uint8_t top_left, int ypos, int xpos, int size, uint8_t *pblock, int mode);
+int  orc_upright_available(int ypos, int xpos, int size, int width);
+int  orc_downleft_available(int ypos, int xpos, int size, int height);
+
 /* ---- motion-search costs (enc/encode_block.c:497-828) ---- */
 unsigned orc_sad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h);
 unsigned orc_widesad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h, int *x);

@@ -9,6 +9,8 @@ golden data are outputs of the reference itself on seeded inputs:
 
   kernels.npz   inputs AND reference outputs of every hot-path function, produced by
                 oracle/_ref/libthorref.so with its SIMD dispatch on (the plain-C path is checked equal here);
+  extras.npz    the same for row a19 (early-skip test) and SURVEY 8f #1 (intra prediction); `--extras-only`
+                regenerates just this file;
   streams.json  md5 of the bitstream and of the reconstruction that oracle/_ref/Thorenc writes for three shipped
                 operating points on seeded synthetic clips (+ that Thordec reproduces the reconstruction).
 
@@ -205,10 +207,97 @@ def coding_orders():
     return res
 
 
+def extras(ref):
+    """rows a19 (early-skip test) and 8f #1 (intra prediction): inputs and reference outputs"""
+    out = {}
+    rng = np.random.default_rng(20261105)
+    # ---- intra prediction: make_top_and_left + get_intra_prediction on one 128x128 plane ----
+    W, H = 128, 128
+    plane = rng.integers(0, 256, (H, W), dtype=np.uint8)
+    plane[40:, 70:] = (plane[40:, 70:] // 32) * 32 + 100 // 4          # a flatter region
+    cases, preds = [], []
+    for size in (4, 8, 16, 32, 64):
+        pos = [(0, 0), (size, 0), (0, size), (size, size)]
+        if size <= 32:
+            pos += [(W - size, size), (size, H - size)]
+        for (x, y) in pos:
+            for mode in range(11):
+                up = int(y > 0 and x + size < W and (mode + x // size) % 2 == 0)
+                dl = int(x > 0 and y + size < H and (mode + y // size) % 3 != 0)
+                left, top = aligned(np.zeros(2 * size + 2, np.uint8)), aligned(np.zeros(2 * size + 2, np.uint8))
+                tl = C.c_uint8(0)
+                rec = plane[y:, x:]
+                ref.make_top_and_left(ptr(left), ptr(top), C.byref(tl), ptr(rec), W, None, 0, 0, 0, y, x, size, up, dl, 0)
+                pb = aligned(np.zeros((size, size), np.uint8))
+                ref.get_intra_prediction(ptr(left), ptr(top), tl.value, y, x, size, ptr(pb), mode)
+                cases.append((x, y, x, size, mode, up | (dl << 1)))
+                preds.append(pb.reshape(-1).copy())
+        if size <= 32:
+            # the four sub-blocks of a tb_split coding block at (64, 32) and at the left picture edge (0, 32)
+            for cbx in (64 if size < 32 else 0, 0):
+                cby = 32 if 2 * size <= 64 else 0
+                for i in (0, size):
+                    for j in (0, size):
+                        for mode in (1, 4, 7, 8, 0):
+                            left, top = aligned(np.zeros(2 * size + 2, np.uint8)), aligned(np.zeros(2 * size + 2, np.uint8))
+                            tl = C.c_uint8(0)
+                            ref.make_top_and_left(ptr(left), ptr(top), C.byref(tl), ptr(plane[cby:, cbx:]), W, ptr(plane[cby + i:, cbx + j:]), W,
+                                                  i, j, cby, cbx, size, 1, 0, 1)
+                            pb = aligned(np.zeros((size, size), np.uint8))
+                            ref.get_intra_prediction(ptr(left), ptr(top), tl.value, cby + i, cbx + j, size, ptr(pb), mode)
+                            up = 1 if (j == 0 or i == 0) else 0          # cb_upright_available = 1, cb_downleft_available = 0
+                            dl = 1 if (j == 0 and i == 0) else 0
+                            cases.append((cbx + j, cby + i, cbx, size, mode, up | (dl << 1)))
+                            preds.append(pb.reshape(-1).copy())
+    out["intra_plane"] = plane
+    out["intra_cases"] = np.array(cases, np.int32)          # x, y, cb_x, size, mode, flags(bit0 upright, bit1 downleft)
+    out["intra_pred"] = np.concatenate(preds)
+
+    # ---- early-skip test: one luma sub-block (16 or 8) + its U and V sub-blocks per case ----
+    for f in (ref.check_early_skip_sub_block, ref.check_early_skip_sub_blockC):
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float]
+    chroma_qp = np.ctypeslib.as_array((C.c_int * 52).in_dll(ref, "chroma_qp"))
+    rows, org, prd = [], [], []
+    for k in range(160):
+        size = 16 if k & 1 else 8
+        qp = int(rng.integers(16, 48))
+        thr = float(np.float32(rng.choice([0.5, 0.8, 1.0, 1.04])))
+        amp = int(rng.choice([1, 2, 3, 5, 8, 14]))
+        cell_o = rng.integers(0, 256, (3, 16, 16), dtype=np.uint8)
+        cell_p = np.clip(cell_o.astype(int) + rng.integers(-amp, amp + 1, (3, 16, 16)) + rng.integers(-amp, amp + 1, (3, 1, 1)), 0, 255).astype(np.uint8)
+        flags = 0
+        for pl in range(3):
+            n = size if pl == 0 else size // 2
+            o = aligned(np.ascontiguousarray(cell_o[pl, :n, :n]))
+            p = aligned(np.ascontiguousarray(cell_p[pl, :n, :n]))
+            if pl == 0:
+                r = ref.check_early_skip_sub_block(None, ptr(o), n, n, qp, ptr(p), thr)
+            else:
+                r = ref.check_early_skip_sub_blockC(None, ptr(o), n, n, int(chroma_qp[qp]), ptr(p), thr)
+            flags |= (1 if r else 0) << pl
+        rows.append((size, qp, flags))
+        org.append(cell_o); prd.append(cell_p)
+        rows[-1] = rows[-1] + (int(np.float32(thr).view(np.uint32)),)
+    out["skip_cases"] = np.array(rows, np.int64)             # size, qp_y, flags (bit0 Y, bit1 U, bit2 V), float32 bits of the threshold
+    out["skip_org"], out["skip_pred"] = np.stack(org), np.stack(prd)
+    assert {int(r[2]) & 1 for r in rows} == {0, 1} and any(r[2] & 6 for r in rows) and any(not (r[2] & 6) for r in rows)
+    return out
+
+
 def main():
     ref = load_ref()
     if ref is None:
         raise SystemExit("oracle/_ref/libthorref.so missing: run `make -C oracle ref` where /root/reference is mounted")
+    set_ref_simd(ref, 1)
+    e1 = extras(ref)
+    set_ref_simd(ref, 0)
+    e0 = extras(ref)
+    for k in e1:
+        assert np.array_equal(e1[k], e0[k]), f"reference SIMD and plain-C paths disagree on {k}"
+    np.savez_compressed(os.path.join(HERE, "extras.npz"), **e1)
+    if "--extras-only" in sys.argv:
+        print("wrote", os.path.join(HERE, "extras.npz"), os.path.getsize(os.path.join(HERE, "extras.npz")), "bytes")
+        return
     set_ref_simd(ref, 1)
     a = kernels(ref)
     set_ref_simd(ref, 0)

@@ -53,20 +53,20 @@ def test_every_declared_symbol_is_exported(lib, header):
 def test_struct_sizes_match_header():
     """compile a C probe against the header and compare with the numpy mirrors in thor_b200/lib.py"""
     sys.path.insert(0, ROOT)
-    from thor_b200.lib import COST_RESULT, COST_TASK, PRED_TASK, SKIP_TASK, TB_TASK
+    from thor_b200.lib import COST_RESULT, COST_TASK, INTRA_TASK, PRED_TASK, SKIP_TASK, TB_TASK
     from thor_b200.ops import LfJob
     probe = r'''
 #include <stdio.h>
 #include "thorcuda.h"
 #include "thorcuda_compat.h"
-int main(void){printf("%zu %zu %zu %zu %zu %zu\n",sizeof(thorcuda_pred_task),sizeof(thorcuda_tb_task),sizeof(thorcuda_cost_task),
-sizeof(thorcuda_cost_result),sizeof(thorcuda_lf_job),sizeof(thorcuda_skip_task));return 0;}
+int main(void){printf("%zu %zu %zu %zu %zu %zu %zu\n",sizeof(thorcuda_pred_task),sizeof(thorcuda_tb_task),sizeof(thorcuda_cost_task),
+sizeof(thorcuda_cost_result),sizeof(thorcuda_lf_job),sizeof(thorcuda_skip_task),sizeof(thorcuda_intra_task));return 0;}
 '''
     exe = os.path.join(ROOT, "build", "abi_probe")
     os.makedirs(os.path.dirname(exe), exist_ok=True)
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", INC, "-x", "c", "-", "-o", exe], input=probe.encode(), check=True)
     out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout.split()
-    assert [int(x) for x in out] == [PRED_TASK.itemsize, TB_TASK.itemsize, COST_TASK.itemsize, COST_RESULT.itemsize, C.sizeof(LfJob), SKIP_TASK.itemsize]
+    assert [int(x) for x in out] == [PRED_TASK.itemsize, TB_TASK.itemsize, COST_TASK.itemsize, COST_RESULT.itemsize, C.sizeof(LfJob), SKIP_TASK.itemsize, INTRA_TASK.itemsize]
 
 
 def test_no_cpu_fallback_without_gpu(lib):

@@ -277,3 +277,103 @@ def test_gpu_frame_tail(g, tb):
     assert md5 == bytes(g["ref_md5"])
     rec.close()
     newref.close()
+
+
+# ------------------------------------------------------- extras.npz: early-skip test (a19), intra prediction ----
+@pytest.fixture(scope="module")
+def gx():
+    return np.load(os.path.join(GOLD, "extras.npz"))
+
+
+def _intra_cases(gx):
+    off = 0
+    for (x, y, cbx, s, mode, flags) in gx["intra_cases"].tolist():
+        yield x, y, cbx, s, mode, flags, gx["intra_pred"][off:off + s * s].reshape(s, s)
+        off += s * s
+
+
+def test_port_intra_prediction(gx, orc):
+    plane = np.ascontiguousarray(gx["intra_plane"])
+    n = 0
+    for (x, y, cbx, s, mode, flags, want) in _intra_cases(gx):
+        left, top, tl = np.zeros(2 * s + 2, np.uint8), np.zeros(2 * s + 2, np.uint8), C.c_uint8(0)
+        orc.orc_intra_neighbours(ptr(plane[y:, x:]), plane.strides[0], x, y, cbx, s, flags & 1, flags >> 1, ptr(left), ptr(top), C.byref(tl))
+        got = np.zeros((s, s), np.uint8)
+        orc.orc_intra_predict(ptr(left), ptr(top), tl.value, y, x, s, ptr(got), mode)
+        assert np.array_equal(got, want), (x, y, cbx, s, mode, flags)
+        n += 1
+    assert n > 300
+
+
+def test_port_early_skip(gx, orc):
+    for f in (orc.orc_early_skip_luma, orc.orc_early_skip_chroma):
+        f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float]
+    for (size, qp, flags, tbits), o, p in zip(gx["skip_cases"].tolist(), gx["skip_org"], gx["skip_pred"]):
+        thr = float(np.uint32(tbits).view(np.float32))
+        got = 0
+        for pl in range(3):
+            n = size if pl == 0 else size // 2
+            ob, pb = np.ascontiguousarray(o[pl, :n, :n]), np.ascontiguousarray(p[pl, :n, :n])
+            if pl == 0:
+                r = orc.orc_early_skip_luma(ptr(ob), n, n, qp, ptr(pb), thr)
+            else:
+                r = orc.orc_early_skip_chroma(ptr(ob), n, n, orc.orc_chroma_qp(qp), ptr(pb), thr)
+            got |= (1 if r else 0) << pl
+        assert got == flags, (size, qp, thr)
+
+
+@pytest.mark.gpu
+def test_gpu_intra_prediction(gx, tb):
+    from thor_b200.lib import INTRA_TASK
+    plane = np.ascontiguousarray(gx["intra_plane"])
+    h, w = plane.shape
+    src, dst = tb.Picture(w, h), tb.Picture(w, h)
+    z = np.zeros((h // 2, w // 2), np.uint8)
+    src.upload(plane, z, z)
+    cases = list(_intra_cases(gx))
+    # predictions overlap in the destination: one call per case group of equal (x, y)
+    done = 0
+    while done < len(cases):
+        batch, seen = [], set()
+        for c in cases[done:]:
+            key = (c[0] // 4, c[1] // 4, c[3])
+            cells = {(c[0] // 4 + a, c[1] // 4 + b) for a in range(c[3] // 4) for b in range(c[3] // 4)}
+            if cells & seen:
+                break
+            seen |= cells
+            batch.append(c)
+        t = np.array([(x, y, cbx, s, 0, mode, flags, 0, 1) for (x, y, cbx, s, mode, flags, _w) in batch], INTRA_TASK)
+        tb.ops.intra_predict_blocks([src, dst], t)
+        tb.sync()
+        got = dst.download()[0]
+        for (x, y, cbx, s, mode, flags, want) in batch:
+            assert np.array_equal(got[y:y + s, x:x + s], want), (x, y, cbx, s, mode, flags)
+        done += len(batch)
+    src.close(); dst.close()
+
+
+@pytest.mark.gpu
+def test_gpu_early_skip(gx, tb):
+    from thor_b200.lib import SKIP_TASK
+    from thor_b200.ops import early_skip_batch, early_skip_thresholds
+    cases = gx["skip_cases"].tolist()
+    n = len(cases)
+    cols = 16
+    w, h = 16 * cols, 16 * ((n + cols - 1) // cols)
+    oy, py = np.zeros((h, w), np.uint8), np.zeros((h, w), np.uint8)
+    oc = [np.zeros((h // 2, w // 2), np.uint8) for _ in range(2)]
+    pc = [np.zeros((h // 2, w // 2), np.uint8) for _ in range(2)]
+    tasks = []
+    for i, ((size, qp, flags, tbits), o, p) in enumerate(zip(cases, gx["skip_org"], gx["skip_pred"])):
+        x, y = 16 * (i % cols), 16 * (i // cols)
+        oy[y:y + 16, x:x + 16], py[y:y + 16, x:x + 16] = o[0], p[0]
+        for k in range(2):
+            oc[k][y // 2:y // 2 + 8, x // 2:x // 2 + 8] = o[1 + k][:8, :8]
+            pc[k][y // 2:y // 2 + 8, x // 2:x // 2 + 8] = p[1 + k][:8, :8]
+        ty, tc = early_skip_thresholds(qp, size, float(np.uint32(tbits).view(np.float32)))
+        tasks.append((x, y, size, 0, 1, 0, ty, tc))
+    org, pred = tb.Picture(w, h), tb.Picture(w, h)
+    org.upload(oy, oc[0], oc[1]); pred.upload(py, pc[0], pc[1])
+    got = early_skip_batch([org, pred], np.array(tasks, SKIP_TASK))
+    assert got.tolist() == [c[2] for c in cases]
+    org.close(); pred.close()

@@ -362,3 +362,73 @@ def test_early_skip(simd):
         assert a == b, (chroma, size, qp, thr, amp)
         seen.add((chroma, a))
     assert seen == {(0, 0), (0, 1), (1, 0), (1, 1)}, "both outcomes must occur for luma and chroma"
+
+
+def _intra_case(rng, size, stride=96):
+    """a random picture patch with the block's top-left at (x, y) of a `stride`-wide plane"""
+    plane = rng.integers(0, 256, (2 * size + 40, stride), dtype=np.uint8)
+    return plane
+
+
+@pytest.mark.parametrize("size", [4, 8, 16, 32, 64])
+def test_intra_neighbours(size):
+    """make_top_and_left (common/intra_prediction.c:57-143), both branches: whole blocks and the four sub-blocks
+    under tb_split, at picture edges and inside, every availability combination."""
+    rng = np.random.default_rng(size)
+    stride = 200
+    plane = rng.integers(0, 256, (200, stride), dtype=np.uint8)
+    n = 0
+    for ypos in (0, 64):
+        for xpos in (0, 64):
+            for up in (0, 1):
+                for dl in (0, 1):
+                    # whole block
+                    cases = [(0, 0, size, 0)]
+                    if size <= 32:
+                        cases += [(i, j, size, 1) for i in (0, size) for j in (0, size)]     # sub-blocks of a 2*size CB
+                    for (i, j, s, split) in cases:
+                        rec = plane[ypos:, xpos:]
+                        L = [np.full(2 * s + 2, 7, np.uint8) for _ in range(2)]
+                        T = [np.full(2 * s + 2, 9, np.uint8) for _ in range(2)]
+                        tl_ref, tl_orc = C.c_uint8(1), C.c_uint8(2)
+                        rb = plane[ypos + i:, xpos + j:]
+                        ref.make_top_and_left(ptr(L[0]), ptr(T[0]), C.byref(tl_ref), ptr(rec), stride, ptr(rb), stride, i, j, ypos, xpos, s, up, dl, split)
+                        if split:
+                            upr = 1 if (j == 0 or (i == 0 and up)) else 0
+                            dwl = 1 if (j == 0 and (i == 0 or dl)) else 0
+                        else:
+                            upr, dwl = up, dl
+                        orc.orc_intra_neighbours(ptr(rb), stride, xpos + j, ypos + i, xpos, s, upr, dwl, ptr(L[1]), ptr(T[1]), C.byref(tl_orc))
+                        assert np.array_equal(L[0][:2 * s], L[1][:2 * s]) and np.array_equal(T[0][:2 * s], T[1][:2 * s]), (ypos, xpos, i, j, up, dl, split)
+                        assert tl_ref.value == tl_orc.value, (ypos, xpos, i, j, up, dl, split)
+                        n += 1
+    assert n >= 16
+
+
+@pytest.mark.parametrize("size", [4, 8, 16, 32, 64])
+def test_intra_modes(size):
+    """get_intra_prediction (common/intra_prediction.c:363-389): all ten modes + an unknown one, smooth and extreme edges."""
+    rng = np.random.default_rng(100 + size)
+    for trial in range(12):
+        if trial < 8:
+            left = rng.integers(0, 256, 2 * size, dtype=np.uint8)
+            top = rng.integers(0, 256, 2 * size, dtype=np.uint8)
+        else:
+            left = np.full(2 * size, 255 if trial & 1 else 0, np.uint8)
+            top = np.full(2 * size, 0 if trial & 1 else 255, np.uint8)
+        tl = int(rng.integers(0, 256))
+        for mode in range(11):
+            for (yp, xp) in ((0, 0), (0, 8), (8, 0), (8, 8)):
+                a = np.zeros((size, size), np.uint8)
+                b = np.ones((size, size), np.uint8)
+                ref.get_intra_prediction(ptr(left), ptr(top), tl, yp, xp, size, ptr(a), mode)
+                orc.orc_intra_predict(ptr(left), ptr(top), tl, yp, xp, size, ptr(b), mode)
+                assert np.array_equal(a, b), (size, mode, yp, xp, trial)
+
+
+def test_intra_availability():
+    for size in (8, 16, 32, 64):
+        for ypos in range(0, 192, size):
+            for xpos in range(0, 192, size):
+                assert ref.get_upright_available(ypos, xpos, size, 192) == orc.orc_upright_available(ypos, xpos, size, 192)
+                assert ref.get_downleft_available(ypos, xpos, size, 192) == orc.orc_downleft_available(ypos, xpos, size, 192)

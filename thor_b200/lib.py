@@ -23,6 +23,10 @@ COST_RESULT = np.dtype([("cost", "<u4"), ("x", "<i2"), ("y", "<i2")])
 SKIP_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("size", "u1"), ("org", "u1"), ("pred", "u1"), ("reserved", "u1"),
                       ("thr_y", "<i4"), ("thr_c", "<i4")])
 assert SKIP_TASK.itemsize == 16
+INTRA_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("cb_x", "<u2"), ("size", "u1"), ("plane", "u1"), ("mode", "u1"), ("flags", "u1"),
+                       ("src", "u1"), ("dst", "u1")])
+assert INTRA_TASK.itemsize == 12
+MODE_DC, MODE_PLANAR, MODE_HOR, MODE_VER, MODE_UPLEFT, MODE_UPRIGHT, MODE_UPUPRIGHT, MODE_UPUPLEFT, MODE_UPLEFTLEFT, MODE_DOWNLEFTLEFT = range(10)
 assert PRED_TASK.itemsize == 20 and TB_TASK.itemsize == 16 and COST_TASK.itemsize == 16 and COST_RESULT.itemsize == 8
 
 
@@ -71,6 +75,7 @@ def cdll():
                 ("thorcuda_sad_table_index", C.c_int64, [I, I, I, I, V, I, I, I, I]),
                 ("thorcuda_early_skip_thresholds", None, [I, I, C.c_float, V, V]),
                 ("thorcuda_early_skip_batch", I, [V, I, V, I, V]),
+                ("thorcuda_intra_predict_blocks", I, [V, I, V, I]),
                 ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):
             fn = getattr(_lib, name)   # AttributeError here means a stale libthorcuda.so: rebuild
             fn.restype = res

@@ -10,6 +10,7 @@ executing on the B200 through libthorcuda (no CPU fallback).
                                        (common/inter_prediction.c:72-180, enc/encode_block.c:1534-1588)
   encode_blocks / reconstruct_blocks   encode_and_reconstruct_block_inter (enc/encode_block.c:1469-1532),
                                        decode_and_reconstruct_block_inter (dec/decode_block.c:90-120)
+  intra_predict_blocks                 make_top_and_left + get_intra_prediction (common/intra_prediction.c:57-389)
   early_skip_thresholds / early_skip_batch  check_early_skip_sub_block(C) (enc/encode_block.c:2507-2610)
   sad_table / cost_batch               sad_calc, widesad_calc, sad_calc_fasthalf/fastquarter, ssd_calc
                                        (enc/encode_block.c:497-797)
@@ -19,7 +20,7 @@ import ctypes as C
 import numpy as np
 
 from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, LIST_COST, LIST_PRED, LIST_TB, COST_RESULT, COST_TASK,
-                  PRED_TASK, SKIP_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
+                  INTRA_TASK, PRED_TASK, SKIP_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
 
 
 class LfJob(C.Structure):  # thorcuda_lf_job
@@ -165,6 +166,12 @@ def cost_batch(kind, pics, tasks):
     check(cdll().thorcuda_cost_batch(int(kind), _handles(pics), len(pics), _p(t), t.size, _p(out)))
     sync()
     return out
+
+
+def intra_predict_blocks(pics, tasks):
+    """Intra prediction of independent blocks (one wavefront level): neighbours from pics[src], prediction into pics[dst]."""
+    t = np.ascontiguousarray(tasks, INTRA_TASK)
+    check(cdll().thorcuda_intra_predict_blocks(_handles(pics), len(pics), _p(t), t.size))
 
 
 def clip_mv(mv, ypos, xpos, fwidth, fheight, size, sign):
