@@ -284,6 +284,24 @@ def merged_lists(tb, streams):
     return (pics, np.concatenate(pred), np.concatenate(tbs), np.concatenate(cost))
 
 
+def bind_to_gpu_numa_node(index):
+    """Run this process (and so first-touch its pinned staging buffers) on the CPUs local to GPU `index`: the e2e leg
+    moves 0.77 GB per step over PCIe and a cross-socket hop shows.  Returns a note for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} cpus local to gpu {index}"
+    except Exception as e:          # no NVML / restricted container: keep the inherited affinity
+        return f"unchanged ({type(e).__name__})"
+    return "unchanged"
+
+
 def run_gpu_arm(args, rank, world, local_rank):
     import thor_b200 as tb
     from thor_b200.workload import algorithmic_bytes, make_job, shard_streams
@@ -293,6 +311,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    affinity = bind_to_gpu_numa_node(local_rank)
     tb.init(local_rank)
     lib = tb.cdll()
 
@@ -399,7 +418,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         achieved = B * ab[dom] / (stage_ms[dom] * 1e-3) / 1e9
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-                "data": "synthetic", "config": workload_config(args, B), "clocks": clocks, "gpu_launches": int(launches),
+                "data": "synthetic", "config": workload_config(args, B), "clocks": clocks, "gpu_launches": int(launches), "cpu_affinity": affinity,
                 "e2e": e2e,
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
@@ -457,17 +476,35 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
 
     h2d = d2h = 0
 
+    phase = {}
+
+    def mark(name, t_prev):
+        t = time.perf_counter()
+        phase[name] = phase.get(name, 0.0) + (t - t_prev)
+        return t
+
     def step():
         nonlocal h2d, d2h
         h2d = d2h = 0
         lists = []
+        tp = time.perf_counter()
         for s, d in zip(streams, host):
             j = s.job
             tb.check(lib.thorcuda_pic_upload(s.org.handle, d["oy"].ctypes.data, d["ou"].ctypes.data, d["ov"].ctypes.data, w, w // 2))
-            tb.ops.blockinfo_upload(s.work, j["blockinfo"])
             h2d += w * h * 3 // 2 + (w // 4) * (h // 4) * 2
+        tp = mark("upload_submit", tp)
         tb.ops.sad_table_build([x for s in streams for x in s.slots], [s.org for s in streams for _ in range(2)],
                                [r for s in streams for r in s.refs], R)
+        # the table fetches go first: they run on the library's copy stream and drain while the kernels below execute
+        for s, d in zip(streams, host):
+            for r in range(2):
+                for bs in (8, 16, 32, 64):
+                    a = d[f"t{r}_{bs}"]
+                    tb.check(lib.thorcuda_sad_table_fetch(s.slots[r], bs, a.ctypes.data, a.nbytes))
+                    d2h += a.nbytes
+        tp = mark("tables_submit", tp)
+        for s in streams:                       # side information is only needed by the frame tail: pack it while the tables drain
+            tb.ops.blockinfo_upload(s.work, s.job["blockinfo"])
         for s, d in zip(streams, host):
             j = s.job
             lc = tb.ops.TaskList(tb.LIST_COST, s.pics, j["cost"])
@@ -480,11 +517,7 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
             lp.predict(1)
             lt.encode(d["coeffq"], d["cbp"], d["ssd"])
             d2h += 16 * j["cost"].size + 2 * lt.pool_entries + 5 * j["tb"].size
-            for r in range(2):
-                for bs in (8, 16, 32, 64):
-                    a = d[f"t{r}_{bs}"]
-                    tb.check(lib.thorcuda_sad_table_fetch(s.slots[r], bs, a.ctypes.data, a.nbytes))
-                    d2h += a.nbytes
+        tp = mark("lists_submit", tp)
         jobs = (tb.ops.LfJob * B)()
         for k, (s, d) in enumerate(zip(streams, host)):
             jobs[k] = tb.ops.LfJob(s.work.handle, s.org.handle, s.newref.handle, s.job["qp"], 15, None, d["bits"].ctypes.data)
@@ -494,11 +527,14 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
             d2h += w * h * 3 // 2 + d["bits"].size
         for l in lists:
             l.close()
+        tp = mark("tail_submit", tp)
         tb.sync()
+        mark("wait", tp)
 
     for _ in range(2):
         step()
     barrier()
+    phase.clear()
     t0 = time.perf_counter()
     n = max(2, args.e2e_steps)
     for _ in range(n):
@@ -514,6 +550,7 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
     measure_e2e.host = host          # kept for the parity check
     return {"value": B * world * n / dt, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "frames_per_step": B, "steps": n, "ms_per_step": 1e3 * dt / n,
+            "host_ms_per_step": {k: round(1e3 * v / n, 3) for k, v in phase.items()},
             "timing": "host wall clock around submit..thorcuda_sync, max over ranks (includes PCIe copies and list building)"}
 
 

@@ -234,7 +234,9 @@ int  thorcuda_early_skip_batch(const thorcuda_pic *pics, int npics, const thorcu
  * uint16 for bs <= 16, uint32 for bs >= 32.  Rectangular partitions (HOR/VER/QUAD halves) are sums
  * of two entries of the next finer level -- SAD is additive -- so the host forms them itself.
  * The call fails if a window of an existing block would leave the padded reference picture.
- * Tables live in HBM in one of THORCUDA_SAD_SLOTS slots; fetch copies one level to the host.
+ * Tables live in HBM in one of THORCUDA_SAD_SLOTS slots; fetch copies one level to the host on the library's
+ * copy stream (ordered after everything queued before it, overlapping kernels queued after it; the data is valid
+ * after thorcuda_sync(); the next build into the slot waits for it).
  * n (org,ref) pairs are processed in ONE launch.                                                     */
 #define THORCUDA_SAD_SLOTS 64
 /* Host helpers for forming table indices (pure host code, usable before thorcuda_init):

@@ -103,6 +103,22 @@ int d2h(void *dst, const void *src, size_t bytes) {
   THOR_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, g_ctx.stream));
   return 0;
 }
+int d2h_bulk(void *dst, const void *src, size_t bytes) {
+  if (!bytes) return 0;
+  Context &c = g_ctx;
+  THOR_CUDA(cudaEventRecord(c.ev_main, c.stream));
+  THOR_CUDA(cudaStreamWaitEvent(c.copy_stream, c.ev_main, 0));
+  THOR_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.copy_stream));
+  c.copy_pending = true;
+  return 0;
+}
+int copies_fence() {
+  Context &c = g_ctx;
+  if (!c.copy_pending) return 0;
+  THOR_CUDA(cudaEventRecord(c.ev_copy, c.copy_stream));
+  THOR_CUDA(cudaStreamWaitEvent(c.stream, c.ev_copy, 0));
+  return 0;
+}
 int sync_pic_view(thorcuda_pic h) {
   const PicView v = g_ctx.pics[h].view();
   return h2d(g_ctx.d_pics + h, &v, sizeof(v));
@@ -144,6 +160,10 @@ int thorcuda_init(int device) {
     return fail("libthorcuda: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
   THOR_CUDA(cudaSetDevice(device));
   THOR_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  THOR_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+  THOR_CUDA(cudaEventCreateWithFlags(&c.ev_main, cudaEventDisableTiming));
+  THOR_CUDA(cudaEventCreateWithFlags(&c.ev_copy, cudaEventDisableTiming));
+  c.copy_pending = false;
   {  // task lists come from the stream-ordered allocator; keep freed blocks cached instead of returning them to the OS
     cudaMemPool_t pool;
     THOR_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -189,6 +209,7 @@ void thorcuda_shutdown(void) {
   Context &c = ctx();
   if (!c.ready) return;
   cudaStreamSynchronize(c.stream);
+  cudaStreamSynchronize(c.copy_stream);
   compat_reset();
   for (int i = 0; i < 256; i++) if (c.lists[i].used) thorcuda_list_destroy(i);
   for (int i = 0; i < THORCUDA_MAX_PICS; i++) if (c.pics[i].used) thorcuda_pic_destroy(i);
@@ -202,7 +223,10 @@ void thorcuda_shutdown(void) {
   for (int i = 0; i < 64; i++) { cudaEventDestroy(c.tm0[i]); cudaEventDestroy(c.tm1[i]); }
   cudaFree(c.d_pics); c.d_pics = nullptr;
   cudaStreamDestroy(c.stream);
-  c.stream = nullptr;
+  cudaStreamDestroy(c.copy_stream);
+  cudaEventDestroy(c.ev_main); cudaEventDestroy(c.ev_copy);
+  c.stream = c.copy_stream = nullptr;
+  c.ev_main = c.ev_copy = nullptr;
   c.ready = false;
 }
 
@@ -211,6 +235,10 @@ const char *thorcuda_last_error(void) { return ctx().err; }
 int thorcuda_sync(void) {
   THOR_NEED_CTX();
   THOR_CUDA(cudaStreamSynchronize(ctx().stream));
+  if (ctx().copy_pending) {
+    THOR_CUDA(cudaStreamSynchronize(ctx().copy_stream));
+    ctx().copy_pending = false;
+  }
   return 0;
 }
 
@@ -268,6 +296,7 @@ void thorcuda_host_free(void *p) {
   auto &v = ctx().pinned;
   for (size_t i = 0; i < v.size(); i++) if (v[i].first == (uintptr_t)p) { v.erase(v.begin() + i); break; }
   cudaStreamSynchronize(ctx().stream);
+  cudaStreamSynchronize(ctx().copy_stream);      // a bulk fetch may still be writing into it
   cudaFreeHost(p);
 }
 

@@ -59,7 +59,14 @@ struct List {
   int tb_first[5] = {0, 0, 0, 0, 0};
   uint32_t *order = nullptr;              // device: sorted position -> task index
   // COST lists
-  thorcuda_cost_result *results = nullptr;
+  thorcuda_cost_result *results = nullptr;   // the buffer the LAST cost call wrote (one of res_buf)
+  thorcuda_cost_result *res_buf[2] = {nullptr, nullptr};
+  int res_next = 0;
+  // Host copies of a list's outputs run on the copy stream (d2h_late): they drain behind the big table fetches
+  // without holding up the kernels queued after them.  Before anything overwrites or frees a buffer with a copy in
+  // flight, the main stream is fenced (list_fence).  Cost results alternate between two buffers so that the usual
+  // fasthalf -> fastquarter pair never needs the fence.
+  bool late_pool = false, late_res[2] = {false, false};
   const void *tasks() const { return blob; }
   const void *tiles() const { return blob + off_tiles; }
   const uint16_t *map() const { return (const uint16_t *)(blob + off_map); }
@@ -80,6 +87,11 @@ struct Context {
   int device = -1;
   int sm_count = 0;
   cudaStream_t stream = nullptr;
+  // large device->host fetches (SAD tables) run on their own stream so that kernels queued after them keep the SMs
+  // busy while the copy engine drains: see d2h_bulk()
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_main = nullptr, ev_copy = nullptr;
+  bool copy_pending = false;
   uint64_t launches = 0;
   char err[512] = {0};
   Pic pics[THORCUDA_MAX_PICS];
@@ -107,6 +119,12 @@ int h2d(void *dst, const void *src, size_t bytes);
 void *stage_acquire(size_t bytes);
 int stage_commit_copy(void *dst, const void *staged, size_t bytes);
 int d2h(void *dst, const void *src, size_t bytes);
+// device->host copy on the copy stream, ordered after everything queued so far on the main stream; the host data is
+// valid after thorcuda_sync().  Whoever overwrites or frees `src` later must call copies_fence() first.
+int d2h_bulk(void *dst, const void *src, size_t bytes);
+int copies_fence();    // make the main stream wait for the bulk copies queued so far
+struct List;
+int list_fence(List *L);   // ... if the list has output copies in flight
 // refresh the device mirror entry of picture h
 int sync_pic_view(thorcuda_pic h);
 // one stand-alone forward / inverse transform on device buffers (transform.cu), queued on the stream

@@ -172,11 +172,14 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
     if (e == cudaSuccess) e = cudaMallocAsync((void **)&L.ssd, (size_t)ntasks * 4 + 16, c.stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(L.pool, 0, L.pool_entries * sizeof(int16_t) + 64, c.stream);
   } else if (kind == THORCUDA_LIST_COST) {
-    e = cudaMallocAsync((void **)&L.results, (size_t)ntasks * sizeof(thorcuda_cost_result), c.stream);
+    e = cudaMallocAsync((void **)&L.res_buf[0], (size_t)ntasks * sizeof(thorcuda_cost_result), c.stream);
+    if (e == cudaSuccess) e = cudaMallocAsync((void **)&L.res_buf[1], (size_t)ntasks * sizeof(thorcuda_cost_result), c.stream);
+    L.results = L.res_buf[0];
   }
   if (e != cudaSuccess) {
     cudaFreeAsync(L.blob, c.stream); if (L.pool) cudaFreeAsync(L.pool, c.stream); if (L.cbp) cudaFreeAsync(L.cbp, c.stream);
     if (L.ssd) cudaFreeAsync(L.ssd, c.stream);
+    for (int i = 0; i < 2; i++) if (L.res_buf[i]) cudaFreeAsync(L.res_buf[i], c.stream);
     L = List();
     return fail("list: device allocation failed (%s)", cudaGetErrorString(e));
   }
@@ -187,14 +190,27 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
 void thorcuda_list_destroy(thorcuda_list h) {
   List *L = get_list(h);
   if (!L) return;
+  list_fence(L);                              // output copies still in flight on the copy stream finish first
   cudaStream_t st = ctx().stream;             // stream-ordered: queued work that uses the list finishes first
   if (L->blob) cudaFreeAsync(L->blob, st);
   if (L->pool) cudaFreeAsync(L->pool, st);
   if (L->cbp) cudaFreeAsync(L->cbp, st);
   if (L->ssd) cudaFreeAsync(L->ssd, st);
-  if (L->results) cudaFreeAsync(L->results, st);
+  for (int i = 0; i < 2; i++) if (L->res_buf[i]) cudaFreeAsync(L->res_buf[i], st);
   *L = List();
 }
+
+}  // extern "C"
+
+namespace thor {
+int list_fence(List *L) {
+  if (!L->late_pool && !L->late_res[0] && !L->late_res[1]) return 0;
+  L->late_pool = L->late_res[0] = L->late_res[1] = false;
+  return copies_fence();
+}
+}  // namespace thor
+
+extern "C" {
 
 size_t thorcuda_list_pool_entries(thorcuda_list h) {
   List *L = get_list(h);

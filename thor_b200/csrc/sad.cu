@@ -562,7 +562,7 @@ int thorcuda_sad_table_fetch(int slot, int bs, void *host_dst, size_t bytes) {
   const size_t have = thorcuda_sad_table_bytes(slot, bs);
   if (!have) return fail("sad_table_fetch: slot %d has no %dx%d table", slot, bs, bs);
   if (bytes > have) return fail("sad_table_fetch: %zu bytes requested, table has %zu", bytes, have);
-  return d2h(host_dst, thorcuda_sad_table_devptr(slot, bs), bytes);
+  return d2h_bulk(host_dst, thorcuda_sad_table_devptr(slot, bs), bytes);
 }
 
 int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, const thorcuda_pic *refs, int range,
@@ -598,6 +598,8 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
       }
     centre_entries += (size_t)2 * gx * gy;
   }
+  // fetches of the previous tables may still be draining on the copy stream: the build must not overwrite them
+  if (copies_fence()) return -1;
   // (re)size the slots
   for (int i = 0; i < n; i++) {
     Pic *o = get_pic(orgs[i]);
@@ -606,7 +608,7 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
       const int bs = 8 << l;
       const size_t bytes = (size_t)(o->w / bs) * (o->h / bs) * nn * (l < 2 ? 2 : 4);
       if (bytes > s.cap[l]) {
-        if (s.tab[l]) { cudaStreamSynchronize(c.stream); cudaFree(s.tab[l]); s.tab[l] = nullptr; s.cap[l] = 0; }
+        if (s.tab[l]) { cudaStreamSynchronize(c.stream); cudaStreamSynchronize(c.copy_stream); cudaFree(s.tab[l]); s.tab[l] = nullptr; s.cap[l] = 0; }
         if (bytes && cudaMalloc(&s.tab[l], bytes + 64) != cudaSuccess) return fail("sad_table: device allocation of %zu bytes failed", bytes);
         s.cap[l] = bytes;
       }
@@ -661,6 +663,11 @@ int thorcuda_cost_list(thorcuda_list hl, int kind, thorcuda_cost_result *host_re
   CostParams P;
   P.pics = c.d_pics; P.map = L->map();
   P.tasks = (const thorcuda_cost_task *)L->tasks();
+  // results alternate between two buffers: the copy of the previous call may still be in flight on the copy stream
+  const int rb = L->res_next;
+  if (L->late_res[rb] && list_fence(L)) return -1;
+  L->results = L->res_buf[rb];
+  L->res_next = rb ^ 1;
   P.out = L->results; P.ntasks = L->ntasks;
   P.pitch = (L->cost_w + 8) / 4;
   P.warp_words = (L->cost_h + 6) * P.pitch;
@@ -674,7 +681,10 @@ int thorcuda_cost_list(thorcuda_list hl, int kind, thorcuda_cost_result *host_re
     default: k_cost_batch<THORCUDA_COST_SSD><<<grid, CW * 32, smem, c.stream>>>(P); break;
   }
   THOR_LAUNCHED();
-  if (host_results) return d2h(host_results, L->results, (size_t)L->ntasks * sizeof(thorcuda_cost_result));
+  if (host_results) {
+    L->late_res[rb] = true;
+    return d2h_bulk(host_results, L->results, (size_t)L->ntasks * sizeof(thorcuda_cost_result));
+  }
   return 0;
 }
 
