@@ -176,6 +176,73 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------- decoder leg (optional) ----
+LDB_LOW = ["-HQperiod", "12", "-mqpP", "1.2", "-dqpI", "-2", "-lambda_coeffI", "0.8", "-lambda_coeffP", "1.2", "-max_num_ref", "2",
+           "-use_block_contexts", "1", "-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
+           "-enable_bipred", "0", "-encoder_speed", "2"]          # config_LDB_low_complexity.txt
+
+
+def write_clip(path, width, height, frames, seed=42):
+    """Seeded 8-bit I420 clip: box-blurred noise texture translating by (1, 2) samples per frame, slow chroma waves."""
+    rng = np.random.default_rng(seed)
+    big = rng.integers(0, 256, (height + 96, width + 96)).astype(np.float32)
+    for ax in (0, 1):                                   # 5-tap box blur through cumulative sums
+        c = np.cumsum(np.pad(big, [(3, 2) if a == ax else (0, 0) for a in (0, 1)], mode="edge"), axis=ax)
+        big = (np.take(c, range(5, c.shape[ax]), axis=ax) - np.take(c, range(0, c.shape[ax] - 5), axis=ax)) / 5
+    big = np.clip((big - 128) * 3 + 128, 0, 255)
+    yy, xx = np.mgrid[0:height // 2, 0:width // 2]
+    with open(path, "wb") as f:
+        for n in range(frames):
+            dy, dx = n % 64, (2 * n) % 64                         # stays inside the texture margin
+            y = big[32 + dy:32 + dy + height, 32 + dx:32 + dx + width]
+            f.write(np.clip(y + rng.normal(0, 2, y.shape), 0, 255).astype(np.uint8).tobytes())
+            f.write((128 + 60 * np.sin((xx + 2 * n) / 23.0) * np.cos(yy / 29.0)).astype(np.uint8).tobytes())
+            f.write((128 + 60 * np.cos(xx / 27.0) * np.sin((yy + n) / 25.0)).astype(np.uint8).tobytes())
+
+
+def decoder_leg(args):
+    """End-to-end DECODE rate of the reference's Thordec against the same decoder with libthorcuda's fused frame tail
+    hooked in (integration/): a 1080p LDB stream encoded by the reference's Thorenc here, decoded
+    by both, outputs compared byte for byte.  Wall clock of the whole process, file I/O included, best of 3."""
+    import tempfile
+    enc, dec = os.path.join(ROOT, "oracle", "_ref", "Thorenc"), os.path.join(ROOT, "oracle", "_ref", "Thordec")
+    tail = os.path.join(ROOT, "integration", "_build", "Thordec_tail")
+    if not all(os.path.exists(x) for x in (enc, dec, tail)):
+        return {"unavailable": "oracle/_ref/Thorenc, Thordec or integration/_build/Thordec_tail not built"}
+    frames = args.decoder_frames
+    # the decoder cycles through its 33 reference slots before it reuses one, and the hook page-locks each slot the
+    # first time it sees it: both stream lengths lie beyond that warm-up
+    short = 40
+    frames = max(frames, short + 16)
+    with tempfile.TemporaryDirectory() as d:
+        yuv = os.path.join(d, "clip.yuv")
+        write_clip(yuv, args.width, args.height, frames)
+        bits = {}
+        for n in (short, frames):                      # two stream lengths: their difference cancels process start-up
+            bits[n] = os.path.join(d, f"clip{n}.bit")
+            subprocess.run([enc, "-if", yuv, "-of", bits[n], "-rf", os.path.join(d, "rec.yuv"), "-stat", os.path.join(d, "stat.txt"),
+                            "-width", str(args.width), "-height", str(args.height), "-n", str(n), "-f", "60", "-qp", "32"] + LDB_LOW,
+                           check=True, capture_output=True, timeout=900)
+        res, outs = {}, {}
+        for name, exe in (("reference", dec), ("gpu_tail", tail)):
+            best = {}
+            for n in (short, frames):
+                for _ in range(3):
+                    out = os.path.join(d, name + ".yuv")
+                    t0 = time.perf_counter()
+                    subprocess.run([exe, bits[n], out], check=True, capture_output=True, timeout=600)
+                    dt = time.perf_counter() - t0
+                    best[n] = min(best.get(n, dt), dt)
+            outs[name] = open(out, "rb").read()
+            res[name + "_fps"] = round((frames - short) / (best[frames] - best[short]), 2)
+            res[name + "_startup_s"] = round(best[short] - short * (best[frames] - best[short]) / (frames - short), 3)
+        res.update({"frames": frames, "stream": f"LDB_low_complexity {args.width}x{args.height} qp 32, {os.path.getsize(bits[frames])} bytes",
+                    "identical_yuv": outs["reference"] == outs["gpu_tail"],
+                    "note": "marginal decode rate between a short and a long stream (process wall clock, file I/O included); "
+                            "only deblock + CLPF + reference creation run on the GPU, prediction and entropy decoding stay on the host"})
+        return res
+
+
 # --------------------------------------------------------------------------------- GPU arm ----
 METRIC = "1080p pixel-pipeline frames/s (LDB medium-complexity frame job, bit-identical to the reference kernels)"
 
@@ -427,6 +494,8 @@ def run_gpu_arm(args, rank, world, local_rank):
                 "stages": per_stage}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_and_parity(args, tb, streams[0])
+        if world == 1 and args.decoder:
+            line["decoder_e2e"] = decoder_leg(args)
         print(json.dumps(line), flush=True)
     barrier()
     if dist is not None:
@@ -606,6 +675,8 @@ def main():
     ap.add_argument("--distinct-jobs", type=int, default=2, help="distinct synthetic frame jobs cycled over the streams")
     ap.add_argument("--e2e-streams", type=int, default=4)
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail (adds ~1 min)")
+    ap.add_argument("--decoder-frames", type=int, default=72)
     ap.add_argument("--cpu-frames", type=int, default=2)
     ap.add_argument("--range", type=int, default=16)
     ap.add_argument("--width", type=int, default=1920)

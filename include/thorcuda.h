@@ -64,6 +64,10 @@ int          thorcuda_pic_stride(thorcuda_pic p, int plane);
 /* copy the visible area host<->device (queued; host rows at the given strides, any alignment).
  * The HOST buffer must stay valid until thorcuda_sync() (it is the DMA source/target; use
  * thorcuda_host_alloc memory for full-speed transfers).                                              */
+/* Page-lock an existing host allocation (e.g. the malloc'ed planes of the reference's create_yuv_frame) so that
+ * uploads / downloads DMA directly instead of going through the staging ring.  unregister before free().       */
+int  thorcuda_host_register(void *p, size_t bytes);
+void thorcuda_host_unregister(void *p);
 int thorcuda_pic_upload(thorcuda_pic p, const uint8_t *y, const uint8_t *u, const uint8_t *v, int stride_y, int stride_c);
 int thorcuda_pic_download(thorcuda_pic p, uint8_t *y, uint8_t *u, uint8_t *v, int stride_y, int stride_c);
 /* whole padded planes (borders included), for tests                                                 */

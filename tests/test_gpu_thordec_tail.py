@@ -1,0 +1,38 @@
+"""The reference DECODER with libthorcuda's fused frame tail hooked in (integration/):
+integration/_build/Thordec_tail = the reference's decoder objects, its decode_frame.c with the deblock / CLPF /
+create_reference_frame call sites substituted at build time, and integration/dec_tail_hook.c.  Every frame's
+deblocking, CLPF (bits parsed from the stream by the hook) and padded reference come from the B200; the decoded
+.yuv must be byte-identical to the stock decoder's for P-frame, B-frame and interpolated-reference streams."""
+import os
+import subprocess
+
+import pytest
+
+from thorref import REF_DIR, ROOT, run_thorenc, write_clip
+
+pytestmark = pytest.mark.gpu
+TAIL = os.path.join(ROOT, "integration", "_build", "Thordec_tail")
+
+
+def _decode(exe, bit, out):
+    r = subprocess.run([exe, bit, out], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    return open(out, "rb").read()
+
+
+@pytest.mark.parametrize("cfg,w,h,frames,qp", [
+    ("LDB_medium_complexity", 416, 240, 5, 30),     # P frames, bi-pred blocks, CLPF bits per superblock; 240 = 3*64 + 48
+    ("LDB_low_complexity", 200, 136, 4, 36),        # partial superblocks right and bottom
+    ("RA_high_efficiency", 128, 128, 9, 32),        # B frames, interpolated references, tb/pb split, delta qp
+])
+def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp):
+    for need in (os.path.join(REF_DIR, "Thorenc"), os.path.join(REF_DIR, "Thordec"), TAIL):
+        if not os.path.exists(need):
+            pytest.skip(f"{need} not built (needs /root/reference at build time)")
+    yuv = str(tmp_path / "clip.yuv")
+    write_clip(yuv, w, h, frames, seed=77)
+    bit, rec, _ = run_thorenc("Thorenc", cfg, yuv, w, h, frames, qp, str(tmp_path / "enc"))
+    cpu = _decode(os.path.join(REF_DIR, "Thordec"), str(tmp_path / "enc.bit"), str(tmp_path / "cpu.yuv"))
+    gpu = _decode(TAIL, str(tmp_path / "enc.bit"), str(tmp_path / "gpu.yuv"))
+    assert cpu == rec, "stock decoder does not reproduce the encoder's reconstruction"
+    assert gpu == cpu, "decoder output with the GPU frame tail differs"

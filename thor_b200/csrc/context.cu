@@ -291,6 +291,21 @@ void *thorcuda_host_alloc(size_t bytes) {
   ctx().pinned.push_back({(uintptr_t)p, bytes});
   return p;
 }
+int thorcuda_host_register(void *p, size_t bytes) {
+  THOR_NEED_CTX();
+  if (!p || !bytes) return fail("host_register: empty range");
+  THOR_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+  ctx().pinned.push_back({(uintptr_t)p, bytes});
+  return 0;
+}
+void thorcuda_host_unregister(void *p) {
+  if (!p) return;
+  auto &v = ctx().pinned;
+  for (size_t i = 0; i < v.size(); i++) if (v[i].first == (uintptr_t)p) { v.erase(v.begin() + i); break; }
+  cudaStreamSynchronize(ctx().stream);
+  cudaStreamSynchronize(ctx().copy_stream);
+  cudaHostUnregister(p);
+}
 void thorcuda_host_free(void *p) {
   if (!p) return;
   auto &v = ctx().pinned;

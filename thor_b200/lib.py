@@ -57,6 +57,7 @@ def cdll():
                 ("thorcuda_init", I, [I]),
                 ("thorcuda_timer_begin", I, []), ("thorcuda_timer_end", I, [I]), ("thorcuda_timer_elapsed_ms", C.c_float, [I]),
                 ("thorcuda_flush_l2", I, [Z]),
+                ("thorcuda_host_register", I, [V, Z]), ("thorcuda_host_unregister", None, [V]),
                 ("thorcuda_pic_create", I, [I, I, I, I]), ("thorcuda_pic_destroy", None, [I]), ("thorcuda_pic_stride", I, [I, I]),
                 ("thorcuda_pic_upload", I, [I, V, V, V, I, I]), ("thorcuda_pic_download", I, [I, V, V, V, I, I]),
                 ("thorcuda_pic_download_padded", I, [I, V, V, V]), ("thorcuda_pic_upload_padded", I, [I, V, V, V]),
