@@ -3,10 +3,42 @@
 (INTEGRATION.md 2.2).  Nothing of the reference is stored in this repository: the script names the three call
 sites it replaces and fails loudly if the reference no longer has them.
 
-usage: apply_hooks.py <reference>/dec/decode_frame.c <out.c>"""
+usage: apply_hooks.py tail  <reference>/dec/decode_frame.c <out.c>     frame tail only
+       apply_hooks.py recon <reference>/dec/decode_frame.c <out.c>     + device-resident reconstruction (2.3)
+       apply_hooks.py block <reference>/dec/decode_block.c <out.c>     the block-level call sites of 2.3"""
+import re
 import sys
 
+mode = sys.argv[1]
+sys.argv = [sys.argv[0]] + sys.argv[2:]
 src = open(sys.argv[1]).read()
+
+if mode == "block":
+    # prediction and reconstruction calls of decode_block() become task recorders with the same arguments
+    n_l = len(re.findall(r"get_inter_prediction_luma\s*\(", src))
+    n_c = len(re.findall(r"get_inter_prediction_chroma\s*\(", src))
+    n_r = len(re.findall(r"decode_and_reconstruct_block_inter\(rec_", src))
+    n_i = len(re.findall(r"decode_and_reconstruct_block_intra\(rec_", src))
+    if (n_l, n_c, n_r, n_i) != (9, 18, 3, 3):
+        raise SystemExit(f"apply_hooks: decode_block.c call sites changed: {(n_l, n_c, n_r, n_i)}")
+    src = re.sub(r"get_inter_prediction_luma\s*\(", "hk_luma(", src)
+    src = re.sub(r"get_inter_prediction_chroma\s*\(", "hk_chroma(", src)
+    src = src.replace("decode_and_reconstruct_block_inter(rec_", "hk_recon_inter(rec_")
+    src = src.replace("decode_and_reconstruct_block_intra(rec_", "hk_recon_intra(rec_")
+    proto = ("void hk_luma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, int pstride, mv_t *mv, int sign, int bipred);\n"
+             "void hk_chroma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, int pstride, mv_t *mv, int sign);\n"
+             "void hk_recon_inter(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock, int16_t *coeffq, int tb_split);\n"
+             "void hk_recon_intra(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock, int16_t *coeffq, int tb_split, int upright_available,\n"
+             "                    int downleft_available, intra_mode_t intra_mode, int ypos, int xpos, int width, int comp);\n")
+    anchor = "extern int chroma_qp[52];\n"
+    if src.count(anchor) != 1:
+        raise SystemExit("apply_hooks: anchor for the prototypes not found in decode_block.c")
+    src = src.replace(anchor, anchor + proto)
+    open(sys.argv[2], "w").write(src)
+    raise SystemExit(0)
+
+tail_call = "thorcuda_dec_tail(decoder_info, stream, qp);" if mode == "tail" else "thorcuda_dec_flush(decoder_info, stream, qp);"
+ref_call = "thorcuda_dec_make_reference" if mode == "tail" else "thorcuda_dec_fetch_reference"
 
 
 def once(text, needle):
@@ -19,16 +51,23 @@ def once(text, needle):
 inc = '#include "temporal_interp.h"\n'
 i = once(src, inc) + len(inc)
 src = (src[:i] + "void thorcuda_dec_tail(decoder_info_t *decoder_info, stream_t *stream, int qp);\n"
-       "void thorcuda_dec_make_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n" + src[i:])
+       "void thorcuda_dec_make_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n"
+       "void thorcuda_dec_frame_begin(decoder_info_t *decoder_info);\n"
+       "void thorcuda_dec_flush(decoder_info_t *decoder_info, stream_t *stream, int qp);\n"
+       "void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n" + src[i:])
+if mode == "recon":
+    loop = "for (k=0;k<num_sb_ver;k++){"
+    i = once(src, loop)
+    src = src[:i] + "thorcuda_dec_frame_begin(decoder_info);\n  " + src[i:]
 # 2. deblock_frame_y / deblock_frame_uv / clpf_frame  ->  one fused call
 a = once(src, "if (decoder_info->deblocking){")
 b = once(src, "/* Sliding window operation")
 for fn in ("deblock_frame_y(", "deblock_frame_uv(", "clpf_frame("):
     if fn not in src[a:b]:
         raise SystemExit(f"apply_hooks: {fn} not where expected")
-src = src[:a] + "thorcuda_dec_tail(decoder_info, stream, qp);\n\n  " + src[b:]
+src = src[:a] + tail_call + "\n\n  " + src[b:]
 # 3. create_reference_frame  ->  fetch the reference the same launch produced
 c = "create_reference_frame(decoder_info->ref[0],decoder_info->rec);"
 i = once(src, c)
-src = src[:i] + "thorcuda_dec_make_reference(decoder_info->ref[0],decoder_info->rec);" + src[i + len(c):]
+src = src[:i] + ref_call + "(decoder_info->ref[0],decoder_info->rec);" + src[i + len(c):]
 open(sys.argv[2], "w").write(src)

@@ -1,0 +1,302 @@
+/* Reference-side binding of libthorcuda's batched reconstruction for the Thor DECODER.
+ *
+ * With this file the decoder keeps only bitstream parsing on the host.  decode_block()'s calls of
+ *     get_inter_prediction_luma / _chroma            -> hk_luma / hk_chroma          (record one prediction task)
+ *     decode_and_reconstruct_block_inter / _intra    -> hk_recon_inter / _intra      (record transform-block tasks,
+ *                                                                                     copy the parsed coefficients)
+ * are substituted in a scratch copy at build time (integration/apply_hooks.py); nothing is computed while the
+ * superblocks are parsed.  After the last superblock thorcuda_dec_flush() runs the frame on the device:
+ *     inter prediction of every block (one launch)  ->  dequantise + inverse transform + reconstruct of every coded
+ *     inter block (one launch)  ->  intra blocks in wavefront levels (a block joins a level once the blocks owning its
+ *     neighbour samples are done; inter blocks are level 0)  ->  the fused frame tail of dec_tail_hook.c.
+ * Reference pictures stay on the device (one device picture per slot of the decoder's reference ring); the filtered
+ * frame and the padded reference are still copied back because this decoder writes its output and builds
+ * interpolated references (interpolate_frames) on the host.
+ * Compiled against the reference's own headers where they lie. */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include "global.h"
+#include "maindec.h"
+#include "thorcuda.h"
+
+void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thorcuda_pic dev_rec, thorcuda_pic dev_ref_out);
+
+static decoder_info_t *g_di;
+static void need(int rc) {
+  if (rc) fatalerror((char *)thorcuda_last_error());
+}
+
+/* ---- device twins of the decoder's pictures ---- */
+#define MAX_TWINS 64
+static struct { const yuv_frame_t *host; thorcuda_pic dev; } twins[MAX_TWINS];
+static int ntwins;
+static thorcuda_pic dev_rec = -1;
+
+static thorcuda_pic twin_of(const yuv_frame_t *f) {
+  for (int i = 0; i < ntwins; i++) if (twins[i].host == f) return twins[i].dev;
+  if (ntwins == MAX_TWINS) fatalerror("thorcuda hook: too many reference pictures");
+  const thorcuda_pic p = thorcuda_pic_create(f->width, f->height, f->pad_hor_y, f->pad_hor_c);
+  if (p < 0) fatalerror((char *)thorcuda_last_error());
+  twins[ntwins].host = f; twins[ntwins].dev = p;
+  ntwins++;
+  return p;
+}
+
+/* ---- per-frame task lists ---- */
+typedef struct { uint8_t plane, size, qp, level_known; uint16_t x, y; int coef; /* index into pool, -1: all zero */
+                 int intra; /* index into intra[], -1: inter */ } Tb;
+static thorcuda_pred_task *pred; static int npred, cpred;
+static Tb *tbs; static int ntbs, ctbs;
+static thorcuda_intra_task *intra; static int nintra, cintra;
+static int16_t *pool; static size_t npool, cpool;
+static thorcuda_pic pics[96]; static const yuv_frame_t *pic_host[96]; static int npics;
+static const yuv_frame_t *interp_used;
+static int last_luma = -1;      /* prediction task the next luma call may complete to a bi-prediction */
+
+static void *grow(void *p, int *cap, int need_n, size_t elem) {
+  if (need_n <= *cap) return p;
+  *cap = need_n * 2 + 1024;
+  p = realloc(p, (size_t)*cap * elem);
+  if (!p) fatalerror("thorcuda hook: out of memory");
+  return p;
+}
+
+void thorcuda_dec_frame_begin(decoder_info_t *di) {
+  g_di = di;
+  if (dev_rec < 0) {
+    const char *dev = getenv("THORCUDA_DEVICE");
+    need(thorcuda_init(dev ? atoi(dev) : 0));
+    dev_rec = thorcuda_pic_create(di->width, di->height, 0, 0);
+    if (dev_rec < 0) fatalerror((char *)thorcuda_last_error());
+  }
+  npred = ntbs = nintra = 0; npool = 0; last_luma = -1; interp_used = NULL;
+  npics = 1; pics[0] = dev_rec; pic_host[0] = NULL;
+}
+
+static int pic_index(const yuv_frame_t *f) {
+  for (int i = 1; i < npics; i++) if (pic_host[i] == f) return i;
+  if (npics == 96) fatalerror("thorcuda hook: too many pictures in one frame");
+  pics[npics] = twin_of(f); pic_host[npics] = f;
+  if (f == g_di->interp_frames[0]) interp_used = f;
+  return npics++;
+}
+
+/* which picture does a sample pointer of decode_block() point into, and where */
+static const yuv_frame_t *locate(const uint8_t *p, int *x, int *y) {
+  const yuv_frame_t *cand[MAX_REF_FRAMES + 1];
+  int n = 0;
+  for (int i = 0; i < MAX_REF_FRAMES; i++) if (g_di->ref[i]) cand[n++] = g_di->ref[i];
+  if (g_di->interp_frames[0]) cand[n++] = g_di->interp_frames[0];
+  for (int i = 0; i < n; i++) {
+    const yuv_frame_t *f = cand[i];
+    if (p >= f->y && p < f->y + (size_t)f->height * f->stride_y) {
+      const size_t off = (size_t)(p - f->y);
+      *y = (int)(off / f->stride_y); *x = (int)(off % f->stride_y);
+      return f;
+    }
+  }
+  fatalerror("thorcuda hook: prediction source is not a reference picture");
+  return NULL;
+}
+
+void hk_luma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, int pstride, mv_t *mv, int sign, int bipred) {
+  int x, y;
+  const yuv_frame_t *f = locate(ref, &x, &y);
+  const int ri = pic_index(f);
+  if (last_luma >= 0) {
+    thorcuda_pred_task *t = &pred[last_luma];
+    if (t->x == x && t->y == y && t->w == width && t->h == height && t->ref1 < 0) {     /* second half of a bi-prediction */
+      t->ref1 = (int8_t)ri; t->mv1x = mv->x; t->mv1y = mv->y; t->sign1 = (uint8_t)sign;
+      last_luma = -1;
+      return;
+    }
+  }
+  pred = (thorcuda_pred_task *)grow(pred, &cpred, npred + 1, sizeof(*pred));
+  thorcuda_pred_task *t = &pred[npred];
+  memset(t, 0, sizeof(*t));
+  t->x = (uint16_t)x; t->y = (uint16_t)y; t->w = (uint8_t)width; t->h = (uint8_t)height;
+  t->ref0 = (int8_t)ri; t->ref1 = -1; t->mv0x = mv->x; t->mv0y = mv->y; t->sign0 = (uint8_t)sign; t->dst = 0;
+  last_luma = npred++;
+}
+
+void hk_chroma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, int pstride, mv_t *mv, int sign) {
+  /* the prediction task covers all three planes with the luma vector, as the decoder does */
+}
+
+static void where_in_rec(const uint8_t *p, int *plane, int *x, int *y) {
+  const yuv_frame_t *r = g_di->rec;
+  const uint8_t *base[3] = {r->y, r->u, r->v};
+  for (int pl = 0; pl < 3; pl++) {
+    const int stride = pl ? r->stride_c : r->stride_y, h = pl ? r->height / 2 : r->height;
+    if (p >= base[pl] && p < base[pl] + (size_t)h * stride) {
+      const size_t off = (size_t)(p - base[pl]);
+      *plane = pl; *y = (int)(off / stride); *x = (int)(off % stride);
+      return;
+    }
+  }
+  fatalerror("thorcuda hook: reconstruction target is not the current picture");
+}
+
+/* one transform block: its parsed levels (n x n array, low q x q corner used) go to the frame's pool */
+static int add_tb(int plane, int x, int y, int n, int qp, const int16_t *coeffq, int intra_index) {
+  const int q = n < 16 ? n : 16;
+  int any = 0;
+  for (int i = 0; i < q && !any; i++)
+    for (int j = 0; j < q; j++) if (coeffq[i * n + j]) { any = 1; break; }
+  if (!any && intra_index < 0) return -1;             /* inter block without coefficients: the prediction is the result */
+  tbs = (Tb *)grow(tbs, &ctbs, ntbs + 1, sizeof(*tbs));
+  Tb *t = &tbs[ntbs];
+  t->plane = (uint8_t)plane; t->size = (uint8_t)n; t->qp = (uint8_t)qp; t->x = (uint16_t)x; t->y = (uint16_t)y;
+  t->intra = intra_index; t->coef = -1;
+  if (any) {
+    if (npool + (size_t)q * q > cpool) {
+      cpool = (npool + (size_t)q * q) * 2 + 65536;
+      pool = (int16_t *)realloc(pool, cpool * sizeof(int16_t));
+      if (!pool) fatalerror("thorcuda hook: out of memory");
+    }
+    t->coef = (int)npool;
+    for (int i = 0; i < q; i++) memcpy(pool + npool + (size_t)i * q, coeffq + i * n, (size_t)q * sizeof(int16_t));
+    npool += (size_t)q * q;
+  }
+  return ntbs++;
+}
+
+void hk_recon_inter(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock, int16_t *coeffq, int tb_split) {
+  int plane, x, y;
+  where_in_rec(rec, &plane, &x, &y);
+  last_luma = -1;
+  if (!tb_split) { add_tb(plane, x, y, size, qp, coeffq, -1); return; }
+  const int s2 = size / 2;
+  for (int i = 0; i < size; i += s2)
+    for (int j = 0; j < size; j += s2)
+      add_tb(plane, x + j, y + i, s2, qp, coeffq + (2 * (i / s2) + (j / s2)) * s2 * s2, -1);
+}
+
+void hk_recon_intra(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock, int16_t *coeffq, int tb_split, int upright_available,
+                    int downleft_available, intra_mode_t intra_mode, int ypos, int xpos, int width, int comp) {
+  last_luma = -1;
+  const int s = tb_split ? size / 2 : size;
+  for (int i = 0; i < size; i += s)
+    for (int j = 0; j < size; j += s) {
+      intra = (thorcuda_intra_task *)grow(intra, &cintra, nintra + 1, sizeof(*intra));
+      thorcuda_intra_task *t = &intra[nintra];
+      memset(t, 0, sizeof(*t));
+      t->x = (uint16_t)(xpos + j); t->y = (uint16_t)(ypos + i); t->cb_x = (uint16_t)xpos; t->size = (uint8_t)s; t->plane = (uint8_t)comp;
+      t->mode = (uint8_t)intra_mode; t->src = t->dst = 0;
+      /* availability of the extra sample per sub-block: common/intra_prediction.c:106-110 */
+      const int up = tb_split ? (j == 0 || (i == 0 && upright_available)) : upright_available;
+      const int dl = tb_split ? (j == 0 && (i == 0 || downleft_available)) : downleft_available;
+      t->flags = (uint8_t)((up ? 1 : 0) | (dl ? 2 : 0));
+      add_tb(comp, xpos + j, ypos + i, s, qp, tb_split ? coeffq + (2 * (i / s) + (j / s)) * s * s : coeffq, nintra);
+      nintra++;
+    }
+}
+
+/* ---- frame execution ---- */
+static thorcuda_tb_task *lt; static int clt;
+static int16_t *lpool; static size_t clpool;
+static int *order, *lvl; static int corder, clvl_cap;
+static int32_t *lmap[3]; static size_t lmap_n[3];
+
+static void run_tbs(const int *idx, int n) {            /* dequantise + inverse + reconstruct of tbs[idx[..]] in place */
+  lt = (thorcuda_tb_task *)grow(lt, &clt, n, sizeof(*lt));
+  size_t need_pool = 0;
+  int m = 0;
+  for (int k = 0; k < n; k++) {
+    const Tb *t = &tbs[idx ? idx[k] : k];
+    if (t->coef < 0) continue;                          /* intra block without coefficients: prediction already in place */
+    const int q = t->size < 16 ? t->size : 16;
+    need_pool += ((size_t)q * q + 7) & ~(size_t)7;
+    m++;
+  }
+  if (!m) return;
+  if (need_pool > clpool) { clpool = need_pool * 2; lpool = (int16_t *)realloc(lpool, clpool * sizeof(int16_t)); }
+  size_t off = 0;
+  m = 0;
+  for (int k = 0; k < n; k++) {
+    const Tb *t = &tbs[idx ? idx[k] : k];
+    if (t->coef < 0) continue;
+    const int q = t->size < 16 ? t->size : 16;
+    thorcuda_tb_task *d = &lt[m++];
+    memset(d, 0, sizeof(*d));
+    d->x = t->x; d->y = t->y; d->size = t->size; d->plane = t->plane; d->qp = t->qp; d->org = d->pred = d->rec = 0;
+    d->coeff_offset = (uint32_t)off;
+    memcpy(lpool + off, pool + t->coef, (size_t)q * q * sizeof(int16_t));
+    off += ((size_t)q * q + 7) & ~(size_t)7;
+  }
+  need(thorcuda_reconstruct_blocks(pics, 1, lt, m, lpool));
+}
+
+void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
+  const yuv_frame_t *rec = di->rec;
+  if (interp_used) {      /* built on the host by interpolate_frames + pad_yuv_frame just before this frame */
+    const yuv_frame_t *f = interp_used;
+    need(thorcuda_pic_upload_padded(twin_of(f), f->y - f->pad_ver_y * f->stride_y - f->pad_hor_y,
+                                    f->u - f->pad_ver_c * f->stride_c - f->pad_hor_c, f->v - f->pad_ver_c * f->stride_c - f->pad_hor_c));
+  }
+  /* 1. every inter block: prediction straight into the picture, then the coded ones are reconstructed in place */
+  if (npred) need(thorcuda_predict_blocks(pics, npics, pred, npred, di->bipred, 3));
+  int ninter = 0;
+  order = (int *)grow(order, &corder, ntbs + 1, sizeof(int));
+  for (int i = 0; i < ntbs; i++) if (tbs[i].intra < 0) order[ninter++] = i;
+  if (ninter) run_tbs(order, ninter);
+  /* 2. intra blocks by wavefront level */
+  if (nintra) {
+    int maxl = 0;
+    lvl = (int *)grow(lvl, &clvl_cap, ntbs + 1, sizeof(int));
+    for (int pl = 0; pl < 3; pl++) {
+      const size_t n = (size_t)((pl ? rec->width / 2 : rec->width) / 4 + 1) * ((pl ? rec->height / 2 : rec->height) / 4 + 1);
+      if (n > lmap_n[pl]) { lmap[pl] = (int32_t *)realloc(lmap[pl], n * sizeof(int32_t)); lmap_n[pl] = n; }
+      memset(lmap[pl], 0, n * sizeof(int32_t));
+    }
+    for (int i = 0; i < ntbs; i++) {
+      const Tb *t = &tbs[i];
+      lvl[i] = 0;
+      if (t->intra < 0) continue;                       /* inter blocks are level 0 and their map entries stay 0 */
+      const thorcuda_intra_task *it = &intra[t->intra];
+      const int pl = t->plane, W = ((pl ? rec->width / 2 : rec->width) / 4 + 1), u = t->size / 4, ux = t->x / 4, uy = t->y / 4;
+      const int32_t *M = lmap[pl];
+      int dep = 0;
+      if (t->y > 0) {
+        const int x1 = ux + u + ((it->flags & 1) ? 1 : 0);
+        for (int x = ux > 0 ? ux - 1 : 0; x < x1; x++) if (M[(uy - 1) * W + x] > dep) dep = M[(uy - 1) * W + x];
+      }
+      if (t->x > 0) {
+        const int y1 = uy + u + ((it->flags & 2) ? 1 : 0);
+        for (int y = uy > 0 ? uy - 1 : 0; y < y1; y++) if (M[y * W + ux - 1] > dep) dep = M[y * W + ux - 1];
+      }
+      lvl[i] = dep + 1;
+      if (lvl[i] > maxl) maxl = lvl[i];
+      for (int y = uy; y < uy + u; y++)
+        for (int x = ux; x < ux + u; x++) lmap[pl][y * W + x] = lvl[i];
+    }
+    /* counting sort of the intra blocks by level */
+    int *count = (int *)calloc((size_t)maxl + 2, sizeof(int));
+    for (int i = 0; i < ntbs; i++) if (lvl[i]) count[lvl[i] + 1]++;
+    for (int l = 1; l <= maxl + 1; l++) count[l] += count[l - 1];
+    int *sorted = (int *)malloc((size_t)(nintra + 1) * sizeof(int)), *fill = (int *)malloc((size_t)(maxl + 2) * sizeof(int));
+    memcpy(fill, count, (size_t)(maxl + 2) * sizeof(int));
+    for (int i = 0; i < ntbs; i++) if (lvl[i]) sorted[fill[lvl[i]]++] = i;
+    thorcuda_intra_task *batch = (thorcuda_intra_task *)malloc((size_t)(nintra + 1) * sizeof(*batch));
+    for (int l = 1; l <= maxl; l++) {
+      const int a = count[l], b = count[l + 1];
+      for (int k = a; k < b; k++) batch[k - a] = intra[tbs[sorted[k]].intra];
+      need(thorcuda_intra_predict_blocks(pics, 1, batch, b - a));
+      run_tbs(sorted + a, b - a);
+    }
+    free(batch); free(fill); free(sorted); free(count);
+  }
+  /* 3. the frame tail, into the device twin of the ring slot the new reference will occupy */
+  thorcuda_dec_tail_device(di, stream, qp, dev_rec, twin_of(di->ref[MAX_REF_FRAMES - 1]));
+}
+
+/* create_reference_frame: the padded reference already sits in the slot's device twin; the host copy feeds
+ * interpolate_frames */
+void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
+  ref->frame_num = rec->frame_num;
+  need(thorcuda_pic_download_padded(twin_of(ref), ref->y - ref->pad_ver_y * ref->stride_y - ref->pad_hor_y,
+                                    ref->u - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c,
+                                    ref->v - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c));
+  need(thorcuda_sync());
+}

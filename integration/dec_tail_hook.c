@@ -70,7 +70,6 @@ static void setup(const yuv_frame_t *rec) {
   dev_rec = thorcuda_pic_create(dev_w, dev_h, 0, 0);
   dev_ref = thorcuda_pic_create(dev_w, dev_h, PADDING_Y, PADDING_Y / 2);
   if (dev_rec < 0 || dev_ref < 0) fatalerror((char *)thorcuda_last_error());
-  sb_bits = (uint8_t *)thorcuda_host_alloc((size_t)(dev_w / MAX_BLOCK_SIZE + 1) * (dev_h / MAX_BLOCK_SIZE + 1));
 }
 
 /* does clpf_frame ask its decision callback about superblock (k, l)?  -- any 8x8 block that is not bi-predicted and
@@ -85,15 +84,13 @@ static int sb_signals(const deblock_data_t *dd, int width, int k, int l) {
   return 0;
 }
 
-void thorcuda_dec_tail(decoder_info_t *di, stream_t *stream, int qp) {
+/* blockinfo + CLPF bits + fused launch + download of the filtered frame, for a reconstruction that already sits in
+ * device picture `rec_dev`; the new padded reference is written into `ref_out_dev` */
+void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thorcuda_pic rec_dev, thorcuda_pic ref_out_dev) {
   yuv_frame_t *rec = di->rec;
-  if (t_on < 0) { t_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (t_on) atexit(report); }
-  setup(rec);
   double t0 = now_ms();
-  lock_frame(rec);
-  need(thorcuda_pic_upload(dev_rec, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));
-  MARK(0);
-  need(thorcuda_blockinfo_upload(dev_rec, di->deblock_data));
+  if (!sb_bits) sb_bits = (uint8_t *)thorcuda_host_alloc((size_t)(rec->width / MAX_BLOCK_SIZE + 1) * (rec->height / MAX_BLOCK_SIZE + 1));
+  need(thorcuda_blockinfo_upload(rec_dev, di->deblock_data));
   MARK(1);
   int stages = THORCUDA_LF_MAKE_REF;
   if (di->deblocking) stages |= THORCUDA_LF_DEBLOCK_Y | THORCUDA_LF_DEBLOCK_UV;
@@ -108,11 +105,22 @@ void thorcuda_dec_tail(decoder_info_t *di, stream_t *stream, int qp) {
     stages |= THORCUDA_LF_CLPF;
   }
   MARK(2);
-  need(thorcuda_loopfilter_frame(dev_rec, -1, dev_ref, qp, stages, sb_bits, NULL));
+  need(thorcuda_loopfilter_frame(rec_dev, -1, ref_out_dev, qp, stages, sb_bits, NULL));
   MARK(3);
   /* the filtered frame is what gets written out and displayed */
-  need(thorcuda_pic_download(dev_rec, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));
+  need(thorcuda_pic_download(rec_dev, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));
   MARK(4);
+}
+
+void thorcuda_dec_tail(decoder_info_t *di, stream_t *stream, int qp) {
+  yuv_frame_t *rec = di->rec;
+  if (t_on < 0) { t_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (t_on) atexit(report); }
+  setup(rec);
+  double t0 = now_ms();
+  lock_frame(rec);
+  need(thorcuda_pic_upload(dev_rec, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));
+  MARK(0);
+  thorcuda_dec_tail_device(di, stream, qp, dev_rec, dev_ref);
 }
 
 void thorcuda_dec_make_reference(yuv_frame_t *ref, yuv_frame_t *rec) {

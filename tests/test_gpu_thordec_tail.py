@@ -11,7 +11,7 @@ import pytest
 from thorref import REF_DIR, ROOT, run_thorenc, write_clip
 
 pytestmark = pytest.mark.gpu
-TAIL = os.path.join(ROOT, "integration", "_build", "Thordec_tail")
+BUILD = os.path.join(ROOT, "integration", "_build")
 
 
 def _decode(exe, bit, out):
@@ -25,7 +25,12 @@ def _decode(exe, bit, out):
     ("LDB_low_complexity", 200, 136, 4, 36),        # partial superblocks right and bottom
     ("RA_high_efficiency", 128, 128, 9, 32),        # B frames, interpolated references, tb/pb split, delta qp
 ])
-def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp):
+@pytest.mark.parametrize("exe", ["Thordec_tail", "Thordec_gpu"])
+def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
+    """Thordec_tail: deblock + CLPF + reference creation on the device (2.2).  Thordec_gpu: additionally every
+    prediction, inverse transform and reconstruction -- inter blocks in two launches, intra blocks in wavefront
+    levels -- with the reference pictures resident on the device (2.3); the host only parses the stream."""
+    TAIL = os.path.join(BUILD, exe)
     for need in (os.path.join(REF_DIR, "Thorenc"), os.path.join(REF_DIR, "Thordec"), TAIL):
         if not os.path.exists(need):
             pytest.skip(f"{need} not built (needs /root/reference at build time)")
