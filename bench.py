@@ -206,9 +206,9 @@ def decoder_leg(args):
     by both, outputs compared byte for byte.  Wall clock of the whole process, file I/O included, best of 3."""
     import tempfile
     enc, dec = os.path.join(ROOT, "oracle", "_ref", "Thorenc"), os.path.join(ROOT, "oracle", "_ref", "Thordec")
-    tail = os.path.join(ROOT, "integration", "_build", "Thordec_tail")
-    if not all(os.path.exists(x) for x in (enc, dec, tail)):
-        return {"unavailable": "oracle/_ref/Thorenc, Thordec or integration/_build/Thordec_tail not built"}
+    tail, full = os.path.join(ROOT, "integration", "_build", "Thordec_tail"), os.path.join(ROOT, "integration", "_build", "Thordec_gpu")
+    if not all(os.path.exists(x) for x in (enc, dec, tail, full)):
+        return {"unavailable": "oracle/_ref/Thorenc, Thordec or integration/_build/Thordec_tail, Thordec_gpu not built"}
     frames = args.decoder_frames
     # the decoder cycles through its 33 reference slots before it reuses one, and the hook page-locks each slot the
     # first time it sees it: both stream lengths lie beyond that warm-up
@@ -224,7 +224,7 @@ def decoder_leg(args):
                             "-width", str(args.width), "-height", str(args.height), "-n", str(n), "-f", "60", "-qp", "32"] + LDB_LOW,
                            check=True, capture_output=True, timeout=900)
         res, outs = {}, {}
-        for name, exe in (("reference", dec), ("gpu_tail", tail)):
+        for name, exe in (("reference", dec), ("gpu_tail", tail), ("gpu_recon", full)):
             best = {}
             for n in (short, frames):
                 for _ in range(3):
@@ -236,10 +236,12 @@ def decoder_leg(args):
             outs[name] = open(out, "rb").read()
             res[name + "_fps"] = round((frames - short) / (best[frames] - best[short]), 2)
             res[name + "_startup_s"] = round(best[short] - short * (best[frames] - best[short]) / (frames - short), 3)
+            res[name + "_seconds"] = {str(n): round(best[n], 3) for n in (short, frames)}
         res.update({"frames": frames, "stream": f"LDB_low_complexity {args.width}x{args.height} qp 32, {os.path.getsize(bits[frames])} bytes",
-                    "identical_yuv": outs["reference"] == outs["gpu_tail"],
+                    "identical_yuv": outs["reference"] == outs["gpu_tail"] == outs["gpu_recon"],
                     "note": "marginal decode rate between a short and a long stream (process wall clock, file I/O included); "
-                            "only deblock + CLPF + reference creation run on the GPU, prediction and entropy decoding stay on the host"})
+                            "gpu_tail: deblock + CLPF + reference creation on the GPU; gpu_recon: prediction, inverse transform and "
+                            "reconstruction as well (references device-resident), the host parses the stream and writes the output"})
         return res
 
 
@@ -675,8 +677,8 @@ def main():
     ap.add_argument("--distinct-jobs", type=int, default=2, help="distinct synthetic frame jobs cycled over the streams")
     ap.add_argument("--e2e-streams", type=int, default=4)
     ap.add_argument("--e2e-steps", type=int, default=5)
-    ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail (adds ~1 min)")
-    ap.add_argument("--decoder-frames", type=int, default=72)
+    ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail / the whole reconstruction on the GPU (adds ~1 min)")
+    ap.add_argument("--decoder-frames", type=int, default=104)
     ap.add_argument("--cpu-frames", type=int, default=2)
     ap.add_argument("--range", type=int, default=16)
     ap.add_argument("--width", type=int, default=1920)

@@ -13,15 +13,45 @@
  * frame and the padded reference are still copied back because this decoder writes its output and builds
  * interpolated references (interpolate_frames) on the host.
  * Compiled against the reference's own headers where they lie. */
+#define _POSIX_C_SOURCE 199309L
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include "global.h"
 #include "maindec.h"
+#include "getbits.h"
 #include "thorcuda.h"
 
 void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thorcuda_pic dev_rec, thorcuda_pic dev_ref_out);
 
+/* THORCUDA_HOOK_TIMING=1: host milliseconds per phase and frame, printed at exit */
+static double tp[6], t_mark, t_hk[3];
+#define HK_T0 const double hk0_ = tp_on > 0 ? ms_now() : 0
+#define HK_T1(i) do { if (tp_on > 0 && tp_seen >= 36) t_hk[i] += ms_now() - hk0_; } while (0)
+static int tp_frames, tp_on = -1, tp_levels, tp_intra, tp_pred, tp_tbs;
+static double ms_now(void) {
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return 1e3 * ts.tv_sec + 1e-6 * ts.tv_nsec;
+}
+static int tp_seen;            /* frames seen; the first 36 (CUDA start-up, first use of every reference slot) are not counted */
+static void lap(int i) {
+  if (tp_on <= 0) return;
+  const double t = ms_now();
+  if (tp_seen >= 36) tp[i] += t - t_mark;
+  t_mark = t;
+}
+static void tp_report(void) {
+  static const char *name[6] = {"parse + record", "inter submit", "intra levels", "tail", "fetch ref + sync", "between frames"};
+  const int n = tp_frames ? tp_frames : 1;
+  for (int i = 0; i < 6; i++) fprintf(stderr, "thorcuda recon hook: %-18s %8.3f ms/frame\n", name[i], tp[i] / n);
+  fprintf(stderr, "thorcuda recon hook: inside hk_luma %.3f, hk_recon_inter %.3f, hk_recon_intra %.3f ms/frame\n", t_hk[0] / n, t_hk[1] / n, t_hk[2] / n);
+  fprintf(stderr, "thorcuda recon hook: per frame %d prediction tasks, %d transform blocks, %d intra blocks in %d levels\n",
+          tp_pred / n, tp_tbs / n, tp_intra / n, tp_levels / n);
+}
+
+static int dry = -1;      /* THORCUDA_HOOK_DRY=1: record nothing, run nothing (measures the host's parsing alone; output is garbage) */
 static decoder_info_t *g_di;
 static void need(int rc) {
   if (rc) fatalerror((char *)thorcuda_last_error());
@@ -64,6 +94,10 @@ static void *grow(void *p, int *cap, int need_n, size_t elem) {
 
 void thorcuda_dec_frame_begin(decoder_info_t *di) {
   g_di = di;
+  if (dry < 0) dry = getenv("THORCUDA_HOOK_DRY") != NULL;
+  if (tp_on < 0) { tp_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (tp_on) { atexit(tp_report); t_mark = ms_now(); } }
+  lap(5);
+  if (dry) return;
   if (dev_rec < 0) {
     const char *dev = getenv("THORCUDA_DEVICE");
     need(thorcuda_init(dev ? atoi(dev) : 0));
@@ -102,6 +136,8 @@ static const yuv_frame_t *locate(const uint8_t *p, int *x, int *y) {
 
 void hk_luma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, int pstride, mv_t *mv, int sign, int bipred) {
   int x, y;
+  if (dry) return;
+  HK_T0;
   const yuv_frame_t *f = locate(ref, &x, &y);
   const int ri = pic_index(f);
   if (last_luma >= 0) {
@@ -109,6 +145,7 @@ void hk_luma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, i
     if (t->x == x && t->y == y && t->w == width && t->h == height && t->ref1 < 0) {     /* second half of a bi-prediction */
       t->ref1 = (int8_t)ri; t->mv1x = mv->x; t->mv1y = mv->y; t->sign1 = (uint8_t)sign;
       last_luma = -1;
+      HK_T1(0);
       return;
     }
   }
@@ -118,6 +155,7 @@ void hk_luma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, i
   t->x = (uint16_t)x; t->y = (uint16_t)y; t->w = (uint8_t)width; t->h = (uint8_t)height;
   t->ref0 = (int8_t)ri; t->ref1 = -1; t->mv0x = mv->x; t->mv0y = mv->y; t->sign0 = (uint8_t)sign; t->dst = 0;
   last_luma = npred++;
+  HK_T1(0);
 }
 
 void hk_chroma(uint8_t *pblock, uint8_t *ref, int width, int height, int stride, int pstride, mv_t *mv, int sign) {
@@ -164,18 +202,23 @@ static int add_tb(int plane, int x, int y, int n, int qp, const int16_t *coeffq,
 
 void hk_recon_inter(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock, int16_t *coeffq, int tb_split) {
   int plane, x, y;
+  if (dry) return;
+  HK_T0;
   where_in_rec(rec, &plane, &x, &y);
   last_luma = -1;
-  if (!tb_split) { add_tb(plane, x, y, size, qp, coeffq, -1); return; }
+  if (!tb_split) { add_tb(plane, x, y, size, qp, coeffq, -1); HK_T1(1); return; }
   const int s2 = size / 2;
   for (int i = 0; i < size; i += s2)
     for (int j = 0; j < size; j += s2)
       add_tb(plane, x + j, y + i, s2, qp, coeffq + (2 * (i / s2) + (j / s2)) * s2 * s2, -1);
+  HK_T1(1);
 }
 
 void hk_recon_intra(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock, int16_t *coeffq, int tb_split, int upright_available,
                     int downleft_available, intra_mode_t intra_mode, int ypos, int xpos, int width, int comp) {
   last_luma = -1;
+  if (dry) return;
+  HK_T0;
   const int s = tb_split ? size / 2 : size;
   for (int i = 0; i < size; i += s)
     for (int j = 0; j < size; j += s) {
@@ -191,6 +234,7 @@ void hk_recon_intra(uint8_t *rec, int stride, int size, int qp, uint8_t *pblock,
       add_tb(comp, xpos + j, ypos + i, s, qp, tb_split ? coeffq + (2 * (i / s) + (j / s)) * s * s : coeffq, nintra);
       nintra++;
     }
+  HK_T1(2);
 }
 
 /* ---- frame execution ---- */
@@ -230,6 +274,9 @@ static void run_tbs(const int *idx, int n) {            /* dequantise + inverse 
 
 void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   const yuv_frame_t *rec = di->rec;
+  lap(0);
+  if (dry) { if (di->clpf && getbits(stream, 1)) fatalerror("dry run needs a stream without CLPF"); return; }
+  if (tp_seen >= 36) { tp_pred += npred; tp_tbs += ntbs; tp_intra += nintra; }
   if (interp_used) {      /* built on the host by interpolate_frames + pad_yuv_frame just before this frame */
     const yuv_frame_t *f = interp_used;
     need(thorcuda_pic_upload_padded(twin_of(f), f->y - f->pad_ver_y * f->stride_y - f->pad_hor_y,
@@ -241,6 +288,7 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   order = (int *)grow(order, &corder, ntbs + 1, sizeof(int));
   for (int i = 0; i < ntbs; i++) if (tbs[i].intra < 0) order[ninter++] = i;
   if (ninter) run_tbs(order, ninter);
+  lap(1);
   /* 2. intra blocks by wavefront level */
   if (nintra) {
     int maxl = 0;
@@ -279,6 +327,7 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
     memcpy(fill, count, (size_t)(maxl + 2) * sizeof(int));
     for (int i = 0; i < ntbs; i++) if (lvl[i]) sorted[fill[lvl[i]]++] = i;
     thorcuda_intra_task *batch = (thorcuda_intra_task *)malloc((size_t)(nintra + 1) * sizeof(*batch));
+    if (tp_seen >= 36) tp_levels += maxl;
     for (int l = 1; l <= maxl; l++) {
       const int a = count[l], b = count[l + 1];
       for (int k = a; k < b; k++) batch[k - a] = intra[tbs[sorted[k]].intra];
@@ -287,16 +336,21 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
     }
     free(batch); free(fill); free(sorted); free(count);
   }
+  lap(2);
   /* 3. the frame tail, into the device twin of the ring slot the new reference will occupy */
   thorcuda_dec_tail_device(di, stream, qp, dev_rec, twin_of(di->ref[MAX_REF_FRAMES - 1]));
+  lap(3);
 }
 
 /* create_reference_frame: the padded reference already sits in the slot's device twin; the host copy feeds
  * interpolate_frames */
 void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
   ref->frame_num = rec->frame_num;
+  if (dry) { lap(4); if (tp_seen++ >= 36) tp_frames++; return; }
   need(thorcuda_pic_download_padded(twin_of(ref), ref->y - ref->pad_ver_y * ref->stride_y - ref->pad_hor_y,
                                     ref->u - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c,
                                     ref->v - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c));
   need(thorcuda_sync());
+  lap(4);
+  if (tp_seen++ >= 36) tp_frames++;
 }
