@@ -5,7 +5,8 @@ sites it replaces and fails loudly if the reference no longer has them.
 
 usage: apply_hooks.py tail  <reference>/dec/decode_frame.c <out.c>     frame tail only
        apply_hooks.py recon <reference>/dec/decode_frame.c <out.c>     + device-resident reconstruction (2.3)
-       apply_hooks.py block <reference>/dec/decode_block.c <out.c>     the block-level call sites of 2.3"""
+       apply_hooks.py block <reference>/dec/decode_block.c <out.c>     the block-level call sites of 2.3
+       apply_hooks.py enc   <reference>/enc/encode_frame.c <out.c>     frame tail of the encoder (2.2)"""
 import re
 import sys
 
@@ -34,6 +35,28 @@ if mode == "block":
     if src.count(anchor) != 1:
         raise SystemExit("apply_hooks: anchor for the prototypes not found in decode_block.c")
     src = src.replace(anchor, anchor + proto)
+    open(sys.argv[2], "w").write(src)
+    raise SystemExit(0)
+
+if mode == "enc":
+    # enc/encode_frame.c: the same three call sites on the encoder side
+    def once_e(text, needle):
+        if text.count(needle) != 1:
+            raise SystemExit(f"apply_hooks: expected exactly one {needle!r} in {sys.argv[1]}")
+        return text.index(needle)
+    inc = "extern int chroma_qp[52];\n"
+    i = once_e(src, inc) + len(inc)
+    src = (src[:i] + "void thorcuda_enc_tail(encoder_info_t *encoder_info, stream_t *stream, int qp);\n"
+           "void thorcuda_enc_make_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n" + src[i:])
+    a = once_e(src, "if (encoder_info->params->deblocking){")
+    b = once_e(src, "/* Sliding window operation")
+    for fn in ("deblock_frame_y(", "deblock_frame_uv(", "clpf_frame(", "putbits(1, !sb_signal, stream);"):
+        if fn not in src[a:b]:
+            raise SystemExit(f"apply_hooks: {fn} not where expected")
+    src = src[:a] + "thorcuda_enc_tail(encoder_info, stream, qp);\n\n  " + src[b:]
+    c = "create_reference_frame(encoder_info->ref[0],encoder_info->rec);"
+    i = once_e(src, c)
+    src = src[:i] + "thorcuda_enc_make_reference(encoder_info->ref[0],encoder_info->rec);" + src[i + len(c):]
     open(sys.argv[2], "w").write(src)
     raise SystemExit(0)
 

@@ -43,3 +43,28 @@ def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
     gpu = _decode(TAIL, str(tmp_path / "enc.bit"), str(tmp_path / "gpu.yuv"))
     assert cpu == rec, "stock decoder does not reproduce the encoder's reconstruction"
     assert gpu == cpu, "decoder output with the GPU frame tail differs"
+
+
+@pytest.mark.parametrize("cfg,w,h,frames,qp", [
+    ("LDB_medium_complexity", 416, 240, 4, 30),
+    ("LDB_low_complexity", 200, 136, 4, 36),
+    ("RA_high_efficiency", 128, 128, 9, 32),
+])
+def test_thorenc_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp):
+    """integration/_build/Thorenc_tail: the reference ENCODER with deblocking, the CLPF decision (against the original
+    frame) and reference creation on the device; bitstream and reconstruction must match the stock encoder's."""
+    exe = os.path.join(BUILD, "Thorenc_tail")
+    for need in (os.path.join(REF_DIR, "Thorenc"), exe):
+        if not os.path.exists(need):
+            pytest.skip(f"{need} not built (needs /root/reference at build time)")
+    from thorref import THOR_CONFIGS
+    yuv = str(tmp_path / "clip.yuv")
+    write_clip(yuv, w, h, frames, seed=91)
+    bit_cpu, rec_cpu, _ = run_thorenc("Thorenc", cfg, yuv, w, h, frames, qp, str(tmp_path / "cpu"))
+    pre = str(tmp_path / "gpu")
+    cmd = [exe, "-if", yuv, "-of", pre + ".bit", "-rf", pre + "_rec.yuv", "-stat", pre + "_stat.txt", "-width", str(w), "-height", str(h),
+           "-n", str(frames), "-f", "30", "-qp", str(qp)] + THOR_CONFIGS[cfg]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert open(pre + ".bit", "rb").read() == bit_cpu, "bitstream differs"
+    assert open(pre + "_rec.yuv", "rb").read() == rec_cpu, "reconstruction differs"
