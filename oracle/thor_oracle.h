@@ -76,6 +76,16 @@ void orc_intra_predict(const uint8_t *left, const uint8_t *top, uint8_t top_left
 int  orc_upright_available(int ypos, int xpos, int size, int width);
 int  orc_downleft_available(int ypos, int xpos, int size, int height);
 
+/* ---- temporal interpolation (orc_interp.c; reference common/temporal_interp.c:61-1053) ---- */
+int  orc_interp_levels(int width, int height);
+void orc_interp_counters(long *out6, int reset);
+void orc_interp_field_size(int width, int height, int *bw, int *bh);
+void orc_interpolate_frames(uint8_t *out_y, uint8_t *out_u, uint8_t *out_v, int out_stride_y, int out_stride_c,
+                            const uint8_t *ref0_y, const uint8_t *ref0_u, const uint8_t *ref0_v,
+                            const uint8_t *ref1_y, const uint8_t *ref1_u, const uint8_t *ref1_v,
+                            int width, int height, int stride_y, int stride_c, int pad_y, int ratio, int pos,
+                            int16_t *dbg_mv0, int16_t *dbg_mv1);
+
 /* ---- motion-search costs (enc/encode_block.c:497-828) ---- */
 unsigned orc_sad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h);
 unsigned orc_widesad(const uint8_t *a, const uint8_t *b, int as, int bs, int w, int h, int *x);

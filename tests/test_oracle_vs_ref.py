@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from thorref import (BLOCKINFO, Picture, blocky_frame, YuvFrame, load_oracle, load_ref, ptr, random_blockinfo,
+from thorref import (BLOCKINFO, Picture, blocky_frame, YuvFrame, interp_pair, load_oracle, load_ref, ptr, random_blockinfo,
                      set_ref_simd, smooth_frame)
 
 ref = load_ref()
@@ -432,3 +432,51 @@ def test_intra_availability():
             for xpos in range(0, 192, size):
                 assert ref.get_upright_available(ypos, xpos, size, 192) == orc.orc_upright_available(ypos, xpos, size, 192)
                 assert ref.get_downleft_available(ypos, xpos, size, 192) == orc.orc_downleft_available(ypos, xpos, size, 192)
+
+
+# ------------------------------------------------------------------ temporal interpolation (8f #2) ----
+def oracle_interpolate(p0, p1, ratio, pos, want_field=False):
+    """oracle/orc_interp.c on two thorref.Picture references -> Picture (visible part) [, mv0, mv1]"""
+    w, h = p0.width, p0.height
+    out = Picture(w, h, 96, 48)
+    bw, bh = C.c_int(), C.c_int()
+    orc.orc_interp_field_size(w, h, C.byref(bw), C.byref(bh))
+    mv0 = np.zeros((bh.value, bw.value, 2), np.int16)
+    mv1 = np.zeros((bh.value, bw.value, 2), np.int16)
+    orc.orc_interpolate_frames(C.c_void_p(out.origin_ptr(0)), C.c_void_p(out.origin_ptr(1)), C.c_void_p(out.origin_ptr(2)), out.stride_y, out.stride_c,
+                               C.c_void_p(p0.origin_ptr(0)), C.c_void_p(p0.origin_ptr(1)), C.c_void_p(p0.origin_ptr(2)),
+                               C.c_void_p(p1.origin_ptr(0)), C.c_void_p(p1.origin_ptr(1)), C.c_void_p(p1.origin_ptr(2)),
+                               w, h, p0.stride_y, p0.stride_c, p0.pad_y, ratio, pos, ptr(mv0), ptr(mv1))
+    return (out, mv0, mv1) if want_field else out
+
+
+@pytest.mark.parametrize("case", [(416, 240, "scene", (3, 5)), (192, 136, "scene", (-7, 12)), (128, 128, "noise", None),
+                                  (320, 192, "scene", (40, -70)), (64, 48, "scene", (1, 2)), (200, 72, "noise", None),
+                                  (416, 240, "scene", (6, 200))])
+@pytest.mark.parametrize("rp", [(2, 1), (4, 1), (4, 3), (8, 3), (3, 1)])
+def test_interpolate_frames(simd, case, rp):
+    w, h, kind, motion = case
+    ratio, pos = rp
+    p0, p1 = interp_pair(w, h, seed=w + ratio, motion=motion or (0, 0), kind=kind)
+    s0, s1 = p0.as_ref_struct(), p1.as_ref_struct()
+    want = Picture(w, h, 96, 48)
+    sw = want.as_ref_struct()
+    ref.interpolate_frames(C.byref(sw), C.byref(s0), C.byref(s1), ratio, pos)
+    got = oracle_interpolate(p0, p1, ratio, pos)
+    for i in range(3):
+        assert np.array_equal(want.plane(i), got.plane(i)), f"plane {i}"
+    assert not np.array_equal(got.plane(0), p0.plane(0)) and not np.array_equal(got.plane(0), p1.plane(0))
+
+
+def test_interpolate_coverage():
+    """the cases above reach every branch: clamped SADs, skipped blocks, all three blend forms, refinement rounds"""
+    tot = np.zeros(6, np.int64)
+    for (w, h, kind, motion) in [(416, 240, "scene", (3, 5)), (416, 240, "scene", (6, 200)), (128, 128, "noise", None)]:
+        for (ratio, pos) in [(2, 1), (8, 3)]:
+            p0, p1 = interp_pair(w, h, seed=w + ratio, motion=motion or (0, 0), kind=kind)
+            orc.orc_interp_counters(None, 1)
+            oracle_interpolate(p0, p1, ratio, pos)
+            c = np.zeros(6, np.int64)
+            orc.orc_interp_counters(ptr(c), 0)
+            tot += c
+    assert (tot > 0).all(), tot

@@ -102,6 +102,13 @@ class Picture:
         f.pad_hor_c = f.pad_ver_c = self.pad_c
         return f
 
+    def pad_edges(self):
+        """edge replication into the border (reference pad_yuv_frame, common/common_frame.c:405-462)"""
+        for i, (b, p) in enumerate(((self.buf_y, self.pad_y), (self.buf_u, self.pad_c), (self.buf_v, self.pad_c))):
+            if p:
+                b[...] = np.pad(self.plane(i), p, mode="edge")[:b.shape[0], :b.shape[1]] if b.shape[1] == self.plane(i).shape[1] + 2 * p \
+                    else np.pad(np.pad(self.plane(i), p, mode="edge"), ((0, 0), (0, b.shape[1] - self.plane(i).shape[1] - 2 * p)))
+
     def copy(self):
         q = Picture(self.width, self.height, self.pad_y, self.pad_c)
         q.buf_y[...], q.buf_u[...], q.buf_v[...] = self.buf_y, self.buf_u, self.buf_v
@@ -123,6 +130,35 @@ def smooth_frame(width, height, seed, shift=(0, 0)):
     u = (128 + 60 * np.sin((xx + shift[1]) / 23.0) * np.cos(yy / 29.0)).astype(np.uint8)
     v = (128 + 60 * np.cos(xx / 27.0) * np.sin((yy + shift[0]) / 25.0)).astype(np.uint8)
     return y, u, v
+
+
+def interp_pair(width, height, seed, motion=(3, 5), kind="scene"):
+    """Two padded reference pictures (pad 96/48 like the codec's reference ring) for the temporal-interpolation tests:
+    a textured background moving by `motion` (dy, dx) between them, a static band on the left (skip path), an object
+    moving the other way, noise.  kind="noise": two unrelated pictures (the search wanders, vectors leave the picture)."""
+    rng = np.random.default_rng(seed)
+    pics = []
+    for k in range(2):
+        if kind == "noise":
+            y = rng.integers(0, 256, (height, width), dtype=np.uint8)
+            u = rng.integers(0, 256, (height // 2, width // 2), dtype=np.uint8)
+            v = rng.integers(0, 256, (height // 2, width // 2), dtype=np.uint8)
+        else:
+            y, u, v = smooth_frame(width, height, seed)
+            y, u, v = (np.roll(a, (k * motion[0] // d, k * motion[1] // d), (0, 1)).copy() for a, d in ((y, 1), (u, 2), (v, 2)))
+            if k == 1:
+                y0 = pics[0].plane(0)
+                band = max(16, width // 4)
+                y[:, :band] = y0[:, :band]                                   # static part
+                oh, ow = height // 3, width // 3
+                oy, ox = height // 3, width // 2
+                y[oy:oy + oh, ox:ox + ow] = y0[oy + 2:oy + 2 + oh, ox - 6:ox - 6 + ow]   # an object moving against the background
+            y = np.clip(y.astype(np.int16) + rng.integers(-2, 3, y.shape), 0, 255).astype(np.uint8)
+        p = Picture(width, height, 96, 48)
+        p.set_visible(y, u, v)
+        p.pad_edges()
+        pics.append(p)
+    return pics
 
 
 def random_blockinfo(width, height, rng, p_split=0.55, intra_frac=0.2):
