@@ -203,6 +203,23 @@ typedef struct {
 } thorcuda_intra_task;      /* 12 bytes */
 int thorcuda_intra_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, int ntasks);
 
+/* ------------------------------------------------------------ temporal interpolation ---- */
+/* interpolate_frames (common/temporal_interp.c:972-1053): the picture between two references that B frames of the
+ * RA / HDB configurations use as reference 0 (callers: enc/mainenc.c:328,385, dec/decode_frame.c:92-109).
+ *   ref0, ref1  padded pictures of equal geometry (the codec's reference ring: border 96 / 48); the border must be
+ *               valid (thorcuda_pad_frame / the fused frame tail), it is read wherever a vector leaves the picture
+ *   ratio, pos  distance between the references and position of the new picture, the reference's arguments:
+ *               weights wt0 = pos > ratio/2 ? pos : ratio - pos, wt1 = ratio - wt0; the picture roles swap when
+ *               pos > ratio/2 (:120-126)
+ *   dst         receives the visible picture; the caller pads it (thorcuda_pad_frame) like decode_frame.c:107.
+ * Pictures smaller than 32 in either dimension have no pyramid level: the call does nothing, like the reference.
+ * All work is queued on the library stream (3 + 2 launches per level).                                             */
+int thorcuda_interpolate_frames(thorcuda_pic dst, thorcuda_pic ref0, thorcuda_pic ref1, int ratio, int pos);
+int thorcuda_interp_levels(int width, int height);     /* pyramid levels: min(4, (int)(log2(min(w, h)) - 4)) (:977) */
+/* inspection: the final full-resolution motion field of the last call (vectors into the farther picture, 1/8 pel,
+ * x then y, one per 8x8 block, bw = 2*ceil(w/16) per row); mv1 may be NULL to query the size only. Synchronous.   */
+int thorcuda_interp_field(int16_t *mv1, int *bw, int *bh);
+
 /* ------------------------------------------------------------ early-skip test ---- */
 /* Significance test of a skip candidate (check_early_skip_block, enc/encode_block.c:2612-2741) for one
  * size x size luma sub-block (size = min(block size, 16): 16 or 8) and its two chroma sub-blocks, given the

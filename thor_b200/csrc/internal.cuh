@@ -130,6 +130,7 @@ int sync_pic_view(thorcuda_pic h);
 // one stand-alone forward / inverse transform on device buffers (transform.cu), queued on the stream
 int tb_raw(int size, int fast, int inverse, const int16_t *d_in, int16_t *d_out);
 void compat_reset();   // compat.cu: drop the per-block API's scratch pictures (thorcuda_shutdown)
+void interp_reset();   // tinterp.cu: drop the interpolation scratch (thorcuda_shutdown)
 
 #define THOR_CUDA(call)                                                                   \
   do {                                                                                    \

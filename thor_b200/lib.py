@@ -77,6 +77,8 @@ def cdll():
                 ("thorcuda_early_skip_thresholds", None, [I, I, C.c_float, V, V]),
                 ("thorcuda_early_skip_batch", I, [V, I, V, I, V]),
                 ("thorcuda_intra_predict_blocks", I, [V, I, V, I]),
+                ("thorcuda_interpolate_frames", I, [I, I, I, I, I]), ("thorcuda_interp_levels", I, [I, I]),
+                ("thorcuda_interp_field", I, [V, V, V]),
                 ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):
             fn = getattr(_lib, name)   # AttributeError here means a stale libthorcuda.so: rebuild
             fn.restype = res

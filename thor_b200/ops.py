@@ -11,6 +11,7 @@ executing on the B200 through libthorcuda (no CPU fallback).
   encode_blocks / reconstruct_blocks   encode_and_reconstruct_block_inter (enc/encode_block.c:1469-1532),
                                        decode_and_reconstruct_block_inter (dec/decode_block.c:90-120)
   intra_predict_blocks                 make_top_and_left + get_intra_prediction (common/intra_prediction.c:57-389)
+  interpolate_frames                   interpolate_frames (common/temporal_interp.c:972-1053)
   early_skip_thresholds / early_skip_batch  check_early_skip_sub_block(C) (enc/encode_block.c:2507-2610)
   sad_table / cost_batch               sad_calc, widesad_calc, sad_calc_fasthalf/fastquarter, ssd_calc
                                        (enc/encode_block.c:497-797)
@@ -172,6 +173,21 @@ def intra_predict_blocks(pics, tasks):
     """Intra prediction of independent blocks (one wavefront level): neighbours from pics[src], prediction into pics[dst]."""
     t = np.ascontiguousarray(tasks, INTRA_TASK)
     check(cdll().thorcuda_intra_predict_blocks(_handles(pics), len(pics), _p(t), t.size))
+
+
+def interpolate_frames(new_frame, ref0, ref1, ratio, pos):
+    """interpolate_frames (common/temporal_interp.c:972): the picture at `pos` of `ratio` between two padded references
+    into new_frame's visible area (pad it afterwards like decode_frame.c:107).  Queued; no sync."""
+    check(cdll().thorcuda_interpolate_frames(new_frame.handle, ref0.handle, ref1.handle, int(ratio), int(pos)))
+
+
+def interp_field():
+    """the level-0 motion field of the last interpolate_frames call: int16 [bh, bw, 2] (x, y; 1/8 pel, into the farther picture)"""
+    bw, bh = C.c_int(), C.c_int()
+    check(cdll().thorcuda_interp_field(None, C.byref(bw), C.byref(bh)))
+    mv = np.zeros((bh.value, bw.value, 2), np.int16)
+    check(cdll().thorcuda_interp_field(_p(mv), None, None))
+    return mv
 
 
 def clip_mv(mv, ypos, xpos, fwidth, fheight, size, sign):
