@@ -182,6 +182,14 @@ LDB_LOW = ["-HQperiod", "12", "-mqpP", "1.2", "-dqpI", "-2", "-lambda_coeffI", "
            "-enable_bipred", "0", "-encoder_speed", "2"]          # config_LDB_low_complexity.txt
 
 
+_RA = ["-HQperiod", "1", "-num_reorder_pics", "7", "-interp_ref", "1", "-intra_period", "64", "-dqpI", "-2", "-dqpB0", "3", "-dqpB1", "1",
+       "-dqpB2", "0", "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.1", "-mqpB1", "1.2", "-mqpB2", "1.3", "-lambda_coeffI", "0.8",
+       "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2"]
+RA_LOW = _RA + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0", "-max_num_ref", "2",
+                "-use_block_contexts", "1", "-enable_bipred", "1", "-encoder_speed", "2"]       # config_RA_low_complexity.txt
+DEC_CONFIGS = {"LDB_low_complexity": LDB_LOW, "RA_low_complexity": RA_LOW}
+
+
 def write_clip(path, width, height, frames, seed=42):
     """Seeded 8-bit I420 clip: box-blurred noise texture translating by (1, 2) samples per frame, slow chroma waves."""
     rng = np.random.default_rng(seed)
@@ -221,7 +229,8 @@ def decoder_leg(args):
         for n in (short, frames):                      # two stream lengths: their difference cancels process start-up
             bits[n] = os.path.join(d, f"clip{n}.bit")
             subprocess.run([enc, "-if", yuv, "-of", bits[n], "-rf", os.path.join(d, "rec.yuv"), "-stat", os.path.join(d, "stat.txt"),
-                            "-width", str(args.width), "-height", str(args.height), "-n", str(n), "-f", "60", "-qp", "32"] + LDB_LOW,
+                            "-width", str(args.width), "-height", str(args.height), "-n", str(n), "-f", "60", "-qp", "32"]
+                           + DEC_CONFIGS[args.decoder_config],
                            check=True, capture_output=True, timeout=900)
         res, outs = {}, {}
         for name, exe in (("reference", dec), ("gpu_tail", tail), ("gpu_recon", full)):
@@ -237,7 +246,7 @@ def decoder_leg(args):
             res[name + "_fps"] = round((frames - short) / (best[frames] - best[short]), 2)
             res[name + "_startup_s"] = round(best[short] - short * (best[frames] - best[short]) / (frames - short), 3)
             res[name + "_seconds"] = {str(n): round(best[n], 3) for n in (short, frames)}
-        res.update({"frames": frames, "stream": f"LDB_low_complexity {args.width}x{args.height} qp 32, {os.path.getsize(bits[frames])} bytes",
+        res.update({"frames": frames, "stream": f"{args.decoder_config} {args.width}x{args.height} qp 32, {os.path.getsize(bits[frames])} bytes",
                     "identical_yuv": outs["reference"] == outs["gpu_tail"] == outs["gpu_recon"],
                     "note": "marginal decode rate between a short and a long stream (process wall clock, file I/O included); "
                             "gpu_tail: deblock + CLPF + reference creation on the GPU; gpu_recon: prediction, inverse transform and "
@@ -679,6 +688,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail / the whole reconstruction on the GPU (adds ~1 min)")
     ap.add_argument("--decoder-frames", type=int, default=104)
+    ap.add_argument("--decoder-config", default="LDB_low_complexity", choices=sorted(DEC_CONFIGS),
+                    help="stream of the decoder leg; RA_low_complexity has B frames with interpolated references (one interpolate_frames per B frame)")
     ap.add_argument("--cpu-frames", type=int, default=2)
     ap.add_argument("--range", type=int, default=16)
     ap.add_argument("--width", type=int, default=1920)

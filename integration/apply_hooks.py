@@ -77,11 +77,18 @@ src = (src[:i] + "void thorcuda_dec_tail(decoder_info_t *decoder_info, stream_t 
        "void thorcuda_dec_make_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n"
        "void thorcuda_dec_frame_begin(decoder_info_t *decoder_info);\n"
        "void thorcuda_dec_flush(decoder_info_t *decoder_info, stream_t *stream, int qp);\n"
-       "void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n" + src[i:])
+       "void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n"
+       "void thorcuda_dec_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos);\n" + src[i:])
 if mode == "recon":
     loop = "for (k=0;k<num_sb_ver;k++){"
     i = once(src, loop)
     src = src[:i] + "thorcuda_dec_frame_begin(decoder_info);\n  " + src[i:]
+    # interpolated reference: interpolate_frames + pad_yuv_frame on the device twins of the reference ring
+    m = re.findall(r"interpolate_frames\(decoder_info->interp_frames\[0\], ref1, ref2, off1\+off2 , off2\);\s*"
+                   r"pad_yuv_frame\(decoder_info->interp_frames\[0\]\);", src)
+    if len(m) != 1:
+        raise SystemExit("apply_hooks: interpolate_frames call site changed in decode_frame.c")
+    src = src.replace(m[0], "thorcuda_dec_interpolate(decoder_info->interp_frames[0], ref1, ref2, off1+off2, off2);")
 # 2. deblock_frame_y / deblock_frame_uv / clpf_frame  ->  one fused call
 a = once(src, "if (decoder_info->deblocking){")
 b = once(src, "/* Sliding window operation")

@@ -9,9 +9,9 @@
  *     inter prediction of every block (one launch)  ->  dequantise + inverse transform + reconstruct of every coded
  *     inter block (one launch)  ->  intra blocks in wavefront levels (a block joins a level once the blocks owning its
  *     neighbour samples are done; inter blocks are level 0)  ->  the fused frame tail of dec_tail_hook.c.
- * Reference pictures stay on the device (one device picture per slot of the decoder's reference ring); the filtered
- * frame and the padded reference are still copied back because this decoder writes its output and builds
- * interpolated references (interpolate_frames) on the host.
+ * Reference pictures stay on the device (one device picture per slot of the decoder's reference ring), and so do the
+ * interpolated references of B frames (interpolate_frames + pad_yuv_frame run on the ring's device twins); only the
+ * filtered frame is copied back, because this decoder writes its output on the host.
  * Compiled against the reference's own headers where they lie. */
 #define _POSIX_C_SOURCE 199309L
 #include <stdio.h>
@@ -81,7 +81,6 @@ static Tb *tbs; static int ntbs, ctbs;
 static thorcuda_intra_task *intra; static int nintra, cintra;
 static int16_t *pool; static size_t npool, cpool;
 static thorcuda_pic pics[96]; static const yuv_frame_t *pic_host[96]; static int npics;
-static const yuv_frame_t *interp_used;
 static int last_luma = -1;      /* prediction task the next luma call may complete to a bi-prediction */
 
 static void *grow(void *p, int *cap, int need_n, size_t elem) {
@@ -104,7 +103,7 @@ void thorcuda_dec_frame_begin(decoder_info_t *di) {
     dev_rec = thorcuda_pic_create(di->width, di->height, 0, 0);
     if (dev_rec < 0) fatalerror((char *)thorcuda_last_error());
   }
-  npred = ntbs = nintra = 0; npool = 0; last_luma = -1; interp_used = NULL;
+  npred = ntbs = nintra = 0; npool = 0; last_luma = -1;
   npics = 1; pics[0] = dev_rec; pic_host[0] = NULL;
 }
 
@@ -112,7 +111,6 @@ static int pic_index(const yuv_frame_t *f) {
   for (int i = 1; i < npics; i++) if (pic_host[i] == f) return i;
   if (npics == 96) fatalerror("thorcuda hook: too many pictures in one frame");
   pics[npics] = twin_of(f); pic_host[npics] = f;
-  if (f == g_di->interp_frames[0]) interp_used = f;
   return npics++;
 }
 
@@ -277,11 +275,6 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   lap(0);
   if (dry) { if (di->clpf && getbits(stream, 1)) fatalerror("dry run needs a stream without CLPF"); return; }
   if (tp_seen >= 36) { tp_pred += npred; tp_tbs += ntbs; tp_intra += nintra; }
-  if (interp_used) {      /* built on the host by interpolate_frames + pad_yuv_frame just before this frame */
-    const yuv_frame_t *f = interp_used;
-    need(thorcuda_pic_upload_padded(twin_of(f), f->y - f->pad_ver_y * f->stride_y - f->pad_hor_y,
-                                    f->u - f->pad_ver_c * f->stride_c - f->pad_hor_c, f->v - f->pad_ver_c * f->stride_c - f->pad_hor_c));
-  }
   /* 1. every inter block: prediction straight into the picture, then the coded ones are reconstructed in place */
   if (npred) need(thorcuda_predict_blocks(pics, npics, pred, npred, di->bipred, 3));
   int ninter = 0;
@@ -342,14 +335,19 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   lap(3);
 }
 
-/* create_reference_frame: the padded reference already sits in the slot's device twin; the host copy feeds
- * interpolate_frames */
+/* interpolate_frames + pad_yuv_frame (dec/decode_frame.c:92-109) on the device twins: nothing travels */
+void thorcuda_dec_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos) {
+  if (dry < 0) dry = getenv("THORCUDA_HOOK_DRY") != NULL;
+  if (dry) return;
+  need(thorcuda_interpolate_frames(twin_of(dst), twin_of(ref0), twin_of(ref1), ratio, pos));
+  need(thorcuda_pad_frame(twin_of(dst)));
+}
+
+/* create_reference_frame: the padded reference already sits in the slot's device twin, which is all the decoder
+ * reads from now on (prediction and interpolation are on the device); the host only waits for the output frame */
 void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
   ref->frame_num = rec->frame_num;
   if (dry) { lap(4); if (tp_seen++ >= 36) tp_frames++; return; }
-  need(thorcuda_pic_download_padded(twin_of(ref), ref->y - ref->pad_ver_y * ref->stride_y - ref->pad_hor_y,
-                                    ref->u - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c,
-                                    ref->v - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c));
   need(thorcuda_sync());
   lap(4);
   if (tp_seen++ >= 36) tp_frames++;

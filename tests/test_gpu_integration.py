@@ -25,6 +25,7 @@ def _decode(exe, bit, out):
     ("LDB_low_complexity", 200, 136, 4, 36),        # partial superblocks right and bottom
     ("RA_high_efficiency", 128, 128, 9, 32),        # B frames, interpolated references, tb/pb split, delta qp
     ("RA_high_efficiency", 192, 136, 17, 38),       # two sub-GOPs of the B hierarchy, partial superblock row, coarse qp
+    ("RA_low_complexity", 416, 240, 17, 32),        # 4-level interpolation pyramid (device-side in Thordec_gpu), 240 = 3*64 + 48
     ("LDB_medium_complexity", 136, 72, 14, 22),     # fine qp (dense coefficients), HQ-period frame, 33-slot ring not yet wrapped
 ])
 @pytest.mark.parametrize("exe", ["Thordec_tail", "Thordec_gpu"])

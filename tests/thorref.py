@@ -235,6 +235,8 @@ THOR_CONFIGS = {
                                  "-enable_bipred", "0", "-encoder_speed", "2"],
     "LDB_medium_complexity": _LD + ["-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "0.8",
                                     "-enable_bipred", "1", "-encoder_speed", "1"],
+    "RA_low_complexity": _RA + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
+                                "-max_num_ref", "2", "-enable_bipred", "1", "-encoder_speed", "2"],
     "RA_high_efficiency": _RA + ["-intra_rdo", "1", "-enable_tb_split", "1", "-enable_pb_split", "1", "-early_skip_thr", "0.3",
                                  "-max_num_ref", "4", "-enable_bipred", "1", "-encoder_speed", "0", "-max_delta_qp", "1"],
 }
