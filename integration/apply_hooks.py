@@ -6,7 +6,8 @@ sites it replaces and fails loudly if the reference no longer has them.
 usage: apply_hooks.py tail  <reference>/dec/decode_frame.c <out.c>     frame tail only
        apply_hooks.py recon <reference>/dec/decode_frame.c <out.c>     + device-resident reconstruction (2.3)
        apply_hooks.py block <reference>/dec/decode_block.c <out.c>     the block-level call sites of 2.3
-       apply_hooks.py enc   <reference>/enc/encode_frame.c <out.c>     frame tail of the encoder (2.2)"""
+       apply_hooks.py enc   <reference>/enc/encode_frame.c <out.c>     frame tail of the encoder (2.2)
+       apply_hooks.py main  <reference>/dec/maindec.c <out.c>          output writes of the pipelined decoder (2.3)"""
 import re
 import sys
 
@@ -35,6 +36,25 @@ if mode == "block":
     if src.count(anchor) != 1:
         raise SystemExit("apply_hooks: anchor for the prototypes not found in decode_block.c")
     src = src.replace(anchor, anchor + proto)
+    open(sys.argv[2], "w").write(src)
+    raise SystemExit(0)
+
+if mode == "main":
+    # dec/maindec.c: the two write_yuv_frame calls go through the hook (a picture still in flight on the device is held
+    # back), and the queue is drained before the statistics are printed
+    call = "write_yuv_frame(&rec[op_rec_buffer_idx],width,height,outfile);"
+    if src.count(call) != 2:
+        raise SystemExit("apply_hooks: maindec.c no longer has the two write_yuv_frame call sites")
+    src = src.replace(call, "thorcuda_dec_write_frame(&rec[op_rec_buffer_idx],width,height,outfile);")
+    stats = "bit_count_t bit_count = decoder_info.bit_count;"
+    if src.count(stats) != 1:
+        raise SystemExit("apply_hooks: anchor after the output tail not found in maindec.c")
+    src = src.replace(stats, "thorcuda_dec_finish();\n    " + stats)
+    anchor = "int main(int argc, char** argv)"
+    if src.count(anchor) != 1:
+        raise SystemExit("apply_hooks: main() not found in maindec.c")
+    src = src.replace(anchor, "void thorcuda_dec_write_frame(yuv_frame_t *frame, int width, int height, FILE *outfile);\n"
+                              "void thorcuda_dec_finish(void);\n" + anchor)
     open(sys.argv[2], "w").write(src)
     raise SystemExit(0)
 

@@ -84,6 +84,8 @@ static int sb_signals(const deblock_data_t *dd, int width, int k, int l) {
   return 0;
 }
 
+uint8_t *thorcuda_dec_out_compact;     /* set by dec_recon_hook.c: pinned w*h*3/2 target of the frame download */
+
 /* blockinfo + CLPF bits + fused launch + download of the filtered frame, for a reconstruction that already sits in
  * device picture `rec_dev`; the new padded reference is written into `ref_out_dev` */
 void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thorcuda_pic rec_dev, thorcuda_pic ref_out_dev) {
@@ -107,8 +109,14 @@ void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thor
   MARK(2);
   need(thorcuda_loopfilter_frame(rec_dev, -1, ref_out_dev, qp, stages, sb_bits, NULL));
   MARK(3);
-  /* the filtered frame is what gets written out and displayed */
-  need(thorcuda_pic_download(rec_dev, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));
+  /* the filtered frame is what gets written out and displayed; the pipelined decoder (dec_recon_hook.c) takes it in a
+   * pinned compact buffer and copies it into `rec` once the frame is complete */
+  if (thorcuda_dec_out_compact) {
+    uint8_t *o = thorcuda_dec_out_compact;
+    const size_t ny = (size_t)rec->width * rec->height;
+    need(thorcuda_pic_download(rec_dev, o, o + ny, o + ny + ny / 4, rec->width, rec->width / 2));
+  } else
+    need(thorcuda_pic_download(rec_dev, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));
   MARK(4);
 }
 

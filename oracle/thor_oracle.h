@@ -94,6 +94,12 @@ unsigned orc_sad_fasthalf(const uint8_t *a, const uint8_t *b, int as, int bs, in
 unsigned orc_sad_fastquarter(const uint8_t *o, const uint8_t *r, int os, int rs, int w, int h, int *x, int *y);
 void     orc_clip_mv(int16_t *mvx, int16_t *mvy, int ypos, int xpos, int fwidth, int fheight, int size, int sign);
 
+/* ---- bit-cost model (enc/putvlc.c, enc/write_bits.c): lengths only, orc_bits.c ---- */
+int orc_vlc_len(unsigned n, unsigned cn);                      /* quote_vlc; -1 where the reference aborts */
+int orc_mv_bits(int mvx, int mvy, int mvpx, int mvpy);         /* write_mv */
+int orc_find_code(int run, int level, int maxrun, int chroma, int eob);
+int orc_coeff_bits(const int16_t *coeff, int stride, int size, int type);   /* write_coeff; 0 for an all-zero block */
+
 #ifdef __cplusplus
 }
 #endif

@@ -480,3 +480,95 @@ def test_interpolate_coverage():
             orc.orc_interp_counters(ptr(c), 0)
             tot += c
     assert (tot > 0).all(), tot
+
+
+# ---------------------------------------------------------------- bit-cost model ----
+class RefStream(C.Structure):      # enc/putbits.h:36-43
+    _fields_ = [("bytesize", C.c_uint32), ("bytepos", C.c_uint32), ("bitstream", C.c_void_p), ("bitbuf", C.c_uint32), ("bitrest", C.c_uint32)]
+
+
+def ref_stream(nbytes=1 << 16):
+    buf = np.zeros(nbytes, np.uint8)
+    s = RefStream(nbytes, 0, buf.ctypes.data, 0, 32)
+    s._keep = buf
+    return s
+
+
+def ref_bitpos(s):                 # get_bit_pos, enc/putbits.c:131-134
+    return 8 * s.bytepos + 32 - s.bitrest
+
+
+def coeff_block(rng, size, kind):
+    """quantised levels as the encoder leaves them: n x n array, only the low min(n,16)^2 corner populated"""
+    q = min(size, 16)
+    c = np.zeros((size, size), np.int16)
+    if kind == "dc1":
+        c[0, 0] = rng.choice([-1, 1])
+    elif kind == "dc":
+        c[0, 0] = rng.integers(-40, 41) or 3
+    elif kind == "sparse":
+        k = rng.integers(1, 6)
+        for _ in range(k):
+            c[rng.integers(0, q), rng.integers(0, q)] = rng.choice([-3, -2, -1, 1, 1, 1, 2, 5])
+    elif kind == "lowfreq":
+        m = min(q, 4)
+        c[:m, :m] = rng.integers(-6, 7, (m, m))
+    elif kind == "dense":
+        c[:q, :q] = rng.integers(-2, 3, (q, q))
+    elif kind == "large":
+        c[:q, :q] = np.where(rng.random((q, q)) < 0.3, rng.integers(-3000, 3001, (q, q)), 0)
+    elif kind == "last":
+        c[q - 1, q - 1] = rng.choice([-1, 1, 2, -7])
+        c[0, 0] = rng.integers(-2, 3)
+    if not c.any():
+        c[0, 1] = 2
+    return c
+
+
+COEFF_KINDS = ["dc1", "dc", "sparse", "lowfreq", "dense", "large", "last"]
+
+
+def test_vlc_tables():
+    """orc_vlc_len == quote_vlc for every table and the code numbers each can see"""
+    ref.quote_vlc.restype = C.c_int
+    for n in range(14):
+        hi = 3 if n == 8 else 5000
+        for cn in list(range(min(hi, 700))) + ([] if n == 8 else [1023, 1024, 4095, 4096, 65535, 65536, 131071]):
+            assert orc.orc_vlc_len(n, cn) == ref.quote_vlc(n, cn), (n, cn)
+
+
+def test_find_code():
+    for chroma in (0, 1):
+        for maxrun in (0, 1, 3, 4, 5, 14, 62, 254):
+            for run in range(0, maxrun + 1):
+                for level in (1, 2, 9):
+                    assert orc.orc_find_code(run, level, maxrun, chroma, 0) == ref.find_code(run, level, maxrun, chroma, 0)
+        assert orc.orc_find_code(0, 0, 0, chroma, 1) == ref.find_code(0, 0, 0, chroma, 1)
+
+
+@pytest.mark.parametrize("size", [4, 8, 16, 32, 64])
+def test_coeff_bits(size):
+    """orc_coeff_bits == bits write_coeff puts into a real stream, all four block types, from single +-1 to dense and huge levels"""
+    rng = np.random.default_rng(size)
+    for kind in COEFF_KINDS:
+        for rep in range(12 if size <= 16 else 5):
+            c = coeff_block(rng, size, kind)
+            for typ in range(4):
+                s = ref_stream()
+                ref.write_coeff(C.byref(s), ptr(c), size, typ)
+                want = ref_bitpos(s)
+                got = orc.orc_coeff_bits(ptr(c), size, size, typ)
+                assert got == want, (size, kind, rep, typ, got, want)
+    assert orc.orc_coeff_bits(ptr(np.zeros((size, size), np.int16)), size, size, 0) == 0
+
+
+def test_mv_bits():
+    class Mv(C.Structure):
+        _fields_ = [("x", C.c_int16), ("y", C.c_int16)]        # common/types.h:105-109
+    rng = np.random.default_rng(3)
+    for _ in range(300):
+        mv, mvp = rng.integers(-600, 601, 2), rng.integers(-600, 601, 2)
+        s = ref_stream()
+        a, b = Mv(int(mv[0]), int(mv[1])), Mv(int(mvp[0]), int(mvp[1]))
+        ref.write_mv(C.byref(s), C.byref(a), C.byref(b))
+        assert orc.orc_mv_bits(int(mv[0]), int(mv[1]), int(mvp[0]), int(mvp[1])) == ref_bitpos(s)

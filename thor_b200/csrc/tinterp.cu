@@ -157,12 +157,33 @@ __device__ __forceinline__ int field_cost(const Nbrs &n, short2 v, int lambda) {
 
 constexpr int EW = 6;      // warps per CTA: skip test + 5 candidates
 
+// The wavefront hand-over.  A row publishes "blocks finished" with a release store after the vectors; the row below polls
+// with a RELAXED gpu-scope load and then reads the vectors with relaxed gpu-scope loads (both are served by L2, and the
+// vector load is only issued once the flag value has come back).  An acquire load would also work but invalidates the
+// SM's L1 on every block, which turns each picture-row load of the search into an L2 round trip.
+__device__ __forceinline__ int ld_flag(const int *p) {
+  int v;
+  asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ short2 ld_mv_l2(const short2 *p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return make_short2((short)(v & 0xffff), (short)(v >> 16));
+}
+__device__ __forceinline__ void st_mv_l2(short2 *p, short2 v) {
+  const uint32_t w = (uint32_t)(uint16_t)v.x | ((uint32_t)(uint16_t)v.y << 16);
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
+}
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 struct EstSmem {
   int row;
-  int skip;
-  uint32_t init[5], fin[5];
-  short2 mv[5];
-  short2 skip_mv;
+  int skip[2];               // [block parity]: results of a block are read while the next block is already being searched
+  uint32_t init[2][5], fin[2][5];
+  short2 mv[2][5];
+  short2 skip_mv[2];
+  short2 nxt_ur[2];          // up-right neighbour of the NEXT block, fetched by warp 0 while the candidates are searched
 };
 
 // cost of vector v for the 16x16 block at (xs, ys), spread over an 8-lane group (gl = lane in group); every lane of the
@@ -188,23 +209,33 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
   const int row = S.row, by = 2 * row;
   if (row >= nrows) return;
   const int lambda = GUIDED ? 750 : 3000;
-  short2 left = make_short2(0, 0);
+  const short2 zero = make_short2(0, 0);
+  const short2 *above = L.pre + (ptrdiff_t)(by - 2) * bw;                // the row of vectors above (by > 0 only)
+  // neighbours of the first block: wait until the row above has finished two blocks
+  if (threadIdx.x == 0) {
+    short2 u = zero, r = zero;
+    if (row > 0) {
+      const int need = min(2, ncols);
+      while (ld_flag(L.progress + row - 1) < need) __nanosleep(20);
+      u = ld_mv_l2(above);
+      if (bw > 2) r = ld_mv_l2(above + 2);
+    }
+    S.nxt_ur[0] = u;
+    S.nxt_ur[1] = r;
+  }
+  __syncthreads();
+  short2 left = zero, ul = zero, up = S.nxt_ur[0], ur = S.nxt_ur[1];
+  __syncthreads();                                                       // S.nxt_ur[1] is rewritten during block 0
 
   for (int col = 0; col < ncols; col++) {
-    const int bx = 2 * col, xs = bx * 8, ys = by * 8, pos = by * bw + bx;
-    if (row > 0 && threadIdx.x == 0) {
-      const int need = min(col + 2, ncols);
-      while (ld_acquire(L.progress + row - 1) < need) __nanosleep(40);
-    }
-    __syncthreads();                                                    // also: S.* of the previous block are consumed
-    // ---- neighbours, skip vector, candidates: uniform scalar work, done by every thread ----
+    const int bx = 2 * col, xs = bx * 8, ys = by * 8, pos = by * bw + bx, par = col & 1;
     Nbrs nb;
     nb.has_ur = by > 0 && bx < bw - 2;
     nb.has_up = by > 0;
     nb.has_left = bx > 0;
-    nb.ur = nb.has_ur ? ldmv(L.pre + (by - 2) * bw + bx + 2) : make_short2(0, 0);
-    nb.up = nb.has_up ? ldmv(L.pre + (by - 2) * bw + bx) : make_short2(0, 0);
-    nb.ul = (by > 0 && bx > 0) ? ldmv(L.pre + (by - 2) * bw + bx - 2) : make_short2(0, 0);
+    nb.ur = nb.has_ur ? ur : zero;
+    nb.up = up;
+    nb.ul = ul;
     nb.left = left;
     nb.kind = (bx == 0 && by == 0) ? 0 : (by > 0 && bx > 0 && bx < bw - 2) ? 1 : by == 0 ? 2 : bx == 0 ? 3 : 0;
 
@@ -215,7 +246,7 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
       if (nb.has_ur) v[n++] = nb.ur;
       if (nb.has_left) v[n++] = nb.left;
       if (nb.has_up) v[n++] = nb.up;
-      short2 sk = make_short2(0, 0);
+      short2 sk = zero;
       if (n) {
         int best = 0, bc = COST_MAX;
         for (int j = 0; j < n; j++) {
@@ -235,19 +266,38 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
       s += __shfl_xor_sync(0xffffffffu, s, 2);
       s += __shfl_xor_sync(0xffffffffu, s, 4);
       const bool ok = __all_sync(0xffffffffu, in && s <= 8 * 64);
-      if (lane == 0) { S.skip = ok; S.skip_mv = sk; }
+      if (lane == 0) { S.skip[par] = ok; S.skip_mv[par] = sk; }
+      // ---- look ahead, off the critical path of the candidate warps ----
+      if (col + 1 < ncols) {
+        // the picture rows the next block will most likely read (this block's skip vector, one block to the right):
+        // lanes 0..15 pic[1], 16..31 pic[0]; only every eighth block actually starts a new 128-byte line
+        if (in && x0 + 32 <= L.w + L.pad && x1 + 32 <= L.w + L.pad) {
+          const int r = lane & 15;
+          prefetch_l1(lane < 16 ? L.y[1] + (ptrdiff_t)(y1 + r) * L.stride + x1 + 31 : L.y[0] + (ptrdiff_t)(y0 + r) * L.stride + x0 + 31);
+        }
+        // the next block's up-right vector, once the row above has produced it
+        if (lane == 0) {
+          short2 r = zero;
+          if (row > 0) {
+            const int need = min(col + 3, ncols);
+            while (ld_flag(L.progress + row - 1) < need) __nanosleep(20);
+            if (bx + 4 < bw) r = ld_mv_l2(above + bx + 4);
+          }
+          S.nxt_ur[par ^ 1] = r;
+        }
+      }
     }
     // candidate list (:303-351): zero, guide, up-right, left, up, without duplicates
     short2 cand[5];
     int nc = 0;
-    cand[nc++] = make_short2(0, 0);
+    cand[nc++] = zero;
     {
       short2 t[4];
       bool has[4];
       if (GUIDED) {
         const short2 g = L.guide[(by / 2) * L.guide_bw + bx / 2];
         t[0] = make_short2((short)(g.x << 1), (short)(g.y << 1));                // :266-267
-      } else t[0] = make_short2(0, 0);
+      } else t[0] = zero;
       has[0] = GUIDED;
       t[1] = nb.ur; has[1] = nb.has_ur;
       t[2] = nb.left; has[2] = nb.has_left;
@@ -265,16 +315,14 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
         }
       }
     }
-    uint32_t my_init = 0, my_fin = 0;
-    short2 my_mv = make_short2(0, 0);
     const int c = warp - 1;
     if (warp >= 1 && c < nc) {
       // this warp's candidate, refined on its own by the cross search (:674-712)
-      short2 cur = make_short2(0, 0);
+      short2 cur = zero;
 #pragma unroll
       for (int i = 0; i < 5; i++) if (i == c) cur = cand[i];
       uint32_t cost = block_cost(L, nb, lambda, xs, ys, cur, gl);
-      my_init = cost;
+      const uint32_t my_init = cost;
       int shift = GUIDED ? 3 : 6, budget = GUIDED ? 8 : 64;
       while (shift >= 3 && budget > 0) {
         const int off = 1 << shift;
@@ -301,30 +349,38 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
         } else shift--;
         budget -= 4;
       }
-      my_fin = cost;
-      my_mv = cur;
+      if (lane == 0) { S.init[par][c] = my_init; S.fin[par][c] = cost; S.mv[par][c] = cur; }
     }
-    if (warp >= 1 && c < nc && lane == 0) { S.init[c] = my_init; S.fin[c] = my_fin; S.mv[c] = my_mv; }
-    __syncthreads();
+    __syncthreads();                                                    // the only barrier of a block
     short2 best;
-    if (S.skip) best = S.skip_mv;
+    if (S.skip[par]) best = S.skip_mv[par];
     else {
       // the reference's sequential selection (:685, :713-717) replayed on the speculative results
       uint32_t best_cost = COST_MAX;
       best = cand[0];
       for (int i = 0; i < nc; i++) {
-        uint32_t cost = S.init[i];
+        uint32_t cost = S.init[par][i];
         short2 mv = cand[0];
 #pragma unroll
         for (int k = 0; k < 5; k++) if (k == i) mv = cand[k];
-        if (((uint32_t)(4 + i) * cost) / 8 < best_cost) { cost = S.fin[i]; mv = S.mv[i]; }
+        if (((uint32_t)(4 + i) * cost) / 8 < best_cost) { cost = S.fin[par][i]; mv = S.mv[par][i]; }
         if (cost < best_cost) { best_cost = cost; best = mv; }
       }
     }
+    if (threadIdx.x == EW * 32 - 1) {
+      // publish: the four 8x8 entries of the block, then the progress counter (release orders it after them).  Done by a
+      // thread of the last warp, so that warp 0 starts the next block's skip test at once.
+      st_mv_l2(L.pre + pos, best);
+      st_mv_l2(L.pre + pos + 1, best);
+      st_mv_l2(L.pre + pos + bw, best);
+      st_mv_l2(L.pre + pos + bw + 1, best);
+      st_release(L.progress + row, col + 1);
+    }
+    // the next block's neighbours: its up-left is this block's up, its up is this block's up-right
+    ul = up;
+    up = nb.ur;
+    ur = S.nxt_ur[par ^ 1];
     left = best;
-    if (threadIdx.x < 4) L.pre[pos + (threadIdx.x >> 1) * bw + (threadIdx.x & 1)] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) { __threadfence(); st_release(L.progress + row, col + 1); }
   }
 }
 
