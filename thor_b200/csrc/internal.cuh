@@ -55,6 +55,7 @@ struct List {
   int16_t *pool = nullptr;                // quantised coefficients
   uint8_t *cbp = nullptr;
   uint32_t *ssd = nullptr;
+  uint32_t *bits = nullptr;               // write_coeff bit counts (bits.cu)
   int ntb[5] = {0, 0, 0, 0, 0};           // tasks per transform size 4,8,16,32,64 (tasks are sorted by size)
   int tb_first[5] = {0, 0, 0, 0, 0};
   uint32_t *order = nullptr;              // device: sorted position -> task index

@@ -170,6 +170,7 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
     e = cudaMallocAsync((void **)&L.pool, L.pool_entries * sizeof(int16_t) + 64, c.stream);
     if (e == cudaSuccess) e = cudaMallocAsync((void **)&L.cbp, (size_t)ntasks + 16, c.stream);
     if (e == cudaSuccess) e = cudaMallocAsync((void **)&L.ssd, (size_t)ntasks * 4 + 16, c.stream);
+    if (e == cudaSuccess) e = cudaMallocAsync((void **)&L.bits, (size_t)ntasks * 4 + 16, c.stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(L.pool, 0, L.pool_entries * sizeof(int16_t) + 64, c.stream);
   } else if (kind == THORCUDA_LIST_COST) {
     e = cudaMallocAsync((void **)&L.res_buf[0], (size_t)ntasks * sizeof(thorcuda_cost_result), c.stream);
@@ -179,6 +180,7 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
   if (e != cudaSuccess) {
     cudaFreeAsync(L.blob, c.stream); if (L.pool) cudaFreeAsync(L.pool, c.stream); if (L.cbp) cudaFreeAsync(L.cbp, c.stream);
     if (L.ssd) cudaFreeAsync(L.ssd, c.stream);
+    if (L.bits) cudaFreeAsync(L.bits, c.stream);
     for (int i = 0; i < 2; i++) if (L.res_buf[i]) cudaFreeAsync(L.res_buf[i], c.stream);
     L = List();
     return fail("list: device allocation failed (%s)", cudaGetErrorString(e));
@@ -196,6 +198,7 @@ void thorcuda_list_destroy(thorcuda_list h) {
   if (L->pool) cudaFreeAsync(L->pool, st);
   if (L->cbp) cudaFreeAsync(L->cbp, st);
   if (L->ssd) cudaFreeAsync(L->ssd, st);
+  if (L->bits) cudaFreeAsync(L->bits, st);
   for (int i = 0; i < 2; i++) if (L->res_buf[i]) cudaFreeAsync(L->res_buf[i], st);
   *L = List();
 }
