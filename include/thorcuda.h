@@ -220,6 +220,20 @@ int thorcuda_interp_levels(int width, int height);     /* pyramid levels: min(4,
  * x then y, one per 8x8 block, bw = 2*ceil(w/16) per row); mv1 may be NULL to query the size only. Synchronous.   */
 int thorcuda_interp_field(int16_t *mv1, int *bw, int *bh);
 
+/* ------------------------------------------------------------ bit-cost model ---- */
+/* First slice of the device-side bit-cost model: for every task of a transform-block list the exact
+ * number of bits write_coeff (enc/write_bits.c:110-253) emits for the block's quantised levels -- the pool contents
+ * thorcuda_encode_list has just produced, or host_coeffq (pool_entries int16, uploaded first) when non-NULL.  The block
+ * type is the task's coeff_type (bit0 chroma, bit1 intra), the transform size its size (the chroma code tables switch
+ * at size <= 8, :196,:239).  A block without levels costs 0 (the reference does not call write_coeff for it).
+ * host_bits (ntasks uint32, may be NULL) is valid after thorcuda_sync().  With it cost_calc's `nbits`
+ * (enc/encode_block.c:1218-1228) of a trial encode is these counts plus the host's mode / vector / cbp bits. */
+int thorcuda_coeff_bits_list(thorcuda_list l, const int16_t *host_coeffq, uint32_t *host_bits);
+/* host arithmetic (no device work): quote_vlc (enc/putvlc.c:133-229; -1 where the reference aborts) and the bits of
+ * write_mv (enc/write_bits.c:50-69) = quote_mv_bits (enc/encode_block.c:799-814) */
+int thorcuda_vlc_len(unsigned n, unsigned cn);
+int thorcuda_mv_bits(int mvx, int mvy, int mvpx, int mvpy);
+
 /* ------------------------------------------------------------ early-skip test ---- */
 /* Significance test of a skip candidate (check_early_skip_block, enc/encode_block.c:2612-2741) for one
  * size x size luma sub-block (size = min(block size, 16): 16 or 8) and its two chroma sub-blocks, given the

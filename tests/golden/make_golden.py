@@ -11,6 +11,8 @@ golden data are outputs of the reference itself on seeded inputs:
                 oracle/_ref/libthorref.so with its SIMD dispatch on (the plain-C path is checked equal here);
   extras.npz    the same for row a19 (early-skip test) and SURVEY 8f #1 (intra prediction); `--extras-only`
                 regenerates just this file;
+  bits.npz      SURVEY 8f #3 (bit-cost model): bits the reference's write_coeff / write_mv put into a stream and
+                quote_vlc's lengths, on seeded inputs; `--bits-only` regenerates just this file;
   streams.json  md5 of the bitstream and of the reconstruction that oracle/_ref/Thorenc writes for three shipped
                 operating points on seeded synthetic clips (+ that Thordec reproduces the reconstruction).
 
@@ -28,8 +30,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
-from thorref import (BLOCKINFO, THOR_CONFIGS, Picture, blocky_frame, load_ref, ptr, random_blockinfo, run_thordec, run_thorenc,  # noqa: E402
-                     set_ref_simd, smooth_frame, write_clip)
+from thorref import (BLOCKINFO, COEFF_KINDS, THOR_CONFIGS, Picture, blocky_frame, coeff_block, load_ref, ptr, random_blockinfo,  # noqa: E402
+                     ref_bitpos, ref_stream, run_thordec, run_thorenc, set_ref_simd, smooth_frame, write_clip)
 
 
 class Mv(C.Structure):
@@ -284,10 +286,43 @@ def extras(ref):
     return out
 
 
+def bits(ref):
+    """SURVEY 8f #3, first slice: bit counts of the reference's entropy coder.  write_coeff into a real stream for seeded
+    level blocks of every size / type (levels stored in libthorcuda's pool layout: the low q x q corner, q = min(n, 16)),
+    quote_vlc for every table, write_mv for seeded vector pairs."""
+    rng = np.random.default_rng(20261106)
+    sizes, types, want, levels = [], [], [], []
+    for size in (4, 8, 16, 32, 64):
+        q = min(size, 16)
+        for kind in COEFF_KINDS:
+            for rep in range(6 if size <= 16 else 3):
+                c = coeff_block(rng, size, kind)
+                for typ in range(4):
+                    s = ref_stream()
+                    ref.write_coeff(C.byref(s), ptr(c), size, typ)
+                    sizes.append(size); types.append(typ); want.append(ref_bitpos(s))
+                    levels.append(c[:q, :q].reshape(-1).copy())
+    ref.quote_vlc.restype = C.c_int
+    vlc = [(n, cn, ref.quote_vlc(n, cn)) for n in range(14) for cn in (list(range(3)) if n == 8 else list(range(0, 200)) + [255, 256, 1023, 1024, 40000])]
+    mvs = []
+    for _ in range(200):
+        mv, mvp = rng.integers(-600, 601, 2), rng.integers(-600, 601, 2)
+        s = ref_stream()
+        a, b = Mv(int(mv[0]), int(mv[1])), Mv(int(mvp[0]), int(mvp[1]))
+        ref.write_mv(C.byref(s), C.byref(a), C.byref(b))
+        mvs.append((int(mv[0]), int(mv[1]), int(mvp[0]), int(mvp[1]), ref_bitpos(s)))
+    return {"coeff_size": np.array(sizes, np.uint8), "coeff_type": np.array(types, np.uint8), "coeff_bits": np.array(want, np.uint32),
+            "coeff_levels": np.concatenate(levels).astype(np.int16), "vlc": np.array(vlc, np.int32), "mv": np.array(mvs, np.int32)}
+
+
 def main():
     ref = load_ref()
     if ref is None:
         raise SystemExit("oracle/_ref/libthorref.so missing: run `make -C oracle ref` where /root/reference is mounted")
+    np.savez_compressed(os.path.join(HERE, "bits.npz"), **bits(ref))
+    if "--bits-only" in sys.argv:
+        print("wrote", os.path.join(HERE, "bits.npz"), os.path.getsize(os.path.join(HERE, "bits.npz")), "bytes")
+        return
     set_ref_simd(ref, 1)
     e1 = extras(ref)
     set_ref_simd(ref, 0)

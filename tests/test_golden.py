@@ -377,3 +377,59 @@ def test_gpu_early_skip(gx, tb):
     got = early_skip_batch([org, pred], np.array(tasks, SKIP_TASK))
     assert got.tolist() == [c[2] for c in cases]
     org.close(); pred.close()
+
+
+# ------------------------------------------------------- bits.npz: bit-cost model ----
+@pytest.fixture(scope="module")
+def gb():
+    return np.load(os.path.join(GOLD, "bits.npz"))
+
+
+def _coeff_cases(gb):
+    off = 0
+    for size, typ, want in zip(gb["coeff_size"].tolist(), gb["coeff_type"].tolist(), gb["coeff_bits"].tolist()):
+        q = min(size, 16)
+        yield size, typ, want, gb["coeff_levels"][off:off + q * q]
+        off += q * q
+
+
+def test_port_coeff_bits(gb, orc):
+    n = 0
+    for size, typ, want, lev in _coeff_cases(gb):
+        c = np.ascontiguousarray(lev)
+        assert orc.orc_coeff_bits(ptr(c), min(size, 16), size, typ) == want, (size, typ)
+        n += 1
+    assert n == gb["coeff_bits"].size and n > 500
+    for n_, cn, want in gb["vlc"].tolist():
+        assert orc.orc_vlc_len(n_, cn) == want, (n_, cn)
+    for mx, my, px, py, want in gb["mv"].tolist():
+        assert orc.orc_mv_bits(mx, my, px, py) == want
+
+
+def test_host_bit_helpers(gb):
+    """thorcuda_vlc_len / thorcuda_mv_bits are host arithmetic: checked here without a GPU"""
+    import thor_b200 as tb
+    for n_, cn, want in gb["vlc"].tolist():
+        assert tb.ops.vlc_len(n_, cn) == want, (n_, cn)
+    for mx, my, px, py, want in gb["mv"].tolist():
+        assert tb.ops.mv_bits((mx, my), (px, py)) == want
+
+
+@pytest.mark.gpu
+def test_gpu_coeff_bits(gb, tb):
+    cases = list(_coeff_cases(gb))
+    tasks = np.zeros(len(cases), tb.TB_TASK)
+    pic = tb.Picture(64, 64)
+    for i, (size, typ, want, lev) in enumerate(cases):
+        tasks[i]["size"], tasks[i]["coeff_type"], tasks[i]["plane"] = size, typ, 0
+        tasks[i]["org"] = tasks[i]["pred"] = tasks[i]["rec"] = 0
+    entries = tb.ops.pool_layout(tasks)
+    pool = np.zeros(entries, np.int16)
+    for i, (size, typ, want, lev) in enumerate(cases):
+        off = int(tasks[i]["coeff_offset"])
+        pool[off:off + lev.size] = lev
+    got = tb.ops.coeff_bits([pic], tasks, pool)
+    want = np.array([c[2] for c in cases], np.uint32)
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, f"{bad.size} of {want.size} differ, first: case {bad[0]} size {cases[bad[0]][0]} type {cases[bad[0]][1]} got {got[bad[0]]} want {want[bad[0]]}"
+    pic.close()

@@ -1,0 +1,88 @@
+"""GPU parity (bit-exact, through the C ABI) of the coefficient bit counts (first slice:
+thorcuda_coeff_bits_list = write_coeff of enc/write_bits.c:110-253 as a length) against the CPU oracle (oracle/orc_bits.c,
+itself pinned to the reference's write_coeff writing into a real stream): synthetic level blocks of every size, type
+and density, and the levels the device's own encoder leg leaves in the pool."""
+import numpy as np
+import pytest
+
+from test_gpu_blocks import make_tb_tasks, tb_pictures
+from thorref import COEFF_KINDS, coeff_block, load_oracle, ptr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tb():
+    import thor_b200
+    thor_b200.init(0)
+    yield thor_b200
+    thor_b200.shutdown()
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return load_oracle()
+
+
+def oracle_bits(orc, tasks, pool):
+    out = np.zeros(tasks.size, np.uint32)
+    for i, t in enumerate(tasks):
+        q = min(int(t["size"]), 16)
+        c = np.ascontiguousarray(pool[int(t["coeff_offset"]):int(t["coeff_offset"]) + q * q])
+        out[i] = orc.orc_coeff_bits(ptr(c), q, int(t["size"]), int(t["coeff_type"]))
+    return out
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_coeff_bits_synthetic(tb, orc, seed):
+    """every size x block type x level pattern, incl. all-zero blocks (0 bits), a single +-1 (the 2-bit chroma short cut),
+    a level at the last scan position (no end-of-block code) and levels up to +-3000 (escape codes)"""
+    rng = np.random.default_rng(seed)
+    blocks = []
+    for size in (4, 8, 16, 32, 64):
+        for kind in COEFF_KINDS + ["zero"]:
+            for rep in range(40 if size <= 16 else 12):
+                c = np.zeros((size, size), np.int16) if kind == "zero" else coeff_block(rng, size, kind)
+                blocks.append((size, int(rng.integers(0, 4)), c))
+    order = rng.permutation(len(blocks))
+    tasks = np.zeros(len(blocks), tb.TB_TASK)
+    for i, k in enumerate(order):
+        tasks[i]["size"], tasks[i]["coeff_type"] = blocks[k][0], blocks[k][1]
+    entries = tb.ops.pool_layout(tasks)
+    pool = np.zeros(entries, np.int16)
+    for i, k in enumerate(order):
+        q = min(blocks[k][0], 16)
+        off = int(tasks[i]["coeff_offset"])
+        pool[off:off + q * q] = blocks[k][2][:q, :q].reshape(-1)
+    pic = tb.Picture(64, 64)
+    got = tb.ops.coeff_bits([pic], tasks, pool)
+    want = oracle_bits(orc, tasks, pool)
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, f"{bad.size} of {want.size} differ; first: task {bad[0]} {tasks[bad[0]]} got {got[bad[0]]} want {want[bad[0]]}"
+    assert (want == 0).sum() >= 5 * 12 and want.max() > 2000
+    pic.close()
+
+
+@pytest.mark.parametrize("wh,qps,intra", [((256, 192), (22, 32, 37), False), ((416, 240), (8, 30), True), ((1920, 1080), (32,), False)])
+def test_coeff_bits_after_encode(tb, orc, wh, qps, intra):
+    """the encoder leg and the bit count on ONE resident list: levels never leave the device between the two launches"""
+    w, h = wh
+    rng = np.random.default_rng(w + qps[0])
+    opl, ppl, org, pred = tb_pictures(tb, w, h, 5 + qps[0], noise=14)
+    rec = tb.Picture(w, h)
+    tasks = make_tb_tasks(tb, w, h, rng, qps, sizes_luma=(16, 64) if w >= 1920 else (8, 64), intra_frame=intra)
+    tb.ops.pool_layout(tasks)
+    lst = tb.ops.TaskList(tb.LIST_TB, [org, pred, rec], tasks)
+    coeffq = np.zeros(lst.pool_entries, np.int16)
+    cbp = np.zeros(lst.ntasks, np.uint8)
+    bits = np.zeros(lst.ntasks, np.uint32)
+    lst.encode(coeffq, cbp, None)
+    lst.coeff_bits(bits)
+    tb.sync()
+    lst.close()
+    want = oracle_bits(orc, tasks, coeffq)
+    assert np.array_equal(bits, want)
+    assert np.array_equal(bits != 0, cbp != 0), "a block has bits exactly when it has coefficients"
+    assert 0 < (cbp != 0).sum() < cbp.size
+    for p in (org, pred, rec):
+        p.close()

@@ -270,3 +270,49 @@ def run_thordec(exe, bit, out_yuv, timeout=600):
     if r.returncode != 0:
         raise RuntimeError(f"{exe} failed ({r.returncode}):\n{r.stdout[-2000:]}\n{r.stderr[-2000:]}")
     return open(out_yuv, "rb").read()
+
+
+# ---------------------------------------------------------------- bit-cost model helpers ----
+class RefStream(C.Structure):      # enc/putbits.h:36-43
+    _fields_ = [("bytesize", C.c_uint32), ("bytepos", C.c_uint32), ("bitstream", C.c_void_p), ("bitbuf", C.c_uint32), ("bitrest", C.c_uint32)]
+
+
+def ref_stream(nbytes=1 << 16):
+    buf = np.zeros(nbytes, np.uint8)
+    s = RefStream(nbytes, 0, buf.ctypes.data, 0, 32)
+    s._keep = buf
+    return s
+
+
+def ref_bitpos(s):                 # get_bit_pos, enc/putbits.c:131-134
+    return 8 * s.bytepos + 32 - s.bitrest
+
+
+def coeff_block(rng, size, kind):
+    """quantised levels as the encoder leaves them: n x n array, only the low min(n,16)^2 corner populated"""
+    q = min(size, 16)
+    c = np.zeros((size, size), np.int16)
+    if kind == "dc1":
+        c[0, 0] = rng.choice([-1, 1])
+    elif kind == "dc":
+        c[0, 0] = rng.integers(-40, 41) or 3
+    elif kind == "sparse":
+        k = rng.integers(1, 6)
+        for _ in range(k):
+            c[rng.integers(0, q), rng.integers(0, q)] = rng.choice([-3, -2, -1, 1, 1, 1, 2, 5])
+    elif kind == "lowfreq":
+        m = min(q, 4)
+        c[:m, :m] = rng.integers(-6, 7, (m, m))
+    elif kind == "dense":
+        c[:q, :q] = rng.integers(-2, 3, (q, q))
+    elif kind == "large":
+        c[:q, :q] = np.where(rng.random((q, q)) < 0.3, rng.integers(-3000, 3001, (q, q)), 0)
+    elif kind == "last":
+        c[q - 1, q - 1] = rng.choice([-1, 1, 2, -7])
+        c[0, 0] = rng.integers(-2, 3)
+    if not c.any():
+        c[0, 1] = 2
+    return c
+
+
+COEFF_KINDS = ["dc1", "dc", "sparse", "lowfreq", "dense", "large", "last"]

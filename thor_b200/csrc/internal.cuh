@@ -132,6 +132,7 @@ int sync_pic_view(thorcuda_pic h);
 int tb_raw(int size, int fast, int inverse, const int16_t *d_in, int16_t *d_out);
 void compat_reset();   // compat.cu: drop the per-block API's scratch pictures (thorcuda_shutdown)
 void interp_reset();   // tinterp.cu: drop the interpolation scratch (thorcuda_shutdown)
+void bits_reset();     // bits.cu: the scan tables are uploaded again after a shutdown
 
 #define THOR_CUDA(call)                                                                   \
   do {                                                                                    \

@@ -12,6 +12,7 @@ executing on the B200 through libthorcuda (no CPU fallback).
                                        decode_and_reconstruct_block_inter (dec/decode_block.c:90-120)
   intra_predict_blocks                 make_top_and_left + get_intra_prediction (common/intra_prediction.c:57-389)
   interpolate_frames                   interpolate_frames (common/temporal_interp.c:972-1053)
+  coeff_bits / vlc_len / mv_bits       write_coeff, quote_vlc, write_mv as bit counts (enc/write_bits.c, enc/putvlc.c)
   early_skip_thresholds / early_skip_batch  check_early_skip_sub_block(C) (enc/encode_block.c:2507-2610)
   sad_table / cost_batch               sad_calc, widesad_calc, sad_calc_fasthalf/fastquarter, ssd_calc
                                        (enc/encode_block.c:497-797)
@@ -116,6 +117,9 @@ class TaskList:
     def reconstruct(self, coeffq=None):
         check(cdll().thorcuda_reconstruct_list(self.handle, _p(coeffq)))
 
+    def coeff_bits(self, bits=None, coeffq=None):
+        check(cdll().thorcuda_coeff_bits_list(self.handle, _p(coeffq), _p(bits)))
+
     def cost(self, kind, results=None):
         check(cdll().thorcuda_cost_list(self.handle, int(kind), _p(results)))
 
@@ -157,6 +161,29 @@ def reconstruct_blocks(pics, tasks, coeffq):
     lst.reconstruct(cq)
     sync()
     lst.close()
+
+
+def coeff_bits(pics, tasks, coeffq):
+    """write_coeff (enc/write_bits.c:110-253) bit counts of the blocks of a TB task list whose levels are `coeffq`
+    (pool layout: q*q int16 per task at coeff_offset, q = min(size, 16)).  Returns uint32 per task."""
+    lst = TaskList(LIST_TB, pics, tasks)
+    cq = np.zeros(lst.pool_entries, np.int16)
+    cq[:min(cq.size, coeffq.size)] = coeffq[:cq.size]
+    bits = np.zeros(lst.ntasks, np.uint32)
+    lst.coeff_bits(bits, cq)
+    sync()
+    lst.close()
+    return bits
+
+
+def vlc_len(n, cn):
+    """quote_vlc (enc/putvlc.c:133-229)"""
+    return int(cdll().thorcuda_vlc_len(int(n), int(cn)))
+
+
+def mv_bits(mv, mvp):
+    """write_mv / quote_mv_bits: bits of the vector difference, mv and mvp as (x, y)"""
+    return int(cdll().thorcuda_mv_bits(int(mv[0]), int(mv[1]), int(mvp[0]), int(mvp[1])))
 
 
 def cost_batch(kind, pics, tasks):
