@@ -477,6 +477,19 @@ def run_gpu_arm(args, rank, world, local_rank):
             stage_ms[name] += lib.thorcuda_timer_elapsed_ms(tid) / reps
     clocks = sampler.stop()          # sampled over the timed steps and the per-stage timed passes (all under load)
 
+    # outside the metric (the reference arm has no such stage): the write_coeff bit counts of every transform block of the
+    # step, on the levels the transform stage has just left in the pool
+    l_tb.coeff_bits()
+    tb.sync()
+    tid = lib.thorcuda_timer_begin()
+    for _ in range(20):
+        l_tb.coeff_bits()
+    lib.thorcuda_timer_end(tid)
+    bits_ms = lib.thorcuda_timer_elapsed_ms(tid) / 20
+    nbits = np.zeros(l_tb.ntasks, np.uint32)
+    l_tb.coeff_bits(nbits)
+    tb.sync()
+
     # ---- e2e: host buffers in, host buffers out, every step ----
     e2e = measure_e2e(args, tb, lib, streams[:min(B, args.e2e_streams)], barrier, dist, world)
 
@@ -502,7 +515,10 @@ def run_gpu_arm(args, rank, world, local_rank):
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                              "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": ncu_traffic(dom, jobs[0], B),
                              "launch_ms": round(stage_ms[dom] / n_launch, 4), "algorithmic_bytes_per_launch": int(B * ab[dom] / n_launch)},
-                "stages": per_stage}
+                "stages": per_stage,
+                "extra_stages": {"coeff_bits": {"ms": round(bits_ms, 4), "transform_blocks": int(l_tb.ntasks), "coded": int((nbits != 0).sum()),
+                                                "mean_bits_per_coded_block": round(float(nbits.sum()) / max(1, int((nbits != 0).sum())), 1),
+                                                "note": "not part of `value`: exact write_coeff bit counts of the step's transform blocks"}}}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_and_parity(args, tb, streams[0])
         if world == 1 and args.decoder:
