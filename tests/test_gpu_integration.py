@@ -26,6 +26,8 @@ def _decode(exe, bit, out):
     ("RA_high_efficiency", 128, 128, 9, 32),        # B frames, interpolated references, tb/pb split, delta qp
     ("RA_high_efficiency", 192, 136, 17, 38),       # two sub-GOPs of the B hierarchy, partial superblock row, coarse qp
     ("RA_low_complexity", 416, 240, 17, 32),        # 4-level interpolation pyramid (device-side in Thordec_gpu), 240 = 3*64 + 48
+    ("HDB16_low_complexity", 256, 192, 33, 34),     # two 16-frame sub-GOPs: interpolation ratios 2..16, four B levels
+    ("RA16_medium_complexity", 192, 128, 17, 30),
     ("LDB_medium_complexity", 136, 72, 14, 22),     # fine qp (dense coefficients), HQ-period frame, 33-slot ring not yet wrapped
 ])
 @pytest.mark.parametrize("exe", ["Thordec_tail", "Thordec_gpu"])

@@ -230,7 +230,17 @@ _RA = ["-HQperiod", "1", "-num_reorder_pics", "7", "-interp_ref", "1", "-intra_p
        "-dqpB2", "0", "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.1", "-mqpB1", "1.2", "-mqpB2", "1.3", "-lambda_coeffI", "0.8",
        "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2",
        "-use_block_contexts", "1"]
+_B16 = ["-HQperiod", "1", "-num_reorder_pics", "15", "-interp_ref", "1", "-dqpI", "-2", "-dqpB0", "2", "-dqpB1", "1", "-dqpB2", "0", "-dqpB3", "0",
+        "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.075", "-mqpB1", "1.15", "-mqpB2", "1.225", "-mqpB3", "1.3", "-lambda_coeffI", "0.8",
+        "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2",
+        "-lambda_coeffB3", "1.2", "-use_block_contexts", "1"]
 THOR_CONFIGS = {
+    # config_HDB16_low_complexity.txt: 16-frame dyadic B hierarchy without intra period ("HDB16" is a GOP structure, 8-bit)
+    "HDB16_low_complexity": _B16 + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
+                                    "-max_num_ref", "2", "-enable_bipred", "1", "-encoder_speed", "2"],
+    # config_RA16_medium_complexity.txt
+    "RA16_medium_complexity": _B16 + ["-intra_period", "64", "-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0",
+                                      "-early_skip_thr", "0.8", "-max_num_ref", "2", "-enable_bipred", "1", "-encoder_speed", "1"],
     "LDB_low_complexity": _LD + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
                                  "-enable_bipred", "0", "-encoder_speed", "2"],
     "LDB_medium_complexity": _LD + ["-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "0.8",

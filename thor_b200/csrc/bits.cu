@@ -7,11 +7,11 @@
 // encoder's cost_calc (enc/encode_block.c:1218-1228) needs `nbits` of every trial encode, and the coefficients are
 // the part of it that scales with the pixels (mode, vector and cbp bits are a few table look-ups per block).
 //
-// One warp per transform block.  The low q x q corner (q = min(size, 16)) is read coalesced and scattered into scan
-// order in shared memory; ballots give the non-zero map and the last position.  write_coeff's two-mode scan (level
-// mode after a level > 1, run mode after a zero or a +-1) is inherently sequential in the number of CODED symbols, so
-// it is replayed warp-uniformly, but run mode jumps from one non-zero level to the next through the map instead of
-// stepping over the zeros.
+// One warp per transform block.  The low q x q corner (q = min(size, 16)) is read with one vector load per lane (a block
+// without levels ends there) and scattered into scan order in shared memory.  write_coeff's two-mode scan looks
+// sequential, but the mode, the run start and the level table of a position are functions of bit masks of the
+// EARLIER positions (level present, level > 1, level > 3), so after three ballots per 32 positions every lane prices
+// the symbol at its own position and the warp adds up: the cost is the same for sparse and dense blocks.
 #include <string.h>
 #include "internal.cuh"
 
@@ -49,59 +49,109 @@ constexpr int BW = 8;      // warps (= blocks in flight) per CTA
 __global__ void __launch_bounds__(BW * 32) k_coeff_bits(const thorcuda_tb_task *__restrict__ tasks, int ntasks,
                                                         const int16_t *__restrict__ pool, uint32_t *__restrict__ bits) {
   __shared__ int16_t S[BW][256];          // the block's levels in scan order
-  __shared__ uint32_t M[BW][8];           // non-zero map, bit p = scan position p
+  __shared__ uint8_t sScan[16 + 64 + 256];   // c_scan is indexed per lane: from constant memory that access would serialise
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < (16 + 64 + 256) / 4; i += BW * 32) reinterpret_cast<uint32_t *>(sScan)[i] = reinterpret_cast<const uint32_t *>(c_scan)[i];
+  __syncthreads();
   int16_t *s = S[warp];
-  uint32_t *nzmap = M[warp];
   for (int t = blockIdx.x * BW + warp; t < ntasks; t += gridDim.x * BW) {
     const thorcuda_tb_task task = tasks[t];
     const int size = task.size, q = min(size, 16), n = q * q;
     const bool chroma = task.coeff_type & 1, intra = (task.coeff_type >> 1) & 1;
-    const uint8_t *scan = c_scan + (q == 4 ? 0 : q == 8 ? 16 : 80);
+    const uint8_t *scan = sScan + (q == 4 ? 0 : q == 8 ? 16 : 80);
     const int16_t *c = pool + task.coeff_offset;
-    for (int r = lane; r < n; r += 32) s[scan[r]] = c[r];
-    __syncwarp();
-    int last = -1;
-    for (int k = 0; k < (n + 31) / 32; k++) {
-      const int p = 32 * k + lane;
-      const uint32_t m = __ballot_sync(0xffffffffu, p < n && s[p] != 0);
-      if (lane == 0) nzmap[k] = m;
-      if (m) last = 32 * k + ilog2u(m);
+    // the corner as one vector load per lane (8 levels; 4 for a 4x4 block, whose pool slot is only 8-byte aligned);
+    // a block without levels -- nearly half of an encoder's blocks -- ends here
+    const int per = q == 4 ? 4 : 8;
+    uint32_t w[4] = {0, 0, 0, 0};
+    if (lane * per < n) {
+      if (q == 4) { const uint2 v = *reinterpret_cast<const uint2 *>(c + 4 * lane); w[0] = v.x; w[1] = v.y; }
+      else { const uint4 v = *reinterpret_cast<const uint4 *>(c + 8 * lane); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
+    }
+    if (!__any_sync(0xffffffffu, (w[0] | w[1] | w[2] | w[3]) != 0)) {
+      if (lane == 0) bits[t] = 0;
+      continue;
+    }
+    if (lane * per < n) {
+#pragma unroll
+      for (int j = 0; j < 8; j++)
+        if (j < per) s[scan[lane * per + j]] = (int16_t)(w[j >> 1] >> (16 * (j & 1)));
     }
     __syncwarp();
-    int total = 0;
-    if (last >= 0) {
-      const int first = abs((int)s[0]);
-      if (chroma && last == 0 && first == 1) total = 2;                   // :148-153: flag + sign, nothing else
-      else {
-        total = chroma ? 1 : 0;
-        int adaptive = intra && !chroma;                                  // table of the next level-mode symbol
-        bool level_mode = true;
-        int pos = 0, maxrun = 0;
-        const bool small_chroma = chroma && size <= 8;
-        while (pos <= last) {
-          if (level_mode) {                                               // :166-178
-            const int level = abs((int)s[pos]);
-            total += vlc_len(adaptive, (uint32_t)level) + (level > 0);
-            if (!chroma) adaptive = level > 3;
-            pos++;
-            if (level == 0) { level_mode = false; maxrun = n - pos - 1; }
-          } else {                                                        // :181-218, zeros skipped through the map
-            int w = pos >> 5;
-            uint32_t m = nzmap[w] & (0xffffffffu << (pos & 31));
-            while (!m) m = nzmap[++w];
-            const int nz = 32 * w + __ffs(m) - 1, run = nz - pos, v = s[nz], level = abs(v);
-            total += event_len(find_code(run, level, maxrun, chroma), small_chroma, false);
-            total += level > 1 ? vlc_len(0, (uint32_t)(2 * (level - 2) + (v < 0))) : 1;
-            pos = nz + 1;
-            level_mode = level > 1;
-            maxrun = n - pos - 1;
-          }
-        }
-        if (pos < n && level_mode) { total += vlc_len(adaptive, 0); pos++; }   // :222-234
-        if (pos < n) total += event_len(chroma ? 0 : 2, small_chroma, true);      // :237-250
+    // ---- pass 1: per 32-position word, which positions hold a level, a level > 1, a level > 3 ----
+    const int nw = n >= 32 ? n >> 5 : 1;
+    int lv[8];                               // |level| of position 32k + lane (bit 16: negative)
+    uint32_t nz[8], big[8], gt3[8];
+    int last = -1;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      nz[k] = big[k] = gt3[k] = 0;
+      lv[k] = 0;
+      if (k < nw) {
+        const int p = 32 * k + lane, v = p < n ? (int)s[p] : 0, a = abs(v);
+        lv[k] = a | (v < 0 ? 0x10000 : 0);
+        nz[k] = __ballot_sync(0xffffffffu, a != 0);
+        big[k] = __ballot_sync(0xffffffffu, a > 1);
+        gt3[k] = __ballot_sync(0xffffffffu, a > 3);
+        if (nz[k]) last = 32 * k + ilog2u(nz[k]);
       }
     }
+    // ---- pass 2: every position prices its own symbol ----
+    // write_coeff's mode before position p follows from the nearest earlier position that is not +-1: level mode after a
+    // level > 1 (or at the start), run mode after a zero (:176-178, :216).  A run starts behind the nearest earlier CODED
+    // position (a level, or a zero met in level mode).  The level table is adaptive only for intra luma: > 3 of the
+    // previous symbol if that was coded in level mode, else table 0 (the zero that opened the run reset it).
+    const bool small_chroma = chroma && size <= 8;
+    const uint32_t below = (1u << lane) - 1;
+    bool carry_level = true;                 // mode at the first position of the word
+    int carry_start = 0;                     // run start at the first position of the word
+    uint32_t prev_level_msb = 0, prev_gt3_msb = 0;   // bit 31 of the previous word's level-mode / > 3 masks
+    int acc = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      if (k < nw && 32 * k <= last) {
+        const uint32_t dec = ~nz[k] | big[k];                       // positions that decide the mode of what follows
+        const uint32_t md = dec & below;
+        const bool level_mode = md ? (big[k] >> ilog2u(md)) & 1 : carry_level;
+        const uint32_t lm = __ballot_sync(0xffffffffu, level_mode);
+        const uint32_t coded = nz[k] | (~nz[k] & lm);
+        const uint32_t mc = coded & below;
+        const int start = mc ? 32 * k + ilog2u(mc) + 1 : carry_start;
+        const int p = 32 * k + lane, a = lv[k] & 0xffff, neg = lv[k] >> 16;
+        if (p <= last) {
+          if (level_mode) {                                         // :166-178
+            int table = 0;
+            if (!chroma) {
+              if (p == 0) table = intra;
+              else {
+                const uint32_t pl = lane ? (lm >> (lane - 1)) & 1 : prev_level_msb, pg = lane ? (gt3[k] >> (lane - 1)) & 1 : prev_gt3_msb;
+                table = pl & pg;
+              }
+            }
+            acc += vlc_len(table, (uint32_t)a) + (a > 0);
+          } else if (a) {                                           // :191-218
+            acc += event_len(find_code(p - start, a, n - start - 1, chroma), small_chroma, false);
+            acc += a > 1 ? vlc_len(0, (uint32_t)(2 * (a - 2) + neg)) : 1;
+          }
+          if (p == last) {                                          // what follows the last level (:222-250)
+            int pos = p + 1;
+            if (pos < n && (a > 1 || level_mode)) {                 // still in level mode: one zero level first
+              acc += 1 + ((!chroma && level_mode && a > 3) ? 1 : 0);
+              pos++;
+            }
+            if (pos < n) acc += small_chroma ? 1 : chroma ? 2 : 3;  // end of block: table 0 cn 0 / 2 bits / table 2 cn 3
+          }
+        }
+        carry_level = dec ? (big[k] >> ilog2u(dec)) & 1 : carry_level;
+        carry_start = coded ? 32 * k + ilog2u(coded) + 1 : carry_start;
+        prev_level_msb = lm >> 31;
+        prev_gt3_msb = gt3[k] >> 31;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    int total = acc + (chroma ? 1 : 0);                              // :147-158: the chroma flag bit
+    if (chroma && last == 0 && (nz[0] & 1) && !(big[0] & 1)) total = 2;   // a lone +-1: flag + sign, nothing else
     if (lane == 0) bits[t] = (uint32_t)total;
     __syncwarp();
   }
