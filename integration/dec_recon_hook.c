@@ -278,12 +278,29 @@ static void run_tbs(const int *idx, int n) {            /* dequantise + inverse 
 /* ---- one frame in flight ----
  * The device works on frame n while the host parses frame n+1: thorcuda_dec_flush(n) queues everything, including the
  * download of the filtered frame into a pinned compact buffer, and returns without waiting.  The frame is completed
- * (wait for the event behind its download + copy into the decoder's own picture) at the start of flush(n+1); maindec's write_yuv_frame calls go
+ * (wait for the event behind its download) at the start of flush(n+1); maindec's write_yuv_frame calls go
  * through thorcuda_dec_write_frame, which holds back a picture that is still in flight (and everything behind it, the
  * output stays in order) until then.  THORCUDA_HOOK_SERIAL=1 completes every frame at once (the old behaviour). */
 static struct { yuv_frame_t *rec; int timer; } inflight;      /* timer: CUDA events around the frame's device work */
 
-static uint8_t *out_pin;
+/* the filtered picture of each of the decoder's output slots lives in a pinned compact (w*h*3/2) buffer: the device
+ * writes it there, the output thread writes the file from there; the decoder's own rec picture is never filled in
+ * (nothing reads it any more: prediction, filters and reference creation are on the device) */
+static struct { const yuv_frame_t *f; uint8_t *pin; } outs[MAX_REORDER_BUFFER + 2];
+static int nouts;
+static uint8_t *pin_of(const yuv_frame_t *f, int create) {
+  for (int i = 0; i < nouts; i++) if (outs[i].f == f) return outs[i].pin;
+  if (!create) return NULL;
+  if (nouts == (int)(sizeof(outs) / sizeof(outs[0]))) fatalerror("thorcuda hook: more output pictures than the reorder buffer holds");
+  outs[nouts].f = f;
+  outs[nouts].pin = (uint8_t *)thorcuda_host_alloc((size_t)f->width * f->height * 3 / 2);
+  if (!outs[nouts].pin) fatalerror("thorcuda hook: pinned allocation failed");
+  return outs[nouts++].pin;
+}
+static void write_compact(const uint8_t *pin, int width, int height, FILE *file) {
+  const size_t n = (size_t)width * height * 3 / 2;
+  if (fwrite(pin, 1, n, file) != n) fatalerror("Error writing the decoded picture");
+}
 static struct { yuv_frame_t *f; int w, h; FILE *file; } wq[2 * MAX_REORDER_BUFFER + 4];
 static int nwq, serial = -1;
 
@@ -295,11 +312,6 @@ static void complete_inflight(void) {
   const float ms = thorcuda_timer_elapsed_ms(inflight.timer);
   if (ms < 0) fatalerror("thorcuda hook: waiting for the frame failed");
   if (tp_seen >= 36) dev_ms += ms;
-  output_wait_for(r);
-  const uint8_t *src = out_pin;
-  for (int i = 0; i < r->height; i++, src += r->width) memcpy(r->y + (size_t)i * r->stride_y, src, (size_t)r->width);
-  for (int i = 0; i < r->height / 2; i++, src += r->width / 2) memcpy(r->u + (size_t)i * r->stride_c, src, (size_t)r->width / 2);
-  for (int i = 0; i < r->height / 2; i++, src += r->width / 2) memcpy(r->v + (size_t)i * r->stride_c, src, (size_t)r->width / 2);
   inflight.rec = NULL;
 }
 
@@ -307,7 +319,7 @@ static void complete_inflight(void) {
  * write_yuv_frame (2160 fwrite calls for a 1080p picture, 1.3 ms) runs on its own thread, in request order; the
  * decoder only waits for it when it is about to overwrite a picture that has not been written yet. */
 #define OQ 64
-static struct { yuv_frame_t *f; int w, h; FILE *file; } oq[OQ];
+static struct { yuv_frame_t *f; const uint8_t *pin; int w, h; FILE *file; } oq[OQ];
 static unsigned oq_head, oq_tail;                   /* tail: next to write, head: next free; both only grow */
 static pthread_mutex_t oq_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t oq_cv = PTHREAD_COND_INITIALIZER;
@@ -322,7 +334,8 @@ static void *writer_main(void *arg) {
     if (oq_tail == oq_head) break;
     const unsigned k = oq_tail % OQ;
     pthread_mutex_unlock(&oq_mu);
-    write_yuv_frame(oq[k].f, oq[k].w, oq[k].h, oq[k].file);
+    if (oq[k].pin) write_compact(oq[k].pin, oq[k].w, oq[k].h, oq[k].file);
+    else write_yuv_frame(oq[k].f, oq[k].w, oq[k].h, oq[k].file);
     pthread_mutex_lock(&oq_mu);
     oq_tail++;
     pthread_cond_broadcast(&oq_cv);
@@ -333,7 +346,9 @@ static void *writer_main(void *arg) {
 
 static void output_frame(yuv_frame_t *f, int w, int h, FILE *file) {
   if (sync_out < 0) sync_out = getenv("THORCUDA_HOOK_SYNC_OUTPUT") != NULL;
-  if (sync_out || !file) { write_yuv_frame(f, w, h, file); return; }
+  const uint8_t *pin = pin_of(f, 0);         /* NULL only in a dry run: the decoder's own (unfilled) picture is written */
+  if (!file) return;                         /* write_yuv_frame is not called without an output file either (its fwrite would fault) */
+  if (sync_out) { if (pin) write_compact(pin, w, h, file); else write_yuv_frame(f, w, h, file); return; }
   pthread_mutex_lock(&oq_mu);
   if (!oq_started) {
     if (pthread_create(&oq_thread, NULL, writer_main, NULL)) fatalerror("thorcuda hook: cannot start the output thread");
@@ -341,7 +356,7 @@ static void output_frame(yuv_frame_t *f, int w, int h, FILE *file) {
   }
   while (oq_head - oq_tail == OQ) pthread_cond_wait(&oq_cv, &oq_mu);
   const unsigned k = oq_head % OQ;
-  oq[k].f = f; oq[k].w = w; oq[k].h = h; oq[k].file = file;
+  oq[k].f = f; oq[k].pin = pin; oq[k].w = w; oq[k].h = h; oq[k].file = file;
   oq_head++;
   pthread_cond_broadcast(&oq_cv);
   pthread_mutex_unlock(&oq_mu);
@@ -458,11 +473,8 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   lap(2);
   /* 3. the frame tail, into the device twin of the ring slot the new reference will occupy */
   if (serial < 0) serial = getenv("THORCUDA_HOOK_SERIAL") != NULL;
-  if (!out_pin) {
-    out_pin = (uint8_t *)thorcuda_host_alloc((size_t)rec->width * rec->height * 3 / 2);
-    if (!out_pin) fatalerror("thorcuda hook: pinned allocation failed");
-  }
-  thorcuda_dec_out_compact = out_pin;
+  output_wait_for(di->rec);                  /* the slot's previous picture (32 frames ago) must have left for the file */
+  thorcuda_dec_out_compact = pin_of(di->rec, 1);
   thorcuda_dec_tail_device(di, stream, qp, dev_rec, twin_of(di->ref[MAX_REF_FRAMES - 1]));
   need(thorcuda_timer_end(frame_timer));
   inflight.rec = di->rec;

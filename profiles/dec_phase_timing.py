@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Host-phase table of integration/_build/Thordec_gpu (THORCUDA_HOOK_TIMING=1) on a 1080p stream encoded here by the
 reference's Thorenc, pipelined (default) and serial (THORCUDA_HOOK_SERIAL=1).  Measurement tooling.
-    python profiles/dec_phase_timing.py [LDB_low_complexity|RA_low_complexity] [frames]"""
+    python profiles/dec_phase_timing.py [LDB_low_complexity|RA_low_complexity] [frames] [WxH]"""
 import os
 import subprocess
 import sys
@@ -14,13 +14,14 @@ import bench  # noqa: E402
 
 cfg = sys.argv[1] if len(sys.argv) > 1 else "LDB_low_complexity"
 frames = int(sys.argv[2]) if len(sys.argv) > 2 else 105
+W, H = (int(v) for v in (sys.argv[3] if len(sys.argv) > 3 else "1920x1080").split("x"))
 enc, dec = os.path.join(ROOT, "oracle/_ref/Thorenc"), os.path.join(ROOT, "oracle/_ref/Thordec")
 gpu = os.path.join(ROOT, "integration/_build/Thordec_gpu")
-with tempfile.TemporaryDirectory() as d:
+with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as d:
     yuv, bit = os.path.join(d, "c.yuv"), os.path.join(d, "c.bit")
-    bench.write_clip(yuv, 1920, 1080, frames)
-    subprocess.run([enc, "-if", yuv, "-of", bit, "-rf", os.path.join(d, "r.yuv"), "-stat", os.path.join(d, "s.txt"), "-width", "1920",
-                    "-height", "1080", "-n", str(frames), "-f", "60", "-qp", "32"] + bench.DEC_CONFIGS[cfg], check=True, capture_output=True)
+    bench.write_clip(yuv, W, H, frames)
+    subprocess.run([enc, "-if", yuv, "-of", bit, "-rf", os.path.join(d, "r.yuv"), "-stat", os.path.join(d, "s.txt"), "-width", str(W),
+                    "-height", str(H), "-n", str(frames), "-f", "60", "-qp", "32"] + bench.DEC_CONFIGS[cfg], check=True, capture_output=True)
     outs = {}
     for name, exe, env in (("stock", dec, {}), ("pipelined", gpu, {"THORCUDA_HOOK_TIMING": "1"}),
                            ("serial", gpu, {"THORCUDA_HOOK_TIMING": "1", "THORCUDA_HOOK_SERIAL": "1"})):

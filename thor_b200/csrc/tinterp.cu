@@ -43,11 +43,21 @@ __host__ __device__ __forceinline__ int scale_component(int v, int numer, int de
   if (denom < 0) { denom = -denom; prod = -prod; }
   return prod >= 0 ? (prod + denom / 2) / denom : -((-prod + denom / 2) / denom);
 }
+// the same rounding division for the device: denom = wt0 is a small positive frame distance, so |v * numer| + denom / 2
+// stays below 2^24 and the quotient is exactly the high word of a multiplication by ceil(2^32 / denom) -- the integer
+// division costs ~40 dependent instructions on the block search's critical path, four times per candidate
+__device__ __forceinline__ int scale_exact(int v, int numer, int denom) {
+  if (denom > 255 || denom < 2) return scale_component(v, numer, denom);
+  const int prod = v * numer;
+  const uint32_t magic = 0xffffffffu / (uint32_t)denom + 1;       // uniform: hoisted out of the loops by the compiler
+  const int q = (int)__umulhi((uint32_t)abs(prod) + (uint32_t)(denom >> 1), magic);
+  return prod >= 0 ? q : -q;
+}
 __device__ __forceinline__ short2 to_pic0(short2 v, int wt0, int wt1) {
   const int numer = -wt1, denom = wt0;
   if (numer == denom) return v;
   if (numer == -denom) return make_short2((short)-v.x, (short)-v.y);
-  return make_short2((short)scale_component(v.x, numer, denom), (short)scale_component(v.y, numer, denom));
+  return make_short2((short)scale_exact(v.x, numer, denom), (short)scale_exact(v.y, numer, denom));
 }
 __device__ __forceinline__ int pel(int v) { return (v + 4) >> 3; }
 __device__ __forceinline__ int l1(short2 a, short2 b) { return abs(a.x - b.x) + abs(a.y - b.y); }
@@ -199,6 +209,30 @@ __device__ __forceinline__ uint32_t block_cost(const LevelView &L, const Nbrs &n
   return s + (uint32_t)field_cost(nb, v, lambda);
 }
 
+// block_cost of v (returned to every lane) and of the group's cross point t (returned to the group) in ONE round of
+// loads: the candidate's own cost and its first cross iteration are independent, and the search is bound by the latency
+// of that chain.  v is spread over all 32 lanes (row lane / 2, 8-sample half lane & 1), t over the group as in block_cost.
+__device__ __forceinline__ void block_cost_pair(const LevelView &L, const Nbrs &nb, int lambda, int xs, int ys, short2 v, short2 t,
+                                                int lane, int gl, uint32_t &cost_v, uint32_t &cost_t) {
+  const short2 v0 = to_pic0(v, L.wt0, L.wt1), t0 = to_pic0(t, L.wt0, L.wt1);
+  const int vx0 = xs + pel(v0.x), vy0 = ys + pel(v0.y), vx1 = xs + pel(v.x), vy1 = ys + pel(v.y);
+  const int tx0 = xs + pel(t0.x), ty0 = ys + pel(t0.y), tx1 = xs + pel(t.x), ty1 = ys + pel(t.y);
+  const bool vin = inside(L, vx0, vy0, 16) && inside(L, vx1, vy1, 16), tin = inside(L, tx0, ty0, 16) && inside(L, tx1, ty1, 16);
+  const int h8 = 8 * (lane & 1);
+  uint32_t sv = sad_rows<8>(L, vx0 + h8, vy0, vx1 + h8, vy1, lane >> 1, 1, vin);
+  uint32_t st = sad_rows<16>(L, tx0, ty0, tx1, ty1, 2 * gl, 2, tin);
+  sv += __shfl_xor_sync(0xffffffffu, sv, 1);
+  st += __shfl_xor_sync(0xffffffffu, st, 1);
+  sv += __shfl_xor_sync(0xffffffffu, sv, 2);
+  st += __shfl_xor_sync(0xffffffffu, st, 2);
+  sv += __shfl_xor_sync(0xffffffffu, sv, 4);
+  st += __shfl_xor_sync(0xffffffffu, st, 4);
+  sv += __shfl_xor_sync(0xffffffffu, sv, 8);
+  sv += __shfl_xor_sync(0xffffffffu, sv, 16);
+  cost_v = sv + (uint32_t)field_cost(nb, v, lambda);
+  cost_t = st + (uint32_t)field_cost(nb, t, lambda);
+}
+
 template <bool GUIDED>
 __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
   __shared__ EstSmem S;
@@ -319,11 +353,12 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
     if (warp >= 1 && c < nc) {
       // this warp's candidate, refined on its own by the cross search (:674-712)
       short2 cur = zero;
+      uint32_t my_init = 0;
 #pragma unroll
       for (int i = 0; i < 5; i++) if (i == c) cur = cand[i];
-      uint32_t cost = block_cost(L, nb, lambda, xs, ys, cur, gl);
-      const uint32_t my_init = cost;
       int shift = GUIDED ? 3 : 6, budget = GUIDED ? 8 : 64;
+      uint32_t cost = 0, tc = 0;
+      bool first = true;                     // the first cross iteration always runs: priced together with the candidate
       while (shift >= 3 && budget > 0) {
         const int off = 1 << shift;
         short2 t = cur;
@@ -331,7 +366,11 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
         else if (grp == 1) t.x = (short)(cur.x + off);
         else if (grp == 2) t.y = (short)(cur.y - off);
         else t.y = (short)(cur.y + off);
-        const uint32_t tc = block_cost(L, nb, lambda, xs, ys, t, gl);
+        if (first) {
+          block_cost_pair(L, nb, lambda, xs, ys, cur, t, lane, gl, cost, tc);
+          my_init = cost;
+          first = false;
+        } else tc = block_cost(L, nb, lambda, xs, ys, t, gl);
         // the reference takes the four points in order, each against the best so far: the smallest wins, the first on ties
         uint32_t bestc = cost;
         int bestk = -1;
