@@ -83,6 +83,10 @@ int thorcuda_pic_copy(thorcuda_pic dst, thorcuda_pic src);
  * 4x4 luma unit, (h/4)*(w/4) entries, host memory).  Uploaded, packed to 2 bytes/unit on the device
  * and attached to picture `rec` (it describes that picture's blocks).                               */
 int thorcuda_blockinfo_upload(thorcuda_pic rec, const void *deblock_data);
+/* The same, and additionally which superblocks clpf_frame asks its decision callback about (common/common_frame.c:507-521:
+ * some 8x8 block of the SB is not bi-predicted and has coded coefficients): sb_signals[k * (w/64) + l], (h/64)*(w/64)
+ * bytes, written before the call returns.  The decoder reads one CLPF bit from the stream per signalling superblock. */
+int thorcuda_blockinfo_upload_signals(thorcuda_pic rec, const void *deblock_data, uint8_t *sb_signals);
 
 #define THORCUDA_LF_DEBLOCK_Y   1   /* deblock_frame_y   common/common_frame.c:46-241               */
 #define THORCUDA_LF_DEBLOCK_UV  2   /* deblock_frame_uv  common/common_frame.c:243-321              */

@@ -29,7 +29,7 @@ void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thor
 extern uint8_t *thorcuda_dec_out_compact;
 
 /* THORCUDA_HOOK_TIMING=1: host milliseconds per phase and frame, printed at exit */
-static double tp[6], t_mark, t_hk[3];
+static double tp[6], t_mark, t_hk[5];
 #define HK_T0 const double hk0_ = tp_on > 0 ? ms_now() : 0
 #define HK_T1(i) do { if (tp_on > 0 && tp_seen >= 36) t_hk[i] += ms_now() - hk0_; } while (0)
 static double dev_ms;
@@ -51,6 +51,7 @@ static void tp_report(void) {
   const int n = tp_frames ? tp_frames : 1;
   for (int i = 0; i < 6; i++) fprintf(stderr, "thorcuda recon hook: %-18s %8.3f ms/frame\n", name[i], tp[i] / n);
   fprintf(stderr, "thorcuda recon hook: inside hk_luma %.3f, hk_recon_inter %.3f, hk_recon_intra %.3f ms/frame\n", t_hk[0] / n, t_hk[1] / n, t_hk[2] / n);
+  fprintf(stderr, "thorcuda recon hook: inside thorcuda_dec_write_frame %.3f, thorcuda_dec_interpolate %.3f ms/frame (both between frames)\n", t_hk[3] / n, t_hk[4] / n);
   fprintf(stderr, "thorcuda recon hook: device time of a frame's reconstruction (CUDA events, without interpolate_frames) %.3f ms/frame\n", dev_ms / n);
   fprintf(stderr, "thorcuda recon hook: per frame %d prediction tasks, %d transform blocks, %d intra blocks in %d levels\n",
           tp_pred / n, tp_tbs / n, tp_intra / n, tp_levels / n);
@@ -400,10 +401,12 @@ static void drain_writes(int all) {
 
 /* maindec.c's write_yuv_frame(&rec[i], width, height, outfile) */
 void thorcuda_dec_write_frame(yuv_frame_t *frame, int width, int height, FILE *outfile) {
-  if (nwq == 0 && frame != inflight.rec) { output_frame(frame, width, height, outfile); return; }
+  HK_T0;
+  if (nwq == 0 && frame != inflight.rec) { output_frame(frame, width, height, outfile); HK_T1(3); return; }
   if (nwq == (int)(sizeof(wq) / sizeof(wq[0]))) drain_writes(1);
   wq[nwq].f = frame; wq[nwq].w = width; wq[nwq].h = height; wq[nwq].file = outfile;
   nwq++;
+  HK_T1(3);
 }
 
 /* before maindec.c prints its statistics and closes the output */
@@ -489,8 +492,10 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
 void thorcuda_dec_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos) {
   if (dry < 0) dry = getenv("THORCUDA_HOOK_DRY") != NULL;
   if (dry) return;
+  HK_T0;
   need(thorcuda_interpolate_frames(twin_of(dst), twin_of(ref0), twin_of(ref1), ratio, pos));
   need(thorcuda_pad_frame(twin_of(dst)));
+  HK_T1(4);
 }
 
 /* create_reference_frame: the padded reference already sits in the slot's device twin, which is all the decoder

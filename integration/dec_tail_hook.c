@@ -36,7 +36,7 @@ static void report(void) {
 
 static thorcuda_pic dev_rec = -1, dev_ref = -1;
 static int dev_w, dev_h;
-static uint8_t *sb_bits;
+static uint8_t *sb_bits, *sb_sig;
 
 /* page-lock a frame's planes the first time it is seen (the decoder allocates its frames once, with malloc) */
 static const void *locked[128];
@@ -72,18 +72,6 @@ static void setup(const yuv_frame_t *rec) {
   if (dev_rec < 0 || dev_ref < 0) fatalerror((char *)thorcuda_last_error());
 }
 
-/* does clpf_frame ask its decision callback about superblock (k, l)?  -- any 8x8 block that is not bi-predicted and
- * has coded coefficients in some plane */
-static int sb_signals(const deblock_data_t *dd, int width, int k, int l) {
-  const int upr = width / MIN_PB_SIZE;
-  for (int m = 0; m < MAX_BLOCK_SIZE; m += 8)
-    for (int n = 0; n < MAX_BLOCK_SIZE; n += 8) {
-      const deblock_data_t *b = dd + ((k * MAX_BLOCK_SIZE + m) / MIN_PB_SIZE) * upr + (l * MAX_BLOCK_SIZE + n) / MIN_PB_SIZE;
-      if (b->mode != MODE_BIPRED && (b->cbp.y || b->cbp.u || b->cbp.v)) return 1;
-    }
-  return 0;
-}
-
 uint8_t *thorcuda_dec_out_compact;     /* set by dec_recon_hook.c: pinned w*h*3/2 target of the frame download */
 
 /* blockinfo + CLPF bits + fused launch + download of the filtered frame, for a reconstruction that already sits in
@@ -92,7 +80,8 @@ void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thor
   yuv_frame_t *rec = di->rec;
   double t0 = now_ms();
   if (!sb_bits) sb_bits = (uint8_t *)thorcuda_host_alloc((size_t)(rec->width / MAX_BLOCK_SIZE + 1) * (rec->height / MAX_BLOCK_SIZE + 1));
-  need(thorcuda_blockinfo_upload(rec_dev, di->deblock_data));
+  if (!sb_sig) sb_sig = (uint8_t *)malloc((size_t)(rec->width / MAX_BLOCK_SIZE + 1) * (rec->height / MAX_BLOCK_SIZE + 1));
+  need(thorcuda_blockinfo_upload_signals(rec_dev, di->deblock_data, sb_sig));   /* one pass over deblock_data for both */
   MARK(1);
   int stages = THORCUDA_LF_MAKE_REF;
   if (di->deblocking) stages |= THORCUDA_LF_DEBLOCK_Y | THORCUDA_LF_DEBLOCK_UV;
@@ -100,10 +89,8 @@ void thorcuda_dec_tail_device(decoder_info_t *di, stream_t *stream, int qp, thor
    * then one bit per signalling superblock in raster order */
   if (di->clpf && getbits(stream, 1)) {
     const int all = getbits(stream, 1);
-    const int nh = rec->width / MAX_BLOCK_SIZE, nv = rec->height / MAX_BLOCK_SIZE;
-    for (int k = 0; k < nv; k++)
-      for (int l = 0; l < nh; l++)
-        sb_bits[k * nh + l] = sb_signals(di->deblock_data, rec->width, k, l) ? (uint8_t)(all ? 1 : getbits(stream, 1)) : 0;
+    const int nsb = (rec->width / MAX_BLOCK_SIZE) * (rec->height / MAX_BLOCK_SIZE);
+    for (int i = 0; i < nsb; i++) sb_bits[i] = sb_sig[i] ? (uint8_t)(all ? 1 : getbits(stream, 1)) : 0;
     stages |= THORCUDA_LF_CLPF;
   }
   MARK(2);

@@ -62,7 +62,7 @@ def cdll():
                 ("thorcuda_pic_upload", I, [I, V, V, V, I, I]), ("thorcuda_pic_download", I, [I, V, V, V, I, I]),
                 ("thorcuda_pic_download_padded", I, [I, V, V, V]), ("thorcuda_pic_upload_padded", I, [I, V, V, V]),
                 ("thorcuda_pic_devptr", V, [I, I]), ("thorcuda_pic_copy", I, [I, I]),
-                ("thorcuda_blockinfo_upload", I, [I, V]),
+                ("thorcuda_blockinfo_upload", I, [I, V]), ("thorcuda_blockinfo_upload_signals", I, [I, V, V]),
                 ("thorcuda_loopfilter_frame", I, [I, I, I, I, I, V, V]), ("thorcuda_loopfilter_frames", I, [I, V]),
                 ("thorcuda_pad_frame", I, [I]),
                 ("thorcuda_list_create", I, [I, V, I, V, I]), ("thorcuda_list_destroy", None, [I]),
