@@ -131,7 +131,7 @@ def make_pred_tasks(tb, w, h, rng, nrefs, dst_index, mv_sigma=24, bi_frac=0.3, r
     return _arr(tasks, tb.PRED_TASK)
 
 
-@pytest.mark.parametrize("wh,bipred", [((416, 240), 1), ((416, 240), 0), ((200, 136), 1), ((1920, 1080), 1)])
+@pytest.mark.parametrize("wh,bipred", [((416, 240), 1), ((416, 240), 0), ((200, 136), 1), ((1920, 1080), 1), ((3840, 2160), 1)])
 def test_predict_blocks(tb, orc, wh, bipred):
     w, h = wh
     rng = np.random.default_rng(w + bipred)
@@ -243,7 +243,7 @@ def tb_pictures(tb, w, h, seed, noise):
 
 
 @pytest.mark.parametrize("wh,qps,intra", [((256, 192), (22, 32, 37), False), ((256, 192), (0, 13, 51), True),
-                                          ((416, 240), (30,), False), ((1920, 1080), (32,), False)])
+                                          ((416, 240), (30,), False), ((1920, 1080), (32,), False), ((3840, 2160), (32,), False)])
 def test_encode_blocks(tb, orc, wh, qps, intra):
     w, h = wh
     rng = np.random.default_rng(w + qps[0])
@@ -374,7 +374,7 @@ def numpy_sad_tables(org_y, ref_pic, R, centres):
 
 
 @pytest.mark.parametrize("wh,R,with_centres", [((416, 240), 8, False), ((200, 136), 16, True), ((128, 128), 32, True),
-                                               ((1920, 1080), 16, False)])
+                                               ((1920, 1080), 16, False), ((3840, 2160), 16, False)])
 def test_sad_table(tb, orc, wh, R, with_centres):
     w, h = wh
     rng = np.random.default_rng(w + R)

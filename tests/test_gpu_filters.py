@@ -99,7 +99,7 @@ def test_clpf(tb, wh, enc):
         dorg.close()
 
 
-@pytest.mark.parametrize("wh", [(416, 240), (200, 136), (1920, 1080)])
+@pytest.mark.parametrize("wh", [(416, 240), (200, 136), (1920, 1080), (3840, 2160)])     # 2160 = 33*64 + 48: the last SB row is partial
 def test_fused_frame_tail_and_reference(tb, wh):
     """deblock Y+UV -> CLPF (encoder decision) -> create_reference_frame in one call."""
     w, h = wh

@@ -47,7 +47,8 @@ def device_pic(tb, p):
 
 
 CASES = [(416, 240, "scene", (3, 5)), (192, 136, "scene", (-7, 12)), (128, 128, "noise", None), (320, 192, "scene", (40, -70)),
-         (64, 48, "scene", (1, 2)), (200, 72, "noise", None), (416, 240, "scene", (6, 200)), (1920, 1080, "scene", (4, -9))]
+         (64, 48, "scene", (1, 2)), (200, 72, "noise", None), (416, 240, "scene", (6, 200)), (1920, 1080, "scene", (4, -9)),
+         (3840, 2160, "scene", (-6, 11))]
 
 
 @pytest.mark.parametrize("case", CASES, ids=[f"{c[0]}x{c[1]}-{c[2]}-{i}" for i, c in enumerate(CASES)])
