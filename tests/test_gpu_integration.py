@@ -71,3 +71,24 @@ def test_thorenc_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp):
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
     assert open(pre + ".bit", "rb").read() == bit_cpu, "bitstream differs"
     assert open(pre + "_rec.yuv", "rb").read() == rec_cpu, "reconstruction differs"
+
+
+@pytest.mark.parametrize("env", [{"THORCUDA_HOOK_SERIAL": "1"}, {"THORCUDA_HOOK_SYNC_OUTPUT": "1"},
+                                 {"THORCUDA_HOOK_SERIAL": "1", "THORCUDA_HOOK_SYNC_OUTPUT": "1"}, {"THORCUDA_HOOK_TIMING": "1"}])
+def test_thordec_gpu_pipeline_switches(tmp_path, env):
+    """Thordec_gpu keeps one frame in flight and writes the output on its own thread; the switches that turn either off
+    (and the timing report) must not change a byte.  RA stream: pictures leave the decoder out of coding order."""
+    exe = os.path.join(BUILD, "Thordec_gpu")
+    for need in (os.path.join(REF_DIR, "Thorenc"), os.path.join(REF_DIR, "Thordec"), exe):
+        if not os.path.exists(need):
+            pytest.skip(f"{need} not built (needs /root/reference at build time)")
+    w, h, frames = 192, 136, 25
+    yuv = str(tmp_path / "clip.yuv")
+    write_clip(yuv, w, h, frames, seed=5)
+    run_thorenc("Thorenc", "RA_low_complexity", yuv, w, h, frames, 33, str(tmp_path / "enc"))
+    cpu = _decode(os.path.join(REF_DIR, "Thordec"), str(tmp_path / "enc.bit"), str(tmp_path / "cpu.yuv"))
+    r = subprocess.run([exe, str(tmp_path / "enc.bit"), str(tmp_path / "gpu.yuv")], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, **env))
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert open(str(tmp_path / "gpu.yuv"), "rb").read() == cpu
+    assert len(cpu) == frames * w * h * 3 // 2
