@@ -650,6 +650,8 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
     return {"value": B * world * n / dt, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "frames_per_step": B, "steps": n, "ms_per_step": 1e3 * dt / n,
             "host_ms_per_step": {k: round(1e3 * v / n, 3) for k, v in phase.items()},
+            # the step moves this many bytes over PCIe per second: compare with the link (Gen5 x16: ~57 GB/s measured D2H)
+            "pcie_GBps": {"d2h": round(d2h * n / dt / 1e9, 1), "h2d": round(h2d * n / dt / 1e9, 2)},
             "timing": "host wall clock around submit..thorcuda_sync, max over ranks (includes PCIe copies and list building)"}
 
 

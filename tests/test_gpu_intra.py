@@ -192,3 +192,70 @@ def test_intra_frame_wavefront(tb, orc):
     for pl in range(3):
         assert np.array_equal(got[pl], planes[pl]), f"plane {pl}"
     rec.close()
+
+
+def test_intra_trial_costs(tb, orc):
+    """The encoder's intra trial loop (enc/encode_block.c:1230-1329, 2224-2310: every mode of a block is predicted,
+    trial-encoded and priced) as three batched calls on resident lists: intra_predict_blocks -> encode_list (ssd) ->
+    coeff_bits_list (write_coeff's bits).  Ten modes of every block at once, mode m of all blocks in scratch picture m.
+    SSD, bits and therefore cost_calc's ssd + (int)(lambda * nbits + 0.5) ranking agree with the oracle for every trial."""
+    from test_gpu_blocks import oracle_tb
+    from thor_b200.lib import INTRA_TASK
+    w, h, qp, lam = 256, 192, 30, 38.5
+    rng = np.random.default_rng(11)
+    yy, xx = np.mgrid[0:h, 0:w]
+    # horizontal stripes under the 8x8 blocks, vertical stripes under the 16x16 ones, a smooth ramp under the 32x32 ones
+    base = np.where(xx < 56, 128 + 60 * np.sin(yy / 2.5), np.where(xx < 136, 128 + 60 * np.sin(xx / 2.5), 60 + 0.5 * xx + 0.3 * yy)).astype(np.float64)
+    org = [np.clip(base + rng.normal(0, 6, (h, w)), 0, 255).astype(np.uint8),
+           rng.integers(90, 170, (h // 2, w // 2)).astype(np.uint8), rng.integers(90, 170, (h // 2, w // 2)).astype(np.uint8)]
+    rec = [np.clip(o.astype(np.int32) + rng.integers(-3, 4, o.shape), 0, 255).astype(np.uint8) for o in org]   # "already coded" surroundings
+    d_org, d_rec = tb.Picture(w, h), tb.Picture(w, h)
+    d_org.upload(*org)
+    d_rec.upload(*rec)
+    scratch = [tb.Picture(w, h) for _ in range(10)]
+    # disjoint blocks (their trials share the scratch pictures), none on a picture edge
+    blocks = [(8, 8, 8), (24, 8, 8), (8, 24, 8), (24, 24, 8), (64, 16, 16), (96, 16, 16), (64, 48, 16), (96, 48, 16),
+              (144, 32, 32), (208, 32, 32), (144, 96, 32), (208, 96, 32)]
+    # one intra task + one transform task per (block, mode)
+    it, tt = [], []
+    for (x, y, s) in blocks:
+        for m in range(10):
+            it.append((x, y, x, s, 0, m, 1 | 2, 0, 1 + m % 5))        # src = pics[0] (rec), dst = the mode's scratch picture
+            t = np.zeros((), tb.TB_TASK)
+            t["x"], t["y"], t["size"], t["plane"], t["qp"], t["coeff_type"], t["fast"] = x, y, s, 0, qp, 2, 0
+            t["org"], t["pred"], t["rec"] = 0, 1 + m, 1 + m              # pics = [org, scratch 0..9]; reconstruct in place
+            tt.append(t)
+    it = np.array(it, INTRA_TASK)
+    for half in (0, 1):                                                 # at most 8 pictures per intra call: five modes each
+        sel = np.array([k for k in range(len(it)) if (k % 10) // 5 == half])
+        tb.ops.intra_predict_blocks([d_rec] + scratch[5 * half:5 * half + 5], it[sel])
+    tasks = np.zeros(len(tt), tb.TB_TASK)
+    for k, t in enumerate(tt):
+        tasks[k] = t[()]
+    tb.ops.pool_layout(tasks)
+    lst = tb.ops.TaskList(tb.LIST_TB, [d_org] + scratch, tasks)
+    ssd, cbp, bits = np.zeros(lst.ntasks, np.uint32), np.zeros(lst.ntasks, np.uint8), np.zeros(lst.ntasks, np.uint32)
+    lst.encode(None, cbp, ssd)
+    lst.coeff_bits(bits)
+    tb.sync()
+    lst.close()
+    k = 0
+    winners = set()
+    for (x, y, s) in blocks:
+        cost_gpu, cost_cpu = [], []
+        for m in range(10):
+            pred = oracle_intra(orc, rec[0], x, y, x, s, m, 3)
+            pred_plane = np.zeros((h, w), np.uint8)
+            pred_plane[y:y + s, x:x + s] = pred
+            _, wcq, wcbp, wssd = oracle_tb(orc, org[0], pred_plane, tasks[k])
+            q = min(s, 16)
+            wbits = orc.orc_coeff_bits(ptr(np.ascontiguousarray(wcq)), q, s, 2) if wcbp else 0
+            assert (int(ssd[k]), int(cbp[k]), int(bits[k])) == (wssd, wcbp, wbits), (x, y, s, m)
+            cost_gpu.append(int(ssd[k]) + int(lam * int(bits[k]) + 0.5))
+            cost_cpu.append(wssd + int(lam * wbits + 0.5))
+            k += 1
+        assert cost_gpu == cost_cpu
+        winners.add(int(np.argmin(cost_gpu)))
+    assert len(winners) >= 3, "the trial costs must discriminate between modes"
+    for p in [d_org, d_rec] + scratch:
+        p.close()
