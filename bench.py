@@ -235,23 +235,31 @@ def decoder_leg(args):
                             "-width", str(args.width), "-height", str(args.height), "-n", str(n), "-f", "60", "-qp", "32"]
                            + DEC_CONFIGS[args.decoder_config],
                            check=True, capture_output=True, timeout=900)
-        res, outs = {}, {}
+        res, outs, steady = {}, {}, {}
         for name, exe in (("reference", dec), ("gpu_tail", tail), ("gpu_recon", full)):
             best = {}
             for n in (short, frames):
                 for _ in range(5):                     # CUDA start-up varies by tenths of a second from run to run
                     out = os.path.join(d, name + ".yuv")
                     t0 = time.perf_counter()
-                    subprocess.run([exe, bits[n], out], check=True, capture_output=True, timeout=600)
+                    r = subprocess.run([exe, bits[n], out], check=True, capture_output=True, text=True, timeout=600,
+                                       env=dict(os.environ, THORCUDA_HOOK_TIMING="1"))
                     dt = time.perf_counter() - t0
                     best[n] = min(best.get(n, dt), dt)
+                    for ln in r.stderr.splitlines():          # the hooked decoder's own clock: frame 37 .. output complete
+                        if "steady state" in ln and n == frames:
+                            steady.setdefault(name, []).append(float(ln.split("=")[1].split("frames/s")[0]))
             outs[name] = open(out, "rb").read()
             res[name + "_fps"] = round((frames - short) / (best[frames] - best[short]), 2)
             res[name + "_startup_s"] = round(best[short] - short * (best[frames] - best[short]) / (frames - short), 3)
             res[name + "_seconds"] = {str(n): round(best[n], 3) for n in (short, frames)}
+        for name, v in steady.items():
+            res[name + "_steady_fps"] = round(sorted(v)[len(v) // 2], 1)       # median of the 5 runs of the long stream
         res.update({"frames": frames, "stream": f"{args.decoder_config} {args.width}x{args.height} qp 32, {os.path.getsize(bits[frames])} bytes",
                     "identical_yuv": outs["reference"] == outs["gpu_tail"] == outs["gpu_recon"], "scratch": "tmpfs (/dev/shm)" if shm else "default temporary directory",
-                    "note": "marginal decode rate between a short and a long stream (process wall clock, file I/O included); "
+                    "note": "*_fps: marginal decode rate between a short and a long stream (process wall clock, file I/O included; the CUDA "
+                            "start-up of the hooked decoders varies by +-0.4 s between runs, which this difference only cancels on average); "
+                            "gpu_recon_steady_fps: the hooked decoder's own wall clock from its 37th frame until the output file is complete; "
                             "gpu_tail: deblock + CLPF + reference creation on the GPU; gpu_recon: prediction, inverse transform and "
                             "reconstruction as well (references device-resident), the host parses the stream and writes the output"})
         return res
@@ -708,7 +716,7 @@ def main():
     ap.add_argument("--e2e-streams", type=int, default=4)
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail / the whole reconstruction on the GPU (adds ~1 min)")
-    ap.add_argument("--decoder-frames", type=int, default=104)
+    ap.add_argument("--decoder-frames", type=int, default=168)
     ap.add_argument("--decoder-config", default="LDB_low_complexity", choices=sorted(DEC_CONFIGS),
                     help="stream of the decoder leg; RA_low_complexity has B frames with interpolated references (one interpolate_frames per B frame)")
     ap.add_argument("--cpu-frames", type=int, default=2)

@@ -206,6 +206,16 @@ typedef struct {
   uint8_t  src, dst;        /* indices into pics[]                                                   */
 } thorcuda_intra_task;      /* 12 bytes */
 int thorcuda_intra_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, int ntasks);
+/* A whole frame's intra blocks in ONE call (dec/decode_block.c:48-88 for every intra block of the frame): the caller
+ * sorts the blocks into wavefront levels -- level(block) = 1 + the highest level among the blocks owning the samples it
+ * reads, blocks reconstructed before the call are level 0 -- and passes, both in level order,
+ *   tasks[intra_first[l] .. intra_first[l+1])   the predictions of level l, and
+ *   tb[tb_first[l] .. tb_first[l+1])            the coded transform blocks of level l (decoder leg: pred = rec = the
+ *                                                picture, coefficients in host_coeffq at their coeff_offset);
+ * per level the predictions are written, then the coded blocks are reconstructed in place.  Tasks and coefficients
+ * are uploaded once; the device work is two launches per level, queued on the library stream.                        */
+int thorcuda_intra_reconstruct_levels(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, const int *intra_first,
+                                      const thorcuda_tb_task *tb, const int *tb_first, int nlevels, const int16_t *host_coeffq);
 
 /* ------------------------------------------------------------ temporal interpolation ---- */
 /* interpolate_frames (common/temporal_interp.c:972-1053): the picture between two references that B frames of the

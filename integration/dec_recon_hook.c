@@ -32,7 +32,7 @@ extern uint8_t *thorcuda_dec_out_compact;
 static double tp[6], t_mark, t_hk[5];
 #define HK_T0 const double hk0_ = tp_on > 0 ? ms_now() : 0
 #define HK_T1(i) do { if (tp_on > 0 && tp_seen >= 36) t_hk[i] += ms_now() - hk0_; } while (0)
-static double dev_ms;
+static double dev_ms, t_steady0, t_finish;       /* wall clock when the 37th frame starts / when the output is complete */
 static int tp_frames, tp_on = -1, tp_levels, tp_intra, tp_pred, tp_tbs;
 static double ms_now(void) {
   struct timespec ts;
@@ -50,6 +50,9 @@ static void tp_report(void) {
   static const char *name[6] = {"parse + record", "inter submit + writes", "intra levels", "tail", "wait for previous frame + copy", "between frames"};
   const int n = tp_frames ? tp_frames : 1;
   for (int i = 0; i < 6; i++) fprintf(stderr, "thorcuda recon hook: %-18s %8.3f ms/frame\n", name[i], tp[i] / n);
+  if (t_finish > t_steady0 && t_steady0 > 0 && tp_frames)
+    fprintf(stderr, "thorcuda recon hook: steady state %.3f ms/frame wall clock = %.1f frames/s (frame 37 .. output complete, %d frames)\n",
+            (t_finish - t_steady0) / tp_frames, 1e3 * tp_frames / (t_finish - t_steady0), tp_frames);
   fprintf(stderr, "thorcuda recon hook: inside hk_luma %.3f, hk_recon_inter %.3f, hk_recon_intra %.3f ms/frame\n", t_hk[0] / n, t_hk[1] / n, t_hk[2] / n);
   fprintf(stderr, "thorcuda recon hook: inside thorcuda_dec_write_frame %.3f, thorcuda_dec_interpolate %.3f ms/frame (both between frames)\n", t_hk[3] / n, t_hk[4] / n);
   fprintf(stderr, "thorcuda recon hook: device time of a frame's reconstruction (CUDA events, without interpolate_frames) %.3f ms/frame\n", dev_ms / n);
@@ -102,6 +105,7 @@ void thorcuda_dec_frame_begin(decoder_info_t *di) {
   if (dry < 0) dry = getenv("THORCUDA_HOOK_DRY") != NULL;
   if (tp_on < 0) { tp_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (tp_on) { atexit(tp_report); t_mark = ms_now(); } }
   lap(5);
+  if (tp_on > 0 && tp_seen == 36) t_steady0 = ms_now();
   if (dry) return;
   if (dev_rec < 0) {
     const char *dev = getenv("THORCUDA_DEVICE");
@@ -410,7 +414,10 @@ void thorcuda_dec_write_frame(yuv_frame_t *frame, int width, int height, FILE *o
 }
 
 /* before maindec.c prints its statistics and closes the output */
-void thorcuda_dec_finish(void) { drain_writes(1); complete_inflight(); output_finish(); }
+void thorcuda_dec_finish(void) {
+  drain_writes(1); complete_inflight(); output_finish();
+  if (tp_on > 0) t_finish = ms_now();            /* every picture is in the output file */
+}
 
 void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   const yuv_frame_t *rec = di->rec;
@@ -463,15 +470,37 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
     int *sorted = (int *)malloc((size_t)(nintra + 1) * sizeof(int)), *fill = (int *)malloc((size_t)(maxl + 2) * sizeof(int));
     memcpy(fill, count, (size_t)(maxl + 2) * sizeof(int));
     for (int i = 0; i < ntbs; i++) if (lvl[i]) sorted[fill[lvl[i]]++] = i;
+    /* all levels in ONE call: predictions and coded transform blocks in level order, two launches per level */
     thorcuda_intra_task *batch = (thorcuda_intra_task *)malloc((size_t)(nintra + 1) * sizeof(*batch));
+    int *ifirst = (int *)malloc((size_t)(maxl + 2) * sizeof(int)), *tfirst = (int *)malloc((size_t)(maxl + 2) * sizeof(int));
     if (tp_seen >= 36) tp_levels += maxl;
-    for (int l = 1; l <= maxl; l++) {
-      const int a = count[l], b = count[l + 1];
-      for (int k = a; k < b; k++) batch[k - a] = intra[tbs[sorted[k]].intra];
-      need(thorcuda_intra_predict_blocks(pics, 1, batch, b - a));
-      run_tbs(sorted + a, b - a);
+    lt = (thorcuda_tb_task *)grow(lt, &clt, nintra + 1, sizeof(*lt));
+    size_t need_pool = 0;
+    for (int k = 0; k < nintra; k++) {
+      const Tb *t = &tbs[sorted[k]];
+      if (t->coef >= 0) { const int q = t->size < 16 ? t->size : 16; need_pool += ((size_t)q * q + 7) & ~(size_t)7; }
     }
-    free(batch); free(fill); free(sorted); free(count);
+    if (need_pool > clpool) { clpool = need_pool * 2; lpool = (int16_t *)realloc(lpool, clpool * sizeof(int16_t)); }
+    size_t off = 0;
+    int m = 0;
+    for (int l = 1; l <= maxl; l++) {
+      ifirst[l - 1] = count[l]; tfirst[l - 1] = m;
+      for (int k = count[l]; k < count[l + 1]; k++) {
+        const Tb *t = &tbs[sorted[k]];
+        batch[k] = intra[t->intra];
+        if (t->coef < 0) continue;                      /* no coefficients: the prediction is the reconstruction */
+        const int q = t->size < 16 ? t->size : 16;
+        thorcuda_tb_task *d = &lt[m++];
+        memset(d, 0, sizeof(*d));
+        d->x = t->x; d->y = t->y; d->size = t->size; d->plane = t->plane; d->qp = t->qp; d->org = d->pred = d->rec = 0;
+        d->coeff_offset = (uint32_t)off;
+        memcpy(lpool + off, pool + t->coef, (size_t)q * q * sizeof(int16_t));
+        off += ((size_t)q * q + 7) & ~(size_t)7;
+      }
+    }
+    ifirst[maxl] = nintra; tfirst[maxl] = m;
+    need(thorcuda_intra_reconstruct_levels(pics, 1, batch, ifirst, lt, tfirst, maxl, lpool));
+    free(batch); free(ifirst); free(tfirst); free(fill); free(sorted); free(count);
   }
   lap(2);
   /* 3. the frame tail, into the device twin of the ring slot the new reference will occupy */

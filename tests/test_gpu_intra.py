@@ -191,6 +191,32 @@ def test_intra_frame_wavefront(tb, orc):
     got = rec.download()
     for pl in range(3):
         assert np.array_equal(got[pl], planes[pl]), f"plane {pl}"
+
+    # ---- the same frame in ONE call: tasks and coefficients uploaded once, two launches per level ----
+    rec.upload(*[np.zeros_like(p) for p in planes])
+    order = [i for lv in sorted(levels) for i in levels[lv]]
+    it = np.array([(tbs[i][1], tbs[i][2], tbs[i][3], tbs[i][4], tbs[i][0], tbs[i][5], tbs[i][6], 0, 0) for i in order], INTRA_TASK)
+    coded = [i for i in order if coefs[i].any()]                   # blocks without levels: the prediction is the reconstruction
+    tt = np.zeros(len(coded), tb.TB_TASK)
+    for k, i in enumerate(coded):
+        pl, x, y, cbx, s, mode, f, qp = tbs[i]
+        tt[k]["x"], tt[k]["y"], tt[k]["size"], tt[k]["plane"], tt[k]["qp"] = x, y, s, pl, qp
+    total = tb.ops.pool_layout(tt)
+    pool = np.zeros(total, np.int16)
+    for k, i in enumerate(coded):
+        o = int(tt[k]["coeff_offset"])
+        pool[o:o + coefs[i].size] = coefs[i].reshape(-1)
+    ifirst, tfirst = [0], [0]
+    for lv in sorted(levels):
+        ifirst.append(ifirst[-1] + len(levels[lv]))
+        tfirst.append(tfirst[-1] + sum(1 for i in levels[lv] if coefs[i].any()))
+    assert tfirst[-1] == len(coded) and 0 < len(coded) < len(order)
+    n0 = tb.launch_count()
+    tb.ops.intra_reconstruct_levels([rec], it, ifirst, tt, tfirst, pool)
+    assert tb.launch_count() - n0 <= 2 * len(levels)
+    got = rec.download()
+    for pl in range(3):
+        assert np.array_equal(got[pl], planes[pl]), f"one call, plane {pl}"
     rec.close()
 
 

@@ -125,7 +125,9 @@ int d2h(void *dst, const void *src, size_t bytes);
 int d2h_bulk(void *dst, const void *src, size_t bytes);
 int copies_fence();    // make the main stream wait for the bulk copies queued so far
 struct List;
-int list_fence(List *L);   // ... if the list has output copies in flight
+int list_fence(List *L);
+// transform.cu: the transform-block kernel over a sub-range of every size class of a TB list (nullptr: everything)
+int run_tb_classes(List *L, int decode, bool want_ssd, const int *class_first, const int *class_count);   // ... if the list has output copies in flight
 // refresh the device mirror entry of picture h
 int sync_pic_view(thorcuda_pic h);
 // one stand-alone forward / inverse transform on device buffers (transform.cu), queued on the stream

@@ -126,12 +126,10 @@ using namespace thor;
 
 extern "C" {
 
-int thorcuda_intra_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, int ntasks) {
-  THOR_NEED_CTX();
+// validates the tasks, fills the picture views and uploads the tasks to the library's scratch; P.tasks then points at them
+static int intra_prepare(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, int ntasks, IntraParams &P) {
   Context &c = ctx();
-  if (ntasks <= 0) return 0;
   if (npics <= 0 || npics > 8) return fail("intra: npics %d out of range (1..8)", npics);
-  IntraParams P;
   memset(&P, 0, sizeof(P));
   const Pic *pp[8];
   for (int i = 0; i < npics; i++) {
@@ -160,9 +158,65 @@ int thorcuda_intra_predict_blocks(const thorcuda_pic *pics, int npics, const tho
   if (h2d(d, tasks, tbytes)) return -1;
   P.tasks = (const thorcuda_intra_task *)d;
   P.ntasks = ntasks;
-  k_intra<<<(ntasks + IW - 1) / IW, IW * 32, 0, c.stream>>>(P);
+  return 0;
+}
+
+int thorcuda_intra_predict_blocks(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, int ntasks) {
+  THOR_NEED_CTX();
+  if (ntasks <= 0) return 0;
+  IntraParams P;
+  if (intra_prepare(pics, npics, tasks, ntasks, P)) return -1;
+  k_intra<<<(ntasks + IW - 1) / IW, IW * 32, 0, ctx().stream>>>(P);
   THOR_LAUNCHED();
   return 0;
+}
+
+int thorcuda_intra_reconstruct_levels(const thorcuda_pic *pics, int npics, const thorcuda_intra_task *tasks, const int *intra_first,
+                                      const thorcuda_tb_task *tb, const int *tb_first, int nlevels, const int16_t *host_coeffq) {
+  THOR_NEED_CTX();
+  if (nlevels <= 0) return 0;
+  if (!intra_first || !tb_first) return fail("intra levels: NULL level table");
+  if (intra_first[0] != 0 || tb_first[0] != 0) return fail("intra levels: the level tables must start at 0");
+  for (int l = 0; l < nlevels; l++)
+    if (intra_first[l + 1] < intra_first[l] || tb_first[l + 1] < tb_first[l]) return fail("intra levels: level %d has a negative size", l);
+  const int nintra = intra_first[nlevels], ntb = tb_first[nlevels];
+  if (ntb > 0 && (!tb || !host_coeffq)) return fail("intra levels: transform blocks without tasks or coefficients");
+  IntraParams P;
+  memset(&P, 0, sizeof(P));
+  if (nintra > 0 && intra_prepare(pics, npics, tasks, nintra, P)) return -1;
+  // ONE resident transform-block list for the whole frame.  List creation sorts by size class but keeps the task order
+  // inside a class, and the caller's tasks are in level order: a level is a contiguous range of every class.
+  thorcuda_list hl = -1;
+  List *L = nullptr;
+  if (ntb > 0) {
+    hl = thorcuda_list_create(THORCUDA_LIST_TB, pics, npics, tb, ntb);
+    if (hl < 0) return -1;
+    L = get_list(hl);
+    if (h2d(L->pool, host_coeffq, L->pool_entries * sizeof(int16_t))) { thorcuda_list_destroy(hl); return -1; }
+  }
+  int done[5] = {0, 0, 0, 0, 0}, rc = 0;
+  const thorcuda_intra_task *dtasks = P.tasks;
+  for (int l = 0; l < nlevels && !rc; l++) {
+    const int ni = intra_first[l + 1] - intra_first[l];
+    if (ni > 0) {
+      P.tasks = dtasks + intra_first[l];
+      P.ntasks = ni;
+      k_intra<<<(ni + IW - 1) / IW, IW * 32, 0, ctx().stream>>>(P);
+      ctx().launches++;
+      if (cudaGetLastError() != cudaSuccess) rc = fail("intra levels: launch failed");
+    }
+    if (L && tb_first[l + 1] > tb_first[l]) {
+      int first[5], count[5] = {0, 0, 0, 0, 0};
+      for (int i = tb_first[l]; i < tb_first[l + 1]; i++) {
+        const int sz = tb[i].size;
+        count[sz == 4 ? 0 : sz == 8 ? 1 : sz == 16 ? 2 : sz == 32 ? 3 : 4]++;
+      }
+      for (int k = 0; k < 5; k++) { first[k] = L->tb_first[k] + done[k]; done[k] += count[k]; }
+      if (run_tb_classes(L, 1, false, first, count)) rc = -1;
+    }
+  }
+  if (hl >= 0) thorcuda_list_destroy(hl);          // stream-ordered: the queued launches finish first
+  return rc;
 }
 
 }  // extern "C"

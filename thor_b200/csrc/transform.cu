@@ -587,7 +587,9 @@ __global__ void __launch_bounds__(TW * 32) k_skip_test(const SkipParams P) {
   if (lane == 0) P.flags[ti] = (uint8_t)((y ? 1 : 0) | (u ? 2 : 0) | (v ? 4 : 0));
 }
 
-static int run_tb(List *L, int decode, bool want_ssd) {
+// One launch over a sub-range of every size class of the list: class_first / class_count are indexed like List::ntb
+// (4, 8, 16, 32, 64) and address the class-sorted `order` array.  nullptr: the whole list.
+int run_tb_classes(List *L, int decode, bool want_ssd, const int *class_first, const int *class_count) {
   Context &c = ctx();
   if (upload_tables()) return -1;
   TbParams P;
@@ -601,10 +603,11 @@ static int run_tb(List *L, int decode, bool want_ssd) {
   int cta = 0;
   for (int k = 0; k < 5; k++) {
     const int lk = 4 - k;
-    P.first[k] = L->tb_first[lk]; P.count[k] = L->ntb[lk];
+    const int n = class_count ? class_count[lk] : L->ntb[lk];
+    P.first[k] = class_first ? class_first[lk] : L->tb_first[lk]; P.count[k] = n;
     P.cta_first[k] = cta;
     const int per_cta = TW * upw[k] * TB_ITERS;
-    cta += (L->ntb[lk] + per_cta - 1) / per_cta;
+    cta += (n + per_cta - 1) / per_cta;
   }
   P.cta_first[5] = cta;
   if (!cta) return 0;
@@ -617,6 +620,7 @@ static int run_tb(List *L, int decode, bool want_ssd) {
   THOR_LAUNCHED();
   return 0;
 }
+static int run_tb(List *L, int decode, bool want_ssd) { return run_tb_classes(L, decode, want_ssd, nullptr, nullptr); }
 
 }  // namespace thor
 

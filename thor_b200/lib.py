@@ -77,6 +77,7 @@ def cdll():
                 ("thorcuda_early_skip_thresholds", None, [I, I, C.c_float, V, V]),
                 ("thorcuda_early_skip_batch", I, [V, I, V, I, V]),
                 ("thorcuda_intra_predict_blocks", I, [V, I, V, I]),
+                ("thorcuda_intra_reconstruct_levels", I, [V, I, V, V, V, V, I, V]),
                 ("thorcuda_interpolate_frames", I, [I, I, I, I, I]), ("thorcuda_interp_levels", I, [I, I]),
                 ("thorcuda_interp_field", I, [V, V, V]),
                 ("thorcuda_coeff_bits_list", I, [I, V, V]), ("thorcuda_vlc_len", I, [C.c_uint, C.c_uint]),

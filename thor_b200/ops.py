@@ -202,6 +202,17 @@ def intra_predict_blocks(pics, tasks):
     check(cdll().thorcuda_intra_predict_blocks(_handles(pics), len(pics), _p(t), t.size))
 
 
+def intra_reconstruct_levels(pics, intra_tasks, intra_first, tb_tasks, tb_first, coeffq):
+    """A frame's intra blocks in one call: per wavefront level the predictions, then the coded transform blocks in place
+    (thorcuda_intra_reconstruct_levels).  intra_first / tb_first: nlevels + 1 offsets into the level-ordered task arrays."""
+    it = np.ascontiguousarray(intra_tasks, INTRA_TASK)
+    tt = np.ascontiguousarray(tb_tasks, TB_TASK)
+    fi, ft = np.ascontiguousarray(intra_first, np.int32), np.ascontiguousarray(tb_first, np.int32)
+    cq = np.ascontiguousarray(coeffq, np.int16)
+    check(cdll().thorcuda_intra_reconstruct_levels(_handles(pics), len(pics), _p(it), _p(fi), _p(tt), _p(ft), fi.size - 1, _p(cq)))
+    sync()
+
+
 def interpolate_frames(new_frame, ref0, ref1, ratio, pos):
     """interpolate_frames (common/temporal_interp.c:972): the picture at `pos` of `ratio` between two padded references
     into new_frame's visible area (pad it afterwards like decode_frame.c:107).  Queued; no sync."""
