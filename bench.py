@@ -502,7 +502,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     tb.sync()
 
     # ---- e2e: host buffers in, host buffers out, every step ----
-    e2e = measure_e2e(args, tb, lib, streams[:min(B, args.e2e_streams)], barrier, dist, world)
+    e2e = measure_e2e(args, tb, lib, streams, barrier, dist, world)
 
     if rank == 0:
         peaks = {}
@@ -546,7 +546,14 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
     side information and the three task lists; D2H of the SAD tables (4 levels x 2 refs), sub-pel results,
     coefficients / cbp / ssd, CLPF bits and the reconstructed frame."""
     from thor_b200.lib import COST_RESULT
-    B = len(streams)
+    # Two independent groups of streams are kept in flight: group B is submitted while group A's results (0.77 GB of SAD
+    # tables per 4 frames) are still crossing PCIe, and a group's next frame is only submitted once its previous results
+    # have arrived in host memory (thorcuda_fence_wait) -- what an encoder serving several streams does.
+    E = max(1, min(args.e2e_streams, len(streams)))
+    depth = 2 if len(streams) >= 2 * E and not args.e2e_serial else 1
+    groups = [streams[i * E:(i + 1) * E] for i in range(depth)]
+    streams = groups[0]
+    B = E
     R = args.range
     n2 = (2 * R) ** 2
     w, h = args.width, args.height
@@ -555,8 +562,9 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
         p = lib.thorcuda_host_alloc(nbytes)
         return np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(p)).view(dtype), p
 
-    host = []
-    for s in streams:
+    hosts = [[] for _ in groups]
+    for gi, s in [(gi, s) for gi, g in enumerate(groups) for s in g]:
+        host = hosts[gi]
         j = s.job
         d = {"allocs": []}
 
@@ -590,10 +598,25 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
         phase[name] = phase.get(name, 0.0) + (t - t_prev)
         return t
 
-    def step():
+    pending = [None] * depth
+
+    def retire(g):
+        if pending[g] is None:
+            return
+        tp = time.perf_counter()
+        fence, lists = pending[g]
+        tb.check(lib.thorcuda_fence_wait(fence))            # this group's results are in host memory
+        for l in lists:
+            l.close()
+        pending[g] = None
+        mark("wait", tp)
+
+    def step(g=0):
         nonlocal h2d, d2h
         h2d = d2h = 0
         lists = []
+        streams, host = groups[g], hosts[g]
+        retire(g)
         tp = time.perf_counter()
         for s, d in zip(streams, host):
             j = s.job
@@ -632,35 +655,44 @@ def measure_e2e(args, tb, lib, streams, barrier, dist, world):
         for s, d in zip(streams, host):
             tb.check(lib.thorcuda_pic_download(s.work.handle, d["ry"].ctypes.data, d["ru"].ctypes.data, d["rv"].ctypes.data, w, w // 2))
             d2h += w * h * 3 // 2 + d["bits"].size
-        for l in lists:
-            l.close()
         tp = mark("tail_submit", tp)
-        tb.sync()
-        mark("wait", tp)
+        fence = lib.thorcuda_fence_record()
+        if fence < 0:
+            tb.check(-1)
+        pending[g] = (fence, lists)
+
+    def drain():
+        for g in range(depth):
+            retire(g)
 
     for _ in range(2):
-        step()
+        for g in range(depth):
+            step(g)
+    drain()
     barrier()
     phase.clear()
     t0 = time.perf_counter()
-    n = max(2, args.e2e_steps)
-    for _ in range(n):
-        step()
+    n = max(2, args.e2e_steps) * depth
+    for it in range(n):
+        step(it % depth)
+    drain()
     dt = time.perf_counter() - t0
     if dist is not None:
         import torch
         t = torch.tensor([dt], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
+    host = hosts[0]
     for d in host:
         d["keep"] = True
     measure_e2e.host = host          # kept for the parity check
     return {"value": B * world * n / dt, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-            "frames_per_step": B, "steps": n, "ms_per_step": 1e3 * dt / n,
+            "frames_per_step": B, "steps": n, "ms_per_step": 1e3 * dt / n, "groups_in_flight": depth,
             "host_ms_per_step": {k: round(1e3 * v / n, 3) for k, v in phase.items()},
             # the step moves this many bytes over PCIe per second: compare with the link (Gen5 x16: ~57 GB/s measured D2H)
             "pcie_GBps": {"d2h": round(d2h * n / dt / 1e9, 1), "h2d": round(h2d * n / dt / 1e9, 2)},
-            "timing": "host wall clock around submit..thorcuda_sync, max over ranks (includes PCIe copies and list building)"}
+            "timing": "host wall clock from the first submit until the last group's results are in host memory, max over ranks (includes "
+                      "PCIe copies and list building); a group's step is submitted only after its previous results have arrived"}
 
 
 def cpu_baseline_and_parity(args, tb, stream):
@@ -715,6 +747,7 @@ def main():
     ap.add_argument("--distinct-jobs", type=int, default=2, help="distinct synthetic frame jobs cycled over the streams")
     ap.add_argument("--e2e-streams", type=int, default=4)
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-serial", action="store_true", help="e2e leg: one group of streams, wait for every step before the next is submitted")
     ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail / the whole reconstruction on the GPU (adds ~1 min)")
     ap.add_argument("--decoder-frames", type=int, default=168)
     ap.add_argument("--decoder-config", default="LDB_low_complexity", choices=sorted(DEC_CONFIGS),

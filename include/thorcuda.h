@@ -35,6 +35,11 @@ int         thorcuda_init(int device);
 void        thorcuda_shutdown(void);
 const char *thorcuda_last_error(void);
 int         thorcuda_sync(void);                   /* wait for all queued work                       */
+/* A marker behind everything queued SO FAR (library stream and the bulk fetches of its copy stream): wait for it without
+ * waiting for what is queued later.  For callers that keep several independent groups of streams in flight: submit
+ * group B while group A's results are still crossing PCIe, then wait for A alone.  At most 16 open fences; wait frees. */
+int         thorcuda_fence_record(void);           /* returns the fence id, or -1                    */
+int         thorcuda_fence_wait(int id);
 void       *thorcuda_stream(void);                 /* the cudaStream_t all work is queued on         */
 /* number of kernels this library has launched since init (bench.py "gpu_launches")                 */
 uint64_t    thorcuda_launch_count(void);

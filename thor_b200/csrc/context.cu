@@ -223,6 +223,10 @@ void thorcuda_shutdown(void) {
   }
   for (auto &s : c.stage) { s.buf.release(); cudaEventDestroy(s.ev); s.ev = nullptr; s.pending = false; }
   for (int i = 0; i < 64; i++) { cudaEventDestroy(c.tm0[i]); cudaEventDestroy(c.tm1[i]); }
+  for (int i = 0; i < 16; i++) {
+    if (c.fn_made[i]) { cudaEventDestroy(c.fn_main[i]); cudaEventDestroy(c.fn_copy[i]); }
+    c.fn_made[i] = c.fn_used[i] = false;
+  }
   cudaFree(c.d_pics); c.d_pics = nullptr;
   cudaStreamDestroy(c.stream);
   cudaStreamDestroy(c.copy_stream);
@@ -241,6 +245,38 @@ int thorcuda_sync(void) {
     THOR_CUDA(cudaStreamSynchronize(ctx().copy_stream));
     ctx().copy_pending = false;
   }
+  return 0;
+}
+
+/* A marker behind everything queued so far -- kernels and copies on the library stream AND the bulk fetches on its copy
+ * stream -- that can be waited for without waiting for what is queued later: a caller that works on several independent
+ * groups of streams submits group B while group A's results are still travelling, and waits for A alone. */
+int thorcuda_fence_record(void) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  for (int i = 0; i < 16; i++)
+    if (!c.fn_used[i]) {
+      if (!c.fn_made[i]) {
+        if (cudaEventCreateWithFlags(&c.fn_main[i], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c.fn_copy[i], cudaEventDisableTiming) != cudaSuccess) { fail("fence: event creation failed"); return -1; }
+        c.fn_made[i] = true;
+      }
+      if (cudaEventRecord(c.fn_main[i], c.stream) != cudaSuccess) { fail("fence: record failed"); return -1; }
+      c.fn_copy_set[i] = c.copy_pending;
+      if (c.copy_pending && cudaEventRecord(c.fn_copy[i], c.copy_stream) != cudaSuccess) { fail("fence: record failed"); return -1; }
+      c.fn_used[i] = true;
+      return i;
+    }
+  fail("fence: all 16 fences are in use");
+  return -1;
+}
+int thorcuda_fence_wait(int id) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (id < 0 || id >= 16 || !c.fn_used[id]) return fail("fence: bad id %d", id);
+  c.fn_used[id] = false;
+  THOR_CUDA(cudaEventSynchronize(c.fn_main[id]));
+  if (c.fn_copy_set[id]) THOR_CUDA(cudaEventSynchronize(c.fn_copy[id]));
   return 0;
 }
 

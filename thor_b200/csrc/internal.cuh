@@ -104,6 +104,8 @@ struct Context {
   DevBuf raw_info, scratch, flush, lfjobs, sadjobs, centres;
   cudaEvent_t tm0[64], tm1[64];
   bool tm_used[64] = {false};
+  cudaEvent_t fn_main[16], fn_copy[16];   // thorcuda_fence_record / _wait
+  bool fn_used[16] = {false}, fn_made[16] = {false}, fn_copy_set[16] = {false};
   SadSlot sad[THORCUDA_SAD_SLOTS];
 };
 
