@@ -183,3 +183,30 @@ def test_batched_frames_one_launch(tb):
         assert np.array_equal(pv[:, :w // 2 + 96], href.buf_v[:, :w // 2 + 96])
     for p in pics:
         p.close()
+
+
+def test_fences(tb):
+    """thorcuda_fence_record / _wait: a marker behind the work queued so far (library stream + bulk fetches); waiting for
+    it makes that work's host outputs valid without a full thorcuda_sync."""
+    lib = tb.cdll()
+    w, h = 416, 240
+    rng = np.random.default_rng(9)
+    planes = [rng.integers(0, 256, (h, w), dtype=np.uint8), rng.integers(0, 256, (h // 2, w // 2), dtype=np.uint8),
+              rng.integers(0, 256, (h // 2, w // 2), dtype=np.uint8)]
+    a, b = tb.Picture(w, h), tb.Picture(w, h)
+    a.upload(*planes)
+    tb.check(lib.thorcuda_pic_copy(b.handle, a.handle))
+    f = lib.thorcuda_fence_record()
+    assert 0 <= f < 16
+    ids = [lib.thorcuda_fence_record() for _ in range(15)]
+    assert all(0 <= i < 16 for i in ids) and len(set(ids + [f])) == 16
+    assert lib.thorcuda_fence_record() == -1, "a 17th open fence must be refused"
+    tb.check(lib.thorcuda_fence_wait(f))
+    for i in ids:
+        tb.check(lib.thorcuda_fence_wait(i))
+    assert lib.thorcuda_fence_wait(f) != 0, "a fence can be waited for once"
+    assert lib.thorcuda_fence_wait(99) != 0
+    got = b.download()
+    for i in range(3):
+        assert np.array_equal(got[i], planes[i])
+    a.close(); b.close()
