@@ -566,3 +566,57 @@ def test_early_skip_batch(tb, orc, wh, qp, thr, noise):
     for bit in (1, 2, 4):                                    # both outcomes occur for every plane
         assert 0 < np.count_nonzero(want & bit) < len(want)
     org.close(); pred.close()
+
+
+@pytest.mark.parametrize("qp", [0, 20, 32, 51])
+def test_encode_blocks_extreme_residuals(tb, orc, qp):
+    """SURVEY 8c's adversarial inputs for the transform chain: residuals of +255 / -255 everywhere, a +-255 checkerboard,
+    +-255 columns, one impulse and zero, for every transform size and both quantiser types -- the int16 intermediate
+    clips, the dead zone at qp 51 and the full coefficient range at qp 0."""
+    w, h = 512, 128
+    sizes = [(0, 0, 64), (64, 0, 32), (96, 0, 16), (112, 0, 8), (120, 0, 4), (64, 32, 32), (96, 16, 16), (112, 8, 8), (120, 4, 4)]
+    yy, xx = np.mgrid[0:h, 0:w]
+    patterns = []                                    # (org, pred) luma planes; residual = org - pred
+    patterns.append((np.full((h, w), 255), np.zeros((h, w))))
+    patterns.append((np.zeros((h, w)), np.full((h, w), 255)))
+    cb = ((xx + yy) & 1) * 255
+    patterns.append((cb, 255 - cb))
+    col = (xx & 1) * 255
+    patterns.append((col, 255 - col))
+    imp = np.zeros((h, w)); imp[::4, ::4] = 255
+    patterns.append((imp, np.zeros((h, w))))
+    patterns.append((np.full((h, w), 77), np.full((h, w), 77)))
+    total = 0
+    for k, (o, p) in enumerate(patterns):
+        oy, py = o.astype(np.uint8), p.astype(np.uint8)
+        oc, pc = np.ascontiguousarray(oy[::2, ::2]), np.ascontiguousarray(py[::2, ::2])
+        org, pred, rec = tb.Picture(w, h), tb.Picture(w, h), tb.Picture(w, h)
+        org.upload(oy, oc, oc)
+        pred.upload(py, pc, pc)
+        tasks = []
+        for rep, (x0, fast, ctype) in enumerate([(0, 0, 0), (128, 1, 2)]):       # inter / intra quantiser, fast flag for 32 and 64
+            for (x, y, s) in sizes:
+                t = np.zeros((), tb.TB_TASK)
+                t["x"], t["y"], t["size"], t["plane"], t["qp"], t["coeff_type"], t["fast"] = x0 + x, y, s, 0, qp, ctype, fast
+                t["org"], t["pred"], t["rec"] = 0, 1, 2
+                tasks.append(t)
+        for (x, y, s) in [(0, 0, 32), (32, 0, 16), (48, 0, 8), (56, 0, 4)]:      # chroma
+            t = np.zeros((), tb.TB_TASK)
+            t["x"], t["y"], t["size"], t["plane"], t["qp"], t["coeff_type"] = x, y, s, 1, qp, 1
+            t["org"], t["pred"], t["rec"] = 0, 1, 2
+            tasks.append(t)
+        tasks = _arr(tasks, tb.TB_TASK)
+        tb.ops.pool_layout(tasks)
+        coeffq, cbp, ssd = tb.ops.encode_blocks([org, pred, rec], tasks)
+        got = rec.download()
+        for i, t in enumerate(tasks):
+            pl, n, x, y = int(t["plane"]), int(t["size"]), int(t["x"]), int(t["y"])
+            wrec, wcq, wcbp, wssd = oracle_tb(orc, (oy, oc, oc)[pl], (py, pc, pc)[pl], t)
+            q, off = min(n, 16), int(t["coeff_offset"])
+            assert cbp[i] == wcbp and ssd[i] == wssd, (k, i, t)
+            assert np.array_equal(coeffq[off:off + q * q].reshape(q, q), wcq), (k, i, t)
+            assert np.array_equal(got[pl][y:y + n, x:x + n], wrec), (k, i, t)
+            total += 1
+        for pic in (org, pred, rec):
+            pic.close()
+    assert total == len(patterns) * 22
