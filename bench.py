@@ -530,6 +530,16 @@ def run_gpu_arm(args, rank, world, local_rank):
                 "extra_stages": {"coeff_bits": {"ms": round(bits_ms, 4), "transform_blocks": int(l_tb.ntasks), "coded": int((nbits != 0).sum()),
                                                 "mean_bits_per_coded_block": round(float(nbits.sum()) / max(1, int((nbits != 0).sum())), 1),
                                                 "note": "not part of `value`: exact write_coeff bit counts of the step's transform blocks"}}}
+        # The SAD table is bound by the integer ALU pipe, not by HBM: W*H*(2R)^2 abs-diffs per (frame, ref)
+        # pair against the rate of a register-only VABSDIFF4 loop measured on this device just now.
+        alu_peak = lib.thorcuda_calibrate_absdiff(0)
+        if alu_peak > 0:
+            pairs = len(slots)
+            absdiffs = float(args.width) * args.height * (2 * args.range) ** 2 * pairs
+            alu = absdiffs / (stage_ms["sad_table"] * 1e-3)
+            line["roofline"]["alu"] = {"kernel": "sad_table", "achieved": round(alu / 1e12, 2), "peak": round(alu_peak / 1e12, 2),
+                                       "unit": "T abs-diff/s", "frac": round(alu / alu_peak, 4),
+                                       "peak_source": "thorcuda_calibrate_absdiff (register-only VABSDIFF4.ACC loop, measured in this run)"}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_and_parity(args, tb, streams[0])
         if world == 1 and args.decoder:

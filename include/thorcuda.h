@@ -43,6 +43,9 @@ int         thorcuda_fence_wait(int id);
 void       *thorcuda_stream(void);                 /* the cudaStream_t all work is queued on         */
 /* number of kernels this library has launched since init (bench.py "gpu_launches")                 */
 uint64_t    thorcuda_launch_count(void);
+/* abs-diffs per second of a register-only VABSDIFF4 loop on this device: the ceiling of the integer ALU pipe that bounds
+ * the SAD kernels (the denominator of bench.py's roofline.alu).  iters <= 0: default length.  Synchronous.       */
+double      thorcuda_calibrate_absdiff(int iters);
 /* CUDA-event timing of everything queued between begin and end, on the library's stream (ms).
  * Nestable up to 64 open timers: begin returns a timer id, end(id) queues the stop event,
  * elapsed(id) synchronises on it.                                                                    */

@@ -210,3 +210,13 @@ def test_fences(tb):
     for i in range(3):
         assert np.array_equal(got[i], planes[i])
     a.close(); b.close()
+
+
+def test_calibrate_absdiff(tb):
+    """The register-only VABSDIFF4 loop behind bench.py's roofline.alu: a plausible rate for a B200 (148 SMs x 64 ALU
+    lanes x 4 abs-diffs at 1.5-2.1 GHz = 57-80 T/s), and stable between two runs."""
+    lib = tb.cdll()
+    a = lib.thorcuda_calibrate_absdiff(0)
+    b = lib.thorcuda_calibrate_absdiff(8192)
+    assert 20e12 < a < 120e12 and 20e12 < b < 120e12
+    assert abs(a - b) / max(a, b) < 0.25

@@ -537,6 +537,22 @@ static int launch_sad(int gx, int gy, int n, const SadJob *d_jobs) {
   return 0;
 }
 
+// register-only VABSDIFF4.ACC loop for thorcuda_calibrate_absdiff
+__global__ void __launch_bounds__(256) k_absdiff_peak(uint32_t *out, int iters) {
+  uint32_t a[16], x = threadIdx.x * 0x01010101u + blockIdx.x, y = ~x;
+#pragma unroll
+  for (int k = 0; k < 16; k++) a[k] = k;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int k = 0; k < 16; k++) a[k] = sad4(x, y + k, a[k]);
+    x += 0x00010001u;
+  }
+  uint32_t r = 0;
+#pragma unroll
+  for (int k = 0; k < 16; k++) r ^= a[k];
+  if (r == 0x12345678u) out[threadIdx.x & 15] = r;      // keeps the loop alive, practically never taken
+}
+
 }  // namespace thor
 
 using namespace thor;
@@ -696,6 +712,30 @@ int thorcuda_cost_batch(int kind, const thorcuda_pic *pics, int npics, const tho
   const int rc = thorcuda_cost_list(l, kind, host_results);
   thorcuda_list_destroy(l);
   return rc;
+}
+
+// Peak of the instruction the SAD search is made of, measured on the device it runs on ("calibrate peak with a
+// register-only micro-kernel"): every thread keeps 16 independent VABSDIFF4.ACC chains busy, nothing touches memory.
+// Returns abs-diffs per second (4 per instruction and lane), or a negative value on failure.  Synchronous.
+double thorcuda_calibrate_absdiff(int iters) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (iters <= 0) iters = 4096;
+  uint32_t *d = (uint32_t *)c.scratch.reserve(1 << 16);
+  if (!d) return -1.0;
+  const int ctas = c.sm_count * 8, threads = 256;
+  cudaEvent_t e0, e1;
+  if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return -1.0;
+  k_absdiff_peak<<<ctas, threads, 0, c.stream>>>(d, iters / 8);       // warm-up
+  cudaEventRecord(e0, c.stream);
+  k_absdiff_peak<<<ctas, threads, 0, c.stream>>>(d, iters);
+  cudaEventRecord(e1, c.stream);
+  c.launches += 2;
+  float ms = 0.f;
+  const bool ok = cudaEventSynchronize(e1) == cudaSuccess && cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess && cudaGetLastError() == cudaSuccess;
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (!ok || ms <= 0.f) return -1.0;
+  return 4.0 * 16.0 * (double)iters * threads * ctas / (ms * 1e-3);
 }
 
 }  // extern "C"

@@ -56,7 +56,7 @@ def cdll():
         for name, res, args in (
                 ("thorcuda_init", I, [I]),
                 ("thorcuda_timer_begin", I, []), ("thorcuda_timer_end", I, [I]), ("thorcuda_timer_elapsed_ms", C.c_float, [I]),
-                ("thorcuda_flush_l2", I, [Z]), ("thorcuda_fence_record", I, []), ("thorcuda_fence_wait", I, [I]),
+                ("thorcuda_flush_l2", I, [Z]), ("thorcuda_calibrate_absdiff", C.c_double, [I]), ("thorcuda_fence_record", I, []), ("thorcuda_fence_wait", I, [I]),
                 ("thorcuda_host_register", I, [V, Z]), ("thorcuda_host_unregister", None, [V]),
                 ("thorcuda_pic_create", I, [I, I, I, I]), ("thorcuda_pic_destroy", None, [I]), ("thorcuda_pic_stride", I, [I, I]),
                 ("thorcuda_pic_upload", I, [I, V, V, V, I, I]), ("thorcuda_pic_download", I, [I, V, V, V, I, I]),
