@@ -100,6 +100,18 @@ int orc_mv_bits(int mvx, int mvy, int mvpx, int mvpy);         /* write_mv */
 int orc_find_code(int run, int level, int maxrun, int chroma, int eob);
 int orc_coeff_bits(const int16_t *coeff, int stride, int size, int type);   /* write_coeff; 0 for an all-zero block */
 
+/* write_block (enc/write_bits.c:364-650) on a flat int32 record: what the frame, the block's context and the decision
+ * contribute to the syntax.  cbp_y/u/v are 1-bit flags, or 4-bit masks (sub-block 0 in bit 3) where tb_split is set. */
+enum { ORC_BS_FRAME_TYPE = 0, ORC_BS_NUM_REF, ORC_BS_ENABLE_BIPRED, ORC_BS_INTERP_REF, ORC_BS_NUM_INTRA_MODES, ORC_BS_MAX_DELTA_QP,
+       ORC_BS_SIZE, ORC_BS_CTX_INDEX, ORC_BS_CTX_CBP, ORC_BS_MAX_PB_PART, ORC_BS_MAX_TB_PART, ORC_BS_NUM_SKIP_VEC, ORC_BS_NUM_MERGE_VEC,
+       ORC_BS_DELTA_QP, ORC_BS_MODE, ORC_BS_INTRA_MODE, ORC_BS_PB_PART, ORC_BS_TB_SPLIT, ORC_BS_SKIP_IDX, ORC_BS_REF_IDX0, ORC_BS_REF_IDX1,
+       ORC_BS_CBP_Y, ORC_BS_CBP_U, ORC_BS_CBP_V, ORC_BS_MVP, ORC_BS_MV0 = ORC_BS_MVP + 2, ORC_BS_MV1 = ORC_BS_MV0 + 8,
+       ORC_BS_FIELDS = ORC_BS_MV1 + 8 };
+int orc_block_syntax_bits(const int32_t *d);     /* everything write_block emits except the write_coeff calls */
+/* the whole of write_block: coeff_y is size x size (four contiguous (size/2)^2 sub-blocks under tb_split), coeff_u/v
+ * (size/2)^2 likewise -- block_param_t's layout */
+int orc_block_bits(const int32_t *d, const int16_t *coeff_y, const int16_t *coeff_u, const int16_t *coeff_v);
+
 #ifdef __cplusplus
 }
 #endif

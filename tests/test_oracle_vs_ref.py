@@ -527,3 +527,23 @@ def test_mv_bits():
         a, b = Mv(int(mv[0]), int(mv[1])), Mv(int(mvp[0]), int(mvp[1]))
         ref.write_mv(C.byref(s), C.byref(a), C.byref(b))
         assert orc.orc_mv_bits(int(mv[0]), int(mv[1]), int(mvp[0]), int(mvp[1])) == ref_bitpos(s)
+
+
+def test_block_bits():
+    """orc_block_bits / orc_block_syntax_bits against the reference's write_block (through oracle/bits_shim.c): 4000
+    random blocks over every frame type, mode, partition, context, transform split and cbp pattern."""
+    from thorref import BS, load_ref_bits, random_block_syntax
+    shim = load_ref_bits()
+    rng = np.random.default_rng(11)
+    seen = set()
+    for _ in range(4000):
+        d, cy, cu, cv = random_block_syntax(rng)
+        want = shim.ref_write_block_bits(ptr(d), ptr(cy), ptr(cu), ptr(cv))
+        got = orc.orc_block_bits(ptr(d), ptr(cy), ptr(cu), ptr(cv))
+        assert got == want, d
+        seen.add((int(d[BS["frame_type"]]), int(d[BS["mode"]]), int(d[BS["tb_split"]]), int(d[BS["size"]])))
+        # the syntax part alone: the same block without levels where that is a legal block (no cbp bit set)
+        z = d.copy()
+        z[BS["cbp_y"]:BS["cbp_y"] + 3] = 0
+        assert orc.orc_block_syntax_bits(ptr(z)) == shim.ref_write_block_bits(ptr(z), None, None, None)
+    assert len(seen) > 60

@@ -326,3 +326,87 @@ def coeff_block(rng, size, kind):
 
 
 COEFF_KINDS = ["dc1", "dc", "sparse", "lowfreq", "dense", "large", "last"]
+
+
+# ---- write_block records (oracle/thor_oracle.h ORC_BS_*) ----
+BS = {n: i for i, n in enumerate(
+    "frame_type num_ref enable_bipred interp_ref num_intra_modes max_delta_qp size ctx_index ctx_cbp max_num_pb_part "
+    "max_num_tb_part num_skip_vec num_merge_vec delta_qp mode intra_mode pb_part tb_split skip_idx ref_idx0 ref_idx1 "
+    "cbp_y cbp_u cbp_v".split())}
+BS["mvp"], BS["mv0"], BS["mv1"], BS_FIELDS = 24, 26, 34, 42
+MODE_SKIP, MODE_INTRA, MODE_INTER, MODE_BIPRED, MODE_MERGE = range(5)
+
+
+def load_ref_bits():
+    lib = C.CDLL(os.path.join(REF_DIR, "libthorbits_ref.so"))
+    lib.ref_write_block_bits.restype = C.c_int
+    lib.ref_write_block_bits.argtypes = [C.c_void_p] * 4
+    return lib
+
+
+def random_block_syntax(rng, frame=None):
+    """One block as write_block (enc/write_bits.c:364-650) may meet it: (record int32[42], coeff_y, coeff_u, coeff_v) with
+    the coefficient arrays in block_param_t's layout (quadrants contiguous under tb_split).  Only combinations the
+    reference encoder can produce: no intra mode outside the frame's set, tb_split only where max_num_tb_part allows it,
+    a level wherever a cbp bit says so."""
+    d = np.zeros(BS_FIELDS, np.int32)
+    if frame is None:
+        ft = int(rng.integers(0, 3))
+        frame = dict(frame_type=ft, num_ref=0 if ft == 0 else int(rng.integers(1, 5)), enable_bipred=int(rng.integers(0, 2)),
+                     interp_ref=0 if ft == 0 else int(rng.integers(0, 2)), num_intra_modes=int(rng.choice([4, 8, 10])),
+                     max_delta_qp=int(rng.choice([0, 0, 4])))
+    for k, v in frame.items():
+        d[BS[k]] = v
+    size = int(rng.choice([8, 16, 32, 64]))
+    d[BS["size"]] = size
+    d[BS["ctx_index"]] = rng.integers(0, 6)
+    d[BS["ctx_cbp"]] = rng.integers(-1, 3)
+    d[BS["max_num_pb_part"]] = rng.choice([1, 4])
+    d[BS["max_num_tb_part"]] = rng.choice([1, 2])
+    d[BS["num_skip_vec"]] = rng.integers(1, 5)
+    d[BS["num_merge_vec"]] = rng.integers(1, 5)
+    d[BS["delta_qp"]] = rng.integers(-4, 5)
+    nref = frame["num_ref"]
+    modes = [MODE_INTRA] if frame["frame_type"] == 0 else [MODE_SKIP, MODE_INTRA, MODE_INTER, MODE_MERGE] + ([MODE_BIPRED] if nref > 1 and frame["enable_bipred"] else [])
+    mode = int(rng.choice(modes))
+    d[BS["mode"]] = mode
+    nim = frame["num_intra_modes"]
+    d[BS["intra_mode"]] = rng.integers(0, 4) if nim <= 4 else rng.choice([0, 2, 3, 4, 6, 7, 8, 9]) if nim <= 8 else rng.integers(0, 10)
+    d[BS["pb_part"]] = rng.integers(0, 4) if d[BS["max_num_pb_part"]] > 1 and mode in (MODE_INTER, MODE_BIPRED) else 0
+    d[BS["skip_idx"]] = rng.integers(0, max(1, d[BS["num_skip_vec" if mode == MODE_SKIP else "num_merge_vec"]]))
+    d[BS["ref_idx0"]] = rng.integers(0, max(1, nref))
+    d[BS["ref_idx1"]] = rng.integers(0, max(1, nref))
+    d[BS["mvp"]:BS["mvp"] + 18] = np.where(rng.random(18) < 0.3, 0, rng.integers(-300, 301, 18))
+    if rng.random() < 0.2:
+        d[BS["mv0"]:BS["mv0"] + 2] = d[BS["mvp"]:BS["mvp"] + 2]
+    split = mode in (MODE_INTRA, MODE_INTER) and d[BS["max_num_tb_part"]] > 1 and rng.random() < 0.4
+    d[BS["tb_split"]] = int(split)
+    ty = np.zeros(size * size, np.int16)
+    tu, tv = np.zeros(size * size // 4, np.int16), np.zeros(size * size // 4, np.int16)
+    kind = lambda: COEFF_KINDS[int(rng.integers(0, len(COEFF_KINDS)))]
+    if not split:
+        cbp = rng.integers(0, 2, 3)
+        for flag, arr, n in zip(cbp, (ty, tu, tv), (size, size // 2, size // 2)):
+            if flag:
+                arr[:] = coeff_block(rng, n, kind()).ravel()
+        d[BS["cbp_y"]:BS["cbp_y"] + 3] = cbp
+    elif size > 8:
+        h, q = size // 2, size // 4
+        cbp = rng.integers(0, 16, 3)
+        for mask, arr, n in zip(cbp, (ty, tu, tv), (h, q, q)):
+            for i in range(4):
+                if (mask >> (3 - i)) & 1:
+                    arr[i * n * n:(i + 1) * n * n] = coeff_block(rng, n, kind()).ravel()
+        d[BS["cbp_y"]:BS["cbp_y"] + 3] = cbp
+    else:
+        cy = int(rng.integers(0, 16))
+        for i in range(4):
+            if (cy >> (3 - i)) & 1:
+                ty[i * 16:(i + 1) * 16] = coeff_block(rng, 4, kind()).ravel()
+        cuv = rng.integers(0, 2, 2)
+        for flag, arr in zip(cuv, (tu, tv)):
+            if flag:
+                arr[:] = coeff_block(rng, 4, kind()).ravel()
+        d[BS["cbp_y"]] = cy
+        d[BS["cbp_u"]:BS["cbp_u"] + 2] = cuv
+    return d, ty, tu, tv
