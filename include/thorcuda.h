@@ -251,6 +251,30 @@ int thorcuda_interp_field(int16_t *mv1, int *bw, int *bh);
  * host_bits (ntasks uint32, may be NULL) is valid after thorcuda_sync().  With it cost_calc's `nbits`
  * (enc/encode_block.c:1218-1228) of a trial encode is these counts plus the host's mode / vector / cbp bits. */
 int thorcuda_coeff_bits_list(thorcuda_list l, const int16_t *host_coeffq, uint32_t *host_bits);
+/* Second slice: the whole of write_block (enc/write_bits.c:364-650) as a length -- mode / reference (write_super_mode,
+ * :268-362), delta qp, intra mode, partition, vector differences (write_mv), skip / merge index, cbp codes -- plus the
+ * coefficient bits of the block's transform blocks.  One record per coded block (everything write_block reads):      */
+typedef struct { int16_t x, y; } thorcuda_mv;               /* mv_t, common/types.h:105-109 */
+typedef struct {
+  /* frame_info / params */
+  uint8_t frame_type;                 /* 0 I, 1 P, 2 B (frame_type_t, common/types.h:69-74)                       */
+  uint8_t num_ref, enable_bipred, interp_ref, num_intra_modes, max_delta_qp;
+  /* block_info: block_pos.size, block_context->index / ->cbp, partition limits, candidate counts, delta qp */
+  uint8_t size, ctx_index; int8_t ctx_cbp;
+  uint8_t max_num_pb_part, max_num_tb_part, num_skip_vec, num_merge_vec; int8_t delta_qp;
+  /* block_param: mode 0 skip 1 intra 2 inter 3 bipred 4 merge (block_mode_t, common/types.h:76-83) */
+  uint8_t mode, intra_mode, pb_part, tb_split, skip_idx, ref_idx0, ref_idx1;
+  uint8_t cbp_y, cbp_u, cbp_v;        /* flags; under tb_split 4-bit masks, quadrant 0 in bit 3 (:589-591)        */
+  thorcuda_mv mvp, mv0[4], mv1[4];    /* block_info->mvp, mv_arr0, mv_arr1                                        */
+  uint32_t tb_first;                  /* first transform block of this block in the list, in write_block's order:
+                                         Y U V | tb_split, size > 8: (Y U V) x 4 quadrants | size 8: Y0..Y3 U V;
+                                         0xffffffff: syntax bits only                                              */
+} thorcuda_block_syntax;              /* 64 bytes */
+/* host_bits[i] = what write_block returns for block i.  `l` (a transform-block list on which thorcuda_coeff_bits_list
+ * has run, or -1 for the syntax bits alone) supplies the coefficient bits; a transform block counts where the block's
+ * cbp bit is set, as in the reference.  Records are validated on the host (error, no launch).  host_bits is valid
+ * after thorcuda_sync().                                                                                           */
+int thorcuda_block_bits(thorcuda_list l, const thorcuda_block_syntax *host_blocks, int nblocks, uint32_t *host_bits);
 /* host arithmetic (no device work): quote_vlc (enc/putvlc.c:133-229; -1 where the reference aborts) and the bits of
  * write_mv (enc/write_bits.c:50-69) = quote_mv_bits (enc/encode_block.c:799-814) */
 int thorcuda_vlc_len(unsigned n, unsigned cn);

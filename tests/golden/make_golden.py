@@ -311,7 +311,19 @@ def bits(ref):
         a, b = Mv(int(mv[0]), int(mv[1])), Mv(int(mvp[0]), int(mvp[1]))
         ref.write_mv(C.byref(s), C.byref(a), C.byref(b))
         mvs.append((int(mv[0]), int(mv[1]), int(mvp[0]), int(mvp[1]), ref_bitpos(s)))
-    return {"coeff_size": np.array(sizes, np.uint8), "coeff_type": np.array(types, np.uint8), "coeff_bits": np.array(want, np.uint32),
+    # write_block through oracle/bits_shim.c: 1500 seeded blocks; the levels are kept in pool layout (pack_blocks)
+    from thorref import BS_FIELDS, load_ref_bits, pack_blocks, random_block_syntax
+    shim = load_ref_bits()
+    blocks = [random_block_syntax(rng) for _ in range(1500)]
+    blk_bits = [shim.ref_write_block_bits(ptr(d), ptr(cy), ptr(cu), ptr(cv)) for d, cy, cu, cv in blocks]
+    tb_dtype = np.dtype([("size", "u1"), ("coeff_type", "u1"), ("coeff_offset", "<u4")])
+    blk_dtype = np.dtype([("tb_first", "<u4")])
+    recs, tbs, pool = pack_blocks(blocks, blk_dtype, tb_dtype)
+    blk = {"blk_records": np.stack([b[0] for b in blocks]).astype(np.int32), "blk_bits": np.array(blk_bits, np.uint32),
+           "blk_tb_first": recs["tb_first"].copy(), "blk_tb_size": tbs["size"].copy(), "blk_tb_type": tbs["coeff_type"].copy(),
+           "blk_tb_offset": tbs["coeff_offset"].copy(), "blk_pool": pool}
+    assert blk["blk_records"].shape[1] == BS_FIELDS
+    return {**blk, "coeff_size": np.array(sizes, np.uint8), "coeff_type": np.array(types, np.uint8), "coeff_bits": np.array(want, np.uint32),
             "coeff_levels": np.concatenate(levels).astype(np.int16), "vlc": np.array(vlc, np.int32), "mv": np.array(mvs, np.int32)}
 
 

@@ -433,3 +433,48 @@ def test_gpu_coeff_bits(gb, tb):
     bad = np.flatnonzero(got != want)
     assert bad.size == 0, f"{bad.size} of {want.size} differ, first: case {bad[0]} size {cases[bad[0]][0]} type {cases[bad[0]][1]} got {got[bad[0]]} want {want[bad[0]]}"
     pic.close()
+
+
+def test_port_block_bits(gb, orc):
+    """write_block golden vectors (the reference's own write_block through oracle/bits_shim.c) against the oracle:
+    syntax bits of the record + coefficient bits of the coded transform blocks"""
+    from thorref import block_tbs
+    recs, want = gb["blk_records"], gb["blk_bits"]
+    first, pool = gb["blk_tb_first"], gb["blk_pool"]
+    assert recs.shape[0] == want.size == 1500
+    for i in range(recs.shape[0]):
+        d = np.ascontiguousarray(recs[i])
+        n = orc.orc_block_syntax_bits(ptr(d))
+        for k, (plane, quad, size, coded) in enumerate(block_tbs(d)):
+            t = int(first[i]) + k
+            assert gb["blk_tb_size"][t] == size
+            if coded:
+                q = min(size, 16)
+                off = int(gb["blk_tb_offset"][t])
+                c = np.ascontiguousarray(pool[off:off + q * q])
+                n += orc.orc_coeff_bits(ptr(c), q, size, int(gb["blk_tb_type"][t]))
+        assert n == want[i], (i, recs[i])
+
+
+@pytest.mark.gpu
+def test_gpu_block_bits(gb, tb):
+    """thorcuda_block_bits (syntax on the device + the coefficient bits of the resident list) against the same vectors"""
+    from thorref import BS
+    recs = np.zeros(gb["blk_bits"].size, tb.BLOCK_SYNTAX)
+    for name in tb.BLOCK_SYNTAX.names:
+        if name in ("mvp", "mv0", "mv1"):
+            recs[name] = gb["blk_records"][:, BS[name]:BS[name] + recs[name][0].size].reshape(recs[name].shape)
+        elif name != "tb_first":
+            recs[name] = gb["blk_records"][:, BS[name]]
+    recs["tb_first"] = gb["blk_tb_first"]
+    tasks = np.zeros(gb["blk_tb_size"].size, tb.TB_TASK)
+    tasks["size"], tasks["coeff_type"], tasks["coeff_offset"] = gb["blk_tb_size"], gb["blk_tb_type"], gb["blk_tb_offset"]
+    pic = tb.Picture(64, 64)
+    lst = tb.ops.TaskList(tb.LIST_TB, [pic], tasks)
+    pool = np.zeros(lst.pool_entries, np.int16)
+    pool[:gb["blk_pool"].size] = gb["blk_pool"][:pool.size]
+    lst.coeff_bits(None, pool)
+    got = tb.ops.block_bits(recs, lst)
+    bad = np.flatnonzero(got != gb["blk_bits"])
+    assert bad.size == 0, f"{bad.size} differ; first: block {bad[0]} {recs[bad[0]]} got {got[bad[0]]} want {gb['blk_bits'][bad[0]]}"
+    lst.close(); pic.close()

@@ -86,3 +86,51 @@ def test_coeff_bits_after_encode(tb, orc, wh, qps, intra):
     assert 0 < (cbp != 0).sum() < cbp.size
     for p in (org, pred, rec):
         p.close()
+
+
+@pytest.mark.parametrize("seed,n", [(21, 3000), (22, 20000)])
+def test_block_bits(tb, orc, seed, n):
+    """thorcuda_block_bits = write_block (enc/write_bits.c:364-650) as a length, against the oracle (pinned to the
+    reference's write_block): random blocks of every frame type, mode, partition, context, transform split and cbp
+    pattern; the coefficient bits come from the resident transform-block list of the same blocks."""
+    from thorref import BS, pack_blocks, random_block_syntax
+    rng = np.random.default_rng(seed)
+    blocks = [random_block_syntax(rng) for _ in range(n)]
+    recs, tasks, pool = pack_blocks(blocks, tb.BLOCK_SYNTAX, tb.TB_TASK)
+    want = np.array([orc.orc_block_bits(ptr(d), ptr(cy), ptr(cu), ptr(cv)) for d, cy, cu, cv in blocks], np.uint32)
+    want_syntax = np.array([orc.orc_block_syntax_bits(ptr(d)) for d, _, _, _ in blocks], np.uint32)
+    pic = tb.Picture(64, 64)
+    lst = tb.ops.TaskList(tb.LIST_TB, [pic], tasks)
+    cq = np.zeros(lst.pool_entries, np.int16)
+    cq[:min(cq.size, pool.size)] = pool[:cq.size]
+    lst.coeff_bits(None, cq)
+    got = tb.ops.block_bits(recs, lst)
+    bad = np.flatnonzero(got != want)
+    assert bad.size == 0, f"{bad.size} of {n} differ; first: {recs[bad[0]]} got {got[bad[0]]} want {want[bad[0]]}"
+    got_syntax = tb.ops.block_bits(recs, None)             # no list: the syntax alone
+    assert np.array_equal(got_syntax, want_syntax)
+    nolist = recs.copy()
+    nolist["tb_first"] = tb.NO_TB                          # per block opt-out gives the same
+    assert np.array_equal(tb.ops.block_bits(nolist, lst), want_syntax)
+    modes = {int(d[BS["mode"]]) for d, _, _, _ in blocks}
+    assert modes == {0, 1, 2, 3, 4} and (want > want_syntax).any()
+    lst.close(); pic.close()
+
+
+def test_block_bits_rejects(tb):
+    """malformed records are refused on the host: no launch, an error"""
+    pic = tb.Picture(64, 64)
+    tasks = np.zeros(3, tb.TB_TASK)
+    tasks["size"] = (16, 8, 8)
+    tb.ops.pool_layout(tasks)
+    lst = tb.ops.TaskList(tb.LIST_TB, [pic], tasks)
+    good = np.zeros(1, tb.BLOCK_SYNTAX)
+    good["frame_type"], good["num_ref"], good["size"], good["mode"], good["num_intra_modes"] = 1, 1, 16, 1, 10
+    lst.coeff_bits(None, np.zeros(lst.pool_entries, np.int16))
+    assert tb.ops.block_bits(good, lst)[0] > 0
+    for field, value in (("size", 24), ("mode", 5), ("frame_type", 3), ("pb_part", 4), ("intra_mode", 10), ("cbp_y", 5), ("tb_first", 1)):
+        bad = good.copy()
+        bad[field] = value
+        with pytest.raises(tb.ThorCudaError):
+            tb.ops.block_bits(bad, lst)
+    lst.close(); pic.close()

@@ -410,3 +410,47 @@ def random_block_syntax(rng, frame=None):
         d[BS["cbp_y"]] = cy
         d[BS["cbp_u"]:BS["cbp_u"] + 2] = cuv
     return d, ty, tu, tv
+
+
+def block_tbs(d):
+    """The transform blocks of a write_block record in the order write_block codes them (enc/write_bits.c:572-641):
+    list of (plane 0/1/2, quadrant, transform size, coded) -- empty for a skip block."""
+    size, split = int(d[BS["size"]]), int(d[BS["tb_split"]])
+    cbp = [int(d[BS["cbp_y"]]), int(d[BS["cbp_u"]]), int(d[BS["cbp_v"]])]
+    if d[BS["mode"]] == MODE_SKIP:
+        return []
+    if not split:
+        return [(p, 0, size if p == 0 else size // 2, cbp[p] & 1) for p in range(3)]
+    if size > 8:
+        return [(p, q, size // 2 if p == 0 else size // 4, (cbp[p] >> (3 - q)) & 1) for q in range(4) for p in range(3)]
+    return [(0, q, 4, (cbp[0] >> (3 - q)) & 1) for q in range(4)] + [(1, 0, 4, cbp[1] & 1), (2, 0, 4, cbp[2] & 1)]
+
+
+def pack_blocks(blocks, block_dtype, tb_dtype):
+    """[(record, coeff_y, coeff_u, coeff_v)] -> (thorcuda_block_syntax array, thorcuda_tb_task array with coeff_offset
+    assigned, level pool in libthorcuda's layout: the low q x q corner of every transform block, 8-entry aligned)"""
+    recs = np.zeros(len(blocks), block_dtype)
+    tasks, levels, off = [], [], 0
+    for i, (d, cy, cu, cv) in enumerate(blocks):
+        r = recs[i]
+        for name in block_dtype.names:
+            if name in ("mvp", "mv0", "mv1"):
+                r[name] = d[BS[name]:BS[name] + r[name].size].reshape(r[name].shape)
+            elif name != "tb_first":
+                r[name] = d[BS[name]]
+        tbs = block_tbs(d)
+        r["tb_first"] = len(tasks) if tbs else 0xffffffff
+        intra = int(d[BS["mode"]] == MODE_INTRA) << 1
+        for plane, quad, n, coded in tbs:
+            src = (cy, cu, cv)[plane]
+            q = min(n, 16)
+            c = src[quad * n * n:(quad + 1) * n * n].reshape(n, n)[:q, :q]
+            t = np.zeros((), tb_dtype)
+            t["size"], t["coeff_type"], t["coeff_offset"] = n, intra | (plane > 0), off
+            tasks.append(t)
+            levels.append((off, c.reshape(-1).copy()))
+            off += (q * q + 7) & ~7
+    pool = np.zeros(max(off, 8), np.int16)
+    for o, c in levels:
+        pool[o:o + c.size] = c
+    return recs, np.array(tasks, tb_dtype) if tasks else np.zeros(0, tb_dtype), pool

@@ -157,6 +157,119 @@ __global__ void __launch_bounds__(BW * 32) k_coeff_bits(const thorcuda_tb_task *
   }
 }
 
+// ---- write_block (enc/write_bits.c:364-650) as a length: the syntax around the coefficients ----
+// One thread per block record: a few table look-ups and exp-Golomb lengths, then the coefficient bits of the block's
+// transform blocks (k_coeff_bits' output) where the cbp bit says write_block codes them.
+__device__ __forceinline__ int mvd_len(short2 mv, short2 p) {                      // write_mv :50-69
+  const int dx = mv.x - p.x, dy = mv.y - p.y;
+  return expgolomb_len((uint32_t)(2 * abs(dx) - (dx < 0))) + expgolomb_len((uint32_t)(2 * abs(dy) - (dy < 0)));
+}
+__device__ __forceinline__ int mv_list_len(const short2 *mv, short2 p, int part) {   // :421-444, :468-490
+  int n = mvd_len(mv[0], p);
+  if (part == 1) n += mvd_len(mv[2], mv[0]);
+  else if (part == 2) n += mvd_len(mv[1], mv[0]);
+  else if (part == 3) n += mvd_len(mv[1], mv[0]) + mvd_len(mv[2], mv[0]) + mvd_len(mv[3], mv[0]);
+  return n;
+}
+__device__ __forceinline__ int idx_len(int nvec, int idx) { return nvec == 4 ? 2 : nvec == 3 ? (idx == 0 ? 1 : 2) : nvec == 2 ? 1 : 0; }   // :507-530
+__device__ __forceinline__ int cbp_code(int y, int u, int v, int ctx_cbp) {        // :382, :561-566
+  const int code = (0x47362501u >> (4 * (y + 2 * u + 4 * v))) & 7;               // {1,0,5,2,6,3,7,4}
+  return ctx_cbp == 0 && code < 2 ? 1 - code : code;
+}
+__device__ int super_mode_len(const thorcuda_block_syntax &b) {                    // write_super_mode :268-362, split_flag 0
+  if (b.frame_type == 0) return b.size > 8;
+  const int bip = b.num_ref > 1 && b.enable_bipred, spl = b.size > 8, maxbit = 2 + b.num_ref + spl + bip;
+  const bool demote = (b.ctx_index == 2 || b.ctx_index > 3) && spl;
+  const int m = b.mode, r0 = b.ref_idx0;
+  int code;
+  if (b.interp_ref) {
+    code = m == 0 ? 0 : m == 4 ? 2 : m == 3 ? 3 : m == 1 ? 4 : r0 > 0 ? 4 + r0 : 4 + b.num_ref;
+    if (!bip && code > 3) code--;
+    if (!spl && code > 1) code--;
+    if (demote && code < 3) code = (code + 2) % 3;
+  } else {
+    code = m == 0 ? 0 : m == 4 ? 3 : m == 3 ? 4 : m == 1 ? 5 : r0 > 0 ? 5 + r0 : 2;
+    if (!bip && code > 4) code--;
+    if (!spl && code > 1) code--;
+    if (demote && code < 4) code = (code + 3) & 3;
+  }
+  return code == maxbit ? maxbit : code + 1;
+}
+
+static_assert(sizeof(thorcuda_block_syntax) == 64, "block records are read as four 16-byte words");
+__global__ void __launch_bounds__(128) k_block_bits(const thorcuda_block_syntax *__restrict__ blocks, int n,
+                                                    const uint32_t *__restrict__ tb_bits, int ntb, uint32_t *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  __align__(16) thorcuda_block_syntax b;
+  {
+    const uint4 *src = reinterpret_cast<const uint4 *>(blocks + i);
+    uint4 *dst = reinterpret_cast<uint4 *>(&b);
+#pragma unroll
+    for (int k = 0; k < 4; k++) dst[k] = src[k];
+  }
+  const short2 mvp = make_short2(b.mvp.x, b.mvp.y);
+  const short2 *mv0 = reinterpret_cast<const short2 *>(b.mv0), *mv1 = reinterpret_cast<const short2 *>(b.mv1);
+  const int mode = b.mode, size = b.size, part = b.pb_part;
+  int bits = super_mode_len(b);
+  if (size == 64 && mode != 0 && b.max_delta_qp) bits += vlc_len(0, (uint32_t)abs((int)b.delta_qp)) + (b.delta_qp != 0);   // :389-391
+  if (mode == 1) {                                                                 // intra mode :393-413
+    const int im = b.intra_mode;
+    if (b.num_intra_modes <= 4) bits += 2;
+    else if (b.num_intra_modes <= 8) bits += im == 0 || im == 2 || im == 3 ? 2 : im == 4 || im == 8 || im == 9 ? 4 : 5;   // map {2,8,1,0,5,9,7,6,4,3}, len {2,2,2,4,4,4,5,5}
+    else bits += im < 2 ? 3 : im < 4 ? 2 : im >= 8 ? 4 : 5;                       // map {2,3,1,0,6,9,8,7,5,4}, len {2,2,3,3,4,4,5,5,5,5}
+  } else if (mode == 2) {
+    if (b.max_num_pb_part > 1) bits += part == 0 ? 1 : part == 1 ? 2 : 3;
+    bits += mv_list_len(mv0, mvp, part);
+  } else if (mode == 3) {                                                          // :446-505 (BIPRED_PART 0)
+    short2 p = mvp;
+    if (part == 0) bits += mvd_len(mv0[0], p);
+    if (b.frame_type == 2) p = mv0[0];
+    bits += mv_list_len(mv1, p, part);
+    if (b.frame_type == 1) {
+      if (b.num_ref == 2) { const int c = 2 * b.ref_idx0 + b.ref_idx1; bits += c == 3 ? 3 : c + 1; }
+      else bits += expgolomb_len((uint32_t)(4 * b.ref_idx0 + b.ref_idx1));
+    }
+  } else if (mode == 0) {
+    bits += idx_len(b.num_skip_vec, b.skip_idx);
+  } else {
+    bits += idx_len(b.num_merge_vec, b.skip_idx);
+  }
+  if (mode != 0) {
+    const int cy = b.cbp_y, cu = b.cbp_u, cv = b.cbp_v, split = b.tb_split;
+    const int max_tb = mode == 2 ? (b.max_num_tb_part > 1 ? 2 : 1) : mode == 1 ? b.max_num_tb_part : 1;
+    int code;
+    if (max_tb > 1) {
+      if (split) code = 2;
+      else { code = cbp_code(cy, cu, cv, b.ctx_cbp); if (code > 1) code++; }
+    } else if (mode == 4) {
+      code = (0x47362501u >> (4 * (cy + 2 * cu + 4 * cv))) & 7;
+      code = code == 1 ? 7 : code > 1 ? code - 1 : code;
+    } else code = cbp_code(cy, cu, cv, b.ctx_cbp);
+    bits += vlc_len(0, (uint32_t)code);
+    const uint32_t *tb = tb_bits ? tb_bits + b.tb_first : nullptr;
+    const bool have = tb_bits && b.tb_first != 0xffffffffu;
+    if (!split) {                                                                  // :572-582  Y U V
+      if (have && (size_t)b.tb_first + 3 <= (size_t)ntb) bits += (cy ? tb[0] : 0) + (cu ? tb[1] : 0) + (cv ? tb[2] : 0);
+    } else if (size > 8) {                                                         // :585-612  (Y U V) per quadrant
+      for (int q = 0; q < 4; q++) {
+        const int y = (cy >> (3 - q)) & 1, u = (cu >> (3 - q)) & 1, v = (cv >> (3 - q)) & 1;
+        bits += vlc_len(0, (uint32_t)cbp_code(y, u, v, b.ctx_cbp));
+        if (have && (size_t)b.tb_first + 12 <= (size_t)ntb) bits += (y ? tb[3 * q] : 0) + (u ? tb[3 * q + 1] : 0) + (v ? tb[3 * q + 2] : 0);
+      }
+    } else {                                                                       // :613-641  Y0..Y3 U V
+      const int c = cu + 2 * cv;
+      bits += 4 + (c == 0 ? 1 : c == 1 ? 2 : 3);
+      if (have && (size_t)b.tb_first + 6 <= (size_t)ntb) {
+        for (int q = 0; q < 4; q++) bits += ((cy >> (3 - q)) & 1) ? tb[q] : 0;
+        bits += (cu ? tb[4] : 0) + (cv ? tb[5] : 0);
+      }
+    }
+  }
+  out[i] = (uint32_t)bits;
+}
+
+static DevBuf g_blk_in, g_blk_out;
 static bool scan_ready = false;
 static int upload_scan() {
   if (scan_ready) return 0;
@@ -176,7 +289,7 @@ static int upload_scan() {
   scan_ready = true;
   return 0;
 }
-void bits_reset() { scan_ready = false; }
+void bits_reset() { scan_ready = false; g_blk_in.release(); g_blk_out.release(); }
 
 }  // namespace thor
 
@@ -200,6 +313,37 @@ int thorcuda_coeff_bits_list(thorcuda_list hl, const int16_t *host_coeffq, uint3
     L->late_pool = true;
   }
   return 0;
+}
+
+int thorcuda_block_bits(thorcuda_list hl, const thorcuda_block_syntax *host_blocks, int nblocks, uint32_t *host_bits) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (nblocks <= 0) return 0;
+  if (!host_blocks || !host_bits) return fail("block_bits: null argument");
+  List *L = nullptr;
+  if (hl >= 0) {
+    L = get_list(hl);
+    if (!L || L->kind != THORCUDA_LIST_TB) return fail("block_bits: not a transform-block list");
+  }
+  for (int i = 0; i < nblocks; i++) {                     // what the kernel would otherwise have to guard per thread
+    const thorcuda_block_syntax &b = host_blocks[i];
+    if (b.size != 8 && b.size != 16 && b.size != 32 && b.size != 64) return fail("block_bits: block %d has size %d", i, b.size);
+    if (b.mode > 4 || b.frame_type > 2 || b.pb_part > 3 || b.intra_mode > 9) return fail("block_bits: block %d is malformed", i);
+    if (!b.tb_split && (b.cbp_y | b.cbp_u | b.cbp_v) > 1) return fail("block_bits: block %d has cbp masks without tb_split", i);
+    if (L && b.mode != 0 && b.tb_first != 0xffffffffu) {
+      const uint32_t cnt = !b.tb_split ? 3 : b.size > 8 ? 12 : 6;
+      if ((uint64_t)b.tb_first + cnt > (uint64_t)L->ntasks) return fail("block_bits: block %d: transform blocks %u..%u outside the list", i, b.tb_first, b.tb_first + cnt - 1);
+    }
+  }
+  // the previous call's output copy may still be reading g_blk_out
+  if (copies_fence()) return -1;
+  auto *d_in = (thorcuda_block_syntax *)g_blk_in.reserve((size_t)nblocks * sizeof(thorcuda_block_syntax));
+  auto *d_out = (uint32_t *)g_blk_out.reserve((size_t)nblocks * 4);
+  if (!d_in || !d_out) return fail("block_bits: device allocation failed");
+  if (h2d(d_in, host_blocks, (size_t)nblocks * sizeof(thorcuda_block_syntax))) return -1;
+  k_block_bits<<<(nblocks + 127) / 128, 128, 0, c.stream>>>(d_in, nblocks, L ? L->bits : nullptr, L ? L->ntasks : 0, d_out);
+  THOR_LAUNCHED();
+  return d2h(host_bits, d_out, (size_t)nblocks * 4);
 }
 
 // pure host arithmetic, like thorcuda_clip_mv: the scalar glue of the bit-cost model

@@ -27,6 +27,13 @@ INTRA_TASK = np.dtype([("x", "<u2"), ("y", "<u2"), ("cb_x", "<u2"), ("size", "u1
                        ("src", "u1"), ("dst", "u1")])
 assert INTRA_TASK.itemsize == 12
 MODE_DC, MODE_PLANAR, MODE_HOR, MODE_VER, MODE_UPLEFT, MODE_UPRIGHT, MODE_UPUPRIGHT, MODE_UPUPLEFT, MODE_UPLEFTLEFT, MODE_DOWNLEFTLEFT = range(10)
+BLOCK_SYNTAX = np.dtype([(n, "u1") for n in ("frame_type", "num_ref", "enable_bipred", "interp_ref", "num_intra_modes", "max_delta_qp",
+                                                "size", "ctx_index")] + [("ctx_cbp", "i1")] +
+                        [(n, "u1") for n in ("max_num_pb_part", "max_num_tb_part", "num_skip_vec", "num_merge_vec")] + [("delta_qp", "i1")] +
+                        [(n, "u1") for n in ("mode", "intra_mode", "pb_part", "tb_split", "skip_idx", "ref_idx0", "ref_idx1", "cbp_y", "cbp_u", "cbp_v")] +
+                        [("mvp", "<i2", (2,)), ("mv0", "<i2", (4, 2)), ("mv1", "<i2", (4, 2)), ("tb_first", "<u4")])
+assert BLOCK_SYNTAX.itemsize == 64
+NO_TB = 0xffffffff
 assert PRED_TASK.itemsize == 20 and TB_TASK.itemsize == 16 and COST_TASK.itemsize == 16 and COST_RESULT.itemsize == 8
 
 
@@ -80,7 +87,7 @@ def cdll():
                 ("thorcuda_intra_reconstruct_levels", I, [V, I, V, V, V, V, I, V]),
                 ("thorcuda_interpolate_frames", I, [I, I, I, I, I]), ("thorcuda_interp_levels", I, [I, I]),
                 ("thorcuda_interp_field", I, [V, V, V]),
-                ("thorcuda_coeff_bits_list", I, [I, V, V]), ("thorcuda_vlc_len", I, [C.c_uint, C.c_uint]),
+                ("thorcuda_coeff_bits_list", I, [I, V, V]), ("thorcuda_block_bits", I, [I, V, I, V]), ("thorcuda_vlc_len", I, [C.c_uint, C.c_uint]),
                 ("thorcuda_mv_bits", I, [I, I, I, I]),
                 ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):
             fn = getattr(_lib, name)   # AttributeError here means a stale libthorcuda.so: rebuild

@@ -22,7 +22,7 @@ import ctypes as C
 import numpy as np
 
 from .lib import (LF_CLPF, LF_DEBLOCK_UV, LF_DEBLOCK_Y, LF_MAKE_REF, LIST_COST, LIST_PRED, LIST_TB, COST_RESULT, COST_TASK,
-                  INTRA_TASK, PRED_TASK, SKIP_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
+                  BLOCK_SYNTAX, INTRA_TASK, PRED_TASK, SKIP_TASK, TB_TASK, ThorCudaError, _p, cdll, check, sync)
 
 
 class LfJob(C.Structure):  # thorcuda_lf_job
@@ -173,6 +173,16 @@ def coeff_bits(pics, tasks, coeffq):
     lst.coeff_bits(bits, cq)
     sync()
     lst.close()
+    return bits
+
+
+def block_bits(blocks, tb_list=None):
+    """write_block (enc/write_bits.c:364-650) as a length for an array of BLOCK_SYNTAX records; tb_list: a TaskList
+    (LIST_TB) on which coeff_bits() has run, whose tasks tb_first indexes, or None for the syntax bits alone."""
+    b = np.ascontiguousarray(blocks, BLOCK_SYNTAX)
+    bits = np.zeros(b.size, np.uint32)
+    check(cdll().thorcuda_block_bits(tb_list.handle if tb_list is not None else -1, _p(b), b.size, _p(bits)))
+    sync()
     return bits
 
 
