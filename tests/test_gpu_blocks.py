@@ -157,6 +157,49 @@ def test_predict_blocks(tb, orc, wh, bipred):
         p.close()
 
 
+@pytest.mark.parametrize("wh", [(416, 240), (1920, 1080)])
+def test_predict_mv_at_clip(tb, orc, wh):
+    """SURVEY 8c KAT: vectors exactly at the +-80 pixel clip of clip_mv (enc/encode_block.c:816-828) -- the block lies
+    wholly in the picture's border, 80 pixels outside the frame, at all four corners and the edge midpoints, for every
+    block size and every fractional phase that still satisfies the clip (the integer limit itself: phase 0 at the far
+    side), uni- and bi-predicted."""
+    w, h = wh
+    href = [textured_ref(w, h, 77 + k) for k in range(2)]
+    dref = [dev_ref_from_host(tb, r) for r in href]
+    dst = tb.Picture(w, h)
+    tasks = []
+    for s in (8, 16, 32, 64):
+        xs, ys = (0, (w // 2) & ~63, (w - s) & ~(s - 1)), (0, (h // 2) & ~63, (h - s) & ~(s - 1))
+        k = 0
+        for py in ys:
+            for px in xs:
+                lo_x, hi_x = -4 * (px + 80), 4 * (w + 80 - px - s)
+                lo_y, hi_y = -4 * (py + 80), 4 * (h + 80 - py - s)
+                for (mx, my) in ((lo_x, lo_y), (hi_x, hi_y), (lo_x, hi_y), (hi_x, lo_y), (lo_x + 1 + k % 3, lo_y + 1 + k % 2),
+                                 (hi_x - 1 - k % 3, hi_y - 2), (lo_x + 2, hi_y - 3), (hi_x, 0), (0, lo_y)):
+                    t = np.zeros((), tb.PRED_TASK)
+                    t["x"], t["y"], t["w"], t["h"], t["dst"] = px, py, s, s, 2
+                    t["ref0"], t["ref1"] = k % 2, (1 - k % 2) if k % 3 == 0 else -1
+                    t["mv0x"], t["mv0y"] = mx, my
+                    t["mv1x"], t["mv1y"], t["sign1"] = -hi_x if k % 2 else -lo_x, -lo_y, 1      # negated before use
+                    tasks.append(t)
+                    k += 1
+    tasks = _arr(tasks, tb.PRED_TASK)
+    # the destination blocks overlap between tasks (same corner, nine vectors, four sizes): run groups of disjoint blocks
+    for i in range(36):
+        group = tasks[(tasks["w"] == (8, 16, 32, 64)[i // 9])][i % 9::9]
+        tb.ops.predict_blocks(dref + [dst], group, 1)
+        got = dst.download()
+        for t in group:
+            want = oracle_predict(orc, href, t, 1)
+            for pl in range(3):
+                x, y = (int(t["x"]), int(t["y"])) if pl == 0 else (int(t["x"]) // 2, int(t["y"]) // 2)
+                hh, ww = want[pl].shape
+                assert np.array_equal(got[pl][y:y + hh, x:x + ww], want[pl]), (pl, t)
+    for p in dref + [dst]:
+        p.close()
+
+
 def test_predict_rejects_out_of_range_mv(tb):
     ref = tb.Picture(128, 64, 96, 48)
     dst = tb.Picture(128, 64)

@@ -220,3 +220,33 @@ def test_calibrate_absdiff(tb):
     b = lib.thorcuda_calibrate_absdiff(8192)
     assert 20e12 < a < 120e12 and 20e12 < b < 120e12
     assert abs(a - b) / max(a, b) < 0.25
+
+
+@pytest.mark.parametrize("qp", [15, 17, 18, 20, 32, 51])
+def test_deblock_threshold_kat(tb, qp):
+    """`d < beta` exactly at the boundary: the known-answer picture of thorref.deblock_threshold_case (edges designed with
+    d = beta-2..beta+2; pinned against the reference in tests/test_oracle_vs_ref.py), alone and inside the fused tail"""
+    from thorref import BETA_TABLE, deblock_threshold_case
+    orc = load_oracle()
+    w, h = 192, 128
+    y, u, v, bi, dv, dh = deblock_threshold_case(w, h, qp)
+    rec = HostPic(w, h)
+    rec.set_visible(y, u, v)
+    for stages in (1, 7):
+        host = rec.copy()
+        oracle_chain(orc, host, None, bi, w, h, qp, stages, np.ones(6, np.uint8))
+        dev = tb.Picture(w, h)
+        dev.upload(y, u, v)
+        tb.ops.blockinfo_upload(dev, bi)
+        if stages == 1:
+            tb.ops.loopfilter_frame(dev, qp, 1)
+        else:
+            tb.ops.loopfilter_frame(dev, qp, 3)
+            tb.ops.clpf_frame(dev, org=None, sb_bits_in=np.ones(6, np.uint8))
+        got = dev.download()
+        dev.close()
+        for i in range(3):
+            assert np.array_equal(got[i], host.plane(i)), (stages, "plane", i)
+        if stages == 1 and qp >= 18:
+            moved = got[0][3::8, 8::8] != y[3::8, 8::8]
+            assert np.array_equal(moved, dv[:, :-1] < BETA_TABLE[qp])

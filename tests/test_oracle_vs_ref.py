@@ -547,3 +547,31 @@ def test_block_bits():
         z[BS["cbp_y"]:BS["cbp_y"] + 3] = 0
         assert orc.orc_block_syntax_bits(ptr(z)) == shim.ref_write_block_bits(ptr(z), None, None, None)
     assert len(seen) > 60
+
+
+@pytest.mark.parametrize("qp", [15, 17, 18, 20, 32, 51])
+def test_deblock_threshold_kat(simd, qp):
+    """`d < beta` exactly at the boundary (SURVEY 8c KAT list): edges designed with d = beta-2..beta+2 are filtered by the
+    reference iff d < beta, and the oracle agrees pixel for pixel."""
+    from thorref import BETA_TABLE, deblock_threshold_case
+    w, h = 192, 128
+    y, u, v, bi, dv, dh = deblock_threshold_case(w, h, qp)
+    a = Picture(w, h)
+    a.set_visible(y, u, v)
+    b = a.copy()
+    fa = a.as_ref_struct()
+    ref.deblock_frame_y(C.byref(fa), ptr(bi), w, h, C.c_uint8(qp))
+    orc.orc_deblock_frame_y(C.c_void_p(b.origin_ptr(0)), b.stride_y, ptr(bi), w, h, qp)
+    out = a.plane(0)
+    assert np.array_equal(out, b.plane(0))
+    beta = BETA_TABLE[qp]
+    # a filtered vertical edge moves q0 of row 0 of the tile to its right (a pixel no horizontal filter... row 0 is
+    # touched by the horizontal edge above, so look at row 3, which no horizontal filter writes); likewise column 3
+    moved_v = out[3::8, 8::8] != y[3::8, 8::8]
+    moved_h = out[8::8, 3::8] != y[8::8, 3::8]
+    if qp < 18:                      # beta 0 (qp < 16), or tc 0 (qp < 18: the filter fires and adds a delta clipped to 0)
+        assert np.array_equal(out, y)
+        return
+    assert np.array_equal(moved_v, (dv[:, :-1] < beta)), "vertical edges"
+    assert np.array_equal(moved_h, (dh[:-1, :] < beta)), "horizontal edges"
+    assert moved_v.any() and not moved_v.all() and moved_h.any() and not moved_h.all()

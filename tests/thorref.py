@@ -454,3 +454,29 @@ def pack_blocks(blocks, block_dtype, tb_dtype):
     for o, c in levels:
         pool[o:o + c.size] = c
     return recs, np.array(tasks, tb_dtype) if tasks else np.zeros(0, tb_dtype), pool
+
+
+BETA_TABLE = [0] * 16 + [6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 20, 22, 24, 26, 28, 30, 32, 34, 36, 38, 40, 42, 44, 46, 48, 50,
+                         52, 54, 56, 58, 60, 62, 64]     # common/common_frame.c:36-39
+
+
+def deblock_threshold_case(width, height, qp):
+    """Known-answer picture for the luma deblocking decision `d < beta` (common/common_frame.c:128,214): flat 8x8 tiles
+    in a 100/112 checkerboard, every tile a coded inter block, and in every tile one pixel that makes the activity measure
+    of the edge to its right (pixel (2,7) = p0 of row 2) resp. below it (pixel (7,2) = p0 of column 2) EXACTLY
+    beta-2 .. beta+2, cycling over the tiles.  Neither pixel is read by the other direction's measure nor written by the
+    other direction's filter, so the decisions do not depend on the order the edges are visited in.
+    Returns (y, u, v, blockinfo, dv, dh) with dv/dh the designed d of every tile's right / bottom edge."""
+    beta = BETA_TABLE[qp]
+    th, tw = height // 8, width // 8
+    ty, tx = np.mgrid[0:th, 0:tw]
+    dv = np.maximum(beta + (ty * 3 + tx) % 5 - 2, 0)
+    dh = np.maximum(beta + (ty + tx * 2 + 1) % 5 - 2, 0)
+    y = np.kron(100 + 12 * ((ty + tx) & 1), np.ones((8, 8), int))
+    y[2::8, 7::8] += dv
+    y[7::8, 2::8] += dh
+    y = y.astype(np.uint8)
+    u = np.full((height // 2, width // 2), 128, np.uint8)
+    bi = np.zeros((height // 4) * (width // 4), BLOCKINFO)
+    bi["mode"], bi["size"], bi["cbp_y"] = MODE_INTER, 8, 1
+    return y, u, u.copy(), bi, dv, dh
