@@ -265,6 +265,47 @@ def decoder_leg(args):
         return res
 
 
+LDB_MEDIUM = LDB_LOW[:-12] + ["-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "0.8",
+                             "-enable_bipred", "1", "-encoder_speed", "1"]      # config_LDB_medium_complexity.txt
+
+
+def encoder_leg(args):
+    """End-to-end ENCODE rate (BASELINE metric 1, configs[1]): the reference's Thorenc against the same encoder with
+    libthorcuda's frame tail hooked in (integration/Thorenc_tail: deblocking, CLPF decision, reference creation on the
+    device), LDB medium complexity, .bit and reconstruction compared byte for byte.  Marginal rate between a 2-frame and an
+    n-frame run (cancels start-up and the intra frame).  The motion search, mode decision and entropy coding stay on
+    the host in both (SURVEY Tier A), so this is NOT where the device kernels show: it is reported so that the pixel-pipeline
+    metric above is not mistaken for an encoder speed-up."""
+    import tempfile
+    enc, tail = os.path.join(ROOT, "oracle", "_ref", "Thorenc"), os.path.join(ROOT, "integration", "_build", "Thorenc_tail")
+    if not all(os.path.exists(x) for x in (enc, tail)):
+        return {"unavailable": "oracle/_ref/Thorenc or integration/_build/Thorenc_tail not built"}
+    frames, short = max(args.encoder_frames, 4), 2
+    shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    with tempfile.TemporaryDirectory(dir=shm) as d:
+        yuv = os.path.join(d, "clip.yuv")
+        write_clip(yuv, args.width, args.height, frames)
+        res, outs = {}, {}
+        for name, exe in (("reference", enc), ("gpu_tail", tail)):
+            secs = {}
+            for n in (short, frames):
+                pre = os.path.join(d, f"{name}{n}")
+                for _ in range(3):                     # best of 3: CUDA start-up varies by tenths of a second between runs
+                    t0 = time.perf_counter()
+                    subprocess.run([exe, "-if", yuv, "-of", pre + ".bit", "-rf", pre + "_rec.yuv", "-stat", pre + "_stat.txt",
+                                    "-width", str(args.width), "-height", str(args.height), "-n", str(n), "-f", "60", "-qp", "32"] + LDB_MEDIUM,
+                                   check=True, capture_output=True, timeout=1800)
+                    dt = time.perf_counter() - t0
+                    secs[n] = min(secs.get(n, dt), dt)
+            outs[name] = (open(pre + ".bit", "rb").read(), open(pre + "_rec.yuv", "rb").read())
+            res[name + "_fps"] = round((frames - short) / (secs[frames] - secs[short]), 3)
+            res[name + "_seconds"] = {str(n): round(v, 2) for n, v in secs.items()}
+        res.update({"frames": frames, "config": f"LDB_medium_complexity {args.width}x{args.height} qp 32", "bitstream_bytes": len(outs["reference"][0]),
+                    "identical_bit": outs["reference"][0] == outs["gpu_tail"][0], "identical_rec": outs["reference"][1] == outs["gpu_tail"][1],
+                    "note": "single host thread in both; host RDO / motion-search driver / entropy coding dominate (SURVEY 3.3)"})
+        return res
+
+
 # --------------------------------------------------------------------------------- GPU arm ----
 METRIC = "1080p pixel-pipeline frames/s (LDB medium-complexity frame job, bit-identical to the reference kernels)"
 
@@ -542,6 +583,8 @@ def run_gpu_arm(args, rank, world, local_rank):
                                        "peak_source": "thorcuda_calibrate_absdiff (register-only VABSDIFF4.ACC loop, measured in this run)"}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_and_parity(args, tb, streams[0])
+        if world == 1 and args.encoder:
+            line["encoder_e2e"] = encoder_leg(args)
         if world == 1 and args.decoder:
             line["decoder_e2e"] = decoder_leg(args)
         print(json.dumps(line), flush=True)
@@ -759,6 +802,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--e2e-serial", action="store_true", help="e2e leg: one group of streams, wait for every step before the next is submitted")
     ap.add_argument("--decoder", action="store_true", help="also time Thordec vs Thordec with the GPU frame tail / the whole reconstruction on the GPU (adds ~1 min)")
+    ap.add_argument("--encoder", action="store_true", help="also time Thorenc vs Thorenc with the GPU frame tail (LDB medium, adds ~1 min)")
+    ap.add_argument("--encoder-frames", type=int, default=24)
     ap.add_argument("--decoder-frames", type=int, default=168)
     ap.add_argument("--decoder-config", default="LDB_low_complexity", choices=sorted(DEC_CONFIGS),
                     help="stream of the decoder leg; RA_low_complexity has B frames with interpolated references (one interpolate_frames per B frame)")
