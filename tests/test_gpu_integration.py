@@ -14,6 +14,9 @@ pytestmark = pytest.mark.gpu
 BUILD = os.path.join(ROOT, "integration", "_build")
 
 
+_STREAMS = {}
+
+
 def _decode(exe, bit, out):
     r = subprocess.run([exe, bit, out], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
@@ -29,6 +32,16 @@ def _decode(exe, bit, out):
     ("HDB16_low_complexity", 256, 192, 33, 34),     # two 16-frame sub-GOPs: interpolation ratios 2..16, four B levels
     ("RA16_medium_complexity", 192, 128, 17, 30),
     ("LDB_medium_complexity", 136, 72, 14, 22),     # fine qp (dense coefficients), HQ-period frame, 33-slot ring not yet wrapped
+    # the rest of the 15 shipped configurations ("all 15 configs"), small pictures
+    ("LDB_high_efficiency", 128, 72, 6, 30),        # four references, tb/pb split, delta qp, full search
+    ("HDB_low_complexity", 128, 128, 17, 34),
+    ("HDB_medium_complexity", 128, 72, 9, 30),
+    ("HDB_high_efficiency", 128, 128, 9, 33),
+    ("RA_medium_complexity", 200, 136, 9, 31),
+    ("HDB16_medium_complexity", 128, 72, 17, 32),
+    ("HDB16_high_efficiency", 128, 72, 17, 35),
+    ("RA16_low_complexity", 136, 128, 33, 36),
+    ("RA16_high_efficiency", 128, 128, 17, 29),
 ])
 @pytest.mark.parametrize("exe", ["Thordec_tail", "Thordec_gpu"])
 def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
@@ -39,11 +52,16 @@ def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
     for need in (os.path.join(REF_DIR, "Thorenc"), os.path.join(REF_DIR, "Thordec"), TAIL):
         if not os.path.exists(need):
             pytest.skip(f"{need} not built (needs /root/reference at build time)")
-    yuv = str(tmp_path / "clip.yuv")
-    write_clip(yuv, w, h, frames, seed=77)
-    bit, rec, _ = run_thorenc("Thorenc", cfg, yuv, w, h, frames, qp, str(tmp_path / "enc"))
-    cpu = _decode(os.path.join(REF_DIR, "Thordec"), str(tmp_path / "enc.bit"), str(tmp_path / "cpu.yuv"))
-    gpu = _decode(TAIL, str(tmp_path / "enc.bit"), str(tmp_path / "gpu.yuv"))
+    key = (cfg, w, h, frames, qp)
+    if key not in _STREAMS:                      # one encode + stock decode per stream, shared by the two decoders
+        yuv = str(tmp_path / "clip.yuv")
+        write_clip(yuv, w, h, frames, seed=77)
+        bit, rec, _ = run_thorenc("Thorenc", cfg, yuv, w, h, frames, qp, str(tmp_path / "enc"))
+        _STREAMS[key] = (bit, rec, _decode(os.path.join(REF_DIR, "Thordec"), str(tmp_path / "enc.bit"), str(tmp_path / "cpu.yuv")))
+    bit, rec, cpu = _STREAMS[key]
+    with open(str(tmp_path / "in.bit"), "wb") as f:
+        f.write(bit)
+    gpu = _decode(TAIL, str(tmp_path / "in.bit"), str(tmp_path / "gpu.yuv"))
     assert cpu == rec, "stock decoder does not reproduce the encoder's reconstruction"
     assert gpu == cpu, "decoder output with the GPU frame tail differs"
 
@@ -52,6 +70,10 @@ def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
     ("LDB_medium_complexity", 416, 240, 4, 30),
     ("LDB_low_complexity", 200, 136, 4, 36),
     ("RA_high_efficiency", 128, 128, 9, 32),
+    ("LDB_high_efficiency", 128, 72, 6, 30),
+    ("HDB16_medium_complexity", 128, 72, 17, 32),
+    ("RA16_low_complexity", 136, 128, 33, 36),
+    ("HDB_low_complexity", 200, 136, 9, 34),
 ])
 def test_thorenc_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp):
     """integration/_build/Thorenc_tail: the reference ENCODER with deblocking, the CLPF decision (against the original

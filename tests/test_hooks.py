@@ -52,3 +52,23 @@ def test_apply_hooks_rejects_a_changed_reference(tmp_path):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "integration", "apply_hooks.py"), "recon", p, str(tmp_path / "o.c")],
                        capture_output=True, text=True)
     assert r.returncode != 0 and "apply_hooks" in (r.stdout + r.stderr)
+
+
+def test_thor_configs_match_reference():
+    """tests/thorref.THOR_CONFIGS restates the reference's 15 config_*.txt files as options (the files do not travel to the
+    GPU box): same options, same values, same order, for every file."""
+    import glob
+    from thorref import THOR_CONFIGS
+    files = sorted(glob.glob("/root/reference/config_*.txt"))
+    if not files:
+        pytest.skip("reference tree not mounted")
+    per_run = {"-if", "-of", "-rf", "-stat", "-width", "-height", "-n", "-f", "-qp"}
+    assert len(files) == len(THOR_CONFIGS) == 15
+    for f in files:
+        opts = []
+        for line in open(f, errors="replace"):
+            parts = line.split(";")[0].split()
+            if parts and parts[0] not in per_run:
+                opts += parts[:2]
+        name = os.path.basename(f)[len("config_"):-len(".txt")]
+        assert THOR_CONFIGS[name] == opts, name

@@ -224,32 +224,38 @@ def blocky_frame(width, height, seed):
 # seeded synthetic clip.
 REF_DIR = os.path.join(ORACLE_DIR, "_ref")
 
-_LD = ["-HQperiod", "12", "-mqpP", "1.2", "-dqpI", "-2", "-lambda_coeffI", "0.8", "-lambda_coeffP", "1.2", "-max_num_ref", "2",
-       "-use_block_contexts", "1"]
-_RA = ["-HQperiod", "1", "-num_reorder_pics", "7", "-interp_ref", "1", "-intra_period", "64", "-dqpI", "-2", "-dqpB0", "3", "-dqpB1", "1",
-       "-dqpB2", "0", "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.1", "-mqpB1", "1.2", "-mqpB2", "1.3", "-lambda_coeffI", "0.8",
-       "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2",
-       "-use_block_contexts", "1"]
-_B16 = ["-HQperiod", "1", "-num_reorder_pics", "15", "-interp_ref", "1", "-dqpI", "-2", "-dqpB0", "2", "-dqpB1", "1", "-dqpB2", "0", "-dqpB3", "0",
-        "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.075", "-mqpB1", "1.15", "-mqpB2", "1.225", "-mqpB3", "1.3", "-lambda_coeffI", "0.8",
-        "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2",
-        "-lambda_coeffB3", "1.2", "-use_block_contexts", "1"]
-THOR_CONFIGS = {
-    # config_HDB16_low_complexity.txt: 16-frame dyadic B hierarchy without intra period ("HDB16" is a GOP structure, 8-bit)
-    "HDB16_low_complexity": _B16 + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
-                                    "-max_num_ref", "2", "-enable_bipred", "1", "-encoder_speed", "2"],
-    # config_RA16_medium_complexity.txt
-    "RA16_medium_complexity": _B16 + ["-intra_period", "64", "-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0",
-                                      "-early_skip_thr", "0.8", "-max_num_ref", "2", "-enable_bipred", "1", "-encoder_speed", "1"],
-    "LDB_low_complexity": _LD + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
-                                 "-enable_bipred", "0", "-encoder_speed", "2"],
-    "LDB_medium_complexity": _LD + ["-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "0.8",
-                                    "-enable_bipred", "1", "-encoder_speed", "1"],
-    "RA_low_complexity": _RA + ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0",
-                                "-max_num_ref", "2", "-enable_bipred", "1", "-encoder_speed", "2"],
-    "RA_high_efficiency": _RA + ["-intra_rdo", "1", "-enable_tb_split", "1", "-enable_pb_split", "1", "-early_skip_thr", "0.3",
-                                 "-max_num_ref", "4", "-enable_bipred", "1", "-encoder_speed", "0", "-max_delta_qp", "1"],
+# The 15 shipped operating points (config_<family>_<level>.txt of the reference) as command-line options: the files do not
+# exist on the GPU box.  tests/test_hooks.py::test_thor_configs_match_reference compares them with the files where the
+# reference tree is mounted.  "HDB16" / "RA16" are 16-picture B hierarchies (GOP structures), 8-bit like the rest.
+_B8 = ["-dqpI", "-2", "-dqpB0", "3", "-dqpB1", "1", "-dqpB2", "0", "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.1", "-mqpB1", "1.2",
+       "-mqpB2", "1.3", "-lambda_coeffI", "0.8", "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2", "-lambda_coeffB0", "1.2",
+       "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2"]
+_B16 = ["-dqpI", "-2", "-dqpB0", "2", "-dqpB1", "1", "-dqpB2", "0", "-dqpB3", "0", "-mqpP", "1.2", "-mqpB", "1.2", "-mqpB0", "1.075",
+        "-mqpB1", "1.15", "-mqpB2", "1.225", "-mqpB3", "1.3", "-lambda_coeffI", "0.8", "-lambda_coeffP", "1.2", "-lambda_coeffB", "1.2",
+        "-lambda_coeffB0", "1.2", "-lambda_coeffB1", "1.2", "-lambda_coeffB2", "1.2", "-lambda_coeffB3", "1.2"]
+_FAMILY = {
+    "LDB": ["-HQperiod", "12", "-mqpP", "1.2", "-dqpI", "-2", "-lambda_coeffI", "0.8", "-lambda_coeffP", "1.2"],
+    "HDB": ["-HQperiod", "1", "-num_reorder_pics", "7", "-interp_ref", "1"] + _B8,
+    "RA": ["-HQperiod", "1", "-num_reorder_pics", "7", "-interp_ref", "1", "-intra_period", "64"] + _B8,
+    "HDB16": ["-HQperiod", "1", "-num_reorder_pics", "15", "-interp_ref", "1"] + _B16,
+    "RA16": ["-HQperiod", "1", "-num_reorder_pics", "15", "-interp_ref", "1", "-intra_period", "64"] + _B16,
 }
+
+
+def _level(level, family):
+    if level == "low_complexity":
+        return ["-intra_rdo", "0", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "1.0", "-max_num_ref", "2",
+                "-use_block_contexts", "1", "-enable_bipred", "0" if family == "LDB" else "1", "-encoder_speed", "2"]
+    if level == "medium_complexity":
+        return ["-intra_rdo", "1", "-enable_tb_split", "0", "-enable_pb_split", "0", "-early_skip_thr", "0.8", "-max_num_ref", "2",
+                "-use_block_contexts", "1", "-enable_bipred", "1", "-encoder_speed", "1"]
+    return ["-intra_rdo", "1", "-enable_tb_split", "1", "-enable_pb_split", "1", "-early_skip_thr", "0.3", "-max_num_ref", "4",
+            "-use_block_contexts", "1", "-enable_bipred", "1", "-encoder_speed", "0", "-max_delta_qp", "1"]
+
+
+THOR_CONFIGS = {f"{fam}_{lvl}": opts + _level(lvl, fam) for fam, opts in _FAMILY.items()
+                for lvl in ("low_complexity", "medium_complexity", "high_efficiency")}
+assert len(THOR_CONFIGS) == 15
 
 
 def write_clip(path, width, height, frames, seed):
