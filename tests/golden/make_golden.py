@@ -12,7 +12,7 @@ golden data are outputs of the reference itself on seeded inputs:
   extras.npz    the same for row a19 (early-skip test) and SURVEY 8f #1 (intra prediction); `--extras-only`
                 regenerates just this file;
   bits.npz      SURVEY 8f #3 (bit-cost model): bits the reference's write_coeff / write_mv put into a stream and
-                quote_vlc's lengths, on seeded inputs; `--bits-only` regenerates just this file;
+                quote_vlc's lengths, on seeded inputs; `--bits-only` regenerates just this file (`--streams-only`: just streams.json);
   streams.json  md5 of the bitstream and of the reconstruction that oracle/_ref/Thorenc writes for three shipped
                 operating points on seeded synthetic clips (+ that Thordec reproduces the reconstruction).
 
@@ -30,7 +30,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
-from thorref import (BLOCKINFO, COEFF_KINDS, THOR_CONFIGS, Picture, blocky_frame, coeff_block, load_ref, ptr, random_blockinfo,  # noqa: E402
+from thorref import (BLOCKINFO, COEFF_KINDS, DECODER_STREAMS, THOR_CONFIGS, Picture, blocky_frame, coeff_block, load_ref, ptr, random_blockinfo,  # noqa: E402
                      ref_bitpos, ref_stream, run_thordec, run_thorenc, set_ref_simd, smooth_frame, write_clip)
 
 
@@ -170,7 +170,8 @@ def streams():
     with tempfile.TemporaryDirectory() as d:
         for cfg, w, h, n, qp, seed in (("LDB_low_complexity", 416, 240, 10, 32, 1234), ("LDB_medium_complexity", 192, 136, 6, 30, 7),
                                        ("RA_high_efficiency", 128, 64, 9, 34, 7), ("LDB_low_complexity", 64, 64, 3, 32, 1234),
-                                       ("LDB_medium_complexity", 72, 64, 3, 28, 1234), ("RA_high_efficiency", 64, 64, 3, 34, 1234)):
+                                       ("LDB_medium_complexity", 72, 64, 3, 28, 1234), ("RA_high_efficiency", 64, 64, 3, 34, 1234)) + \
+                tuple(c + (77,) for c in DECODER_STREAMS):
             yuv = os.path.join(d, "clip.yuv")
             write_clip(yuv, w, h, n, seed)
             bit, rec, _ = run_thorenc("Thorenc", cfg, yuv, w, h, n, qp, os.path.join(d, "o"))
@@ -331,6 +332,10 @@ def main():
     ref = load_ref()
     if ref is None:
         raise SystemExit("oracle/_ref/libthorref.so missing: run `make -C oracle ref` where /root/reference is mounted")
+    if "--streams-only" in sys.argv:
+        json.dump(streams(), open(os.path.join(HERE, "streams.json"), "w"), indent=1, sort_keys=True)
+        print("wrote", os.path.join(HERE, "streams.json"))
+        return
     np.savez_compressed(os.path.join(HERE, "bits.npz"), **bits(ref))
     if "--bits-only" in sys.argv:
         print("wrote", os.path.join(HERE, "bits.npz"), os.path.getsize(os.path.join(HERE, "bits.npz")), "bytes")

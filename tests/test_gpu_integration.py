@@ -8,7 +8,10 @@ import subprocess
 
 import pytest
 
-from thorref import REF_DIR, ROOT, run_thorenc, write_clip
+import hashlib
+import json
+
+from thorref import DECODER_STREAMS, REF_DIR, ROOT, run_thorenc, write_clip
 
 pytestmark = pytest.mark.gpu
 BUILD = os.path.join(ROOT, "integration", "_build")
@@ -23,26 +26,7 @@ def _decode(exe, bit, out):
     return open(out, "rb").read()
 
 
-@pytest.mark.parametrize("cfg,w,h,frames,qp", [
-    ("LDB_medium_complexity", 416, 240, 5, 30),     # P frames, bi-pred blocks, CLPF bits per superblock; 240 = 3*64 + 48
-    ("LDB_low_complexity", 200, 136, 4, 36),        # partial superblocks right and bottom
-    ("RA_high_efficiency", 128, 128, 9, 32),        # B frames, interpolated references, tb/pb split, delta qp
-    ("RA_high_efficiency", 192, 136, 17, 38),       # two sub-GOPs of the B hierarchy, partial superblock row, coarse qp
-    ("RA_low_complexity", 416, 240, 17, 32),        # 4-level interpolation pyramid (device-side in Thordec_gpu), 240 = 3*64 + 48
-    ("HDB16_low_complexity", 256, 192, 33, 34),     # two 16-frame sub-GOPs: interpolation ratios 2..16, four B levels
-    ("RA16_medium_complexity", 192, 128, 17, 30),
-    ("LDB_medium_complexity", 136, 72, 14, 22),     # fine qp (dense coefficients), HQ-period frame, 33-slot ring not yet wrapped
-    # the rest of the 15 shipped configurations ("all 15 configs"), small pictures
-    ("LDB_high_efficiency", 128, 72, 6, 30),        # four references, tb/pb split, delta qp, full search
-    ("HDB_low_complexity", 128, 128, 17, 34),
-    ("HDB_medium_complexity", 128, 72, 9, 30),
-    ("HDB_high_efficiency", 128, 128, 9, 33),
-    ("RA_medium_complexity", 200, 136, 9, 31),
-    ("HDB16_medium_complexity", 128, 72, 17, 32),
-    ("HDB16_high_efficiency", 128, 72, 17, 35),
-    ("RA16_low_complexity", 136, 128, 33, 36),
-    ("RA16_high_efficiency", 128, 128, 17, 29),
-])
+@pytest.mark.parametrize("cfg,w,h,frames,qp", DECODER_STREAMS)
 @pytest.mark.parametrize("exe", ["Thordec_tail", "Thordec_gpu"])
 def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
     """Thordec_tail: deblock + CLPF + reference creation on the device (2.2).  Thordec_gpu: additionally every
@@ -57,11 +41,19 @@ def test_thordec_with_gpu_frame_tail(tmp_path, cfg, w, h, frames, qp, exe):
         yuv = str(tmp_path / "clip.yuv")
         write_clip(yuv, w, h, frames, seed=77)
         bit, rec, _ = run_thorenc("Thorenc", cfg, yuv, w, h, frames, qp, str(tmp_path / "enc"))
-        _STREAMS[key] = (bit, rec, _decode(os.path.join(REF_DIR, "Thordec"), str(tmp_path / "enc.bit"), str(tmp_path / "cpu.yuv")))
-    bit, rec, cpu = _STREAMS[key]
+        _STREAMS[key] = (bit, rec, _decode(os.path.join(REF_DIR, "Thordec"), str(tmp_path / "enc.bit"), str(tmp_path / "cpu.yuv")),
+                         hashlib.md5(open(yuv, "rb").read()).hexdigest())
+    bit, rec, cpu, clip_md5 = _STREAMS[key]
     with open(str(tmp_path / "in.bit"), "wb") as f:
         f.write(bit)
     gpu = _decode(TAIL, str(tmp_path / "in.bit"), str(tmp_path / "gpu.yuv"))
+    # the committed hashes of the same stream (tests/golden/streams.json, written where the reference tree is mounted),
+    # when this numpy build reproduces the clip: the stream the box's Thorenc made is the golden one, and so is our output
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "streams.json"))).get(f"{cfg}_{w}x{h}x{frames}_qp{qp}_seed77")
+    assert gold is not None, "stream missing from tests/golden/streams.json: rerun tests/golden/make_golden.py"
+    if clip_md5 == gold["clip_md5"]:
+        assert hashlib.md5(bit).hexdigest() == gold["bit_md5"], "the box's Thorenc does not reproduce the golden stream"
+        assert hashlib.md5(gpu).hexdigest() == gold["rec_md5"], "decoder output differs from the golden reconstruction"
     assert cpu == rec, "stock decoder does not reproduce the encoder's reconstruction"
     assert gpu == cpu, "decoder output with the GPU frame tail differs"
 

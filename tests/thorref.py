@@ -486,3 +486,27 @@ def deblock_threshold_case(width, height, qp):
     bi = np.zeros((height // 4) * (width // 4), BLOCKINFO)
     bi["mode"], bi["size"], bi["cbp_y"] = MODE_INTER, 8, 1
     return y, u, u.copy(), bi, dv, dh
+
+
+# streams of tests/test_gpu_integration.py::test_thordec_with_gpu_frame_tail (clip seed 77); tests/golden/make_golden.py
+# commits the reference's hashes of each
+DECODER_STREAMS = [
+    ("LDB_medium_complexity", 416, 240, 5, 30),     # P frames, bi-pred blocks, CLPF bits per superblock; 240 = 3*64 + 48
+    ("LDB_low_complexity", 200, 136, 4, 36),        # partial superblocks right and bottom
+    ("RA_high_efficiency", 128, 128, 9, 32),        # B frames, interpolated references, tb/pb split, delta qp
+    ("RA_high_efficiency", 192, 136, 17, 38),       # two sub-GOPs of the B hierarchy, partial superblock row, coarse qp
+    ("RA_low_complexity", 416, 240, 17, 32),        # 4-level interpolation pyramid (device-side in Thordec_gpu), 240 = 3*64 + 48
+    ("HDB16_low_complexity", 256, 192, 33, 34),     # two 16-frame sub-GOPs: interpolation ratios 2..16, four B levels
+    ("RA16_medium_complexity", 192, 128, 17, 30),
+    ("LDB_medium_complexity", 136, 72, 14, 22),     # fine qp (dense coefficients), HQ-period frame, 33-slot ring not yet wrapped
+    # the rest of the 15 shipped configurations ("all 15 configs"), small pictures
+    ("LDB_high_efficiency", 128, 72, 6, 30),        # four references, tb/pb split, delta qp, full search
+    ("HDB_low_complexity", 128, 128, 17, 34),
+    ("HDB_medium_complexity", 128, 72, 9, 30),
+    ("HDB_high_efficiency", 128, 128, 9, 33),
+    ("RA_medium_complexity", 200, 136, 9, 31),
+    ("HDB16_medium_complexity", 128, 72, 17, 32),
+    ("HDB16_high_efficiency", 128, 72, 17, 35),
+    ("RA16_low_complexity", 136, 128, 33, 36),
+    ("RA16_high_efficiency", 128, 128, 17, 29),
+]
