@@ -18,7 +18,7 @@
 #include <time.h>
 
 /* THORCUDA_HOOK_TIMING=1: host milliseconds per phase, printed at exit */
-static double t_ph[8], t_leave, t_host;
+static double t_ph[8], t_leave, t_host, t_mark2;
 static int t_on = -1, t_frames;
 static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
 static void report(void) {
@@ -26,6 +26,11 @@ static void report(void) {
   fprintf(stderr, "thorcuda encoder tail, %d frames, host ms per frame:", t_frames);
   for (int i = 0; i < 8; i++) fprintf(stderr, " %s %.3f;", nm[i], t_ph[i] / (t_frames ? t_frames : 1));
   fprintf(stderr, " host between hooks %.3f\n", t_host / (t_frames > 1 ? t_frames - 1 : 1));
+  /* the same interval the marginal rate of two stock runs (2 and n frames) measures, but on this process's own clock:
+   * CUDA start-up and tear-down (1.1-1.6 s, varying by tenths of a second) stay outside */
+  if (t_frames > 2 && t_leave > t_mark2)
+    fprintf(stderr, "thorcuda encoder tail: steady state, %d frames after the second in %.3f s = %.3f frames/s\n", t_frames - 2,
+            (t_leave - t_mark2) * 1e-3, (t_frames - 2) / ((t_leave - t_mark2) * 1e-3));
 }
 #define PHASE(i) do { if (t_on) { const double t_ = now_ms(); t_ph[i] += t_ - t0_; t0_ = t_; } } while (0)
 
@@ -106,5 +111,5 @@ void thorcuda_enc_make_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
                                     ref->v - ref->pad_ver_c * ref->stride_c - ref->pad_hor_c));
   need(thorcuda_sync());
   PHASE(7);
-  if (t_on > 0) t_leave = now_ms();
+  if (t_on > 0) { t_leave = now_ms(); if (t_frames == 2) t_mark2 = t_leave; }
 }
