@@ -237,7 +237,7 @@ def decoder_leg(args):
     shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
     with tempfile.TemporaryDirectory(dir=shm) as d:
         yuv = os.path.join(d, "clip.yuv")
-        write_clip(yuv, args.width, args.height, frames)
+        write_clip(yuv, args.width, args.height, frames, noise=5.0 if args.decoder_hard else 2.0, obj=args.decoder_hard)
         bits = {}
         for n in (short, frames):                      # two stream lengths: their difference cancels process start-up
             bits[n] = os.path.join(d, f"clip{n}.bit")
@@ -265,7 +265,7 @@ def decoder_leg(args):
             res[name + "_seconds"] = {str(n): round(best[n], 3) for n in (short, frames)}
         for name, v in steady.items():
             res[name + "_steady_fps"] = round(sorted(v)[len(v) // 2], 1)       # median of the 5 runs of the long stream
-        res.update({"frames": frames, "stream": f"{args.decoder_config} {args.width}x{args.height} qp 32, {os.path.getsize(bits[frames])} bytes",
+        res.update({"frames": frames, "stream": f"{args.decoder_config} {args.width}x{args.height} qp 32{', hard clip' if args.decoder_hard else ''}, {os.path.getsize(bits[frames])} bytes",
                     "identical_yuv": outs["reference"] == outs["gpu_tail"] == outs["gpu_recon"], "scratch": "tmpfs (/dev/shm)" if shm else "default temporary directory",
                     "note": "*_fps: marginal decode rate between a short and a long stream (process wall clock, file I/O included; the CUDA "
                             "start-up of the hooked decoders varies by +-0.4 s between runs, which this difference only cancels on average); "
@@ -825,6 +825,8 @@ def main():
     ap.add_argument("--encoder-noise", type=float, default=5.0, help="sensor noise (grey levels) of the encoder leg's clip: with the decoder "
                     "leg's clean clip (2.0) the P frames are skipped almost entirely")
     ap.add_argument("--decoder-frames", type=int, default=168)
+    ap.add_argument("--decoder-hard", action="store_true", help="decoder leg on the encoder leg's hard clip (layers drifting against each "
+                    "other, moving patch, noise 5): several times the bits per frame of the default clip")
     ap.add_argument("--decoder-config", default="LDB_low_complexity", choices=sorted(DEC_CONFIGS),
                     help="stream of the decoder leg; RA_low_complexity has B frames with interpolated references (one interpolate_frames per B frame)")
     ap.add_argument("--cpu-frames", type=int, default=2)
