@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Host-phase table of integration/_build/Thordec_gpu (THORCUDA_HOOK_TIMING=1) on a 1080p stream encoded here by the
 reference's Thorenc, pipelined (default) and serial (THORCUDA_HOOK_SERIAL=1).  Measurement tooling.
-    python profiles/dec_phase_timing.py [LDB_low_complexity|RA_low_complexity] [frames] [WxH]"""
+    python profiles/dec_phase_timing.py [LDB_low_complexity|RA_low_complexity] [frames] [WxH] [hard]"""
 import os
 import subprocess
 import sys
@@ -19,7 +19,8 @@ enc, dec = os.path.join(ROOT, "oracle/_ref/Thorenc"), os.path.join(ROOT, "oracle
 gpu = os.path.join(ROOT, "integration/_build/Thordec_gpu")
 with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as d:
     yuv, bit = os.path.join(d, "c.yuv"), os.path.join(d, "c.bit")
-    bench.write_clip(yuv, W, H, frames)
+    hard = len(sys.argv) > 4 and sys.argv[4] == "hard"
+    bench.write_clip(yuv, W, H, frames, noise=5.0 if hard else 2.0, obj=hard)
     subprocess.run([enc, "-if", yuv, "-of", bit, "-rf", os.path.join(d, "r.yuv"), "-stat", os.path.join(d, "s.txt"), "-width", str(W),
                     "-height", str(H), "-n", str(frames), "-f", "60", "-qp", "32"] + bench.DEC_CONFIGS[cfg], check=True, capture_output=True)
     outs = {}
