@@ -1,0 +1,238 @@
+// Frame encoder of libthorcuda -- common definitions of the superblock encoder (enc_core.h).
+//
+// The superblock encoder is written ONCE as "uniform control flow + cooperative pixel loops":
+//   * every thread of the CTA executes the same scalar decision code on the same values (decisions live in registers,
+//     replicated; there is nothing to broadcast),
+//   * pixel / coefficient arrays live in shared memory and are only written inside TFOR loops, which spread the
+//     iterations over the CTA and are followed by a barrier before anybody reads what another thread wrote.
+// Compiled by nvcc for sm_100a this is the product.  Compiled by g++ with THOR_HOSTEMU (one "thread", barriers are
+// no-ops) the very same source runs on the host: tests/hostemu uses that build to check the decision logic against the
+// reference encoder byte for byte in a container without a GPU.  The host build is test infrastructure only --
+// libthorcuda never contains it and has no CPU path.
+#pragma once
+#include <stdint.h>
+#include "enc_abi.h"
+
+#ifdef THOR_HOSTEMU
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#define TD static inline
+#define TDN static __attribute__((noinline))
+#define TCONST static const
+#else
+#include <cuda_runtime.h>
+#define TD __device__ __forceinline__
+#define TDN __device__ __noinline__
+#define TCONST __device__ const
+#endif
+
+namespace thorenc {
+
+constexpr int NT = 256;              // threads per CTA (one CTA encodes one superblock)
+constexpr int NW = NT / 32;
+
+// ---- the cooperating thread group ------------------------------------------------------------------------------
+struct Grp {
+#ifdef THOR_HOSTEMU
+  static constexpr int tid = 0;
+  static constexpr int n = 1;
+  void sync() const {}
+  int sum(int v) { return v; }
+  template <int K> void sumk(int (&v)[K]) {}
+  int any(int p) { return p != 0; }
+  int vmax(int v) { return v; }
+#else
+  int tid;
+  static constexpr int n = NT;
+  int *red;                          // shared: 2 * NW * 8 ints
+  int flip;
+  __device__ void sync() const { __syncthreads(); }
+  __device__ int sum(int v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    int *r = red + (flip ^= 1) * NW * 8;
+    if ((tid & 31) == 0) r[tid >> 5] = v;
+    __syncthreads();
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < NW; w++) t += r[w];
+    return t;
+  }
+  template <int K> __device__ void sumk(int (&v)[K]) {
+    static_assert(K <= 8, "reduction scratch holds 8 values per warp");
+#pragma unroll
+    for (int k = 0; k < K; k++)
+#pragma unroll
+      for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    int *r = red + (flip ^= 1) * NW * 8;
+    if ((tid & 31) == 0)
+#pragma unroll
+      for (int k = 0; k < K; k++) r[(tid >> 5) * 8 + k] = v[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+      int t = 0;
+#pragma unroll
+      for (int w = 0; w < NW; w++) t += r[w * 8 + k];
+      v[k] = t;
+    }
+  }
+  __device__ int any(int p) { return __syncthreads_or(p); }
+  __device__ int vmax(int v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    int *r = red + (flip ^= 1) * NW * 8;
+    if ((tid & 31) == 0) r[tid >> 5] = v;
+    __syncthreads();
+    int t = r[0];
+#pragma unroll
+    for (int w = 1; w < NW; w++) t = max(t, r[w]);
+    return t;
+  }
+#endif
+};
+
+// iterations i = 0 .. cnt-1 spread over the group; NOT followed by a barrier (call g.sync() where a reader follows)
+#define TFOR(g, i, cnt) for (int i = (g).tid; i < (cnt); i += (g).n)
+
+// ---- small helpers ---------------------------------------------------------------------------------------------
+TD int imin(int a, int b) { return a < b ? a : b; }
+TD int imax(int a, int b) { return a > b ? a : b; }
+TD int iabs(int a) { return a < 0 ? -a : a; }
+TD int iclip(int v, int lo, int hi) { return v < lo ? lo : v > hi ? hi : v; }
+TD int clip255(int v) { return v < 0 ? 0 : v > 255 ? 255 : v; }
+TD int ilog2(uint32_t v) {
+#ifdef THOR_HOSTEMU
+  return 31 - __builtin_clz(v);
+#else
+  return 31 - __clz((int)v);
+#endif
+}
+
+// IEEE double product / sum without contraction: the reference's cost terms are (int)(lambda * bits + 0.5) evaluated
+// in double by the host compiler (SSE2, no FMA): enc/encode_block.c:863,1225.
+TD double dmul(double a, double b) {
+#ifdef THOR_HOSTEMU
+  volatile double r = a * b;
+  return r;
+#else
+  return __dmul_rn(a, b);
+#endif
+}
+TD double dadd(double a, double b) {
+#ifdef THOR_HOSTEMU
+  volatile double r = a + b;
+  return r;
+#else
+  return __dadd_rn(a, b);
+#endif
+}
+TD double ddiv(double a, double b) {
+#ifdef THOR_HOSTEMU
+  volatile double r = a / b;
+  return r;
+#else
+  return __ddiv_rn(a, b);
+#endif
+}
+TD double dsqrt(double a) {
+#ifdef THOR_HOSTEMU
+  return sqrt(a);
+#else
+  return __dsqrt_rn(a);
+#endif
+}
+
+// ---- memory access by kind -------------------------------------------------------------------------------------
+// Frame state written during this frame by other superblocks (reconstruction, neighbour units) is read through L2.
+TD uint8_t ld_frame8(const uint8_t *p) {
+#ifdef THOR_HOSTEMU
+  return *p;
+#else
+  return __ldcg(p);
+#endif
+}
+TD thor_enc_unit ld_unit(const thor_enc_unit *p) {
+#ifdef THOR_HOSTEMU
+  return *p;
+#else
+  const int4 v = __ldcg(reinterpret_cast<const int4 *>(p));
+  thor_enc_unit u;
+  *reinterpret_cast<int4 *>(&u) = v;
+  return u;
+#endif
+}
+TD void st_unit(thor_enc_unit *p, const thor_enc_unit &u) {
+#ifdef THOR_HOSTEMU
+  *p = u;
+#else
+  *reinterpret_cast<int4 *>(p) = *reinterpret_cast<const int4 *>(&u);
+#endif
+}
+// Read-only pictures (original, references): cached loads; 4 bytes at any alignment.
+TD uint8_t ld_ro8(const uint8_t *p) {
+#ifdef THOR_HOSTEMU
+  return *p;
+#else
+  return __ldg(p);
+#endif
+}
+TD uint32_t ld_ro32u(const uint8_t *p) {
+#ifdef THOR_HOSTEMU
+  uint32_t v; memcpy(&v, p, 4); return v;
+#else
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const uint32_t *q = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+  const uint32_t lo = __ldg(q);
+  const unsigned sh = (unsigned)(a & 3) * 8;
+  if (sh == 0) return lo;
+  return __funnelshift_r(lo, __ldg(q + 1), sh);
+#endif
+}
+
+// byte-SIMD on packed pixels
+TD uint32_t sad4(uint32_t a, uint32_t b) {
+#ifdef THOR_HOSTEMU
+  uint32_t s = 0;
+  for (int k = 0; k < 4; k++) s += (uint32_t)iabs((int)((a >> (8 * k)) & 255) - (int)((b >> (8 * k)) & 255));
+  return s;
+#else
+  return __vsadu4(a, b);
+#endif
+}
+TD uint32_t havg4(uint32_t a, uint32_t b) {          // (a + b) >> 1 per byte
+#ifdef THOR_HOSTEMU
+  uint32_t r = 0;
+  for (int k = 0; k < 4; k++) r |= ((((a >> (8 * k)) & 255) + ((b >> (8 * k)) & 255)) >> 1) << (8 * k);
+  return r;
+#else
+  return __vhaddu4(a, b);
+#endif
+}
+
+struct Mv { int16_t x, y; };
+TD Mv mkmv(int x, int y) { Mv m; m.x = (int16_t)x; m.y = (int16_t)y; return m; }
+TD bool mv_eq(Mv a, Mv b) { return a.x == b.x && a.y == b.y; }
+
+// inter_pred_t (common/types.h:111-118)
+struct InterPred { Mv mv0, mv1; int ref_idx0, ref_idx1, dir; };
+
+// ---- constant tables -------------------------------------------------------------------------------------------
+// reference common/common_block.c:78-83, :97-98
+TCONST uint8_t kChromaQp[52] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 25,
+                                26, 27, 28, 29, 29, 30, 31, 32, 33, 33, 34, 34, 35, 35, 36, 36, 37, 37, 38, 39, 40, 41, 42, 43, 44, 45};
+TCONST uint16_t kQuant[6] = {26214, 23302, 20560, 18396, 16384, 14564};
+TCONST uint16_t kDequant[6] = {40, 45, 51, 57, 64, 72};
+// enc/encode_block.c:2975-2979 (iq_8x8)
+TCONST uint16_t kIq8x8[52] = {6, 7, 8, 8, 10, 11, 12, 13, 15, 17, 19, 21, 24, 27, 30, 34, 38, 43, 48, 54, 60, 68, 76, 86, 96, 108,
+                              121, 136, 152, 171, 192, 216, 242, 272, 305, 342, 384, 431, 484, 543, 610, 684, 768, 862, 968, 1086,
+                              1219, 1368, 1536, 1724, 1935, 2172};
+// the 32-point cosine ladder the HEVC-style bases of common/transform.c:41-245 are built from (see build_tables)
+TCONST int8_t kCos32[33] = {64, 90, 90, 90, 89, 88, 87, 85, 83, 82, 80, 78, 75, 73, 70, 67, 64, 61, 57, 54, 50, 46, 43, 38, 36, 31, 25, 22, 18, 13, 9, 4, 0};
+// common/inter_prediction.c:47-70
+TCONST int8_t kLumaBi[4][6] = {{0, 0, 64, 0, 0, 0}, {2, -10, 59, 17, -5, 1}, {1, -8, 39, 39, -8, 1}, {1, -5, 17, 59, -10, 2}};
+TCONST int8_t kLumaUni[4][6] = {{0, 0, 64, 0, 0, 0}, {1, -7, 55, 19, -5, 1}, {1, -7, 38, 38, -7, 1}, {1, -5, 19, 55, -7, 1}};
+TCONST int8_t kChroma[8][4] = {{0, 64, 0, 0}, {-2, 58, 10, -2}, {-4, 54, 16, -2}, {-4, 44, 28, -4}, {-4, 36, 36, -4}, {-4, 28, 44, -4}, {-2, 16, 54, -4}, {-2, 10, 58, -2}};
+
+}  // namespace thorenc
