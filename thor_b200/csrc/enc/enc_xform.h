@@ -1,0 +1,196 @@
+// Frame encoder of libthorcuda -- residual, integer transforms, quantiser, reconstruction, distortion.
+#pragma once
+#include "enc_state.h"
+
+namespace thorenc {
+
+// transform() (common/transform.c:249-330) of org - pred for one size x size transform block.  The transform input is
+// formed directly: the residual itself, its f x f box sums for `fast` blocks larger than 16 (:273-293), or its 2x2 sums
+// for 64x64 (:295-307).  Output: S.coeff, the low q x q corner (q = min(size, 16)), stride q.  Ends with a barrier.
+TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, int size, int fast) {
+  int n = size, sh1 = ilog2((uint32_t)size), sh2 = sh1 + 5, f = 1;
+  if (size > 16 && fast) { n = 16; f = size / 16; sh1 = size == 64 ? 8 : 6; sh2 = 9; }
+  else if (size == 64) { n = 32; f = 2; sh1 = 7; sh2 = 10; }
+  const int keep = imin(n, 16);
+  int16_t *in = S.resid;
+  TFOR(g, i, n * n) {
+    const int r = i / n, c = i % n;
+    int s = 0;
+    for (int a = 0; a < f; a++)
+      for (int b = 0; b < f; b++) s += (int)org[(r * f + a) * ostride + c * f + b] - (int)pred[(r * f + a) * pstride + c * f + b];
+    in[i] = (int16_t)s;
+  }
+  g.sync();
+  const int8_t *M = dct_matrix(S, n);
+  TFOR(g, i, keep * n) {                                   // rows of the block -> horizontal frequency k
+    const int r = i / keep, k = i % keep;
+    int acc = 0;
+    for (int c = 0; c < n; c++) acc += M[k * n + c] * in[r * n + c];
+    S.mid[k * 32 + r] = (int16_t)((acc + (1 << (sh1 - 1))) >> sh1);
+  }
+  g.sync();
+  TFOR(g, i, keep * keep) {                                // vertical frequency v
+    const int v = i / keep, k = i % keep;
+    int acc = 0;
+    for (int r = 0; r < n; r++) acc += M[v * n + r] * S.mid[k * 32 + r];
+    S.coeff[v * keep + k] = (int16_t)((acc + (1 << (sh2 - 1))) >> sh2);
+  }
+  g.sync();
+}
+
+// quantize() (enc/encode_block.c:75-178, rdoq == 0) of S.coeff; levels go to coeffq (stride `size`, low q x q corner).
+// Returns cbp (uniform).  Ends with a barrier.
+TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coeff_block_type) {
+  const int intra = (coeff_block_type >> 1) & 1, chroma = coeff_block_type & 1;
+  const int lg = ilog2((uint32_t)size), q = imin(size, 16), nq = q * q;
+  const int scale = kQuant[qp % 6], shift = 21 - lg + qp / 6;
+  const uint8_t *zz = zigzag(S, q);
+  const int tail_off = (intra ? 38 : -26) * (1 << (shift - 8));
+  const int off_small = (intra ? 102 : 51) << (shift - 8), off_big = (intra ? 115 : 90) << (shift - 8);
+  int mylast = -1;
+  TFOR(g, i, nq) {
+    const int c = S.coeff[i], p = zz[i];
+    S.lin[p] = c;
+    if ((iabs(iabs(c) * scale + tail_off) >> shift) != 0) mylast = imax(mylast, p);
+  }
+  const int last = g.vmax(mylast);                         // last_pos (:95-104); barrier inside
+  int mine = 0;
+  TFOR(g, p, nq) {
+    int l = 0;
+    if (p <= last) {
+      const int c = S.lin[p], mag = scale * iabs(c);
+      const int off = ((mag >> shift) == 0 || chroma) ? off_small : off_big;
+      l = (mag + off) >> shift;
+      mine |= l != 0;
+      if (c < 0) l = -l;
+    }
+    S.lev[p] = l;
+  }
+  if (g.tid < 8) S.fire[g.tid] = 0;
+#ifdef THOR_HOSTEMU
+  for (int k = 0; k < 8; k++) S.fire[k] = 0;
+#endif
+  const int cbp = g.any(mine);                             // barrier inside
+  if (cbp) {
+    // "RDOQ light" (:135-168): a level > 1 right behind two zeros is traded for a +-1.  Whether position p can fire at
+    // all depends only on the ORIGINAL levels at p-2, p-1, p (the pass only ever turns zeros and large levels into +-1,
+    // which cannot create a new zero-zero-large pattern); those positions are collected in parallel and walked in order.
+    const int N = chroma ? last + 1 : nq;
+    TFOR(g, p, N) {
+      if (p >= 2 && S.lev[p - 2] == 0 && S.lev[p - 1] == 0 && iabs(S.lev[p]) > 1) {
+#ifdef THOR_HOSTEMU
+        S.fire[p >> 5] |= 1u << (p & 31);
+#else
+        atomicOr(&S.fire[p >> 5], 1u << (p & 31));
+#endif
+      }
+    }
+    g.sync();
+    if (g.tid == 0) {
+      const int thr = (73 * kDequant[qp % 6] << (qp / 6)) >> (4 + lg);
+      for (int w = 0; w < 8; w++) {
+        uint32_t m = S.fire[w];
+        while (m) {
+          const int b = ilog2(m & (0u - m));
+          m &= m - 1;
+          const int p = 32 * w + b;
+          int ok = 1;
+          if (p > 2 && iabs(S.lev[p - 3]) > 1) ok = 0;
+          if (p > 3 && iabs(S.lev[p - 4]) > 1 && iabs(S.lev[p - 3]) > 0) ok = 0;
+          if (p == 2 && (!chroma || last >= 6)) ok = 0;
+          if (!(ok && S.lev[p - 2] == 0 && S.lev[p - 1] == 0 && iabs(S.lev[p]) > 1)) continue;
+          const int k1 = iabs(S.lin[p]), k2 = iabs(S.lin[p - 1]), k3 = iabs(S.lin[p - 2]);
+          if (k1 + imax(k2, k3) < thr) S.lev[p] = S.lin[p] < 0 ? -1 : 1;
+          else if (k2 > k3) S.lev[p - 1] = S.lin[p - 1] < 0 ? -1 : 1;
+          else S.lev[p - 2] = S.lin[p - 2] < 0 ? -1 : 1;
+        }
+      }
+    }
+    g.sync();
+  }
+  TFOR(g, i, nq) coeffq[(i / q) * size + (i % q)] = (int16_t)S.lev[zz[i]];
+  g.sync();
+  return cbp;
+}
+
+// dequantize (common/common_block.c:132-146) + inverse_transform (common/transform.c:432-518) + reconstruct_block
+// (common/common_block.c:148-156).  coeffq: stride `size`; rec: stride rstride.  Ends with a barrier.
+TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int qp, int size) {
+  const int lg = ilog2((uint32_t)size), q = imin(size, 16), n = size == 64 ? 32 : size, keep = imin(n, 16);
+  const int lshift = qp / 6, rshift = lg - 1, scale = kDequant[qp % 6], add = 1 << (rshift - 1);
+  TFOR(g, i, q * q) {
+    const int c = coeffq[(i / q) * size + (i % q)];
+    S.rcoeff[i] = (int16_t)((((c * scale) << lshift) + add) >> rshift);
+  }
+  g.sync();
+  const int8_t *M = dct_matrix(S, n);
+  TFOR(g, i, keep * n) {                                   // column k of the coefficients -> spatial column
+    const int r = i / keep, k = i % keep;
+    int acc = 0;
+    for (int v = 0; v < keep; v++) acc += M[v * n + r] * S.rcoeff[v * q + k];
+    S.mid[k * 32 + r] = (int16_t)iclip((acc + 64) >> 7, -32768, 32767);
+  }
+  g.sync();
+  TFOR(g, i, n * n) {
+    const int r = i / n, c = i % n;
+    int acc = 0;
+    for (int k = 0; k < keep; k++) acc += M[k * n + c] * S.mid[k * 32 + r];
+    S.rblock[i] = (int16_t)iclip((acc + 2048) >> 12, -32768, 32767);
+  }
+  g.sync();
+  if (size == 64) {                                        // 2x nearest-neighbour up-sampling (:507-514)
+    TFOR(g, i, 4096) {
+      const int r = i >> 6, c = i & 63;
+      rec[r * rstride + c] = (uint8_t)clip255(S.rblock[(r >> 1) * 32 + (c >> 1)] + pred[r * pstride + c]);
+    }
+  } else {
+    TFOR(g, i, n * n) {
+      const int r = i / n, c = i % n;
+      rec[r * rstride + c] = (uint8_t)clip255(S.rblock[i] + pred[r * pstride + c]);
+    }
+  }
+  g.sync();
+}
+
+// one transform block of encode_and_reconstruct_block_inter / _intra (enc/encode_block.c:1398-1532): residual ->
+// transform -> quantise -> (dequantise -> inverse transform -> reconstruct | copy the prediction).  Returns the cbp bit.
+TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride,
+                  int16_t *coeffq, int size, int qp, int coeff_type, int fast) {
+  forward_tb(g, S, org, ostride, pred, pstride, size, fast);
+  const int cbp = quantize_tb(g, S, coeffq, qp, size, coeff_type);
+  if (cbp) reconstruct_tb(g, S, coeffq, pred, pstride, rec, rstride, qp, size);
+  else {
+    TFOR(g, i, size * size) {
+      const int r = i / size, c = i % size;
+      rec[r * rstride + c] = pred[r * pstride + c];
+    }
+    g.sync();
+  }
+  return cbp;
+}
+
+// ssd_calc (enc/encode_block.c:782-797) over the three planes of a block: cost_calc's distortion (:1218-1228)
+TDN int ssd_yuv(Grp &g, const Blk &a, const Blk &b, int stride, int width, int height) {
+  int s = 0;
+  TFOR(g, i, width * height) {
+    const int o = (i / width) * stride + (i % width);
+    const int d = (int)a.y[o] - (int)b.y[o];
+    s += d * d;
+  }
+  const int wc = width / 2, sc = stride / 2;
+  TFOR(g, i, wc * (height / 2)) {
+    const int o = (i / wc) * sc + (i % wc);
+    const int du = (int)a.u[o] - (int)b.u[o], dv = (int)a.v[o] - (int)b.v[o];
+    s += du * du + dv * dv;
+  }
+  return g.sum(s);
+}
+
+// cost_calc (enc/encode_block.c:1218-1228)
+TD uint32_t rd_cost(int ssd, int nbits, double lambda) {
+  uint32_t cost = (uint32_t)(ssd + (int32_t)dadd(dmul(lambda, (double)nbits), 0.5));
+  if (cost > (1u << 30)) cost = 1u << 30;
+  return cost;
+}
+
+}  // namespace thorenc
