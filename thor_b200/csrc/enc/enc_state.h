@@ -49,6 +49,9 @@ struct SbMem {
   uint32_t fire[8];                  // quantiser: positions the RDOQ-light pass has to look at
   int acc[64 * 5 + 8];               // SAD accumulators of a batch of candidates
   Mv mvcand[THOR_ENC_MAX_REF][64];   // frame_info.mvcand (enc/mainenc.h:124), reset per superblock
+  // decision of a 16x16 block kept while its 8x8 children are tried (top-down split, enc/encode_block.c:2983-2995)
+  uint8_t keep_y[256], keep_u[64], keep_v[64];
+  int16_t keep_cy[256], keep_cu[64], keep_cv[64];
 #ifndef THOR_HOSTEMU
   int red[2 * NW * 8];
 #endif
