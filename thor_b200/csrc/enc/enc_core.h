@@ -124,3 +124,96 @@ TDN int inter_plane(Enc &E, const uint8_t *org, int size, int qp, const uint8_t 
     }
   return cbp;
 }
+
+// encode_block (enc/encode_block.c:1590-1800) as a trial: prediction, residual coding and reconstruction of the block with
+// the parameters in P, into S.rec / S.tc; returns what write_block would emit (its length).  P.cbp_* / P.tb_split are set.
+TDN int encode_block(Enc &E, const BlockCtx &B, Param &P) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size, sizeC = size / 2, yposC = B.ypos / 2, xposC = B.xpos / 2;
+  const int mode = P.mode;
+  const int qpY = F.qp + B.delta_qp, qpC = kChromaQp[qpY];
+  const int tb_split = imax(0, P.tb_param), zero_block = P.tb_param == -1;
+  const int ctype = (F.frame_type == 0) << 1;
+  const int bip = F.enable_bipred;
+  P.tb_split = tb_split;
+  g.sync();
+  if (mode == 1) {
+    const thor_enc_pic &rec = F.rec;
+    const int upright = upright_available(B.ypos, B.xpos, size, F.width), downleft = downleft_available(B.ypos, B.xpos, size, F.height);
+    P.cbp_y = intra_plane(E, 0, S.org.y, rec.y + B.ypos * rec.stride_y + B.xpos, rec.stride_y, B.ypos, B.xpos, size, qpY, S.pred.y, S.tc.y, S.rec.y,
+                          ctype, tb_split, P.intra_mode, upright, downleft);
+    P.cbp_u = intra_plane(E, 1, S.org.u, rec.u + yposC * rec.stride_c + xposC, rec.stride_c, yposC, xposC, sizeC, qpC, S.pred.u, S.tc.u, S.rec.u,
+                          ctype | 1, tb_split && size > 8, P.intra_mode, upright, downleft);
+    P.cbp_v = intra_plane(E, 2, S.org.v, rec.v + yposC * rec.stride_c + xposC, rec.stride_c, yposC, xposC, sizeC, qpC, S.pred.v, S.tc.v, S.rec.v,
+                          ctype | 1, tb_split && size > 8, P.intra_mode, upright, downleft);
+  } else {
+    Blk &dst = mode == 0 ? S.rec : S.pred;
+    const thor_enc_pic &r0 = ref_pic(F, P.ref_idx0);
+    if (mode == 0 || mode == 4) {                                      // SKIP / MERGE (:1688-1732)
+      if (P.dir == 2) {
+        const thor_enc_pic &r1 = ref_pic(F, P.ref_idx1);
+        inter_yuv(g, S, F, r0, S.p0, B, P.mv0, r0.frame_num >= F.rec.frame_num, bip, 0);
+        inter_yuv(g, S, F, r1, S.p1, B, P.mv1, r1.frame_num >= F.rec.frame_num, bip, 0);
+        average_blocks(g, dst, S.p0, S.p1, B);
+      } else {
+        inter_yuv(g, S, F, r0, dst, B, P.mv0, r0.frame_num > F.rec.frame_num, bip, 0);
+      }
+    } else if (mode == 2) {                                            // INTER (:1734-1739)
+      inter_yuv(g, S, F, r0, dst, B, P.mv0, r0.frame_num > F.rec.frame_num, bip, F.enable_pb_split);
+    } else {                                                           // BIPRED (:1740-1753)
+      const thor_enc_pic &r1 = ref_pic(F, P.ref_idx1);
+      inter_yuv(g, S, F, r0, S.p0, B, P.mv0, r0.frame_num >= F.rec.frame_num, bip, F.enable_pb_split);
+      inter_yuv(g, S, F, r1, S.p1, B, P.mv1, r1.frame_num >= F.rec.frame_num, bip, F.enable_pb_split);
+      average_blocks(g, dst, S.p0, S.p1, B);
+    }
+    if (mode == 0) {
+      P.cbp_y = P.cbp_u = P.cbp_v = 0;
+    } else if (zero_block) {
+      TFOR(g, i, size * size / 4) reinterpret_cast<uint32_t *>(S.rec.y)[i] = reinterpret_cast<const uint32_t *>(S.pred.y)[i];
+      TFOR(g, i, sizeC * sizeC / 4) {
+        reinterpret_cast<uint32_t *>(S.rec.u)[i] = reinterpret_cast<const uint32_t *>(S.pred.u)[i];
+        reinterpret_cast<uint32_t *>(S.rec.v)[i] = reinterpret_cast<const uint32_t *>(S.pred.v)[i];
+      }
+      g.sync();
+      P.cbp_y = P.cbp_u = P.cbp_v = 0;
+    } else {
+      P.cbp_y = inter_plane(E, S.org.y, size, qpY, S.pred.y, S.tc.y, S.rec.y, ctype, tb_split);
+      P.cbp_u = inter_plane(E, S.org.u, sizeC, qpC, S.pred.u, S.tc.u, S.rec.u, ctype | 1, tb_split && size > 8);
+      P.cbp_v = inter_plane(E, S.org.v, sizeC, qpC, S.pred.v, S.tc.v, S.rec.v, ctype | 1, tb_split && size > 8);
+    }
+  }
+  return block_bits(g, S, F, B, P, S.tc);
+}
+
+// copy_best_parameters (enc/encode_block.c:1983-2045): the trial in S.rec / S.tc / P becomes the block's best so far
+TDN void keep_best(Enc &E, const BlockCtx &B, const Param &P, Param &best) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const int size = B.size, ny = size * size / 4, nc = ny / 4;
+  g.sync();
+  TFOR(g, i, ny) reinterpret_cast<uint32_t *>(S.best.y)[i] = reinterpret_cast<const uint32_t *>(S.rec.y)[i];
+  TFOR(g, i, nc) {
+    reinterpret_cast<uint32_t *>(S.best.u)[i] = reinterpret_cast<const uint32_t *>(S.rec.u)[i];
+    reinterpret_cast<uint32_t *>(S.best.v)[i] = reinterpret_cast<const uint32_t *>(S.rec.v)[i];
+  }
+  if (P.cbp_y) TFOR(g, i, ny * 2) reinterpret_cast<uint32_t *>(S.bc.y)[i] = reinterpret_cast<const uint32_t *>(S.tc.y)[i];
+  if (P.cbp_u) TFOR(g, i, nc * 2) reinterpret_cast<uint32_t *>(S.bc.u)[i] = reinterpret_cast<const uint32_t *>(S.tc.u)[i];
+  if (P.cbp_v) TFOR(g, i, nc * 2) reinterpret_cast<uint32_t *>(S.bc.v)[i] = reinterpret_cast<const uint32_t *>(S.tc.v)[i];
+  g.sync();
+  best = P;
+  if (P.mode == 0 || P.mode == 4) {
+    const InterPred &c = P.mode == 0 ? B.skip_cand[P.skip_idx] : B.merge_cand[P.skip_idx];
+    best.ref_idx0 = c.ref_idx0;
+    best.ref_idx1 = c.ref_idx1;
+    for (int i = 0; i < 4; i++) { best.mv0[i] = c.mv0; best.mv1[i] = c.mv1; }
+    best.dir = c.dir;
+  } else if (P.mode == 1) {
+    best.ref_idx0 = best.ref_idx1 = 0;
+    for (int i = 0; i < 4; i++) best.mv0[i] = best.mv1[i] = mkmv(0, 0);
+    best.dir = -1;
+  } else {
+    best.dir = P.mode == 2 ? 0 : 2;
+  }
+}
