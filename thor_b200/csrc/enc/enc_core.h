@@ -217,3 +217,101 @@ TDN void keep_best(Enc &E, const BlockCtx &B, const Param &P, Param &best) {
     best.dir = P.mode == 2 ? 0 : 2;
   }
 }
+
+// ---- early skip (enc/encode_block.c:2481-2785) -------------------------------------------------------------------
+// check_early_skip_transform_coeff's threshold (:2491-2492): the only floating-point step, in double as the reference
+TD int skip_threshold(int qp, int lg, double relative_threshold) {
+  const int shift2 = 21 - lg + qp / 6;
+  const double first_quantizer_level = ddiv((double)(1 << shift2), (double)kQuant[qp % 6]);
+  return (int)dmul(relative_threshold, first_quantizer_level);
+}
+
+// check_early_skip_sub_block (:2507-2543): residual of a size0 x size0 luma sub-block -> 2x2 mean -> transform(size0/2)
+// -> any |coefficient| > threshold.  org: stride ostride; pred: compact stride size0 (size0 >= 8).
+TDN int skip_test_luma(Enc &E, const uint8_t *org, int ostride, int size0, int qp, const uint8_t *pred, float thr) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const int n = size0 / 2, lg = ilog2((uint32_t)n);
+  TFOR(g, i, n * n) {
+    const int r = 2 * (i / n), c = 2 * (i % n);
+    const int s = ((int)org[r * ostride + c] - (int)pred[r * size0 + c]) + ((int)org[r * ostride + c + 1] - (int)pred[r * size0 + c + 1]) +
+                  ((int)org[(r + 1) * ostride + c] - (int)pred[(r + 1) * size0 + c]) + ((int)org[(r + 1) * ostride + c + 1] - (int)pred[(r + 1) * size0 + c + 1]);
+    S.resid[i] = (int16_t)((s + 2) >> 2);
+  }
+  g.sync();
+  forward_core(g, S, n, lg, lg + 5);
+  const int threshold = skip_threshold(qp, lg, dmul(0.5, (double)thr));
+  int sig = 0;
+  TFOR(g, i, n * n) sig |= iabs((int)S.coeff[i]) > threshold;
+  return g.any(sig);
+}
+
+// check_early_skip_sub_blockC (:2545-2610).  The 8-wide form tests every column sum as int16; every other width runs the
+// 4-wide form, which looks at the top-left 4 x 4 samples only (pairs of column sums) -- also for 16 x 16 sub-blocks.
+TDN int skip_test_chroma(Enc &E, const uint8_t *org, int ostride, int size, int qp, const uint8_t *pred, float thr) {
+  Grp &g = E.g;
+  const int threshold = skip_threshold(qp, 5, (double)thr);
+  int sig = 0;
+  if (size == 8) {
+    TFOR(g, j, 8) {
+      int sum = 0;
+      for (int i = 0; i < 8; i++) sum += (int)org[i * ostride + j] - (int)pred[i * 8 + j];
+      sig |= (int16_t)sum > (int16_t)threshold;
+    }
+  } else {
+    TFOR(g, j, 2) {
+      int sum = 0;
+      for (int i = 0; i < 4; i++)
+        sum += (int16_t)((int)org[i * ostride + 2 * j] - (int)pred[i * size + 2 * j]) + (int16_t)((int)org[i * ostride + 2 * j + 1] - (int)pred[i * size + 2 * j + 1]);
+      sig |= sum > threshold;
+    }
+  }
+  return g.any(sig);
+}
+
+// check_early_skip_block (:2613-2741): 1 = no sub-block of the candidate's prediction leaves a significant residual
+TDN int check_early_skip(Enc &E, const BlockCtx &B, const Param &P) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size, size0 = imin(size, 32), sc0 = size0 / 2;
+  const int qpY = F.qp + B.delta_qp, qpC = kChromaQp[qpY];
+  float thr = F.early_skip_thr;
+  if (F.encoder_speed > 1 && size == 64) thr = (float)dmul(1.3, (double)thr);
+  const int bip = F.enable_bipred;
+  const thor_enc_pic &r0 = ref_pic(F, P.ref_idx0);
+  const int stride_y = r0.stride_y, stride_c = r0.stride_c;
+  uint8_t *pb = S.ipred, *pb0 = S.p0.y, *pb1 = S.p1.y;             // compact sub-block predictions
+  Mv mv = P.mv0[0];
+  for (int i = 0; i < size; i += size0)
+    for (int j = 0; j < size; j += size0) {
+      const int offy = (B.ypos + i) * stride_y + B.xpos + j, offc = (B.ypos + i) / 2 * stride_c + (B.xpos + j) / 2;
+      const uint8_t *oy = S.org.y + size * i + j, *ou = S.org.u + (size / 2) * (i / 2) + j / 2, *ov = S.org.v + (size / 2) * (i / 2) + j / 2;
+      if (P.dir == 2) {
+        const thor_enc_pic &r1 = ref_pic(F, P.ref_idx1);
+        const int sign0 = r0.frame_num >= F.frame_num, sign1 = r1.frame_num >= F.frame_num;
+        inter_luma(g, S, pb0, size0, r0.y + offy, stride_y, size0, size0, clip_mv(P.mv0[0], B.ypos, B.xpos, F.width, F.height, size0, sign0), sign0, bip);
+        inter_luma(g, S, pb1, size0, r1.y + offy, stride_y, size0, size0, clip_mv(P.mv1[0], B.ypos, B.xpos, F.width, F.height, size0, sign1), sign1, bip);
+        TFOR(g, k, size0 * size0) pb[k] = (uint8_t)((pb0[k] + pb1[k]) >> 1);
+        g.sync();
+        if (skip_test_luma(E, oy, size, size0, qpY, pb, thr)) return 0;
+        // chroma of a bi-predicted candidate uses the vectors as they are (not clipped): :2683-2704
+        uint8_t *c0u = S.p0.u, *c0v = S.p0.v, *c1u = S.p1.u, *c1v = S.p1.v;
+        inter_chroma(g, c0u, c0v, sc0, r0.u + offc, r0.v + offc, stride_c, sc0, sc0, P.mv0[0], sign0);
+        inter_chroma(g, c1u, c1v, sc0, r1.u + offc, r1.v + offc, stride_c, sc0, sc0, P.mv1[0], sign1);
+        TFOR(g, k, sc0 * sc0) { c0u[k] = (uint8_t)((c0u[k] + c1u[k]) >> 1); c0v[k] = (uint8_t)((c0v[k] + c1v[k]) >> 1); }
+        g.sync();
+        if (skip_test_chroma(E, ou, size / 2, sc0, qpC, c0u, thr)) return 0;
+        if (skip_test_chroma(E, ov, size / 2, sc0, qpC, c0v, thr)) return 0;
+      } else {
+        const int sign = r0.frame_num > F.frame_num;
+        mv = clip_mv(mv, B.ypos, B.xpos, F.width, F.height, size0, sign);
+        inter_luma(g, S, pb, size0, r0.y + offy, stride_y, size0, size0, mv, sign, bip);
+        if (skip_test_luma(E, oy, size, size0, qpY, pb, thr)) return 0;
+        inter_chroma(g, S.p0.u, S.p0.v, sc0, r0.u + offc, r0.v + offc, stride_c, sc0, sc0, mv, sign);
+        if (skip_test_chroma(E, ou, size / 2, sc0, qpC, S.p0.u, thr)) return 0;
+        if (skip_test_chroma(E, ov, size / 2, sc0, qpC, S.p0.v, thr)) return 0;
+      }
+    }
+  return 1;
+}

@@ -4,23 +4,12 @@
 
 namespace thorenc {
 
-// transform() (common/transform.c:249-330) of org - pred for one size x size transform block.  The transform input is
-// formed directly: the residual itself, its f x f box sums for `fast` blocks larger than 16 (:273-293), or its 2x2 sums
-// for 64x64 (:295-307).  Output: S.coeff, the low q x q corner (q = min(size, 16)), stride q.  Ends with a barrier.
-TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, int size, int fast) {
-  int n = size, sh1 = ilog2((uint32_t)size), sh2 = sh1 + 5, f = 1;
-  if (size > 16 && fast) { n = 16; f = size / 16; sh1 = size == 64 ? 8 : 6; sh2 = 9; }
-  else if (size == 64) { n = 32; f = 2; sh1 = 7; sh2 = 10; }
+// the two matrix passes of transform() (common/transform.c:309-329) on S.resid (n x n, stride n): only the low
+// keep x keep outputs are produced (keep = min(n, 16)), each pass rounds, shifts and stores int16.  Output: S.coeff,
+// stride keep.  Ends with a barrier.
+TDN void forward_core(Grp &g, SbMem &S, int n, int sh1, int sh2) {
   const int keep = imin(n, 16);
-  int16_t *in = S.resid;
-  TFOR(g, i, n * n) {
-    const int r = i / n, c = i % n;
-    int s = 0;
-    for (int a = 0; a < f; a++)
-      for (int b = 0; b < f; b++) s += (int)org[(r * f + a) * ostride + c * f + b] - (int)pred[(r * f + a) * pstride + c * f + b];
-    in[i] = (int16_t)s;
-  }
-  g.sync();
+  const int16_t *in = S.resid;
   const int8_t *M = dct_matrix(S, n);
   TFOR(g, i, keep * n) {                                   // rows of the block -> horizontal frequency k
     const int r = i / keep, k = i % keep;
@@ -36,6 +25,24 @@ TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uin
     S.coeff[v * keep + k] = (int16_t)((acc + (1 << (sh2 - 1))) >> sh2);
   }
   g.sync();
+}
+
+// transform() (common/transform.c:249-330) of org - pred for one size x size transform block.  The transform input is
+// formed directly: the residual itself, its f x f box sums for `fast` blocks larger than 16 (:273-293), or its 2x2 sums
+// for 64x64 (:295-307).  Output: S.coeff, the low q x q corner (q = min(size, 16)), stride q.  Ends with a barrier.
+TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, int size, int fast) {
+  int n = size, sh1 = ilog2((uint32_t)size), sh2 = sh1 + 5, f = 1;
+  if (size > 16 && fast) { n = 16; f = size / 16; sh1 = size == 64 ? 8 : 6; sh2 = 9; }
+  else if (size == 64) { n = 32; f = 2; sh1 = 7; sh2 = 10; }
+  TFOR(g, i, n * n) {
+    const int r = i / n, c = i % n;
+    int s = 0;
+    for (int a = 0; a < f; a++)
+      for (int b = 0; b < f; b++) s += (int)org[(r * f + a) * ostride + c * f + b] - (int)pred[(r * f + a) * pstride + c * f + b];
+    S.resid[i] = (int16_t)s;
+  }
+  g.sync();
+  forward_core(g, S, n, sh1, sh2);
 }
 
 // quantize() (enc/encode_block.c:75-178, rdoq == 0) of S.coeff; levels go to coeffq (stride `size`, low q x q corner).
