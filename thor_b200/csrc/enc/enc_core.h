@@ -315,3 +315,118 @@ TDN int check_early_skip(Enc &E, const BlockCtx &B, const Param &P) {
     }
   return 1;
 }
+
+// ---- searches ----------------------------------------------------------------------------------------------------
+// search_intra_prediction_params (enc/encode_block.c:1230-1329): luma SAD of the intra modes in the reference's order
+// DC, HOR, VER, PLANAR [, UPLEFT, UPRIGHT, UPUPRIGHT, UPUPLEFT, UPLEFTLEFT, DOWNLEFTLEFT]; first minimum wins.
+TDN int search_intra(Enc &E, const BlockCtx &B, int num_intra_modes, int *intra_mode) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size;
+  const thor_enc_pic &rec = F.rec;
+  make_top_and_left(E, 0, rec.y + B.ypos * rec.stride_y + B.xpos, rec.stride_y, nullptr, 0, 0, 0, B.ypos, B.xpos, size,
+                    upright_available(B.ypos, B.xpos, size, F.width), downleft_available(B.ypos, B.xpos, size, F.height), 0);
+  int min_sad = 1 << 30;
+  *intra_mode = 0;
+  const int n = num_intra_modes == 4 ? 4 : 10;
+  for (int k = 0; k < n; k++) {
+    const int mode = k == 0 ? 0 : k == 1 ? 2 : k == 2 ? 3 : k == 3 ? 1 : k == 4 ? 4 : k == 5 ? 5 : k == 6 ? 6 : k == 7 ? 7 : k == 8 ? 8 : 9;
+    // the search's DC always averages left and top (:1250 tests "pos >= 0"), unlike get_intra_prediction at a picture edge
+    intra_predict(g, S, 0, 1, 1, size, S.ipred, mode);
+    int acc = 0;
+    TFOR(g, i, size * size / 4) acc += (int)sad4(reinterpret_cast<const uint32_t *>(S.org.y)[i], reinterpret_cast<const uint32_t *>(S.ipred)[i]);
+    const int sad = g.sum(acc);
+    if (sad < min_sad) { min_sad = sad; *intra_mode = mode; }
+  }
+  return min_sad;
+}
+
+// search_inter_prediction_params (enc/encode_block.c:1331-1396): one motion_estimate per prediction block of the partition
+TDN int search_inter(Enc &E, const uint8_t *org_y, const thor_enc_pic &ref, const BlockCtx &B, Mv mvc, Mv mvp, Mv *mv_arr, int part, double lambda,
+                     int sign, int ref_idx, int enable_bipred) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size, rstride = ref.stride_y;
+  const uint8_t *ref_y = ref.y + B.ypos * rstride + B.xpos;
+  const Mv *mvcand = S.mvcand[ref_idx];
+  const int ncand = E.st.mvcand_num[ref_idx];
+  Mv mv, mvp2 = mvp;
+  int sad = 0;
+  if (part == 0) {
+    sad += (int)motion_estimate(g, S, F, org_y, ref_y, size, rstride, size, size, &mv, mvc, mvp2, lambda, sign, B.xpos, B.ypos, mvcand, ncand, enable_bipred);
+    mv_arr[0] = mv_arr[1] = mv_arr[2] = mv_arr[3] = mv;
+  } else if (part == 1) {
+    for (int index = 0; index < 4; index += 2) {
+      const int py = index >> 1;
+      sad += (int)motion_estimate(g, S, F, org_y + py * (size / 2) * size, ref_y + py * (size / 2) * rstride, size, rstride, size, size / 2, &mv, mvc, mvp2,
+                                  lambda, sign, B.xpos, B.ypos, mvcand, ncand, enable_bipred);
+      mv_arr[index] = mv_arr[index + 1] = mv;
+      mvp2 = mv_arr[0];
+    }
+  } else if (part == 2) {
+    for (int index = 0; index < 2; index++) {
+      sad += (int)motion_estimate(g, S, F, org_y + index * (size / 2), ref_y + index * (size / 2), size, rstride, size / 2, size, &mv, mvc, mvp2, lambda,
+                                  sign, B.xpos, B.ypos, mvcand, ncand, enable_bipred);
+      mv_arr[index] = mv_arr[index + 2] = mv;
+      mvp2 = mv_arr[0];
+    }
+  } else {
+    for (int index = 0; index < 4; index++) {
+      const int px = index & 1, py = index >> 1;
+      sad += (int)motion_estimate(g, S, F, org_y + py * (size / 2) * size + px * (size / 2), ref_y + py * (size / 2) * rstride + px * (size / 2), size,
+                                  rstride, size / 2, size / 2, &mv, mvc, mvp2, lambda, sign, B.xpos, B.ypos, mvcand, ncand, enable_bipred);
+      mv_arr[index] = mv;
+      mvp2 = mv_arr[0];
+    }
+  }
+  return sad;
+}
+
+// search_bipred_prediction_params (enc/encode_block.c:2047-2202) with me_mode 0: iterative uni-directional search of one
+// list against the target 2*org - prediction(other list).  (The me_mode 1 search -- mv0 = -mv1 on B frames at
+// encoder_speed 0 -- is motion_estimate_bi, :1102-1215: not built, see encoder.cu's configuration check.)
+TDN void search_bipred(Enc &E, const BlockCtx &B, int part, const Mv *mv_center, Mv mvp, int *ref_idx0, int *ref_idx1, Mv *mv_arr0, Mv *mv_arr1) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size;
+  const double lambda = dsqrt(F.lambda);
+  const int num_iter = F.encoder_speed == 0 ? 2 : 1;
+  int min_ref_idx0 = (F.frame_type == 2 && F.interp_ref == 1) ? 1 : 0, min_ref_idx1 = 0;
+  Mv min0[4], min1[4], mv_all[4];
+  for (int i = 0; i < 4; i++) min0[i] = min1[i] = mvp;
+  int min_sad = 1 << 30;
+  for (int n = 0; n < num_iter; n++) {
+    const int stop = part == 0 ? 0 : 1;
+    for (int list = 1; list >= stop; list--) {
+      const Mv mv = list ? min0[0] : min1[0];
+      int ref_idx = list ? min_ref_idx0 : min_ref_idx1;
+      {
+        const thor_enc_pic &ref = ref_pic(F, ref_idx);
+        inter_yuv(g, S, F, ref, S.pred, B, list ? min0 : min1, ref.frame_num > F.rec.frame_num, 1, 1);
+      }
+      TFOR(g, i, size * size) S.org8[i] = (uint8_t)clip255(2 * (int)S.org.y[i] - (int)S.pred.y[i]);
+      g.sync();
+      int ref_start, ref_end;
+      if (F.frame_type == 1) { ref_start = 0; ref_end = F.num_ref - 1; }
+      else { ref_start = ref_end = (list ? 1 : 0) + (F.interp_ref ? 1 : 0); }
+      for (ref_idx = ref_start; ref_idx <= ref_end; ref_idx++) {
+        const thor_enc_pic &ref = ref_pic(F, ref_idx);
+        const int sign = ref.frame_num > F.rec.frame_num;
+        const Mv mvp2 = (F.frame_type == 2 && list == 1) ? mv : mvp;
+        const int sad = search_inter(E, S.org8, ref, B, mv_center[ref_idx], mvp2, mv_all, part, lambda, sign, ref_idx, 1);
+        for (int i = 0; i < 4; i++) add_mvcandidate(g, S, E.st, ref_idx, mv_all[i]);
+        if (sad < min_sad) {
+          min_sad = sad;
+          if (list) { min_ref_idx1 = ref_idx; for (int i = 0; i < 4; i++) min1[i] = mv_all[i]; }
+          else { min_ref_idx0 = ref_idx; for (int i = 0; i < 4; i++) min0[i] = mv_all[i]; }
+        }
+      }
+    }
+  }
+  *ref_idx0 = min_ref_idx0;
+  *ref_idx1 = min_ref_idx1;
+  for (int i = 0; i < 4; i++) { mv_arr0[i] = min0[i]; mv_arr1[i] = min1[i]; }
+}
