@@ -430,3 +430,137 @@ TDN void search_bipred(Enc &E, const BlockCtx &B, int part, const Mv *mv_center,
   *ref_idx1 = min_ref_idx1;
   for (int i = 0; i < 4; i++) { mv_arr0[i] = min0[i]; mv_arr1[i] = min1[i]; }
 }
+
+// ---- mode decision (enc/encode_block.c:2204-2479) ---------------------------------------------------------------
+TD void try_cost(Enc &E, const BlockCtx &B, Param &P, Param &best, uint32_t &min_cost, int width, int height, uint32_t *cost_out) {
+  const int nbits = encode_block(E, B, P);
+  const uint32_t cost = rd_cost(ssd_yuv(E.g, E.S.org, E.S.rec, B.size, width, height), nbits, E.F.lambda);
+  if (cost < min_cost) { min_cost = cost; keep_best(E, B, P, best); }
+  if (cost_out) *cost_out = cost;
+}
+TD void param_from_cand(Param &P, const InterPred &c, int idx, int mode) {
+  P.mode = mode;
+  P.skip_idx = idx;
+  P.ref_idx0 = c.ref_idx0;
+  P.ref_idx1 = c.ref_idx1;
+  for (int i = 0; i < 4; i++) { P.mv0[i] = c.mv0; P.mv1[i] = c.mv1; }
+  P.dir = c.dir;
+}
+
+TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size, speed = F.encoder_speed;
+  const double lambda = F.lambda;
+  int do_inter = 1, do_intra = 1;
+  const int rectangular = B.bwidth != size || B.bheight != size;
+  const int intra_inter_sad = speed > 0;
+  uint32_t min_cost = 1u << 31, sad_intra = 1u << 31, sad_inter;
+  Param P;
+  P.mode = 0; P.intra_mode = 0; P.skip_idx = 0; P.pb_part = 0; P.ref_idx0 = P.ref_idx1 = 0; P.dir = 0;
+  P.cbp_y = P.cbp_u = P.cbp_v = 0; P.tb_param = 0; P.tb_split = 0;
+  for (int i = 0; i < 4; i++) P.mv0[i] = P.mv1[i] = mkmv(0, 0);
+
+  if (F.frame_type != 0) {                                             // skip candidates (:2251-2279)
+    P.tb_param = 0;
+    P.pb_part = 0;
+    for (int idx = 0; idx < B.num_skip_vec; idx++) {
+      param_from_cand(P, B.skip_cand[idx], idx, 0);
+      try_cost(E, B, P, best, min_cost, B.bwidth, B.bheight, nullptr);
+    }
+  }
+  if (!rectangular && size <= 64) {
+    if (F.frame_type != 0) {
+      P.tb_param = 0;
+      for (int idx = 0; idx < B.num_merge_vec; idx++) {                // merge candidates (:2283-2304)
+        param_from_cand(P, B.merge_cand[idx], idx, 4);
+        try_cost(E, B, P, best, min_cost, size, size, nullptr);
+      }
+      int intra_mode = 0;
+      if (intra_inter_sad) {
+        sad_intra = (uint32_t)search_intra(E, B, F.num_intra_modes, &intra_mode);
+        sad_intra += (uint32_t)(int)dadd(dmul(dsqrt(lambda), 2.0), 0.5);
+      }
+      int min_idx, max_idx;
+      if (E.st.best_ref < 0 || speed < 2 || F.enable_bipred) { min_idx = 0; max_idx = F.num_ref - 1; }
+      else min_idx = max_idx = E.st.best_ref;
+      int worst_cost = 0, best_cost = (int)(1u << 31);
+      Mv mvp = mkmv(0, 0), mv_all[4][4], mv_center[THOR_ENC_MAX_REF];
+      for (int ref_idx = min_idx; ref_idx <= max_idx; ref_idx++) {     // uni-directional inter (:2319-2375)
+        const thor_enc_pic &ref = ref_pic(F, ref_idx);
+        P.ref_idx0 = P.ref_idx1 = ref_idx;
+        mvp = get_mv_pred(F, B.ypos, B.xpos, size);
+        add_mvcandidate(g, S, E.st, ref_idx, mvp);
+        B.mvp = mvp;
+        const int sign = ref.frame_num >= F.rec.frame_num;
+        mv_center[ref_idx] = mvp;
+        sad_inter = 1u << 31;
+        for (int part = 0; part < B.max_num_pb_part; part++) {
+          const uint32_t sad = (uint32_t)search_inter(E, S.org.y, ref, B, mv_center[ref_idx], mvp, mv_all[part], part, dsqrt(lambda), sign, ref_idx, F.enable_bipred);
+          for (int i = 0; i < 4; i++) add_mvcandidate(g, S, E.st, ref_idx, mv_all[part][i]);
+          mv_center[ref_idx] = mv_all[0][0];
+          sad_inter = sad_inter < sad ? sad_inter : sad;
+        }
+        if (intra_inter_sad) {
+          do_inter = sad_inter < sad_intra;
+          if (sad_inter < sad_intra) do_intra = 0;
+        }
+        if (do_inter) {
+          for (int part = 0; part < B.max_num_pb_part; part++) {
+            P.pb_part = part;
+            for (int i = 0; i < 4; i++) P.mv0[i] = P.mv1[i] = mv_all[part][i];
+            P.mode = 2;
+            for (int tb_param = speed < 1 ? -1 : 0; tb_param <= B.max_num_tb_part - 1; tb_param++) {
+              P.tb_param = tb_param;
+              uint32_t cost;
+              try_cost(E, B, P, best, min_cost, size, size, &cost);
+              worst_cost = (uint32_t)worst_cost > cost ? worst_cost : (int)cost;
+              best_cost = (uint32_t)best_cost < cost ? best_cost : (int)cost;
+            }
+          }
+        }
+      }
+      // "one reference convincingly better": the reference's best_ref_idx is never anything but 0 (:2230, :2377)
+      if (worst_cost && worst_cost * 3 > best_cost * 4) E.st.best_ref = 0;
+
+      if (F.num_ref > 1 && F.enable_bipred && do_inter) {              // bi-prediction (:2380-2427)
+        int r0, r1;
+        Mv a0[4], a1[4];
+        search_bipred(E, B, 0, mv_center, mvp, &r0, &r1, a0, a1);
+        P.mode = 3;
+        P.pb_part = 0;
+        P.ref_idx0 = r0;
+        P.ref_idx1 = r1;
+        for (int i = 0; i < 4; i++) { P.mv0[i] = a0[i]; P.mv1[i] = a1[i]; }
+        P.tb_param = 0;
+        try_cost(E, B, P, best, min_cost, size, size, nullptr);
+      }
+    }
+    if (do_intra) {                                                    // intra (:2431-2472)
+      const int max_tb_param = B.max_num_tb_part - 1;
+      int intra_mode = 0;
+      P.mode = 1;
+      if (F.intra_rdo) {
+        uint32_t min_intra_cost = 1u << 31;
+        for (int m = 0; m < F.num_intra_modes; m++) {
+          P.intra_mode = m;
+          for (int tb_param = 0; tb_param <= max_tb_param; tb_param++) {
+            P.tb_param = tb_param;
+            const int nbits = encode_block(E, B, P);
+            const uint32_t cost = rd_cost(ssd_yuv(g, S.org, S.rec, size, size, size), nbits, lambda);
+            if (cost < min_intra_cost) { min_intra_cost = cost; intra_mode = m; }
+          }
+        }
+      } else {
+        search_intra(E, B, F.num_intra_modes, &intra_mode);
+      }
+      P.intra_mode = intra_mode;
+      for (int tb_param = 0; tb_param <= max_tb_param; tb_param++) {
+        P.tb_param = tb_param;
+        try_cost(E, B, P, best, min_cost, size, size, nullptr);
+      }
+    }
+  }
+  return min_cost;
+}
