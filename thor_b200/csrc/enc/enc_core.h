@@ -564,3 +564,197 @@ TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
   }
   return min_cost;
 }
+
+// ---- the quad tree (enc/encode_block.c:2787-3033) ---------------------------------------------------------------
+// What the final encode_block + copy_block_to_frame + copy_deblock_data (:1802-1819, :1947-1981) leave behind, plus the
+// record the host's write_block needs: reconstruction -> picture, neighbour units, node, coefficients.
+TDN void finalize_block(Enc &E, const BlockCtx &B, const Param &P) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  const int size = B.size, z = zidx8(B.ypos, B.xpos);
+  g.sync();
+  {                                                                    // copy_block_to_frame
+    const thor_enc_pic &rec = F.rec;
+    const int wq = B.bwidth / 4;
+    TFOR(g, i, B.bheight * wq) {
+      const int r = i / wq, c = (i % wq) * 4;
+      *reinterpret_cast<uint32_t *>(rec.y + (B.ypos + r) * rec.stride_y + B.xpos + c) = *reinterpret_cast<const uint32_t *>(S.best.y + r * size + c);
+    }
+    const int wc = B.bwidth / 2, sc = size / 2;
+    TFOR(g, i, (B.bheight / 2) * wc) {
+      const int r = i / wc, c = i % wc, off = (B.ypos / 2 + r) * rec.stride_c + B.xpos / 2 + c;
+      rec.u[off] = S.best.u[r * sc + c];
+      rec.v[off] = S.best.v[r * sc + c];
+    }
+  }
+  const int tb_split = imax(0, P.tb_param);
+  {                                                                    // copy_deblock_data
+    const int uw = B.bwidth / 4, div = size / 8, ustride = F.width / 4;
+    TFOR(g, i, (B.bheight / 4) * uw) {
+      const int m = i / uw, n = i % uw, index = 2 * (m / div) + n / div;
+      thor_enc_unit u;
+      u.mv0x = P.mv0[index].x; u.mv0y = P.mv0[index].y; u.mv1x = P.mv1[index].x; u.mv1y = P.mv1[index].y;
+      u.mode = (uint8_t)P.mode;
+      u.size = (uint8_t)size;
+      u.cbp = tb_split ? 7 : (uint8_t)((P.cbp_y ? 1 : 0) | (P.cbp_u ? 2 : 0) | (P.cbp_v ? 4 : 0));   // :1785-1788
+      u.flags = (uint8_t)(tb_split | ((P.mode == 2 ? P.pb_part : 0) << 1));
+      u.ref_idx0 = (int8_t)P.ref_idx0; u.ref_idx1 = (int8_t)P.ref_idx1; u.dir = (int8_t)P.dir;
+      u.pad = 0;
+      st_unit(F.units + (B.ypos / 4 + m) * ustride + B.xpos / 4 + n, u);
+    }
+  }
+  if (P.mode != 0) {                                                   // coefficients where write_block reads them
+    const int ny = size * size / 2, nc = ny / 4;                       // 32-bit words
+    if (P.cbp_y) TFOR(g, i, ny) reinterpret_cast<uint32_t *>(E.coef->y + 64 * z)[i] = reinterpret_cast<const uint32_t *>(S.bc.y)[i];
+    if (P.cbp_u) TFOR(g, i, nc) reinterpret_cast<uint32_t *>(E.coef->u + 16 * z)[i] = reinterpret_cast<const uint32_t *>(S.bc.u)[i];
+    if (P.cbp_v) TFOR(g, i, nc) reinterpret_cast<uint32_t *>(E.coef->v + 16 * z)[i] = reinterpret_cast<const uint32_t *>(S.bc.v)[i];
+  }
+  if (g.tid == 0) {
+    thor_enc_node nd;
+    nd.state = THOR_NODE_CODED;
+    nd.mode = (uint8_t)P.mode; nd.intra_mode = (uint8_t)P.intra_mode; nd.skip_idx = (uint8_t)P.skip_idx; nd.pb_part = (uint8_t)P.pb_part;
+    nd.tb_param = (int8_t)P.tb_param; nd.ref_idx0 = (int8_t)P.ref_idx0; nd.ref_idx1 = (int8_t)P.ref_idx1; nd.dir = (int8_t)P.dir;
+    nd.cbp_y = (uint8_t)P.cbp_y; nd.cbp_u = (uint8_t)P.cbp_u; nd.cbp_v = (uint8_t)P.cbp_v;
+    nd.delta_qp = (int8_t)B.delta_qp;
+    nd.num_skip_vec = (uint8_t)B.num_skip_vec; nd.num_merge_vec = (uint8_t)B.num_merge_vec;
+    nd.ctx_index = (int8_t)B.ctx_index; nd.ctx_cbp = (int8_t)B.ctx_cbp;
+    nd.split_early = 0; nd.pad[0] = nd.pad[1] = 0;
+    nd.mvp[0] = B.mvp.x; nd.mvp[1] = B.mvp.y;
+    for (int i = 0; i < 4; i++) { nd.mv0[i][0] = P.mv0[i].x; nd.mv0[i][1] = P.mv0[i].y; nd.mv1[i][0] = P.mv1[i].x; nd.mv1[i][1] = P.mv1[i].y; }
+    E.nodes[node_index(size, B.ypos, B.xpos)] = nd;
+  }
+  g.sync();
+}
+
+TD void mark_split(Enc &E, const BlockCtx &B) {
+  if (E.g.tid == 0) {
+    thor_enc_node &nd = E.nodes[node_index(B.size, B.ypos, B.xpos)];
+    nd.state = THOR_NODE_SPLIT;
+    nd.ctx_index = (int8_t)B.ctx_index;
+    nd.delta_qp = (int8_t)B.delta_qp;
+  }
+}
+
+template <int SIZE>
+TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  const thor_enc_frame &F = E.F;
+  if (ypos >= F.height || xpos >= F.width) return 0;
+  const int encode_this_size = ypos + SIZE <= F.height && xpos + SIZE <= F.width;
+  const int encode_smaller_size = SIZE > 8 * ((encode_this_size && F.frame_type != 0 && F.encoder_speed > 0) ? 2 : 1);
+  const int top_down = !encode_smaller_size && SIZE > 8;
+  const int encode_rectangular_size = !encode_this_size && F.frame_type != 0;
+  if (!encode_this_size && !encode_smaller_size) return 0;
+  uint32_t cost_small = 1u << 28, cost = 1u << 28;
+
+  BlockCtx B;
+  B.size = SIZE; B.ypos = ypos; B.xpos = xpos;
+  B.bwidth = imin(SIZE, F.width - xpos);
+  B.bheight = imin(SIZE, F.height - ypos);
+  B.max_num_tb_part = F.enable_tb_split == 1 ? 2 : 1;
+  B.max_num_pb_part = F.enable_pb_split ? 4 : 1;
+  B.delta_qp = qp - F.qp;
+  B.mvp = mkmv(0, 0);
+  B.num_skip_vec = B.num_merge_vec = 0;
+  find_block_contexts(F, ypos, xpos, SIZE, B);
+  if (F.frame_type != 0) {
+    B.num_skip_vec = get_mv_skip(F, ypos, xpos, SIZE, B.skip_cand);
+    B.num_merge_vec = get_mv_skip(F, ypos, xpos, SIZE, B.merge_cand);  // get_mv_merge is the same function under LIMITED_SKIP
+  }
+  Param best;
+  best.mode = 0; best.intra_mode = 0; best.skip_idx = 0; best.pb_part = 0; best.ref_idx0 = best.ref_idx1 = 0; best.dir = 0;
+  best.cbp_y = best.cbp_u = best.cbp_v = 0; best.tb_param = 0; best.tb_split = 0;
+  for (int i = 0; i < 4; i++) best.mv0[i] = best.mv1[i] = mkmv(0, 0);
+
+  if (encode_this_size && F.frame_type != 0 && F.early_skip_thr > 0.0f) {
+    // search_early_skip_candidates (:2743-2783)
+    load_org(E, B);
+    uint32_t min_cost = 1u << 31;
+    int early = 0;
+    Param P = best;
+    for (int idx = 0; idx < B.num_skip_vec; idx++) {
+      param_from_cand(P, B.skip_cand[idx], idx, 0);
+      P.tb_param = 0;
+      if (check_early_skip(E, B, P)) {
+        early = 1;
+        try_cost(E, B, P, best, min_cost, SIZE, SIZE, nullptr);
+      }
+    }
+    if (early) {
+      finalize_block(E, B, best);
+      return (int)min_cost;
+    }
+  }
+
+  if (encode_smaller_size) {
+    mark_split(E, B);
+    if constexpr (SIZE > 8) {
+      constexpr int NS = SIZE / 2;
+      cost_small = 0;
+      cost_small += (uint32_t)process_block<NS>(E, ypos, xpos, qp);
+      cost_small += (uint32_t)process_block<NS>(E, ypos + NS, xpos, qp);
+      cost_small += (uint32_t)process_block<NS>(E, ypos, xpos + NS, qp);
+      cost_small += (uint32_t)process_block<NS>(E, ypos + NS, xpos + NS, qp);
+    }
+  }
+
+  if (encode_this_size) {
+    load_org(E, B);
+    cost = mode_decision(E, B, best);
+    const int me_threshold = SIZE * SIZE * kIq8x8[qp] / 8;
+    bool kept = false;
+    if (top_down && cost > (uint32_t)me_threshold) {
+      if constexpr (SIZE == 16) {
+        // the decision of this block waits while its four children are tried
+        g.sync();
+        TFOR(g, i, 256) { S.keep_y[i] = S.best.y[i]; S.keep_cy[i] = S.bc.y[i]; }
+        TFOR(g, i, 64) { S.keep_u[i] = S.best.u[i]; S.keep_v[i] = S.best.v[i]; S.keep_cu[i] = S.bc.u[i]; S.keep_cv[i] = S.bc.v[i]; }
+        g.sync();
+        kept = true;
+        cost_small = 0;
+        cost_small += (uint32_t)process_block<8>(E, ypos, xpos, qp);
+        cost_small += (uint32_t)process_block<8>(E, ypos + 8, xpos, qp);
+        cost_small += (uint32_t)process_block<8>(E, ypos, xpos + 8, qp);
+        cost_small += (uint32_t)process_block<8>(E, ypos + 8, xpos + 8, qp);
+      }
+    }
+    if (cost <= cost_small) {
+      if (kept) {
+        g.sync();
+        TFOR(g, i, 256) { S.best.y[i] = S.keep_y[i]; S.bc.y[i] = S.keep_cy[i]; }
+        TFOR(g, i, 64) { S.best.u[i] = S.keep_u[i]; S.best.v[i] = S.keep_v[i]; S.bc.u[i] = S.keep_cu[i]; S.bc.v[i] = S.keep_cv[i]; }
+        g.sync();
+      }
+      finalize_block(E, B, best);
+    } else {
+      mark_split(E, B);
+    }
+  } else if (encode_rectangular_size) {
+    load_org(E, B);
+    cost = mode_decision(E, B, best);
+    if (cost <= cost_small) finalize_block(E, B, best);
+  }
+  return (int)(cost < cost_small ? cost : cost_small);
+}
+
+// one superblock of encode_frame's loop (enc/encode_frame.c:112-148), including the per-superblock delta-qp search
+TDN void encode_superblock(Enc &E) {
+  const thor_enc_frame &F = E.F;
+  for (int r = 0; r < THOR_ENC_MAX_REF; r++) { E.st.mvcand_num[r] = 0; E.st.mvcand_mask[r] = 0; }
+  E.st.best_ref = -1;
+  const int qp = F.qp;
+  if (F.max_delta_qp) {
+    int min_cost = 1 << 30, best_qp = qp;
+    for (int qp0 = qp - F.max_delta_qp; qp0 <= qp + F.max_delta_qp; qp0 += F.delta_qp_step) {
+      const int cost = process_block<64>(E, E.sb_y, E.sb_x, qp0);
+      if (cost < min_cost) { min_cost = cost; best_qp = qp0; }
+    }
+    process_block<64>(E, E.sb_y, E.sb_x, best_qp);
+  } else {
+    process_block<64>(E, E.sb_y, E.sb_x, qp);
+  }
+}
+
+}  // namespace thorenc
