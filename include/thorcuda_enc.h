@@ -5,9 +5,13 @@
  * node of the 64/32/16/8 quad tree either "split", or one coded block with the parameters write_block()
  * (enc/write_bits.c:364-650) needs.  The host then only runs the reference's own write_super_mode / write_block on these
  * records (the entropy coder is out of scope). */
-#ifndef THOR_ENC_ABI_H
-#define THOR_ENC_ABI_H
+#ifndef THORCUDA_ENC_H
+#define THORCUDA_ENC_H
 #include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
 
 #define THOR_ENC_MAX_REF 6           /* references a frame can address (max_num_ref <= 4, + the interpolated picture) */
 #define THOR_ENC_NODES 85            /* 1 + 4 + 16 + 64 nodes of a superblock's quad tree                              */
@@ -80,4 +84,34 @@ typedef struct {
   int32_t       *progress;           /* per superblock row: superblocks finished (wavefront hand-over), zeroed        */
 } thor_enc_frame;
 
+/* ------------------------------------------------------------------ entry point ---- */
+/* The frame as the caller of the library describes it: pictures by handle (thorcuda.h), everything else as above. */
+typedef struct {
+  int32_t width, height, frame_type, qp, num_ref, interp_ref, num_intra_modes, frame_num;
+  int32_t encoder_speed, enable_bipred, enable_tb_split, enable_pb_split, intra_rdo, max_delta_qp, delta_qp_step,
+          use_block_contexts;
+  float   early_skip_thr;
+  int32_t reserved0;
+  double  lambda;
+  int32_t orig, rec;                    /* thorcuda_pic handles; rec is unpadded                                    */
+  int32_t ref[THOR_ENC_MAX_REF];        /* padded reference pictures (96 / 48), borders valid                       */
+  int32_t ref_frame_num[THOR_ENC_MAX_REF];  /* yuv_frame_t.frame_num of each: the sign of a vector depends on it    */
+} thorcuda_enc_params;
+
+/* Replaces the superblock loop of encode_frame (enc/encode_frame.c:112-148): every superblock's process_block
+ * (enc/encode_block.c:2787-3033) with the searches, trial encodes and rate-distortion decisions it drives runs on the
+ * device, superblock rows as a wavefront (a superblock starts when its left neighbour and the one above-right are done).
+ * On return the work is QUEUED on the library stream:
+ *   - picture `rec` holds the unfiltered reconstruction and carries the frame's side information (as after
+ *     thorcuda_blockinfo_upload): thorcuda_loopfilter_frame can follow directly;
+ *   - host_nodes (nsb * THOR_ENC_NODES) and host_coef (nsb), nsb = ceil(w/64) * ceil(h/64) superblocks in raster order,
+ *     receive the decisions; they are valid after thorcuda_sync().  Page-locked memory (thorcuda_host_alloc) is DMA'd
+ *     directly.
+ * Configurations outside what the device code implements are an error, not a fallback (thorcuda_last_error): sync 1,
+ * rdoq 1, and encoder_speed 0 on B frames (the simultaneous bi-prediction search motion_estimate_bi). */
+int thorcuda_enc_frame(const thorcuda_enc_params *p, thor_enc_node *host_nodes, thor_enc_coef *host_coef);
+
+#ifdef __cplusplus
+}
+#endif
 #endif

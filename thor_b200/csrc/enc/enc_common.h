@@ -11,7 +11,7 @@
 // libthorcuda never contains it and has no CPU path.
 #pragma once
 #include <stdint.h>
-#include "enc_abi.h"
+#include "../../../include/thorcuda_enc.h"
 
 #ifdef THOR_HOSTEMU
 #include <math.h>
