@@ -7,7 +7,10 @@ usage: apply_hooks.py tail  <reference>/dec/decode_frame.c <out.c>     frame tai
        apply_hooks.py recon <reference>/dec/decode_frame.c <out.c>     + device-resident reconstruction (2.3)
        apply_hooks.py block <reference>/dec/decode_block.c <out.c>     the block-level call sites of 2.3
        apply_hooks.py enc   <reference>/enc/encode_frame.c <out.c>     frame tail of the encoder (2.2)
-       apply_hooks.py main  <reference>/dec/maindec.c <out.c>          output writes of the pipelined decoder (2.3)"""
+       apply_hooks.py main  <reference>/dec/maindec.c <out.c>          output writes of the pipelined decoder (2.3)
+       apply_hooks.py encgpu <reference>/enc/encode_frame.c <out.c>    the whole frame encoder on the device (2.4)
+       apply_hooks.py encemu <reference>/enc/encode_frame.c <out.c>    superblock loop only (host emulation, tests)
+       apply_hooks.py mainenc <reference>/enc/mainenc.c <out.c>        interpolated references of the encoder (2.4)"""
 import re
 import sys
 
@@ -77,6 +80,54 @@ if mode == "enc":
     c = "create_reference_frame(encoder_info->ref[0],encoder_info->rec);"
     i = once_e(src, c)
     src = src[:i] + "thorcuda_enc_make_reference(encoder_info->ref[0],encoder_info->rec);" + src[i + len(c):]
+    open(sys.argv[2], "w").write(src)
+    raise SystemExit(0)
+
+
+if mode in ("encgpu", "encemu"):
+    # enc/encode_frame.c: the superblock loop (:112-148) becomes one call; encgpu also takes the frame tail
+    def once_g(text, needle):
+        if text.count(needle) != 1:
+            raise SystemExit(f"apply_hooks: expected exactly one {needle!r} in {sys.argv[1]}")
+        return text.index(needle)
+    inc = "extern int chroma_qp[52];\n"
+    i = once_g(src, inc) + len(inc)
+    src = (src[:i] + "void thorcuda_enc_superblocks(encoder_info_t *encoder_info);\n"
+           "void thorcuda_enc_tail(encoder_info_t *encoder_info, stream_t *stream, int qp);\n"
+           "void thorcuda_enc_make_reference(yuv_frame_t *ref, yuv_frame_t *rec);\n" + src[i:])
+    a = once_g(src, "for (k=0;k<num_sb_ver;k++){")
+    b = once_g(src, "if (encoder_info->params->deblocking){")
+    body = src[a:b]
+    for fn in ("process_block(encoder_info,MAX_BLOCK_SIZE,yposY,xposY,qp);", "frame_info->best_ref = -1;", "write_stream_pos(stream,&stream_pos_ref);"):
+        if fn not in body:
+            raise SystemExit(f"apply_hooks: {fn} not inside the superblock loop")
+    src = src[:a] + "(void)k; (void)l; (void)num_sb_hor; (void)num_sb_ver;\n  thorcuda_enc_superblocks(encoder_info);\n\n  " + src[b:]
+    if mode == "encgpu":
+        a = once_g(src, "if (encoder_info->params->deblocking){")
+        b = once_g(src, "/* Sliding window operation")
+        for fn in ("deblock_frame_y(", "deblock_frame_uv(", "clpf_frame(", "putbits(1, !sb_signal, stream);"):
+            if fn not in src[a:b]:
+                raise SystemExit(f"apply_hooks: {fn} not where expected")
+        src = src[:a] + "thorcuda_enc_tail(encoder_info, stream, qp);\n\n  " + src[b:]
+        c = "create_reference_frame(encoder_info->ref[0],encoder_info->rec);"
+        i = once_g(src, c)
+        src = src[:i] + "thorcuda_enc_make_reference(encoder_info->ref[0],encoder_info->rec);" + src[i + len(c):]
+    open(sys.argv[2], "w").write(src)
+    raise SystemExit(0)
+
+if mode == "mainenc":
+    # enc/mainenc.c: interpolate_frames + pad_yuv_frame of the interpolated reference (:328-329, :385-386) on the device
+    pat = re.compile(r"interpolate_frames\(encoder_info\.interp_frames\[0\], ref1, ref2, ([^;]*?)\);\s*pad_yuv_frame\(encoder_info\.interp_frames\[0\]\);")
+    m = pat.findall(src)
+    if len(m) != 2:
+        raise SystemExit(f"apply_hooks: expected two interpolate_frames call sites in mainenc.c, found {len(m)}")
+    src = pat.sub(lambda mm: "thorcuda_enc_interpolate(encoder_info.interp_frames[0], ref1, ref2, " + mm.group(1) + ");", src)
+    anchor = "int main(int argc, char **argv)"
+    if src.count(anchor) != 1:
+        anchor = "int main(int argc, char** argv)"
+    if src.count(anchor) != 1:
+        raise SystemExit("apply_hooks: main() not found in mainenc.c")
+    src = src.replace(anchor, "void thorcuda_enc_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos);\n" + anchor)
     open(sys.argv[2], "w").write(src)
     raise SystemExit(0)
 
