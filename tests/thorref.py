@@ -267,6 +267,31 @@ def write_clip(path, width, height, frames, seed):
                 f.write(np.ascontiguousarray(p).tobytes())
 
 
+def write_hard_clip(path, width, height, frames, seed, noise=3.0):
+    """Seeded I420 clip that makes an encoder work: a contrast-stretched texture translating by (1, 2) per frame, a second
+    layer drifting the other way under the right half (no single vector predicts the blend), a patch of a quarter of the
+    picture moving on its own by (5, 13), sensor noise, slow chroma waves.  Any size (multiples of 8)."""
+    rng = np.random.default_rng(seed)
+    big = rng.integers(0, 256, (height + 96, width + 96)).astype(np.float32)
+    for ax in (0, 1):
+        c = np.cumsum(np.pad(big, [(3, 2) if a == ax else (0, 0) for a in (0, 1)], mode="edge"), axis=ax)
+        big = (np.take(c, range(5, c.shape[ax]), axis=ax) - np.take(c, range(0, c.shape[ax] - 5), axis=ax)) / 5
+    big = np.clip((big - 128) * 3 + 128, 0, 255)
+    ph, pw = max(16, height // 4 // 8 * 8), max(16, width // 4 // 8 * 8)
+    yy, xx = np.mgrid[0:height // 2, 0:width // 2]
+    with open(path, "wb") as f:
+        for n in range(frames):
+            dy, dx = n % 64, (2 * n) % 64
+            y = big[32 + dy:32 + dy + height, 32 + dx:32 + dx + width].copy()
+            ey, ex = (3 * n) % 64, 63 - n % 64
+            y[:, width // 2:] = 0.5 * y[:, width // 2:] + 0.5 * big[32 + ey:32 + ey + height, 32 + ex:32 + ex + width][::-1, width // 2:]
+            oy, ox = (5 * n) % (height - ph), (13 * n) % (width - pw)
+            y[oy:oy + ph, ox:ox + pw] = big[:ph, :pw][::-1, ::-1]
+            f.write(np.clip(y + rng.normal(0, noise, y.shape), 0, 255).astype(np.uint8).tobytes())
+            f.write((128 + 60 * np.sin((xx + 2 * n) / 23.0) * np.cos(yy / 29.0)).astype(np.uint8).tobytes())
+            f.write((128 + 60 * np.cos(xx / 27.0) * np.sin((yy + n) / 25.0)).astype(np.uint8).tobytes())
+
+
 def run_thorenc(exe, cfg, yuv, width, height, frames, qp, out_prefix, timeout=600):
     """Run a Thorenc binary of oracle/_ref; returns (bitstream bytes, reconstruction bytes, seconds)."""
     import time
