@@ -10,7 +10,7 @@ LIB       := thor_b200/libthorcuda.so
 .PHONY: all oracle clean
 all: $(LIB)
 
-build/%.o: $(CSRC)/%.cu $(CSRC)/internal.cuh $(CSRC)/lists.cuh include/thorcuda.h include/thorcuda_compat.h | build
+build/%.o: $(CSRC)/%.cu $(CSRC)/internal.cuh $(CSRC)/lists.cuh include/thorcuda.h include/thorcuda_compat.h include/thorcuda_enc.h $(wildcard $(CSRC)/enc/*.h) | build
 	$(NVCC) $(NVCCFLAGS) -c -o $@ $< 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; false)
 
 $(LIB): $(OBJS)

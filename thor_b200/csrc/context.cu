@@ -213,6 +213,7 @@ void thorcuda_shutdown(void) {
   compat_reset();
   interp_reset();
   bits_reset();
+  enc_reset();
   for (int i = 0; i < 256; i++) if (c.lists[i].used) thorcuda_list_destroy(i);
   for (int i = 0; i < THORCUDA_MAX_PICS; i++) if (c.pics[i].used) thorcuda_pic_destroy(i);
   DevBuf *bufs[] = {&c.raw_info, &c.scratch, &c.flush, &c.lfjobs, &c.sadjobs, &c.centres};

@@ -137,6 +137,7 @@ int tb_raw(int size, int fast, int inverse, const int16_t *d_in, int16_t *d_out)
 void compat_reset();   // compat.cu: drop the per-block API's scratch pictures (thorcuda_shutdown)
 void interp_reset();   // tinterp.cu: drop the interpolation scratch (thorcuda_shutdown)
 void bits_reset();     // bits.cu: the scan tables are uploaded again after a shutdown
+void enc_reset();      // encoder.cu: the frame encoder's device buffers
 
 #define THOR_CUDA(call)                                                                   \
   do {                                                                                    \
