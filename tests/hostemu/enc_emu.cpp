@@ -13,11 +13,12 @@ extern "C" void thor_emu_encode_frame(const thor_enc_frame *F) {
   using namespace thorenc;
   static SbMem S;
   Grp g;
+  S.frame = *F;
   build_tables(g, S);
   const int nsbx = (F->width + 63) / 64, nsby = (F->height + 63) / 64;
   for (int k = 0; k < nsby; k++)
     for (int l = 0; l < nsbx; l++) {
-      Enc E{g, S, *F, SbState(), F->nodes + (size_t)(k * nsbx + l) * THOR_ENC_NODES, F->coef + (k * nsbx + l), l * 64, k * 64};
+      Enc E{g, S, S.frame, SbState(), F->nodes + (size_t)(k * nsbx + l) * THOR_ENC_NODES, F->coef + (k * nsbx + l), l * 64, k * 64};
       encode_superblock(E);
     }
 }

@@ -27,9 +27,22 @@
 #define TCONST __device__ const
 #endif
 
+// every array the superblock encoder works on lives in shared memory; the device functions are not inlined, so each
+// one tells the compiler (LDS / STS with immediate offsets instead of generic loads through a converted address)
+#ifdef THOR_HOSTEMU
+#define THOR_SHARED(p) ((void)0)
+#define THOR_LOCAL(p) ((void)0)
+#else
+#define THOR_SHARED(p) __builtin_assume(__isShared(p))
+#define THOR_LOCAL(p) __builtin_assume(__isLocal(p))      // per-thread state handed down by reference (stack)
+#endif
+
 namespace thorenc {
 
-constexpr int NT = 256;              // threads per CTA (one CTA encodes one superblock)
+#ifndef THOR_ENC_NT
+#define THOR_ENC_NT 256
+#endif
+constexpr int NT = THOR_ENC_NT;      // threads per CTA (one CTA walks one superblock row)
 constexpr int NW = NT / 32;
 
 // ---- the cooperating thread group ------------------------------------------------------------------------------
@@ -51,6 +64,7 @@ struct Grp {
   __device__ int sum(int v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    THOR_SHARED(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = v;
     __syncthreads();
@@ -65,6 +79,7 @@ struct Grp {
     for (int k = 0; k < K; k++)
 #pragma unroll
       for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    THOR_SHARED(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0)
 #pragma unroll
@@ -82,6 +97,7 @@ struct Grp {
   __device__ int vmax(int v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    THOR_SHARED(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = v;
     __syncthreads();

@@ -8,6 +8,8 @@ namespace thorenc {
 // as) against ref + off[k] (reference picture, stride bs).  Results in S.acc[0..K).  Ends with a barrier.
 // `wide`: each candidate is widesad_calc's five positions x + {-3,-1,0,1,3} (:757-780); results in S.acc[5k .. 5k+5).
 TDN void sad_batch(Grp &g, SbMem &S, const uint8_t *a, int as, const uint8_t *ref, int bs, const int *off, int K, int width, int height, int wide) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(a);
   const int per = wide ? 5 : 1, wq = width >> 2, items = height * wq;
   g.sync();                                                // readers of the previous batch's results are done
   TFOR(g, i, K * per) S.acc[i] = 0;
@@ -44,6 +46,7 @@ TDN void sad_batch(Grp &g, SbMem &S, const uint8_t *a, int as, const uint8_t *re
 // the minimum of widesad_calc: first minimum in the order -3,-1,0,1,3 (enc/encode_block.c:764-776 = the packed minimum of
 // enc/enc_kernels.c:94-97)
 TD unsigned widesad_pick(const int *acc5, int *x) {
+  THOR_SHARED(acc5);
   unsigned best = 1u << 31;
   int bx = 0;
   for (int k = 0; k < 5; k++) {
@@ -59,6 +62,8 @@ TD int dnavg(int a, int b) { return (a + b) >> 1; }
 
 // sad_calc_fasthalf (enc/encode_block.c:497-605): eight bilinear half-pel candidates around the integer position b.
 TDN unsigned sad_fasthalf(Grp &g, const uint8_t *a, int as, const uint8_t *b, int bs, int width, int height, int *x, int *y) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(a);
   int s[8] = {0, 0, 0, 0, 0, 0, 0, 0};                     // top down left right tl tr bl br
   TFOR(g, i, width * height) {
     const int r = i / width, c = i % width;
@@ -117,6 +122,8 @@ TDN unsigned sad_fasthalf(Grp &g, const uint8_t *a, int as, const uint8_t *b, in
 // sad_calc_fastquarter (enc/encode_block.c:609-738): eight quarter-pel candidates; the incoming (*x, *y) select one of
 // four formula sets.
 TDN unsigned sad_fastquarter(Grp &g, const uint8_t *o, int os, const uint8_t *rf, int rs, int width, int height, int *x, int *y) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(o);
   const int sel = (*x & *y) ? 0 : (*x ? 1 : (*y ? 2 : 3));
   int s[8] = {0, 0, 0, 0, 0, 0, 0, 0};                     // tl top tr left right bl down br
   TFOR(g, i, width * height) {
@@ -154,6 +161,8 @@ TD unsigned mv_cost(double lambda, Mv mv, Mv mvp) { return (unsigned)dadd(dmul(l
 
 // add_mvcandidate (enc/encode_block.c:58-73)
 TD void add_mvcandidate(Grp &g, SbMem &S, SbState &st, int ref_idx, Mv mv) {
+  THOR_LOCAL(&st); THOR_LOCAL(&g);
+  THOR_SHARED(&S);
   const Mv imv = mkmv((mv.x + 2) >> 2, (mv.y + 2) >> 2);
   const uint64_t m = (uint64_t)1 << ((((int)imv.y << 3) ^ (int)imv.x) & 63);
   if (!(m & st.mvcand_mask[ref_idx])) {
@@ -170,6 +179,8 @@ TD void add_mvcandidate(Grp &g, SbMem &S, SbState &st, int ref_idx, Mv mv) {
 TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const uint8_t *orig, const uint8_t *ref, int size, int stride_r, int width,
                              int height, Mv *mv_out, Mv mvc, Mv mvp, double lambda, int sign, int xpos, int ypos, const Mv *mvcand, int mvcand_num,
                              int enable_bipred) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(orig); THOR_SHARED(mvcand); THOR_SHARED(&F);
   const int s = sign ? -1 : 1, speed = F.encoder_speed, fw = F.width, fh = F.height;
   unsigned min_sad = 1u << 31, sad;
   Mv mv_opt = mkmv(0, 0), mv_ref = mkmv(((mvc.x + 2) >> 2) << 2, ((mvc.y + 2) >> 2) << 2), cand;

@@ -20,6 +20,8 @@ TD Mv clip_mv(Mv mv, int ypos, int xpos, int fwidth, int fheight, int size, int 
 // Writes width x height samples at dst (shared, stride pstride, 4-byte aligned rows).  Uses S.itmp.  Ends with a barrier.
 TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *ref, int stride, int width, int height, Mv mv, int sign,
                     int bipred) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(dst);
   const int mx = sign ? -mv.x : mv.x, my = sign ? -mv.y : mv.y;
   const int fx = mx & 3, fy = my & 3;
   const uint8_t *src = ref + (my >> 2) * stride + (mx >> 2);
@@ -95,6 +97,8 @@ TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *
 // width, height: chroma size (>= 2).  Ends with a barrier.
 TDN void inter_chroma(Grp &g, uint8_t *dst_u, uint8_t *dst_v, int pstride, const uint8_t *ref_u, const uint8_t *ref_v, int stride, int width,
                       int height, Mv mv, int sign) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(dst_u); THOR_SHARED(dst_v);
   const int mx = sign ? -mv.x : mv.x, my = sign ? -mv.y : mv.y;
   const int fx = mx & 7, fy = my & 7;
   const int off = (my >> 3) * stride + (mx >> 3);
@@ -129,6 +133,9 @@ TDN void inter_chroma(Grp &g, uint8_t *dst_u, uint8_t *dst_v, int pstride, const
 // `split` is the reference's argument (0: one vector for the block; 1: one per quadrant).
 TDN void inter_yuv(Grp &g, SbMem &S, const thor_enc_frame &F, const thor_enc_pic &ref, Blk &dst, const BlockCtx &B, const Mv *mv_arr, int sign,
                    int bipred, int split) {
+  THOR_SHARED(&dst);
+  THOR_LOCAL(&B); THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(&F);
   const int div = split + 1, bwidth = B.bwidth / div, bheight = B.bheight / div, pstride = B.size;
   const int yC = B.ypos / 2, xC = B.xpos / 2;
   const uint8_t *ref_y = ref.y + B.ypos * ref.stride_y + B.xpos;
@@ -153,6 +160,8 @@ TDN void inter_yuv(Grp &g, SbMem &S, const thor_enc_frame &F, const thor_enc_pic
 
 // average_blocks_all (enc/encode_block.c:1569-1588): truncating mean of two predictions
 TDN void average_blocks(Grp &g, Blk &dst, const Blk &a, const Blk &b, const BlockCtx &B) {
+  THOR_SHARED(&dst); THOR_SHARED(&a); THOR_SHARED(&b);
+  THOR_LOCAL(&B); THOR_LOCAL(&g);
   const int size = B.size, wq = B.bwidth / 4, ny = B.bheight * wq;
   TFOR(g, i, ny) {
     const int o = (i / wq) * size + (i % wq) * 4;
@@ -171,6 +180,8 @@ TDN void average_blocks(Grp &g, Blk &dst, const Blk &a, const Blk &b, const Bloc
 // make_top_and_left for the non-split case (:72-99): neighbours of the size x size block at (x, y) of plane `pl` from the
 // reconstructed picture.  top/left hold 2*size samples.  Ends with a barrier.
 TDN void intra_neighbours(Grp &g, SbMem &S, const uint8_t *rec, int stride, int x, int y, int size, int upright, int downleft, int pl) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S);
   uint8_t *top = S.top[pl], *left = S.left[pl];
   const int toplen = upright ? size + 1 : size, leftlen = downleft ? size + 1 : size;
   const uint8_t *p = rec + y * stride + x;
@@ -190,12 +201,16 @@ TDN void intra_neighbours(Grp &g, SbMem &S, const uint8_t *rec, int stride, int 
 
 // [1 2 1] / 4 with the end samples repeated (:39-48)
 TD void smooth121(Grp &g, const uint8_t *in, uint8_t *out, int len) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(in); THOR_SHARED(out);
   TFOR(g, j, len) out[j] = (uint8_t)((in[imax(j - 1, 0)] + 2 * in[j] + in[imin(j + 1, len - 1)] + 2) >> 2);
 }
 
 // get_intra_prediction (:363-389) with the ten mode functions (:145-361); pblock: size x size, stride size.
 // Ends with a barrier.
 TDN void intra_predict(Grp &g, SbMem &S, int pl, int ypos, int xpos, int size, uint8_t *pblock, int mode) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(pblock);
   const uint8_t *top = S.top[pl], *left = S.left[pl];
   const int top_left = S.topleft[pl];
   const int n = size * size, sh = ilog2((uint32_t)size);
@@ -274,6 +289,7 @@ TDN void intra_predict(Grp &g, SbMem &S, int pl, int ypos, int xpos, int size, u
     }
     default: {                                                     // MODE_DC: the available side counts twice at a picture edge
       const uint8_t *a = xpos != 0 ? left : top, *b = ypos != 0 ? top : left;
+      THOR_SHARED(a); THOR_SHARED(b);
       int sum = 0;
       for (int j = 0; j < size; j++) sum += a[j] + b[j];           // uniform: every thread adds the same samples
       const int dc = (sum + size) / (2 * size);

@@ -29,6 +29,7 @@ struct BlockCtx {
 };
 
 struct SbMem {
+  thor_enc_frame frame;              // the frame description: copied from the kernel parameters once per CTA
   Blk org, rec, best, pred, p0, p1;
   Coef tc, bc;                       // coefficients of the trial / of the best trial so far
   int16_t resid[4096];               // transform input of the current transform block (stride = its size)
@@ -69,6 +70,8 @@ TD const int8_t *dct_matrix(const SbMem &S, int n) { return S.dct + (n == 32 ? 0
 TD const uint8_t *zigzag(const SbMem &S, int q) { return S.zz + (q == 4 ? 0 : q == 8 ? 16 : 80); }
 
 TDN void build_tables(Grp &g, SbMem &S) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S);
   // M_N[k][n] = C[(2n+1) * k * 32/N] with the symmetries of cos(pi a / 64): common/transform.c:41-245 (g1..g4mat_hevc)
   TFOR(g, i, 1360) {
     int N, base;
@@ -127,6 +130,7 @@ TD InterPred zero_pred() {
 
 // get_mv_pred (common/inter_prediction.c:182-294): median of three neighbour vectors chosen by availability
 TDN Mv get_mv_pred(const thor_enc_frame &F, int ypos, int xpos, int size) {
+  THOR_SHARED(&F);
   const int bs = size / 4, stride = F.width / 4, idx = (ypos / 4) * stride + xpos / 4;
   const int up0 = idx - stride, up1 = idx - stride + (bs - 1) / 2, up2 = idx - stride + bs - 1;
   const int left0 = idx - 1, left1 = idx + stride * ((bs - 1) / 2) - 1, left2 = idx + stride * (bs - 1) - 1;
@@ -151,6 +155,7 @@ TDN Mv get_mv_pred(const thor_enc_frame &F, int ypos, int xpos, int size) {
 
 // get_mv_skip / get_mv_merge (common/inter_prediction.c:296-600 with LIMITED_SKIP: the two functions are the same)
 TDN int get_mv_skip(const thor_enc_frame &F, int ypos, int xpos, int size, InterPred *cand) {
+  THOR_SHARED(&F);
   const int bs = size / 4, stride = F.width / 4, idx = (ypos / 4) * stride + xpos / 4;
   const int up0 = idx - stride, left0 = idx - 1, upright = idx - stride + bs;
   int up2 = idx - stride + bs - 1, left2 = idx + stride * (bs - 1) - 1;
@@ -169,6 +174,7 @@ TDN int get_mv_skip(const thor_enc_frame &F, int ypos, int xpos, int size, Inter
 
 // find_block_contexts (common/common_block.c:158-178)
 TD void find_block_contexts(const thor_enc_frame &F, int ypos, int xpos, int size, BlockCtx &B) {
+  THOR_LOCAL(&B);
   if (ypos >= 8 && xpos >= 8 && ypos + size < F.height && xpos + size < F.width && F.use_block_contexts && size <= 64) {
     const int bs = F.width / 4, bindex = (ypos / 4) * bs + xpos / 4;
     const thor_enc_unit up = ld_unit(F.units + bindex - bs), lf = ld_unit(F.units + bindex - 1);
@@ -218,6 +224,7 @@ TD int find_code(int run, int level, int maxrun, bool chroma) {
 
 // write_super_mode (enc/write_bits.c:268-362) with split_flag 0, as a length
 TD int super_mode_len(const thor_enc_frame &F, const BlockCtx &B, int mode, int ref_idx0) {
+  THOR_LOCAL(&B);
   if (F.frame_type == 0) return B.size > 8;
   const int bip = F.num_ref > 1 && F.enable_bipred, spl = B.size > 8, maxbit = 2 + F.num_ref + spl + bip;
   const bool demote = (B.ctx_index == 2 || B.ctx_index > 3) && spl;
@@ -239,6 +246,8 @@ TD int super_mode_len(const thor_enc_frame &F, const BlockCtx &B, int mode, int 
 // write_coeff (enc/write_bits.c:110-253) as a length.  coeff: size x size block, stride `size`; the caller guarantees at
 // least one non-zero level (cbp set).  Uses S.scan; every thread returns the same number.
 TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(coeff);
   const int q = imin(size, 16), N = q * q;
   const bool chroma = type & 1, intra = (type >> 1) & 1;
   const uint8_t *zz = zigzag(S, q);
@@ -296,6 +305,8 @@ TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
 
 // write_block (enc/write_bits.c:364-650) as a length
 TDN int block_bits(Grp &g, SbMem &S, const thor_enc_frame &F, const BlockCtx &B, const Param &P, const Coef &C) {
+  THOR_LOCAL(&B); THOR_LOCAL(&P); THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(&F);
   const int mode = P.mode, size = B.size, part = P.pb_part;
   int bits = super_mode_len(F, B, mode, P.ref_idx0);
   if (size == 64 && mode != 0 && F.max_delta_qp) bits += vlc_len(0, (uint32_t)iabs(B.delta_qp)) + (B.delta_qp != 0);

@@ -8,6 +8,8 @@ namespace thorenc {
 // keep x keep outputs are produced (keep = min(n, 16)), each pass rounds, shifts and stores int16.  Output: S.coeff,
 // stride keep.  Ends with a barrier.
 TDN void forward_core(Grp &g, SbMem &S, int n, int sh1, int sh2) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S);
   const int keep = imin(n, 16);
   const int16_t *in = S.resid;
   const int8_t *M = dct_matrix(S, n);
@@ -31,6 +33,8 @@ TDN void forward_core(Grp &g, SbMem &S, int n, int sh1, int sh2) {
 // formed directly: the residual itself, its f x f box sums for `fast` blocks larger than 16 (:273-293), or its 2x2 sums
 // for 64x64 (:295-307).  Output: S.coeff, the low q x q corner (q = min(size, 16)), stride q.  Ends with a barrier.
 TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, int size, int fast) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(org); THOR_SHARED(pred);
   int n = size, sh1 = ilog2((uint32_t)size), sh2 = sh1 + 5, f = 1;
   if (size > 16 && fast) { n = 16; f = size / 16; sh1 = size == 64 ? 8 : 6; sh2 = 9; }
   else if (size == 64) { n = 32; f = 2; sh1 = 7; sh2 = 10; }
@@ -48,6 +52,8 @@ TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uin
 // quantize() (enc/encode_block.c:75-178, rdoq == 0) of S.coeff; levels go to coeffq (stride `size`, low q x q corner).
 // Returns cbp (uniform).  Ends with a barrier.
 TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coeff_block_type) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(coeffq);
   const int intra = (coeff_block_type >> 1) & 1, chroma = coeff_block_type & 1;
   const int lg = ilog2((uint32_t)size), q = imin(size, 16), nq = q * q;
   const int scale = kQuant[qp % 6], shift = 21 - lg + qp / 6;
@@ -123,6 +129,8 @@ TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coe
 // dequantize (common/common_block.c:132-146) + inverse_transform (common/transform.c:432-518) + reconstruct_block
 // (common/common_block.c:148-156).  coeffq: stride `size`; rec: stride rstride.  Ends with a barrier.
 TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int qp, int size) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(coeffq); THOR_SHARED(pred); THOR_SHARED(rec);
   const int lg = ilog2((uint32_t)size), q = imin(size, 16), n = size == 64 ? 32 : size, keep = imin(n, 16);
   const int lshift = qp / 6, rshift = lg - 1, scale = kDequant[qp % 6], add = 1 << (rshift - 1);
   TFOR(g, i, q * q) {
@@ -163,6 +171,8 @@ TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *
 // transform -> quantise -> (dequantise -> inverse transform -> reconstruct | copy the prediction).  Returns the cbp bit.
 TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride,
                   int16_t *coeffq, int size, int qp, int coeff_type, int fast) {
+  THOR_LOCAL(&g);
+  THOR_SHARED(&S); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(rec); THOR_SHARED(coeffq);
   forward_tb(g, S, org, ostride, pred, pstride, size, fast);
   const int cbp = quantize_tb(g, S, coeffq, qp, size, coeff_type);
   if (cbp) reconstruct_tb(g, S, coeffq, pred, pstride, rec, rstride, qp, size);
@@ -178,6 +188,8 @@ TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8
 
 // ssd_calc (enc/encode_block.c:782-797) over the three planes of a block: cost_calc's distortion (:1218-1228)
 TDN int ssd_yuv(Grp &g, const Blk &a, const Blk &b, int stride, int width, int height) {
+  THOR_SHARED(&a); THOR_SHARED(&b);
+  THOR_LOCAL(&g);
   int s = 0;
   TFOR(g, i, width * height) {
     const int o = (i / width) * stride + (i % width);

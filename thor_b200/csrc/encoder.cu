@@ -34,7 +34,7 @@ __device__ __forceinline__ int ld_acquire(const int *p) {
 }
 __device__ __forceinline__ void st_release(int *p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 
-__global__ void __launch_bounds__(NT, 1) k_encode_frame(const thor_enc_frame F, int *ticket) {
+__global__ void __launch_bounds__(NT, 1) k_encode_frame(const thor_enc_frame F_arg, int *ticket) {
   extern __shared__ __align__(16) uint8_t smem[];
   SbMem &S = *reinterpret_cast<SbMem *>(smem);
   __shared__ int s_row;
@@ -43,7 +43,9 @@ __global__ void __launch_bounds__(NT, 1) k_encode_frame(const thor_enc_frame F, 
   g.red = S.red;
   g.flip = 0;
   if (threadIdx.x == 0) s_row = atomicAdd(ticket, 1);
+  for (int i = threadIdx.x; i < (int)(sizeof(thor_enc_frame) / 4); i += NT) reinterpret_cast<int *>(&S.frame)[i] = reinterpret_cast<const int *>(&F_arg)[i];
   __syncthreads();
+  const thor_enc_frame &F = S.frame;
   const int row = s_row;
   const int nsbx = (F.width + 63) / 64, nsby = (F.height + 63) / 64;
   if (row >= nsby) return;
