@@ -33,8 +33,19 @@
 #define THOR_SHARED(p) ((void)0)
 #define THOR_LOCAL(p) ((void)0)
 #else
+#ifdef THOR_NO_SHARED_HINT
+#define THOR_SHARED(p) ((void)0)
+#else
 #define THOR_SHARED(p) __builtin_assume(__isShared(p))
-#define THOR_LOCAL(p) __builtin_assume(__isLocal(p))      // per-thread state handed down by reference (stack)
+#endif
+// The matching hint for per-thread state handed down by reference (__isLocal) is NOT used: with it the kernel hung on the
+// B200 in the bi-prediction path (round 2, build variants v1..v3 under gpurun); cause not understood.  THOR_ENC_LOCAL_HINT
+// re-enables it for experiments.
+#ifdef THOR_ENC_LOCAL_HINT
+#define THOR_LOCAL(p) __builtin_assume(__isLocal(p))
+#else
+#define THOR_LOCAL(p) ((void)0)
+#endif
 #endif
 
 namespace thorenc {
