@@ -31,12 +31,27 @@
 // one tells the compiler (LDS / STS with immediate offsets instead of generic loads through a converted address)
 #ifdef THOR_HOSTEMU
 #define THOR_SHARED(p) ((void)0)
+#define THOR_SHS(p) ((void)0)
+#define THOR_SHF(p) ((void)0)
+#define THOR_SHR(p) ((void)0)
 #define THOR_LOCAL(p) ((void)0)
 #else
-#ifdef THOR_NO_SHARED_HINT
-#define THOR_SHARED(p) ((void)0)
+#define THOR_ASSUME_SHARED(p) __builtin_assume(__isShared(p))
+// Measured on the B200 (round 2, one build variant per group, .bit compared with the reference's): the hint on the SbMem
+// reference (S) and on the reduction scratch (R) keep the streams byte-identical and take a 416x240 frame from 115 to 95 ms;
+// the same hint on pointer PARAMETERS into SbMem (P) changed decisions in the bi-prediction configurations although every
+// such pointer does point into shared memory, and on the frame description (F) it was slower.  P and F stay off.
+#define THOR_SHS(p) THOR_ASSUME_SHARED(p)
+#define THOR_SHR(p) THOR_ASSUME_SHARED(p)
+#ifdef THOR_HINT_P
+#define THOR_SHARED(p) THOR_ASSUME_SHARED(p)
 #else
-#define THOR_SHARED(p) __builtin_assume(__isShared(p))
+#define THOR_SHARED(p) ((void)0)
+#endif
+#ifdef THOR_HINT_F
+#define THOR_SHF(p) THOR_ASSUME_SHARED(p)
+#else
+#define THOR_SHF(p) ((void)0)
 #endif
 // The matching hint for per-thread state handed down by reference (__isLocal) is NOT used: with it the kernel hung on the
 // B200 in the bi-prediction path (round 2, build variants v1..v3 under gpurun); cause not understood.  THOR_ENC_LOCAL_HINT
@@ -75,7 +90,7 @@ struct Grp {
   __device__ int sum(int v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    THOR_SHARED(red);
+    THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = v;
     __syncthreads();
@@ -90,7 +105,7 @@ struct Grp {
     for (int k = 0; k < K; k++)
 #pragma unroll
       for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
-    THOR_SHARED(red);
+    THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0)
 #pragma unroll
@@ -108,7 +123,7 @@ struct Grp {
   __device__ int vmax(int v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
-    THOR_SHARED(red);
+    THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = v;
     __syncthreads();

@@ -34,7 +34,7 @@ TD int node_index(int size, int ypos, int xpos) {
 // copy_frame_to_block (enc/encode_block.c:1821-1838): the original samples of the block, compact, stride = size
 TDN void load_org(Enc &E, const BlockCtx &B) {
   THOR_LOCAL(&E); THOR_LOCAL(&B);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   const thor_enc_pic &o = E.F.orig;
   const int size = B.size, wq = B.bwidth / 4;
@@ -59,7 +59,7 @@ TDN void load_org(Enc &E, const BlockCtx &B) {
 TDN void make_top_and_left(Enc &E, int pl, const uint8_t *rec_frame, int fstride, const uint8_t *rblock, int rbstride, int i, int j, int ypos, int xpos,
                            int size, int cb_upright, int cb_downleft, int tb_split) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   uint8_t *top = E.S.top[pl], *left = E.S.left[pl];
   int downleft, upright;
@@ -91,7 +91,7 @@ TDN void make_top_and_left(Enc &E, int pl, const uint8_t *rec_frame, int fstride
 TDN int intra_plane(Enc &E, int pl, const uint8_t *org, const uint8_t *rec_frame, int fstride, int ypos, int xpos, int size, int qp, uint8_t *pred,
                     int16_t *coeffq, uint8_t *rec, int coeff_type, int tb_split, int intra_mode, int upright, int downleft) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(coeffq); THOR_SHARED(rec);
+  THOR_SHS(&E.S); THOR_SHF(&E.F); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(coeffq); THOR_SHARED(rec);
   Grp &g = E.g;
   SbMem &S = E.S;
   const int fast = E.F.encoder_speed > 1;
@@ -116,7 +116,7 @@ TDN int intra_plane(Enc &E, int pl, const uint8_t *org, const uint8_t *rec_frame
 // encode_and_reconstruct_block_inter (enc/encode_block.c:1469-1532) for one plane
 TDN int inter_plane(Enc &E, const uint8_t *org, int size, int qp, const uint8_t *pred, int16_t *coeffq, uint8_t *rec, int coeff_type, int tb_split) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(coeffq); THOR_SHARED(rec);
+  THOR_SHS(&E.S); THOR_SHF(&E.F); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(coeffq); THOR_SHARED(rec);
   Grp &g = E.g;
   SbMem &S = E.S;
   const int speed = E.F.encoder_speed;
@@ -137,7 +137,7 @@ TDN int inter_plane(Enc &E, const uint8_t *org, int size, int qp, const uint8_t 
 // the parameters in P, into S.rec / S.tc; returns what write_block would emit (its length).  P.cbp_* / P.tb_split are set.
 TDN int encode_block(Enc &E, const BlockCtx &B, Param &P) {
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -200,7 +200,7 @@ TDN int encode_block(Enc &E, const BlockCtx &B, Param &P) {
 // copy_best_parameters (enc/encode_block.c:1983-2045): the trial in S.rec / S.tc / P becomes the block's best so far
 TDN void keep_best(Enc &E, const BlockCtx &B, const Param &P, Param &best) {
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P); THOR_LOCAL(&best);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const int size = B.size, ny = size * size / 4, nc = ny / 4;
@@ -242,7 +242,7 @@ TD int skip_threshold(int qp, int lg, double relative_threshold) {
 // -> any |coefficient| > threshold.  org: stride ostride; pred: compact stride size0 (size0 >= 8).
 TDN int skip_test_luma(Enc &E, const uint8_t *org, int ostride, int size0, int qp, const uint8_t *pred, float thr) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F); THOR_SHARED(org); THOR_SHARED(pred);
+  THOR_SHS(&E.S); THOR_SHF(&E.F); THOR_SHARED(org); THOR_SHARED(pred);
   Grp &g = E.g;
   SbMem &S = E.S;
   const int n = size0 / 2, lg = ilog2((uint32_t)n);
@@ -264,7 +264,7 @@ TDN int skip_test_luma(Enc &E, const uint8_t *org, int ostride, int size0, int q
 // 4-wide form, which looks at the top-left 4 x 4 samples only (pairs of column sums) -- also for 16 x 16 sub-blocks.
 TDN int skip_test_chroma(Enc &E, const uint8_t *org, int ostride, int size, int qp, const uint8_t *pred, float thr) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F); THOR_SHARED(org); THOR_SHARED(pred);
+  THOR_SHS(&E.S); THOR_SHF(&E.F); THOR_SHARED(org); THOR_SHARED(pred);
   Grp &g = E.g;
   const int threshold = skip_threshold(qp, 5, (double)thr);
   int sig = 0;
@@ -288,7 +288,7 @@ TDN int skip_test_chroma(Enc &E, const uint8_t *org, int ostride, int size, int 
 // check_early_skip_block (:2613-2741): 1 = no sub-block of the candidate's prediction leaves a significant residual
 TDN int check_early_skip(Enc &E, const BlockCtx &B, const Param &P) {
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -339,7 +339,7 @@ TDN int check_early_skip(Enc &E, const BlockCtx &B, const Param &P) {
 // DC, HOR, VER, PLANAR [, UPLEFT, UPRIGHT, UPUPRIGHT, UPUPLEFT, UPLEFTLEFT, DOWNLEFTLEFT]; first minimum wins.
 TDN int search_intra(Enc &E, const BlockCtx &B, int num_intra_modes, int *intra_mode) {
   THOR_LOCAL(&E); THOR_LOCAL(&B);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -366,7 +366,7 @@ TDN int search_intra(Enc &E, const BlockCtx &B, int num_intra_modes, int *intra_
 TDN int search_inter(Enc &E, const uint8_t *org_y, const thor_enc_pic &ref, const BlockCtx &B, Mv mvc, Mv mvp, Mv *mv_arr, int part, double lambda,
                      int sign, int ref_idx, int enable_bipred) {
   THOR_LOCAL(&E); THOR_LOCAL(&B);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F); THOR_SHARED(org_y);
+  THOR_SHS(&E.S); THOR_SHF(&E.F); THOR_SHARED(org_y);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -411,7 +411,7 @@ TDN int search_inter(Enc &E, const uint8_t *org_y, const thor_enc_pic &ref, cons
 // encoder_speed 0 -- is motion_estimate_bi, :1102-1215: not built, see encoder.cu's configuration check.)
 TDN void search_bipred(Enc &E, const BlockCtx &B, int part, const Mv *mv_center, Mv mvp, int *ref_idx0, int *ref_idx1, Mv *mv_arr0, Mv *mv_arr1) {
   THOR_LOCAL(&E); THOR_LOCAL(&B);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -458,7 +458,7 @@ TDN void search_bipred(Enc &E, const BlockCtx &B, int part, const Mv *mv_center,
 // ---- mode decision (enc/encode_block.c:2204-2479) ---------------------------------------------------------------
 TD void try_cost(Enc &E, const BlockCtx &B, Param &P, Param &best, uint32_t &min_cost, int width, int height, uint32_t *cost_out) {
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P); THOR_LOCAL(&best);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   const int nbits = encode_block(E, B, P);
   const uint32_t cost = rd_cost(ssd_yuv(E.g, E.S.org, E.S.rec, B.size, width, height), nbits, E.F.lambda);
   if (cost < min_cost) { min_cost = cost; keep_best(E, B, P, best); }
@@ -476,7 +476,7 @@ TD void param_from_cand(Param &P, const InterPred &c, int idx, int mode) {
 
 TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&best);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -599,7 +599,7 @@ TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
 // record the host's write_block needs: reconstruction -> picture, neighbour units, node, coefficients.
 TDN void finalize_block(Enc &E, const BlockCtx &B, const Param &P) {
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -660,7 +660,7 @@ TDN void finalize_block(Enc &E, const BlockCtx &B, const Param &P) {
 
 TD void mark_split(Enc &E, const BlockCtx &B) {
   THOR_LOCAL(&E); THOR_LOCAL(&B);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   if (E.g.tid == 0) {
     thor_enc_node &nd = E.nodes[node_index(B.size, B.ypos, B.xpos)];
     nd.state = THOR_NODE_SPLIT;
@@ -672,7 +672,7 @@ TD void mark_split(Enc &E, const BlockCtx &B) {
 template <int SIZE>
 TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
   SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
@@ -777,7 +777,7 @@ TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
 // one superblock of encode_frame's loop (enc/encode_frame.c:112-148), including the per-superblock delta-qp search
 TDN void encode_superblock(Enc &E) {
   THOR_LOCAL(&E);
-  THOR_SHARED(&E.S); THOR_SHARED(&E.F);
+  THOR_SHS(&E.S); THOR_SHF(&E.F);
   const thor_enc_frame &F = E.F;
   for (int r = 0; r < THOR_ENC_MAX_REF; r++) { E.st.mvcand_num[r] = 0; E.st.mvcand_mask[r] = 0; }
   E.st.best_ref = -1;

@@ -9,7 +9,7 @@ namespace thorenc {
 // `wide`: each candidate is widesad_calc's five positions x + {-3,-1,0,1,3} (:757-780); results in S.acc[5k .. 5k+5).
 TDN void sad_batch(Grp &g, SbMem &S, const uint8_t *a, int as, const uint8_t *ref, int bs, const int *off, int K, int width, int height, int wide) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(a);
+  THOR_SHS(&S); THOR_SHARED(a);
   const int per = wide ? 5 : 1, wq = width >> 2, items = height * wq;
   g.sync();                                                // readers of the previous batch's results are done
   TFOR(g, i, K * per) S.acc[i] = 0;
@@ -162,7 +162,7 @@ TD unsigned mv_cost(double lambda, Mv mv, Mv mvp) { return (unsigned)dadd(dmul(l
 // add_mvcandidate (enc/encode_block.c:58-73)
 TD void add_mvcandidate(Grp &g, SbMem &S, SbState &st, int ref_idx, Mv mv) {
   THOR_LOCAL(&st); THOR_LOCAL(&g);
-  THOR_SHARED(&S);
+  THOR_SHS(&S);
   const Mv imv = mkmv((mv.x + 2) >> 2, (mv.y + 2) >> 2);
   const uint64_t m = (uint64_t)1 << ((((int)imv.y << 3) ^ (int)imv.x) & 63);
   if (!(m & st.mvcand_mask[ref_idx])) {
@@ -180,7 +180,7 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
                              int height, Mv *mv_out, Mv mvc, Mv mvp, double lambda, int sign, int xpos, int ypos, const Mv *mvcand, int mvcand_num,
                              int enable_bipred) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(orig); THOR_SHARED(mvcand); THOR_SHARED(&F);
+  THOR_SHS(&S); THOR_SHARED(orig); THOR_SHARED(mvcand); THOR_SHF(&F);
   const int s = sign ? -1 : 1, speed = F.encoder_speed, fw = F.width, fh = F.height;
   unsigned min_sad = 1u << 31, sad;
   Mv mv_opt = mkmv(0, 0), mv_ref = mkmv(((mvc.x + 2) >> 2) << 2, ((mvc.y + 2) >> 2) << 2), cand;

@@ -21,7 +21,7 @@ TD Mv clip_mv(Mv mv, int ypos, int xpos, int fwidth, int fheight, int size, int 
 TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *ref, int stride, int width, int height, Mv mv, int sign,
                     int bipred) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(dst);
+  THOR_SHS(&S); THOR_SHARED(dst);
   const int mx = sign ? -mv.x : mv.x, my = sign ? -mv.y : mv.y;
   const int fx = mx & 3, fy = my & 3;
   const uint8_t *src = ref + (my >> 2) * stride + (mx >> 2);
@@ -135,7 +135,7 @@ TDN void inter_yuv(Grp &g, SbMem &S, const thor_enc_frame &F, const thor_enc_pic
                    int bipred, int split) {
   THOR_SHARED(&dst);
   THOR_LOCAL(&B); THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(&F);
+  THOR_SHS(&S); THOR_SHF(&F);
   const int div = split + 1, bwidth = B.bwidth / div, bheight = B.bheight / div, pstride = B.size;
   const int yC = B.ypos / 2, xC = B.xpos / 2;
   const uint8_t *ref_y = ref.y + B.ypos * ref.stride_y + B.xpos;
@@ -181,7 +181,7 @@ TDN void average_blocks(Grp &g, Blk &dst, const Blk &a, const Blk &b, const Bloc
 // reconstructed picture.  top/left hold 2*size samples.  Ends with a barrier.
 TDN void intra_neighbours(Grp &g, SbMem &S, const uint8_t *rec, int stride, int x, int y, int size, int upright, int downleft, int pl) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S);
+  THOR_SHS(&S);
   uint8_t *top = S.top[pl], *left = S.left[pl];
   const int toplen = upright ? size + 1 : size, leftlen = downleft ? size + 1 : size;
   const uint8_t *p = rec + y * stride + x;
@@ -210,7 +210,7 @@ TD void smooth121(Grp &g, const uint8_t *in, uint8_t *out, int len) {
 // Ends with a barrier.
 TDN void intra_predict(Grp &g, SbMem &S, int pl, int ypos, int xpos, int size, uint8_t *pblock, int mode) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(pblock);
+  THOR_SHS(&S); THOR_SHARED(pblock);
   const uint8_t *top = S.top[pl], *left = S.left[pl];
   const int top_left = S.topleft[pl];
   const int n = size * size, sh = ilog2((uint32_t)size);

@@ -71,7 +71,7 @@ TD const uint8_t *zigzag(const SbMem &S, int q) { return S.zz + (q == 4 ? 0 : q 
 
 TDN void build_tables(Grp &g, SbMem &S) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S);
+  THOR_SHS(&S);
   // M_N[k][n] = C[(2n+1) * k * 32/N] with the symmetries of cos(pi a / 64): common/transform.c:41-245 (g1..g4mat_hevc)
   TFOR(g, i, 1360) {
     int N, base;
@@ -130,7 +130,7 @@ TD InterPred zero_pred() {
 
 // get_mv_pred (common/inter_prediction.c:182-294): median of three neighbour vectors chosen by availability
 TDN Mv get_mv_pred(const thor_enc_frame &F, int ypos, int xpos, int size) {
-  THOR_SHARED(&F);
+  THOR_SHF(&F);
   const int bs = size / 4, stride = F.width / 4, idx = (ypos / 4) * stride + xpos / 4;
   const int up0 = idx - stride, up1 = idx - stride + (bs - 1) / 2, up2 = idx - stride + bs - 1;
   const int left0 = idx - 1, left1 = idx + stride * ((bs - 1) / 2) - 1, left2 = idx + stride * (bs - 1) - 1;
@@ -155,7 +155,7 @@ TDN Mv get_mv_pred(const thor_enc_frame &F, int ypos, int xpos, int size) {
 
 // get_mv_skip / get_mv_merge (common/inter_prediction.c:296-600 with LIMITED_SKIP: the two functions are the same)
 TDN int get_mv_skip(const thor_enc_frame &F, int ypos, int xpos, int size, InterPred *cand) {
-  THOR_SHARED(&F);
+  THOR_SHF(&F);
   const int bs = size / 4, stride = F.width / 4, idx = (ypos / 4) * stride + xpos / 4;
   const int up0 = idx - stride, left0 = idx - 1, upright = idx - stride + bs;
   int up2 = idx - stride + bs - 1, left2 = idx + stride * (bs - 1) - 1;
@@ -247,7 +247,7 @@ TD int super_mode_len(const thor_enc_frame &F, const BlockCtx &B, int mode, int 
 // least one non-zero level (cbp set).  Uses S.scan; every thread returns the same number.
 TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(coeff);
+  THOR_SHS(&S); THOR_SHARED(coeff);
   const int q = imin(size, 16), N = q * q;
   const bool chroma = type & 1, intra = (type >> 1) & 1;
   const uint8_t *zz = zigzag(S, q);
@@ -306,7 +306,7 @@ TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
 // write_block (enc/write_bits.c:364-650) as a length
 TDN int block_bits(Grp &g, SbMem &S, const thor_enc_frame &F, const BlockCtx &B, const Param &P, const Coef &C) {
   THOR_LOCAL(&B); THOR_LOCAL(&P); THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(&F);
+  THOR_SHS(&S); THOR_SHF(&F);
   const int mode = P.mode, size = B.size, part = P.pb_part;
   int bits = super_mode_len(F, B, mode, P.ref_idx0);
   if (size == 64 && mode != 0 && F.max_delta_qp) bits += vlc_len(0, (uint32_t)iabs(B.delta_qp)) + (B.delta_qp != 0);

@@ -9,7 +9,7 @@ namespace thorenc {
 // stride keep.  Ends with a barrier.
 TDN void forward_core(Grp &g, SbMem &S, int n, int sh1, int sh2) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S);
+  THOR_SHS(&S);
   const int keep = imin(n, 16);
   const int16_t *in = S.resid;
   const int8_t *M = dct_matrix(S, n);
@@ -34,7 +34,7 @@ TDN void forward_core(Grp &g, SbMem &S, int n, int sh1, int sh2) {
 // for 64x64 (:295-307).  Output: S.coeff, the low q x q corner (q = min(size, 16)), stride q.  Ends with a barrier.
 TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, int size, int fast) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(org); THOR_SHARED(pred);
+  THOR_SHS(&S); THOR_SHARED(org); THOR_SHARED(pred);
   int n = size, sh1 = ilog2((uint32_t)size), sh2 = sh1 + 5, f = 1;
   if (size > 16 && fast) { n = 16; f = size / 16; sh1 = size == 64 ? 8 : 6; sh2 = 9; }
   else if (size == 64) { n = 32; f = 2; sh1 = 7; sh2 = 10; }
@@ -53,7 +53,7 @@ TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uin
 // Returns cbp (uniform).  Ends with a barrier.
 TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coeff_block_type) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(coeffq);
+  THOR_SHS(&S); THOR_SHARED(coeffq);
   const int intra = (coeff_block_type >> 1) & 1, chroma = coeff_block_type & 1;
   const int lg = ilog2((uint32_t)size), q = imin(size, 16), nq = q * q;
   const int scale = kQuant[qp % 6], shift = 21 - lg + qp / 6;
@@ -130,7 +130,7 @@ TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coe
 // (common/common_block.c:148-156).  coeffq: stride `size`; rec: stride rstride.  Ends with a barrier.
 TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *pred, int pstride, uint8_t *rec, int rstride, int qp, int size) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(coeffq); THOR_SHARED(pred); THOR_SHARED(rec);
+  THOR_SHS(&S); THOR_SHARED(coeffq); THOR_SHARED(pred); THOR_SHARED(rec);
   const int lg = ilog2((uint32_t)size), q = imin(size, 16), n = size == 64 ? 32 : size, keep = imin(n, 16);
   const int lshift = qp / 6, rshift = lg - 1, scale = kDequant[qp % 6], add = 1 << (rshift - 1);
   TFOR(g, i, q * q) {
@@ -172,7 +172,7 @@ TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *
 TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride,
                   int16_t *coeffq, int size, int qp, int coeff_type, int fast) {
   THOR_LOCAL(&g);
-  THOR_SHARED(&S); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(rec); THOR_SHARED(coeffq);
+  THOR_SHS(&S); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(rec); THOR_SHARED(coeffq);
   forward_tb(g, S, org, ostride, pred, pstride, size, fast);
   const int cbp = quantize_tb(g, S, coeffq, qp, size, coeff_type);
   if (cbp) reconstruct_tb(g, S, coeffq, pred, pstride, rec, rstride, qp, size);
