@@ -81,6 +81,8 @@ struct Grp {
   template <int K> void sumk(int (&v)[K]) {}
   int any(int p) { return p != 0; }
   int vmax(int v) { return v; }
+  void vmax3(int (&v)[3]) {}
+  int orall(int m) { return m; }
 #else
   int tid;
   static constexpr int n = NT;
@@ -120,6 +122,36 @@ struct Grp {
     }
   }
   __device__ int any(int p) { return __syncthreads_or(p); }
+  __device__ int orall(int m) {                                        // bitwise OR of m over the group
+    m = (int)__reduce_or_sync(0xffffffffu, (unsigned)m);
+    THOR_SHR(red);
+    int *r = red + (flip ^= 1) * NW * 8;
+    if ((tid & 31) == 0) r[tid >> 5] = m;
+    __syncthreads();
+    int t = r[0];
+#pragma unroll
+    for (int w = 1; w < NW; w++) t |= r[w];
+    return t;
+  }
+  __device__ void vmax3(int (&v)[3]) {                                 // three maxima with one barrier
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+#pragma unroll
+      for (int o = 16; o; o >>= 1) v[k] = max(v[k], __shfl_xor_sync(0xffffffffu, v[k], o));
+    THOR_SHR(red);
+    int *r = red + (flip ^= 1) * NW * 8;
+    if ((tid & 31) == 0)
+#pragma unroll
+      for (int k = 0; k < 3; k++) r[(tid >> 5) * 8 + k] = v[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      int t = r[k];
+#pragma unroll
+      for (int w = 1; w < NW; w++) t = max(t, r[w * 8 + k]);
+      v[k] = t;
+    }
+  }
   __device__ int vmax(int v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));

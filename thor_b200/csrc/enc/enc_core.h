@@ -152,12 +152,28 @@ TDN int encode_block(Enc &E, const BlockCtx &B, Param &P) {
   if (mode == 1) {
     const thor_enc_pic &rec = F.rec;
     const int upright = upright_available(B.ypos, B.xpos, size, F.width), downleft = downleft_available(B.ypos, B.xpos, size, F.height);
-    P.cbp_y = intra_plane(E, 0, S.org.y, rec.y + B.ypos * rec.stride_y + B.xpos, rec.stride_y, B.ypos, B.xpos, size, qpY, S.pred.y, S.tc.y, S.rec.y,
-                          ctype, tb_split, P.intra_mode, upright, downleft);
-    P.cbp_u = intra_plane(E, 1, S.org.u, rec.u + yposC * rec.stride_c + xposC, rec.stride_c, yposC, xposC, sizeC, qpC, S.pred.u, S.tc.u, S.rec.u,
-                          ctype | 1, tb_split && size > 8, P.intra_mode, upright, downleft);
-    P.cbp_v = intra_plane(E, 2, S.org.v, rec.v + yposC * rec.stride_c + xposC, rec.stride_c, yposC, xposC, sizeC, qpC, S.pred.v, S.tc.v, S.rec.v,
-                          ctype | 1, tb_split && size > 8, P.intra_mode, upright, downleft);
+    if (!tb_split) {
+      // the three predictions only read neighbours outside the block: form them first, then code Y, U and V together
+      make_top_and_left(E, 0, rec.y + B.ypos * rec.stride_y + B.xpos, rec.stride_y, nullptr, 0, 0, 0, B.ypos, B.xpos, size, upright, downleft, 0);
+      intra_predict(g, S, 0, B.ypos, B.xpos, size, S.pred.y, P.intra_mode);
+      make_top_and_left(E, 1, rec.u + yposC * rec.stride_c + xposC, rec.stride_c, nullptr, 0, 0, 0, yposC, xposC, sizeC, upright, downleft, 0);
+      intra_predict(g, S, 1, yposC, xposC, sizeC, S.pred.u, P.intra_mode);
+      make_top_and_left(E, 2, rec.v + yposC * rec.stride_c + xposC, rec.stride_c, nullptr, 0, 0, 0, yposC, xposC, sizeC, upright, downleft, 0);
+      intra_predict(g, S, 2, yposC, xposC, sizeC, S.pred.v, P.intra_mode);
+      const int fast = F.encoder_speed > 1;
+      const TbDesc d[3] = {{S.org.y, size, S.pred.y, size, S.rec.y, size, S.tc.y, size, qpY, ctype, fast},
+                           {S.org.u, sizeC, S.pred.u, sizeC, S.rec.u, sizeC, S.tc.u, sizeC, qpC, ctype | 1, fast},
+                           {S.org.v, sizeC, S.pred.v, sizeC, S.rec.v, sizeC, S.tc.v, sizeC, qpC, ctype | 1, fast}};
+      const int m = encode_tb3(g, S, d, 3);
+      P.cbp_y = m & 1; P.cbp_u = (m >> 1) & 1; P.cbp_v = (m >> 2) & 1;
+    } else {
+      P.cbp_y = intra_plane(E, 0, S.org.y, rec.y + B.ypos * rec.stride_y + B.xpos, rec.stride_y, B.ypos, B.xpos, size, qpY, S.pred.y, S.tc.y, S.rec.y,
+                            ctype, tb_split, P.intra_mode, upright, downleft);
+      P.cbp_u = intra_plane(E, 1, S.org.u, rec.u + yposC * rec.stride_c + xposC, rec.stride_c, yposC, xposC, sizeC, qpC, S.pred.u, S.tc.u, S.rec.u,
+                            ctype | 1, tb_split && size > 8, P.intra_mode, upright, downleft);
+      P.cbp_v = intra_plane(E, 2, S.org.v, rec.v + yposC * rec.stride_c + xposC, rec.stride_c, yposC, xposC, sizeC, qpC, S.pred.v, S.tc.v, S.rec.v,
+                            ctype | 1, tb_split && size > 8, P.intra_mode, upright, downleft);
+    }
   } else {
     Blk &dst = mode == 0 ? S.rec : S.pred;
     const thor_enc_pic &r0 = ref_pic(F, P.ref_idx0);
@@ -189,9 +205,18 @@ TDN int encode_block(Enc &E, const BlockCtx &B, Param &P) {
       g.sync();
       P.cbp_y = P.cbp_u = P.cbp_v = 0;
     } else {
-      P.cbp_y = inter_plane(E, S.org.y, size, qpY, S.pred.y, S.tc.y, S.rec.y, ctype, tb_split);
-      P.cbp_u = inter_plane(E, S.org.u, sizeC, qpC, S.pred.u, S.tc.u, S.rec.u, ctype | 1, tb_split && size > 8);
-      P.cbp_v = inter_plane(E, S.org.v, sizeC, qpC, S.pred.v, S.tc.v, S.rec.v, ctype | 1, tb_split && size > 8);
+      if (!tb_split) {
+        const int speed = F.encoder_speed, fastC = speed > 1, fastY = (size == 64 && speed > 0) || speed > 1;
+        const TbDesc d[3] = {{S.org.y, size, S.pred.y, size, S.rec.y, size, S.tc.y, size, qpY, ctype, fastY},
+                             {S.org.u, sizeC, S.pred.u, sizeC, S.rec.u, sizeC, S.tc.u, sizeC, qpC, ctype | 1, fastC},
+                             {S.org.v, sizeC, S.pred.v, sizeC, S.rec.v, sizeC, S.tc.v, sizeC, qpC, ctype | 1, fastC}};
+        const int m = encode_tb3(g, S, d, 3);
+        P.cbp_y = m & 1; P.cbp_u = (m >> 1) & 1; P.cbp_v = (m >> 2) & 1;
+      } else {
+        P.cbp_y = inter_plane(E, S.org.y, size, qpY, S.pred.y, S.tc.y, S.rec.y, ctype, tb_split);
+        P.cbp_u = inter_plane(E, S.org.u, sizeC, qpC, S.pred.u, S.tc.u, S.rec.u, ctype | 1, tb_split && size > 8);
+        P.cbp_v = inter_plane(E, S.org.v, sizeC, qpC, S.pred.v, S.tc.v, S.rec.v, ctype | 1, tb_split && size > 8);
+      }
     }
   }
   return block_bits(g, S, F, B, P, S.tc);

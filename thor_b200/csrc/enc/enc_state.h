@@ -33,13 +33,15 @@ struct SbMem {
   Blk org, rec, best, pred, p0, p1;
   Coef tc, bc;                       // coefficients of the trial / of the best trial so far
   int16_t resid[4096];               // transform input of the current transform block (stride = its size)
-  int16_t mid[16 * 32];              // transform intermediate
-  int16_t coeff[256];                // low q x q corner of the forward transform, stride q
-  int16_t rcoeff[256];               // dequantised, stride q
-  int16_t rblock[1024];              // inverse transform output (n <= 32), stride n
-  int32_t lin[256], lev[256];        // quantiser: coefficients / levels in scan order
+  // transform scratch: three transform blocks (Y, U, V of a coding block) are in flight at once, slot t at t * stride
+  int16_t mid[3 * 16 * 32];          // transform intermediate
+  int16_t coeff[3 * 256];            // low q x q corner of the forward transform, stride q
+  int16_t rcoeff[3 * 256];           // dequantised, stride q
+  int16_t rblock[3 * 1024];          // inverse transform output (n <= 32), stride n
+  int32_t lin[3 * 256], lev[3 * 256];// quantiser: coefficients / levels in scan order
   int16_t itmp[69 * 64];             // interpolation: first-pass intermediate (rows -2 .. h+2)
-  int16_t scan[256];                 // bit counter: levels in scan order
+  int16_t scan[3 * 256];             // bit counter: levels in scan order (three planes at once)
+  int bits3[4];
   uint8_t ipred[4096];               // search: prediction under test
   uint8_t org8[4096];                // bi-pred search: 2*org - pred (search_bipred_prediction_params)
   uint8_t top[3][132], left[3][132]; // intra neighbours per plane
@@ -47,7 +49,7 @@ struct SbMem {
   uint8_t tf[132], lf[132];          // smoothed neighbour rows
   int8_t dct[32 * 32 + 16 * 16 + 8 * 8 + 4 * 4];
   uint8_t zz[16 + 64 + 256];
-  uint32_t fire[8];                  // quantiser: positions the RDOQ-light pass has to look at
+  uint32_t fire[3 * 8];              // quantiser: positions the RDOQ-light pass has to look at
   int acc[64 * 5 + 8];               // SAD accumulators of a batch of candidates
   Mv mvcand[THOR_ENC_MAX_REF][64];   // frame_info.mvcand (enc/mainenc.h:124), reset per superblock
   // decision of a 16x16 block kept while its 8x8 children are tried (top-down split, enc/encode_block.c:2983-2995)
@@ -243,24 +245,8 @@ TD int super_mode_len(const thor_enc_frame &F, const BlockCtx &B, int mode, int 
   return code == maxbit ? maxbit : code + 1;
 }
 
-// write_coeff (enc/write_bits.c:110-253) as a length.  coeff: size x size block, stride `size`; the caller guarantees at
-// least one non-zero level (cbp set).  Uses S.scan; every thread returns the same number.
-TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
-  THOR_LOCAL(&g);
-  THOR_SHS(&S); THOR_SHARED(coeff);
-  const int q = imin(size, 16), N = q * q;
-  const bool chroma = type & 1, intra = (type >> 1) & 1;
-  const uint8_t *zz = zigzag(S, q);
-  g.sync();                                      // earlier readers of S.scan are done
-  int mylast = -1;
-  TFOR(g, i, N) {
-    const int16_t c = coeff[(i / q) * size + (i % q)];
-    S.scan[zz[i]] = c;
-    if (c) mylast = imax(mylast, (int)zz[i]);
-  }
-  const int last_pos = imax(g.vmax(mylast), 0);    // barrier inside
-  g.sync();
-  const int16_t *s = S.scan;
+// the two-mode scan of write_coeff (:160-250) over levels in scan order, as a length
+TD int scan_bits(const int16_t *s, int N, int last_pos, bool chroma, bool intra, int size) {
   const bool small_chroma = chroma && size <= 8;
   int bits = 0, pos = 0;
   if (chroma) {
@@ -301,6 +287,55 @@ TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
   }
   if (pos < N) bits += small_chroma ? 1 : chroma ? 2 : 3;   // end of block: table 0 cn 0 / 2 bits / table 2 cn 3
   return bits;
+}
+
+// write_coeff (enc/write_bits.c:110-253) as a length.  coeff: size x size block, stride `size`; the caller guarantees at
+// least one non-zero level (cbp set).  Uses S.scan; every thread returns the same number.
+TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
+  THOR_LOCAL(&g);
+  THOR_SHS(&S); THOR_SHARED(coeff);
+  const int q = imin(size, 16), N = q * q;
+  const bool chroma = type & 1, intra = (type >> 1) & 1;
+  const uint8_t *zz = zigzag(S, q);
+  g.sync();                                      // earlier readers of S.scan are done
+  int mylast = -1;
+  TFOR(g, i, N) {
+    const int16_t c = coeff[(i / q) * size + (i % q)];
+    S.scan[zz[i]] = c;
+    if (c) mylast = imax(mylast, (int)zz[i]);
+  }
+  const int last_pos = imax(g.vmax(mylast), 0);    // barrier inside
+  g.sync();
+  return scan_bits(S.scan, N, last_pos, chroma, intra, size);
+}
+
+// write_coeff for the Y, U and V blocks of an unsplit coding block at once (planes with their bit in `mask`): one scatter
+// pass, then the three serial scans run side by side on three warps.  Returns the sum of the lengths.
+TDN int coeff_bits3(Grp &g, SbMem &S, const int16_t *cy, const int16_t *cu, const int16_t *cv, int size, int ctype, int mask) {
+  THOR_SHS(&S);
+  const int qy = imin(size, 16), qc = imin(size / 2, 16);
+  const int c0 = (mask & 1) ? qy * qy : 0, c1 = (mask & 2) ? qc * qc : 0, c2 = (mask & 4) ? qc * qc : 0;
+  g.sync();                                      // earlier readers of S.scan are done
+  int last[3] = {-1, -1, -1};
+  TFOR(g, i, c0 + c1 + c2) {
+    int j, t;
+    if (i < c0) { j = i; t = 0; } else if (i < c0 + c1) { j = i - c0; t = 1; } else { j = i - c0 - c1; t = 2; }
+    const int q = t ? qc : qy, sz = t ? size / 2 : size;
+    const int16_t c = (t == 0 ? cy : t == 1 ? cu : cv)[(j / q) * sz + (j % q)];
+    const int p = zigzag(S, q)[j];
+    S.scan[t * 256 + p] = c;
+    if (c) last[t] = imax(last[t], p);
+  }
+  g.vmax3(last);                                 // barrier inside
+  g.sync();
+  for (int t = g.tid >> 5; t < 3; t += (g.n + 31) >> 5)
+    if ((mask >> t) & 1) {
+      const int q = t ? qc : qy;
+      const int b = scan_bits(S.scan + t * 256, q * q, imax(last[t], 0), t != 0, (ctype >> 1) & 1, t ? size / 2 : size);
+      if ((g.tid & 31) == 0) S.bits3[t] = b;
+    }
+  g.sync();
+  return ((mask & 1) ? S.bits3[0] : 0) + ((mask & 2) ? S.bits3[1] : 0) + ((mask & 4) ? S.bits3[2] : 0);
 }
 
 // write_block (enc/write_bits.c:364-650) as a length
@@ -346,9 +381,8 @@ TDN int block_bits(Grp &g, SbMem &S, const thor_enc_frame &F, const BlockCtx &B,
   } else code = cbp_code(cy, cu, cv, B.ctx_cbp);
   bits += vlc_len(0, (uint32_t)code);
   if (!split) {
-    if (cy) bits += coeff_bits(g, S, C.y, size, ctype);
-    if (cu) bits += coeff_bits(g, S, C.u, size / 2, ctype | 1);
-    if (cv) bits += coeff_bits(g, S, C.v, size / 2, ctype | 1);
+    const int mask = (cy ? 1 : 0) | (cu ? 2 : 0) | (cv ? 4 : 0);
+    if (mask) bits += coeff_bits3(g, S, C.y, C.u, C.v, size, ctype, mask);
   } else if (size > 8) {
     for (int k = 0; k < 4; k++) {
       const int y = (cy >> (3 - k)) & 1, u = (cu >> (3 - k)) & 1, v = (cv >> (3 - k)) & 1;

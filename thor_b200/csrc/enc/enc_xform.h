@@ -186,6 +186,184 @@ TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8
   return cbp;
 }
 
+// ---- up to three transform blocks at once ------------------------------------------------------------------------
+// The Y, U and V transform blocks of a coding block go through the same chain of short phases; done one after the other
+// that is 3 x 14 barriers for at most a few hundred samples each.  encode_tb3 runs every phase over the samples of all
+// (<= 3) blocks together -- same arithmetic per block as forward_tb / quantize_tb / reconstruct_tb above, slot t of the
+// transform scratch per block -- so a trial encode costs one pass through the chain.  Returns the cbp bits (bit t).
+struct TbDesc {
+  const uint8_t *org; int ostride;
+  const uint8_t *pred; int pstride;
+  uint8_t *rec; int rstride;
+  int16_t *coeffq;                    // stride `size`
+  int size, qp, ctype, fast;
+};
+TD int tb_of(int i, int c0, int c1, int &j) {
+  if (i < c0) { j = i; return 0; }
+  if (i < c0 + c1) { j = i - c0; return 1; }
+  j = i - c0 - c1;
+  return 2;
+}
+
+TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
+  THOR_SHS(&S);
+  // geometry per block: forward transform size n (after pooling by f), shifts, kept corner q, inverse size ni
+  int n[3] = {0, 0, 0}, f[3] = {1, 1, 1}, sh1[3] = {0, 0, 0}, sh2[3] = {0, 0, 0}, q[3] = {0, 0, 0}, ni[3] = {0, 0, 0}, lg[3] = {0, 0, 0};
+  for (int t = 0; t < ntb; t++) {
+    const int size = tb[t].size;
+    lg[t] = ilog2((uint32_t)size);
+    n[t] = size; sh1[t] = lg[t]; sh2[t] = lg[t] + 5;
+    if (size > 16 && tb[t].fast) { n[t] = 16; f[t] = size / 16; sh1[t] = size == 64 ? 8 : 6; sh2[t] = 9; }
+    else if (size == 64) { n[t] = 32; f[t] = 2; sh1[t] = 7; sh2[t] = 10; }
+    q[t] = imin(size, 16);
+    ni[t] = size == 64 ? 32 : size;
+  }
+  int c0, c1, tot, j;
+  // 1. transform input
+  c0 = n[0] * n[0]; c1 = n[1] * n[1]; tot = c0 + c1 + n[2] * n[2];
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j), nn = n[t], ff = f[t], r = j / nn, c = j % nn;
+    const uint8_t *o = tb[t].org + (r * ff) * tb[t].ostride + c * ff, *p = tb[t].pred + (r * ff) * tb[t].pstride + c * ff;
+    int sum = 0;
+    for (int a = 0; a < ff; a++)
+      for (int b = 0; b < ff; b++) sum += (int)o[a * tb[t].ostride + b] - (int)p[a * tb[t].pstride + b];
+    S.resid[t * 1024 + j] = (int16_t)sum;
+  }
+  g.sync();
+  // 2. rows -> horizontal frequencies
+  c0 = q[0] * n[0]; c1 = q[1] * n[1]; tot = c0 + c1 + q[2] * n[2];
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], r = j / keep, k = j % keep;
+    const int8_t *M = dct_matrix(S, nn) + k * nn;
+    const int16_t *in = S.resid + t * 1024 + r * nn;
+    int acc = 0;
+    for (int c = 0; c < nn; c++) acc += M[c] * in[c];
+    S.mid[t * 512 + k * 32 + r] = (int16_t)((acc + (1 << (sh1[t] - 1))) >> sh1[t]);
+  }
+  g.sync();
+  // 3. vertical frequencies; 4. scan order + last significant position
+  c0 = q[0] * q[0]; c1 = q[1] * q[1]; tot = c0 + c1 + q[2] * q[2];
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], v = j / keep, k = j % keep;
+    const int8_t *M = dct_matrix(S, nn) + v * nn;
+    const int16_t *m = S.mid + t * 512 + k * 32;
+    int acc = 0;
+    for (int r = 0; r < nn; r++) acc += M[r] * m[r];
+    S.coeff[t * 256 + j] = (int16_t)((acc + (1 << (sh2[t] - 1))) >> sh2[t]);
+  }
+  g.sync();
+  int last[3] = {-1, -1, -1};
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j);
+    const int intra = (tb[t].ctype >> 1) & 1, shift = 21 - lg[t] + tb[t].qp / 6, scale = kQuant[tb[t].qp % 6];
+    const int tail_off = (intra ? 38 : -26) * (1 << (shift - 8));
+    const int c = S.coeff[t * 256 + j], p = zigzag(S, q[t])[j];
+    S.lin[t * 256 + p] = c;
+    if ((iabs(iabs(c) * scale + tail_off) >> shift) != 0) last[t] = imax(last[t], p);
+  }
+  g.vmax3(last);                                                       // barrier inside
+  // 5. levels with the dead-zone offsets (:106-131)
+  int mine = 0;
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j);
+    int l = 0;
+    if (j <= last[t]) {
+      const int intra = (tb[t].ctype >> 1) & 1, chroma = tb[t].ctype & 1, shift = 21 - lg[t] + tb[t].qp / 6;
+      const int c = S.lin[t * 256 + j], mag = kQuant[tb[t].qp % 6] * iabs(c);
+      const int off = (((mag >> shift) == 0 || chroma) ? (intra ? 102 : 51) : (intra ? 115 : 90)) << (shift - 8);
+      l = (mag + off) >> shift;
+      if (l) mine |= 1 << t;
+      if (c < 0) l = -l;
+    }
+    S.lev[t * 256 + j] = l;
+  }
+  TFOR(g, i, 24) S.fire[i] = 0;
+  const int cbp = g.orall(mine);                                       // barrier inside
+  // 6. "RDOQ light" (:135-168), see quantize_tb: candidates found in parallel, walked in order by one thread per block
+  if (cbp) {
+    TFOR(g, i, tot) {
+      const int t = tb_of(i, c0, c1, j);
+      const int N = (tb[t].ctype & 1) ? last[t] + 1 : q[t] * q[t];
+      const int32_t *lev = S.lev + t * 256;
+      if (((cbp >> t) & 1) && j >= 2 && j < N && lev[j - 2] == 0 && lev[j - 1] == 0 && iabs(lev[j]) > 1) {
+#ifdef THOR_HOSTEMU
+        S.fire[t * 8 + (j >> 5)] |= 1u << (j & 31);
+#else
+        atomicOr(&S.fire[t * 8 + (j >> 5)], 1u << (j & 31));
+#endif
+      }
+    }
+    g.sync();
+    if ((g.tid & 31) == 0)
+      for (int t = g.tid >> 5; t < ntb; t += (g.n + 31) >> 5) {
+        if (!((cbp >> t) & 1)) continue;
+        const int chroma = tb[t].ctype & 1, qp = tb[t].qp;
+        const int thr = (73 * kDequant[qp % 6] << (qp / 6)) >> (4 + lg[t]);
+        int32_t *lev = S.lev + t * 256;
+        const int32_t *lin = S.lin + t * 256;
+        for (int w = 0; w < 8; w++) {
+          uint32_t m = S.fire[t * 8 + w];
+          while (m) {
+            const int b = ilog2(m & (0u - m));
+            m &= m - 1;
+            const int p = 32 * w + b;
+            int ok = 1;
+            if (p > 2 && iabs(lev[p - 3]) > 1) ok = 0;
+            if (p > 3 && iabs(lev[p - 4]) > 1 && iabs(lev[p - 3]) > 0) ok = 0;
+            if (p == 2 && (!chroma || last[t] >= 6)) ok = 0;
+            if (!(ok && lev[p - 2] == 0 && lev[p - 1] == 0 && iabs(lev[p]) > 1)) continue;
+            const int k1 = iabs(lin[p]), k2 = iabs(lin[p - 1]), k3 = iabs(lin[p - 2]);
+            if (k1 + imax(k2, k3) < thr) lev[p] = lin[p] < 0 ? -1 : 1;
+            else if (k2 > k3) lev[p - 1] = lin[p - 1] < 0 ? -1 : 1;
+            else lev[p - 2] = lin[p - 2] < 0 ? -1 : 1;
+          }
+        }
+      }
+    g.sync();
+  }
+  // 7. levels back to raster order (the block's coefficient array) and dequantised (common/common_block.c:132-146)
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j), qq = q[t], qp = tb[t].qp, rshift = lg[t] - 1;
+    const int l = (int16_t)S.lev[t * 256 + zigzag(S, qq)[j]];
+    tb[t].coeffq[(j / qq) * tb[t].size + (j % qq)] = (int16_t)l;
+    S.rcoeff[t * 256 + j] = (int16_t)((((l * kDequant[qp % 6]) << (qp / 6)) + (1 << (rshift - 1))) >> rshift);
+  }
+  g.sync();
+  if (cbp) {
+    // 8. inverse transform (common/transform.c:432-518), blocks with levels only
+    int k0 = ((cbp >> 0) & 1) ? q[0] * ni[0] : 0, k1 = ((cbp >> 1) & 1) ? q[1] * ni[1] : 0, k2 = ((cbp >> 2) & 1) ? q[2] * ni[2] : 0;
+    TFOR(g, i, k0 + k1 + k2) {
+      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = j / keep, k = j % keep;
+      const int8_t *M = dct_matrix(S, nn) + r;
+      const int16_t *rc = S.rcoeff + t * 256 + k;
+      int acc = 0;
+      for (int v = 0; v < keep; v++) acc += M[v * nn] * rc[v * keep];
+      S.mid[t * 512 + k * 32 + r] = (int16_t)iclip((acc + 64) >> 7, -32768, 32767);
+    }
+    g.sync();
+    k0 = ((cbp >> 0) & 1) ? ni[0] * ni[0] : 0; k1 = ((cbp >> 1) & 1) ? ni[1] * ni[1] : 0; k2 = ((cbp >> 2) & 1) ? ni[2] * ni[2] : 0;
+    TFOR(g, i, k0 + k1 + k2) {
+      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = j / nn, c = j % nn;
+      const int8_t *M = dct_matrix(S, nn) + c;
+      const int16_t *m = S.mid + t * 512 + r;
+      int acc = 0;
+      for (int k = 0; k < keep; k++) acc += M[k * nn] * m[k * 32];
+      S.rblock[t * 1024 + j] = (int16_t)iclip((acc + 2048) >> 12, -32768, 32767);
+    }
+    g.sync();
+  }
+  // 9. reconstruction (common/common_block.c:148-156): prediction + residual where the block has levels, else the prediction
+  c0 = tb[0].size * tb[0].size; c1 = ntb > 1 ? tb[1].size * tb[1].size : 0; tot = c0 + c1 + (ntb > 2 ? tb[2].size * tb[2].size : 0);
+  TFOR(g, i, tot) {
+    const int t = tb_of(i, c0, c1, j), size = tb[t].size, r = j / size, c = j % size;
+    int v = tb[t].pred[r * tb[t].pstride + c];
+    if ((cbp >> t) & 1) v = clip255(v + (size == 64 ? S.rblock[t * 1024 + (r >> 1) * 32 + (c >> 1)] : S.rblock[t * 1024 + j]));
+    tb[t].rec[r * tb[t].rstride + c] = (uint8_t)v;
+  }
+  g.sync();
+  return cbp;
+}
+
 // ssd_calc (enc/encode_block.c:782-797) over the three planes of a block: cost_calc's distortion (:1218-1228)
 TDN int ssd_yuv(Grp &g, const Blk &a, const Blk &b, int stride, int width, int height) {
   THOR_SHARED(&a); THOR_SHARED(&b);
