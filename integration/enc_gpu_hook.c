@@ -36,6 +36,19 @@ static int t_frames, t_on = -1;
 static void report(void) {
   fprintf(stderr, "thorcuda frame encoder: %d frames; per frame: decisions %.2f ms, entropy coding %.2f ms, tail %.2f ms\n", t_frames,
           t_dev / (t_frames ? t_frames : 1), t_bits / (t_frames ? t_frames : 1), t_tail / (t_frames ? t_frames : 1));
+#ifndef THOR_EMU
+  {
+    int thorcuda_enc_profile(unsigned long long *out32);
+    static const char *nm[] = {"superblock", "wait", "load_org", "early_skip", "pred_inter", "pred_intra", "tb_chain", "bits", "ssd", "keep_best", "search_intra",
+                               "sad_batch", "fasthalf", "fastquarter", "motion_estimate", "finalize", "neighbours", "bipred_search", "mode_decision"};
+    unsigned long long pf[32];
+    if (thorcuda_enc_profile(pf) == 0 && pf[0]) {
+      fprintf(stderr, "thorcuda frame encoder: Mcycles of CTA time by scope (nested scopes overlap):");
+      for (int i = 0; i < 19; i++) fprintf(stderr, " %s %.1f;", nm[i], pf[i] * 1e-6);
+      fprintf(stderr, "\n");
+    }
+  }
+#endif
   if (t_frames > 2) fprintf(stderr, "thorcuda frame encoder: steady state, %d frames after the second in %.3f s = %.3f frames/s\n", t_frames - 2,
                             (t_last - t_first) * 1e-3, (t_frames - 2) / ((t_last - t_first) * 1e-3));
 }

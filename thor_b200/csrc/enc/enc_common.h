@@ -167,6 +167,29 @@ struct Grp {
 #endif
 };
 
+
+// ---- optional cycle accounting (-DTHOR_ENC_PROF): thread 0 of a CTA adds the clocks spent inside a scope to a category
+enum { PF_SB = 0, PF_WAIT, PF_LOAD_ORG, PF_EARLY, PF_PRED_INTER, PF_PRED_INTRA, PF_TB, PF_BITS, PF_SSD, PF_KEEP, PF_SEARCH_INTRA, PF_SAD, PF_HALF,
+       PF_QUARTER, PF_ME, PF_FINAL, PF_NEIGH, PF_BIPRED, PF_MODE, PF_COUNT };
+#if defined(THOR_ENC_PROF) && !defined(THOR_HOSTEMU)
+__device__ unsigned long long g_enc_prof[32];
+__device__ __forceinline__ long long prof_clock() {
+  long long t = 0;
+#ifdef __CUDA_ARCH__
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+#endif
+  return t;
+}
+struct Prof {
+  int c; long long t0;
+  __device__ Prof(int cat) : c(cat), t0(prof_clock()) {}
+  __device__ ~Prof() { if (threadIdx.x == 0) atomicAdd(&g_enc_prof[c], (unsigned long long)(prof_clock() - t0)); }
+};
+#define PROF(cat) Prof prof_scope_##cat(cat)
+#else
+#define PROF(cat) ((void)0)
+#endif
+
 // iterations i = 0 .. cnt-1 spread over the group; NOT followed by a barrier (call g.sync() where a reader follows)
 #define TFOR(g, i, cnt) for (int i = (g).tid; i < (cnt); i += (g).n)
 

@@ -33,6 +33,7 @@ TD int node_index(int size, int ypos, int xpos) {
 
 // copy_frame_to_block (enc/encode_block.c:1821-1838): the original samples of the block, compact, stride = size
 TDN void load_org(Enc &E, const BlockCtx &B) {
+  PROF(PF_LOAD_ORG);
   THOR_LOCAL(&E); THOR_LOCAL(&B);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -58,6 +59,7 @@ TDN void load_org(Enc &E, const BlockCtx &B) {
 // (i, j): position of the sub-block inside the coding block; (ypos, xpos): plane position of the coding block.
 TDN void make_top_and_left(Enc &E, int pl, const uint8_t *rec_frame, int fstride, const uint8_t *rblock, int rbstride, int i, int j, int ypos, int xpos,
                            int size, int cb_upright, int cb_downleft, int tb_split) {
+  PROF(PF_PRED_INTRA);
   THOR_LOCAL(&E);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -224,6 +226,7 @@ TDN int encode_block(Enc &E, const BlockCtx &B, Param &P) {
 
 // copy_best_parameters (enc/encode_block.c:1983-2045): the trial in S.rec / S.tc / P becomes the block's best so far
 TDN void keep_best(Enc &E, const BlockCtx &B, const Param &P, Param &best) {
+  PROF(PF_KEEP);
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P); THOR_LOCAL(&best);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -312,6 +315,7 @@ TDN int skip_test_chroma(Enc &E, const uint8_t *org, int ostride, int size, int 
 
 // check_early_skip_block (:2613-2741): 1 = no sub-block of the candidate's prediction leaves a significant residual
 TDN int check_early_skip(Enc &E, const BlockCtx &B, const Param &P) {
+  PROF(PF_EARLY);
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -363,6 +367,7 @@ TDN int check_early_skip(Enc &E, const BlockCtx &B, const Param &P) {
 // search_intra_prediction_params (enc/encode_block.c:1230-1329): luma SAD of the intra modes in the reference's order
 // DC, HOR, VER, PLANAR [, UPLEFT, UPRIGHT, UPUPRIGHT, UPUPLEFT, UPLEFTLEFT, DOWNLEFTLEFT]; first minimum wins.
 TDN int search_intra(Enc &E, const BlockCtx &B, int num_intra_modes, int *intra_mode) {
+  PROF(PF_SEARCH_INTRA);
   THOR_LOCAL(&E); THOR_LOCAL(&B);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -435,6 +440,7 @@ TDN int search_inter(Enc &E, const uint8_t *org_y, const thor_enc_pic &ref, cons
 // list against the target 2*org - prediction(other list).  (The me_mode 1 search -- mv0 = -mv1 on B frames at
 // encoder_speed 0 -- is motion_estimate_bi, :1102-1215: not built, see encoder.cu's configuration check.)
 TDN void search_bipred(Enc &E, const BlockCtx &B, int part, const Mv *mv_center, Mv mvp, int *ref_idx0, int *ref_idx1, Mv *mv_arr0, Mv *mv_arr1) {
+  PROF(PF_BIPRED);
   THOR_LOCAL(&E); THOR_LOCAL(&B);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -500,6 +506,7 @@ TD void param_from_cand(Param &P, const InterPred &c, int idx, int mode) {
 }
 
 TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
+  PROF(PF_MODE);
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&best);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -623,6 +630,7 @@ TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
 // What the final encode_block + copy_block_to_frame + copy_deblock_data (:1802-1819, :1947-1981) leave behind, plus the
 // record the host's write_block needs: reconstruction -> picture, neighbour units, node, coefficients.
 TDN void finalize_block(Enc &E, const BlockCtx &B, const Param &P) {
+  PROF(PF_FINAL);
   THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&P);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   Grp &g = E.g;
@@ -801,6 +809,7 @@ TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
 
 // one superblock of encode_frame's loop (enc/encode_frame.c:112-148), including the per-superblock delta-qp search
 TDN void encode_superblock(Enc &E) {
+  PROF(PF_SB);
   THOR_LOCAL(&E);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
   const thor_enc_frame &F = E.F;

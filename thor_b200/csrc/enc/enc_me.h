@@ -8,6 +8,7 @@ namespace thorenc {
 // as) against ref + off[k] (reference picture, stride bs).  Results in S.acc[0..K).  Ends with a barrier.
 // `wide`: each candidate is widesad_calc's five positions x + {-3,-1,0,1,3} (:757-780); results in S.acc[5k .. 5k+5).
 TDN void sad_batch(Grp &g, SbMem &S, const uint8_t *a, int as, const uint8_t *ref, int bs, const int *off, int K, int width, int height, int wide) {
+  PROF(PF_SAD);
   THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHARED(a);
   const int per = wide ? 5 : 1, wq = width >> 2, items = height * wq;
@@ -62,6 +63,7 @@ TD int dnavg(int a, int b) { return (a + b) >> 1; }
 
 // sad_calc_fasthalf (enc/encode_block.c:497-605): eight bilinear half-pel candidates around the integer position b.
 TDN unsigned sad_fasthalf(Grp &g, const uint8_t *a, int as, const uint8_t *b, int bs, int width, int height, int *x, int *y) {
+  PROF(PF_HALF);
   THOR_LOCAL(&g);
   THOR_SHARED(a);
   int s[8] = {0, 0, 0, 0, 0, 0, 0, 0};                     // top down left right tl tr bl br
@@ -122,6 +124,7 @@ TDN unsigned sad_fasthalf(Grp &g, const uint8_t *a, int as, const uint8_t *b, in
 // sad_calc_fastquarter (enc/encode_block.c:609-738): eight quarter-pel candidates; the incoming (*x, *y) select one of
 // four formula sets.
 TDN unsigned sad_fastquarter(Grp &g, const uint8_t *o, int os, const uint8_t *rf, int rs, int width, int height, int *x, int *y) {
+  PROF(PF_QUARTER);
   THOR_LOCAL(&g);
   THOR_SHARED(o);
   const int sel = (*x & *y) ? 0 : (*x ? 1 : (*y ? 2 : 3));
@@ -179,6 +182,7 @@ TD void add_mvcandidate(Grp &g, SbMem &S, SbState &st, int ref_idx, Mv mv) {
 TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const uint8_t *orig, const uint8_t *ref, int size, int stride_r, int width,
                              int height, Mv *mv_out, Mv mvc, Mv mvp, double lambda, int sign, int xpos, int ypos, const Mv *mvcand, int mvcand_num,
                              int enable_bipred) {
+  PROF(PF_ME);
   THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHARED(orig); THOR_SHARED(mvcand); THOR_SHF(&F);
   const int s = sign ? -1 : 1, speed = F.encoder_speed, fw = F.width, fh = F.height;

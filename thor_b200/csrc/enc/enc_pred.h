@@ -133,6 +133,7 @@ TDN void inter_chroma(Grp &g, uint8_t *dst_u, uint8_t *dst_v, int pstride, const
 // `split` is the reference's argument (0: one vector for the block; 1: one per quadrant).
 TDN void inter_yuv(Grp &g, SbMem &S, const thor_enc_frame &F, const thor_enc_pic &ref, Blk &dst, const BlockCtx &B, const Mv *mv_arr, int sign,
                    int bipred, int split) {
+  PROF(PF_PRED_INTER);
   THOR_SHARED(&dst);
   THOR_LOCAL(&B); THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHF(&F);
@@ -209,6 +210,7 @@ TD void smooth121(Grp &g, const uint8_t *in, uint8_t *out, int len) {
 // get_intra_prediction (:363-389) with the ten mode functions (:145-361); pblock: size x size, stride size.
 // Ends with a barrier.
 TDN void intra_predict(Grp &g, SbMem &S, int pl, int ypos, int xpos, int size, uint8_t *pblock, int mode) {
+  PROF(PF_PRED_INTRA);
   THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHARED(pblock);
   const uint8_t *top = S.top[pl], *left = S.left[pl];

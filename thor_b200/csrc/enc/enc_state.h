@@ -132,6 +132,7 @@ TD InterPred zero_pred() {
 
 // get_mv_pred (common/inter_prediction.c:182-294): median of three neighbour vectors chosen by availability
 TDN Mv get_mv_pred(const thor_enc_frame &F, int ypos, int xpos, int size) {
+  PROF(PF_NEIGH);
   THOR_SHF(&F);
   const int bs = size / 4, stride = F.width / 4, idx = (ypos / 4) * stride + xpos / 4;
   const int up0 = idx - stride, up1 = idx - stride + (bs - 1) / 2, up2 = idx - stride + bs - 1;
@@ -157,6 +158,7 @@ TDN Mv get_mv_pred(const thor_enc_frame &F, int ypos, int xpos, int size) {
 
 // get_mv_skip / get_mv_merge (common/inter_prediction.c:296-600 with LIMITED_SKIP: the two functions are the same)
 TDN int get_mv_skip(const thor_enc_frame &F, int ypos, int xpos, int size, InterPred *cand) {
+  PROF(PF_NEIGH);
   THOR_SHF(&F);
   const int bs = size / 4, stride = F.width / 4, idx = (ypos / 4) * stride + xpos / 4;
   const int up0 = idx - stride, left0 = idx - 1, upright = idx - stride + bs;
@@ -340,6 +342,7 @@ TDN int coeff_bits3(Grp &g, SbMem &S, const int16_t *cy, const int16_t *cu, cons
 
 // write_block (enc/write_bits.c:364-650) as a length
 TDN int block_bits(Grp &g, SbMem &S, const thor_enc_frame &F, const BlockCtx &B, const Param &P, const Coef &C) {
+  PROF(PF_BITS);
   THOR_LOCAL(&B); THOR_LOCAL(&P); THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHF(&F);
   const int mode = P.mode, size = B.size, part = P.pb_part;

@@ -171,6 +171,7 @@ TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *
 // transform -> quantise -> (dequantise -> inverse transform -> reconstruct | copy the prediction).  Returns the cbp bit.
 TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8_t *pred, int pstride, uint8_t *rec, int rstride,
                   int16_t *coeffq, int size, int qp, int coeff_type, int fast) {
+  PROF(PF_TB);
   THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHARED(org); THOR_SHARED(pred); THOR_SHARED(rec); THOR_SHARED(coeffq);
   forward_tb(g, S, org, ostride, pred, pstride, size, fast);
@@ -206,6 +207,7 @@ TD int tb_of(int i, int c0, int c1, int &j) {
 }
 
 TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
+  PROF(PF_TB);
   THOR_SHS(&S);
   // geometry per block: forward transform size n (after pooling by f), shifts, kept corner q, inverse size ni
   int n[3] = {0, 0, 0}, f[3] = {1, 1, 1}, sh1[3] = {0, 0, 0}, sh2[3] = {0, 0, 0}, q[3] = {0, 0, 0}, ni[3] = {0, 0, 0}, lg[3] = {0, 0, 0};
@@ -366,6 +368,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
 
 // ssd_calc (enc/encode_block.c:782-797) over the three planes of a block: cost_calc's distortion (:1218-1228)
 TDN int ssd_yuv(Grp &g, const Blk &a, const Blk &b, int stride, int width, int height) {
+  PROF(PF_SSD);
   THOR_SHARED(&a); THOR_SHARED(&b);
   THOR_LOCAL(&g);
   int s = 0;

@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(NT, 1) k_encode_frame(const thor_enc_frame F_a
   build_tables(g, S);
   for (int l = 0; l < nsbx; l++) {
     if (row > 0) {
+      PROF(PF_WAIT);
       const int need = min(l + 2, nsbx);
       if (threadIdx.x == 0)
         while (ld_acquire(F.progress + row - 1) < need) __nanosleep(200);
@@ -94,6 +95,17 @@ static thor_enc_pic pic_of(const Pic *p, int frame_num) {
 }  // namespace thor
 
 using namespace thor;
+
+// cycle accounting of the superblock encoder (only in -DTHOR_ENC_PROF builds; otherwise all zero): out[PF_*], 32 entries
+extern "C" int thorcuda_enc_profile(unsigned long long *out32) {
+#ifdef THOR_ENC_PROF
+  THOR_CUDA(cudaDeviceSynchronize());
+  THOR_CUDA(cudaMemcpyFromSymbol(out32, thorenc::g_enc_prof, 32 * sizeof(unsigned long long)));
+#else
+  memset(out32, 0, 32 * sizeof(unsigned long long));
+#endif
+  return 0;
+}
 
 extern "C" int thorcuda_enc_frame(const thorcuda_enc_params *p, thor_enc_node *host_nodes, thor_enc_coef *host_coef) {
   THOR_NEED_CTX();
