@@ -238,7 +238,6 @@ void thorcuda_enc_superblocks(encoder_info_t *ei) {
   const int nsb = ((ei->width + 63) / 64) * ((ei->height + 63) / 64);
   yuv_frame_t *rec = ei->rec, *org = ei->orig;
   check_config(ei);
-  if (t_on < 0) { t_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (t_on) atexit(report); }
   if (dev_rec < 0) {
     const char *dev = getenv("THORCUDA_DEVICE");
     need(thorcuda_init(dev ? atoi(dev) : 0));
@@ -252,6 +251,8 @@ void thorcuda_enc_superblocks(encoder_info_t *ei) {
     g_coef = (thor_enc_coef *)thorcuda_host_alloc((size_t)nsb * sizeof(thor_enc_coef));
     if (!sb_bits || !g_nodes || !g_coef) fatalerror("thorcuda frame encoder: pinned allocation failed");
   }
+  /* registered after the CUDA runtime's own exit handler, so it runs before it */
+  if (t_on < 0) { t_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (t_on) atexit(report); }
   const double t0 = now_ms();
   lock_frame(org); lock_frame(rec);
   need(thorcuda_pic_upload(dev_org, org->y, org->u, org->v, org->stride_y, org->stride_c));
