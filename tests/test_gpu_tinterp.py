@@ -54,7 +54,7 @@ CASES = [(416, 240, "scene", (3, 5)), (192, 136, "scene", (-7, 12)), (128, 128, 
 
 # Found in round 2 through the encoder (RA streams at 200x136): k_estimate picks different vectors than the reference in the
 # bottom partial block row of these pictures.  Not fixed yet; the encoder binding interpolates on the host by default.
-KNOWN_BAD = {(200, 136, "scene", (-9, 14)), (200, 136, "noise", None)}
+KNOWN_BAD = {(200, 136, "scene", (3, 5)), (200, 136, "noise", None)}
 
 
 @pytest.mark.parametrize("case", CASES, ids=[f"{c[0]}x{c[1]}-{c[2]}-{i}" for i, c in enumerate(CASES)])
