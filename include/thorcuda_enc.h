@@ -107,8 +107,8 @@ typedef struct {
  *   - host_nodes (nsb * THOR_ENC_NODES) and host_coef (nsb), nsb = ceil(w/64) * ceil(h/64) superblocks in raster order,
  *     receive the decisions; they are valid after thorcuda_sync().  Page-locked memory (thorcuda_host_alloc) is DMA'd
  *     directly.
- * Configurations outside what the device code implements are an error, not a fallback (thorcuda_last_error): sync 1,
- * rdoq 1, and encoder_speed 0 on B frames (the simultaneous bi-prediction search motion_estimate_bi). */
+ * The reference's -sync 1 and -rdoq 1 (off in every shipped configuration) are not built: callers must refuse them
+ * (integration/enc_gpu_hook.c does), there is no fallback. */
 int thorcuda_enc_frame(const thorcuda_enc_params *p, thor_enc_node *host_nodes, thor_enc_coef *host_coef);
 
 #ifdef __cplusplus

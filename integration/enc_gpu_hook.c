@@ -151,8 +151,6 @@ static void check_config(const encoder_info_t *ei) {
   const enc_params *p = ei->params;
   if (p->sync) fatalerror("thorcuda frame encoder: -sync 1 is not built");
   if (p->rdoq) fatalerror("thorcuda frame encoder: -rdoq 1 is not built");
-  if (p->encoder_speed == 0 && ei->frame_info.frame_type == B_FRAME && p->enable_bipred)
-    fatalerror("thorcuda frame encoder: the simultaneous bi-prediction search of B frames at -encoder_speed 0 is not built");
   if (ei->frame_info.num_ref > THOR_ENC_MAX_REF) fatalerror("thorcuda frame encoder: too many reference pictures");
 }
 

@@ -438,7 +438,7 @@ TDN int search_inter(Enc &E, const uint8_t *org_y, const thor_enc_pic &ref, cons
 
 // search_bipred_prediction_params (enc/encode_block.c:2047-2202) with me_mode 0: iterative uni-directional search of one
 // list against the target 2*org - prediction(other list).  (The me_mode 1 search -- mv0 = -mv1 on B frames at
-// encoder_speed 0 -- is motion_estimate_bi, :1102-1215: not built, see encoder.cu's configuration check.)
+// encoder_speed 0 -- is motion_estimate_bi in enc_me.h, called from mode_decision.)
 TDN void search_bipred(Enc &E, const BlockCtx &B, int part, const Mv *mv_center, Mv mvp, int *ref_idx0, int *ref_idx1, Mv *mv_arr0, Mv *mv_arr1) {
   PROF(PF_BIPRED);
   THOR_LOCAL(&E); THOR_LOCAL(&B);
@@ -596,6 +596,21 @@ TDN uint32_t mode_decision(Enc &E, BlockCtx &B, Param &best) {
         for (int i = 0; i < 4; i++) { P.mv0[i] = a0[i]; P.mv1[i] = a1[i]; }
         P.tb_param = 0;
         try_cost(E, B, P, best, min_cost, size, size, nullptr);
+        if (F.frame_type == 2 && speed == 0) {
+          // search_bipred_prediction_params with me_mode 1 (:2079-2110): mv0 = -mv1 through the two references' signs
+          const int i0 = F.interp_ref ? 1 : 0, i1 = F.interp_ref ? 2 : 1;
+          const thor_enc_pic &q0 = ref_pic(F, i0), &q1 = ref_pic(F, i1);
+          const int off = B.ypos * q0.stride_y + B.xpos;
+          Mv mv;
+          motion_estimate_bi(g, S, F, S.org.y, q0.y + off, q1.y + off, size, q0.stride_y, &mv, mv_center[i0], mvp, dsqrt(lambda), 0, B.xpos, B.ypos,
+                             S.mvcand[i0], E.st.mvcand_num[i0], 2);
+          P.pb_part = 0;
+          P.ref_idx0 = i0;
+          P.ref_idx1 = i1;
+          for (int i = 0; i < 4; i++) P.mv0[i] = P.mv1[i] = mv;
+          P.tb_param = 0;
+          try_cost(E, B, P, best, min_cost, size, size, nullptr);
+        }
       }
     }
     if (do_intra) {                                                    // intra (:2431-2472)

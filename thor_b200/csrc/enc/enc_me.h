@@ -321,4 +321,65 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
   return cmin < min_sad ? cmin : min_sad;
 }
 
+// motion_estimate_bi (enc/encode_block.c:1102-1215): one vector used with opposite signs in two references (B frames at
+// encoder_speed 0).  3x3 telescope from 8 samples down to a quarter sample around mvc with true interpolation of both
+// references, then six extra candidates taken from -- and, as in the reference, WRITTEN INTO -- the candidate list: entries
+// num..3 are zeroed, entry 4 becomes mvp, entry 5 zero (the list's length is left alone; later searches see the changes).
+TDN unsigned motion_estimate_bi(Grp &g, SbMem &S, const thor_enc_frame &F, const uint8_t *orig, const uint8_t *ref0, const uint8_t *ref1, int size,
+                                int stride_r, Mv *mv_out, Mv mvc, Mv mvp, double lambda, int sign, int xpos, int ypos, Mv *mvcand, int mvcand_num,
+                                int enable_bipred) {
+  THOR_SHS(&S);
+  const int fw = F.width, fh = F.height, n = size * size;
+  uint32_t min_sad = 1u << 31;
+  Mv mv_opt = mkmv(0, 0), mv_ref = mkmv(((mvc.x + 2) >> 2) << 2, ((mvc.y + 2) >> 2) << 2);
+  uint8_t *rf0 = S.p0.y, *rf1 = S.p1.y;
+  int pass = 0;
+  for (int step = 32;; ) {
+    // pass 0: the telescope at this step; pass 1 (after step 0): the extra candidates
+    const int ncand = pass ? 6 : 9;
+    for (int c = 0; c < ncand; c++) {
+      Mv cand;
+      if (!pass) {
+        const int k = (c / 3 - 1) * step, l = (c % 3 - 1) * step;
+        if (step < 32 && k == 0 && l == 0) continue;
+        if (step == 1) {
+          const int vf = mv_ref.y & 3, hf = mv_ref.x & 3;
+          bool skip;
+          if (vf == 0 && hf == 0) skip = iabs(k) != iabs(l);
+          else if (vf == 2 && hf == 2) skip = true;
+          else skip = iabs(k) == iabs(l);
+          if (skip) continue;
+        }
+        cand = mkmv(mv_ref.x + l, mv_ref.y + k);
+      } else {
+        cand = mvcand[c];
+      }
+      cand = clip_mv(cand, ypos, xpos, fw, fh, size, sign);
+      inter_luma(g, S, rf0, size, ref0, stride_r, size, size, cand, sign, enable_bipred);
+      cand = clip_mv(cand, ypos, xpos, fw, fh, size, 1 - sign);
+      inter_luma(g, S, rf1, size, ref1, stride_r, size, size, cand, 1 - sign, enable_bipred);
+      int acc = 0;
+      TFOR(g, i, n / 4) acc += (int)sad4(reinterpret_cast<const uint32_t *>(orig)[i], havg4(reinterpret_cast<const uint32_t *>(rf0)[i], reinterpret_cast<const uint32_t *>(rf1)[i]));
+      int sad = g.sum(acc);
+      sad += (int)dadd(dmul(lambda, (double)mv_bits((int16_t)(cand.y - mvp.y), (int16_t)(cand.x - mvp.x))), 0.5);
+      if ((uint32_t)sad < min_sad) { min_sad = (uint32_t)sad; mv_opt = cand; }
+    }
+    if (pass) break;
+    mv_ref = mv_opt;
+    step >>= 1;
+    if (step == 0) {
+      g.sync();
+      if (g.tid == 0) {
+        for (int idx = mvcand_num; idx < 4; idx++) mvcand[idx] = mkmv(0, 0);
+        mvcand[4] = mvp;
+        mvcand[5] = mkmv(0, 0);
+      }
+      g.sync();
+      pass = 1;
+    }
+  }
+  *mv_out = mv_opt;
+  return min_sad;
+}
+
 }  // namespace thorenc

@@ -117,8 +117,6 @@ extern "C" int thorcuda_enc_frame(const thorcuda_enc_params *p, thor_enc_node *h
   if (p->max_delta_qp && p->delta_qp_step <= 0) return fail("enc_frame: delta_qp_step %d", p->delta_qp_step);
   if (p->num_ref < 0 || p->num_ref > THOR_ENC_MAX_REF || (p->frame_type != 0 && p->num_ref == 0)) return fail("enc_frame: %d reference pictures", p->num_ref);
   if (p->encoder_speed < 0 || p->encoder_speed > 2) return fail("enc_frame: encoder_speed %d", p->encoder_speed);
-  if (p->encoder_speed == 0 && p->frame_type == 2 && p->enable_bipred)
-    return fail("enc_frame: the simultaneous bi-prediction search of B frames at encoder_speed 0 (motion_estimate_bi) is not built");
   Pic *org = get_pic(p->orig), *rec = get_pic(p->rec);
   if (!org || !rec) return fail("enc_frame: bad picture handle");
   if (org->w != p->width || org->h != p->height || rec->w != p->width || rec->h != p->height) return fail("enc_frame: orig / rec size differs from %dx%d", p->width, p->height);
