@@ -44,7 +44,7 @@ def test_headers_declare_something():
                         "widesad_calc_simd", "transform", "inverse_transform"])
 
 
-@pytest.mark.parametrize("header", ["thorcuda.h", "thorcuda_compat.h"])
+@pytest.mark.parametrize("header", ["thorcuda.h", "thorcuda_compat.h", "thorcuda_enc.h"])
 def test_every_declared_symbol_is_exported(lib, header):
     missing = [n for n in declared_functions(header) if not hasattr(lib, n)]
     assert not missing, f"declared in include/{header} but not exported by libthorcuda.so: {missing}"
