@@ -204,6 +204,9 @@ void thorcuda_enc_superblocks(encoder_info_t *ei) {
 static void need(int rc) { if (rc) fatalerror((char *)thorcuda_last_error()); }
 
 static thorcuda_pic dev_rec = -1, dev_org = -1, dev_newref = -1, dev_interp = -1;
+static int dev_timer = -1;            /* CUDA-event timer around a frame's device work (upload .. tail) */
+static FILE *frame_log;               /* THORCUDA_HOOK_FRAMELOG: one line per frame: index, host clock (ms), device ms */
+static double t_dev_events;
 static uint8_t *sb_bits;
 /* the encoder's reference ring by handle: the host pictures keep their identity (pointers rotate,
  * enc/encode_frame.c:168-177), each has a device twin created the first time it is seen */
@@ -253,6 +256,7 @@ void thorcuda_enc_superblocks(encoder_info_t *ei) {
   if (t_on < 0) { t_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (t_on) atexit(report); }
   const double t0 = now_ms();
   lock_frame(org); lock_frame(rec);
+  dev_timer = thorcuda_timer_begin();
   need(thorcuda_pic_upload(dev_org, org->y, org->u, org->v, org->stride_y, org->stride_c));
   const enc_params *p = ei->params;
   const frame_info_t *fi = &ei->frame_info;
@@ -289,7 +293,9 @@ void thorcuda_enc_tail(encoder_info_t *ei, stream_t *stream, int qp) {
   if (ei->params->clpf) stages |= THORCUDA_LF_CLPF;
   need(thorcuda_loopfilter_frame(dev_rec, dev_org, dev_newref, qp, stages, NULL, sb_bits));
   need(thorcuda_pic_download(dev_rec, rec->y, rec->u, rec->v, rec->stride_y, rec->stride_c));   /* -rf output, PSNR */
+  if (dev_timer >= 0) thorcuda_timer_end(dev_timer);
   need(thorcuda_sync());
+  if (dev_timer >= 0) { t_dev_events = thorcuda_timer_elapsed_ms(dev_timer); dev_timer = -1; }
   if (ei->params->clpf) {
     putbits(1, 1, stream);            /* frame-level enable */
     putbits(1, 0, stream);            /* "every superblock signals its own bit" */
@@ -311,6 +317,8 @@ void thorcuda_enc_make_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
   t_frames++;
   t_last = now_ms();
   if (t_frames == 2) t_first = t_last;
+  if (!frame_log && getenv("THORCUDA_HOOK_FRAMELOG")) frame_log = fopen(getenv("THORCUDA_HOOK_FRAMELOG"), "w");
+  if (frame_log) { fprintf(frame_log, "%d %.3f %.3f %llu\n", t_frames - 1, t_last, t_dev_events, (unsigned long long)thorcuda_launch_count()); fflush(frame_log); }
 }
 
 /* interpolate_frames + pad_yuv_frame (enc/mainenc.c:328-329, :385-386).  Default: the reference's own interpolate_frames on

@@ -158,6 +158,9 @@ int thorcuda_init(int device) {
   THOR_CUDA(cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10)
     return fail("libthorcuda: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+  // THORCUDA_BLOCKING_SYNC=1: host threads sleep in thorcuda_sync() instead of spinning -- for many encoder / decoder processes
+  // per host (one per stream, bench.py), whose frames take far longer on the device than a wake-up costs
+  if (getenv("THORCUDA_BLOCKING_SYNC")) cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync);
   THOR_CUDA(cudaSetDevice(device));
   THOR_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
   THOR_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
