@@ -34,35 +34,62 @@ __device__ __forceinline__ int ld_acquire(const int *p) {
 }
 __device__ __forceinline__ void st_release(int *p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 
-__global__ void __launch_bounds__(NT, 1) k_encode_frame(const thor_enc_frame F_arg, int *ticket) {
+// Scheduling.  Superblock (r, c) may start when (r, c-1) and (r-1, min(c+1, last)) are finished.  Nothing but `progress`
+// carries over from one superblock to the next (the candidate lists and best_ref are reset per superblock,
+// enc/encode_frame.c:117-121), so a CTA is not tied to a row: every CTA repeatedly claims the next superblock of the lowest
+// row that is ready and not being worked on (one lock word per row).  With one CTA per row about half of each CTA's life
+// is spent waiting for the row above while it holds an SM; pulling work lets fewer CTAs (about rows/2 + a few) finish the
+// frame in the same number of wavefront steps, which is what lets twice as many independent frames share the device.
+// The lowest unfinished row is always either ready or being worked on, so any number of resident CTAs >= 1 makes progress.
+__global__ void __launch_bounds__(NT, 1) k_encode_frame(const thor_enc_frame F_arg, int *busy) {
   extern __shared__ __align__(16) uint8_t smem[];
   SbMem &S = *reinterpret_cast<SbMem *>(smem);
-  __shared__ int s_row;
+  __shared__ int s_row, s_col;
   Grp g;
   g.tid = threadIdx.x;
   g.red = S.red;
   g.flip = 0;
-  if (threadIdx.x == 0) s_row = atomicAdd(ticket, 1);
   for (int i = threadIdx.x; i < (int)(sizeof(thor_enc_frame) / 4); i += NT) reinterpret_cast<int *>(&S.frame)[i] = reinterpret_cast<const int *>(&F_arg)[i];
   __syncthreads();
   const thor_enc_frame &F = S.frame;
-  const int row = s_row;
   const int nsbx = (F.width + 63) / 64, nsby = (F.height + 63) / 64;
-  if (row >= nsby) return;
   build_tables(g, S);
-  for (int l = 0; l < nsbx; l++) {
-    if (row > 0) {
+  for (;;) {
+    if (threadIdx.x == 0) {
       PROF(PF_WAIT);
-      const int need = min(l + 2, nsbx);
-      if (threadIdx.x == 0)
-        while (ld_acquire(F.progress + row - 1) < need) __nanosleep(200);
-      __syncthreads();
+      int row = -1, col = 0;
+      for (;;) {
+        bool all_done = true;
+        for (int r = 0; r < nsby && row < 0; r++) {
+          const int done = ld_acquire(F.progress + r);
+          if (done >= nsbx) continue;
+          all_done = false;
+          if (r > 0 && ld_acquire(F.progress + r - 1) < min(done + 2, nsbx)) continue;   // waits for the row above (a lower row may still be ready)
+          if (atomicCAS(busy + r, 0, 1) == 0) {
+            __threadfence();
+            col = ld_acquire(F.progress + r);                // re-read under the lock
+            if (col < nsbx && (r == 0 || ld_acquire(F.progress + r - 1) >= min(col + 2, nsbx))) row = r;
+            else atomicExch(busy + r, 0);
+          }
+        }
+        if (row >= 0 || all_done) break;
+        __nanosleep(500);
+      }
+      s_row = row;
+      s_col = col;
     }
+    __syncthreads();
+    const int row = s_row, l = s_col;
+    if (row < 0) return;
     Enc E{g, S, F, SbState(), F.nodes + (size_t)(row * nsbx + l) * THOR_ENC_NODES, F.coef + (row * nsbx + l), l * 64, row * 64};
     encode_superblock(E);
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) st_release(F.progress + row, l + 1);
+    if (threadIdx.x == 0) {
+      st_release(F.progress + row, l + 1);
+      __threadfence();
+      atomicExch(busy + row, 0);
+    }
   }
 }
 
@@ -146,17 +173,22 @@ extern "C" int thorcuda_enc_frame(const thorcuda_enc_params *p, thor_enc_node *h
   F.units = (thor_enc_unit *)g_units.reserve(nunits * sizeof(thor_enc_unit));
   F.nodes = (thor_enc_node *)g_nodes.reserve(node_bytes);
   F.coef = (thor_enc_coef *)g_coef.reserve(coef_bytes);
-  int *sync = (int *)g_sync.reserve((size_t)(nsby + 1) * sizeof(int));
+  int *sync = (int *)g_sync.reserve((size_t)(2 * nsby) * sizeof(int));      // row locks | progress
   if (!F.units || !F.nodes || !F.coef || !sync) return fail("enc_frame: device allocation failed");
-  F.progress = sync + 1;
+  F.progress = sync + nsby;
   THOR_CUDA(cudaMemsetAsync(F.units, 0, nunits * sizeof(thor_enc_unit), c.stream));   // encode_frame's memset of deblock_data (:74)
   THOR_CUDA(cudaMemsetAsync(F.nodes, 0, node_bytes, c.stream));
-  THOR_CUDA(cudaMemsetAsync(sync, 0, (size_t)(nsby + 1) * sizeof(int), c.stream));
+  THOR_CUDA(cudaMemsetAsync(sync, 0, (size_t)(2 * nsby) * sizeof(int), c.stream));
   if (!g_attr_set) {
     THOR_CUDA(cudaFuncSetAttribute(k_encode_frame, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SbMem)));
     g_attr_set = true;
   }
-  k_encode_frame<<<nsby, NT, sizeof(SbMem), c.stream>>>(F, sync);
+  // CTAs per frame: by default as many as the wavefront can ever keep busy, min(rows, ceil(cols / 2)) -- the shortest frame
+  // time; THORCUDA_ENC_CTAS lowers it when many frames share the device (bench.py: more streams per GPU at nearly the same
+  // time per frame)
+  int ctas = std::min(nsby, (nsbx + 1) / 2);
+  if (const char *e = getenv("THORCUDA_ENC_CTAS")) ctas = std::max(1, std::min(atoi(e), nsby));
+  k_encode_frame<<<ctas, NT, sizeof(SbMem), c.stream>>>(F, sync);
   THOR_LAUNCHED();
   if (!rec->info) THOR_CUDA(cudaMalloc((void **)&rec->info, nunits * 2));
   k_units_to_info<<<(unsigned)((nunits + 255) / 256), 256, 0, c.stream>>>(F.units, rec->info, (int)nunits);
