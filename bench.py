@@ -187,35 +187,47 @@ def encoder_e2e_leg(args, workdir, env):
     return res, ref
 
 
+def cut_stream(bit, chunks, out):
+    """the first `chunks` coded frames of a stream (frames are 4-byte-length-prefixed chunks, enc/putbits.c:57-95)"""
+    import struct
+    data, i = open(bit, "rb").read(), 0
+    for _ in range(chunks):
+        i += 4 + struct.unpack(">I", data[i:i + 4])[0]
+    open(out, "wb").write(data[:i])
+
+
 def decoder_e2e_leg(args, workdir):
-    """stock Thordec vs Thordec_gpu (whole reconstruction on the device) on RA streams the stock encoder makes here"""
+    """stock Thordec vs Thordec_gpu (whole reconstruction on the device) on RA streams the stock encoder makes here; rate between
+    a short and a long stream (both end on a sub-GOP boundary), which cancels process and CUDA start-up"""
     if not all(os.path.exists(x) for x in (REF_ENC, REF_DEC, GPU_DEC)):
         return {"unavailable": "oracle/_ref/Thorenc, Thordec or integration/_build/Thordec_gpu not built"}
     from thorref import write_hard_clip
     out = {}
-    for (w, h, n) in ((1920, 1080, 40), (3840, 2160, 17)):
+    for (w, h, short, n) in ((1920, 1080, 41, 89), (3840, 2160, 17, 33)):
         yuv = os.path.join(workdir, f"dec_{w}x{h}.yuv")
         write_hard_clip(yuv, w, h, n, 43, noise=2.0)
         pre = os.path.join(workdir, f"dec_{w}x{h}")
-        subprocess.run(enc_cmd(REF_ENC, "RA_low_complexity", yuv, w, h, n, 32, pre, rec=True), check=True, capture_output=True, timeout=1800)
+        subprocess.run(enc_cmd(REF_ENC, "RA_low_complexity", yuv, w, h, n, 32, pre, rec=True), check=True, capture_output=True, timeout=2400)
         os.remove(yuv)
-        res = {"stream": f"RA_low_complexity {w}x{h} qp 32, {n} frames, {os.path.getsize(pre + '.bit')} bytes"}
+        cut_stream(pre + ".bit", short, pre + "_short.bit")
+        res = {"stream": f"RA_low_complexity {w}x{h} qp 32, {short} and {n} frames, {os.path.getsize(pre + '.bit')} bytes"}
         outs = {}
         for name, exe in (("stock", REF_DEC), ("gpu", GPU_DEC)):
-            best = None
-            for _ in range(2):
-                t0 = time.perf_counter()
-                subprocess.run([exe, pre + ".bit", pre + f"_{name}.yuv"], check=True, capture_output=True, timeout=900)
-                dt = time.perf_counter() - t0
-                best = dt if best is None else min(best, dt)
+            best = {}
+            for key, bit in (("short", pre + "_short.bit"), ("long", pre + ".bit")):
+                for _ in range(3):
+                    t0 = time.perf_counter()
+                    subprocess.run([exe, bit, pre + f"_{name}.yuv"], check=True, capture_output=True, timeout=900)
+                    dt = time.perf_counter() - t0
+                    best[key] = min(best.get(key, dt), dt)
             outs[name] = open(pre + f"_{name}.yuv", "rb").read()
             os.remove(pre + f"_{name}.yuv")
-            res[name + "_fps"] = round(n / best, 2)
-            res[name + "_seconds"] = round(best, 3)
+            res[name + "_fps"] = round((n - short) / max(best["long"] - best["short"], 1e-6), 2)
+            res[name + "_seconds"] = {k: round(v, 3) for k, v in best.items()}
         res["identical_yuv"] = outs["stock"] == outs["gpu"] == open(pre + "_rec.yuv", "rb").read()
         os.remove(pre + "_rec.yuv")
         out[f"{w}x{h}"] = res
-    out["note"] = "whole-process wall clock, best of 2, files in tmpfs; the hooked decoder's figure includes its CUDA start-up (0.4-0.6 s)"
+    out["note"] = "frames per second between the short and the long stream (process wall clock, best of 3 each, files in tmpfs)"
     return out
 
 
@@ -223,7 +235,7 @@ def decoder_e2e_leg(args, workdir):
 def workload_config(args, streams):
     return {"workload": f"Thorenc config_{args.config}.txt {args.width}x{args.height} 8-bit synthetic (hard clip, noise 5), qp {args.qp}: "
                         f"whole encode, decisions on the device, entropy coding on the host",
-            "streams_per_gpu": streams, "frames_per_step": streams, "qp": args.qp,
+            "streams_per_gpu": streams, "frames_per_step": streams, "ctas_per_frame": args.ctas_per_frame, "qp": args.qp,
             "l2": "every frame's working set (original, 2 references, reconstruction, decisions: ~23 MB) is new data per step and stream; "
                   "the streams' frames together exceed the 126 MB L2",
             "parallelism": "independent streams (one encoder process each, CUDA MPS), one rank per GPU, no collective"}
@@ -292,13 +304,15 @@ def run_gpu_arm(args, rank, world, local_rank):
         barrier()
         env = {"CUDA_VISIBLE_DEVICES": str(local_rank)} if world > 1 or "CUDA_VISIBLE_DEVICES" not in os.environ else {}
         mps_on = allmax(1.0 if mps.on else 0.0) > 0          # rank 0 knows; everybody uses the same pipe directory
+        senv = dict(env, THORCUDA_ENC_CTAS=str(args.ctas_per_frame))
         if mps_on:
+            senv.update({"CUDA_MPS_PIPE_DIRECTORY": os.path.join(mps_dir, "pipe"), "CUDA_MPS_LOG_DIRECTORY": os.path.join(mps_dir, "log")})
             env.update({"CUDA_MPS_PIPE_DIRECTORY": os.path.join(mps_dir, "pipe"), "CUDA_MPS_LOG_DIRECTORY": os.path.join(mps_dir, "log")})
         sampler = ClockSampler(local_rank)
         try:
             barrier()
             sampler.start()
-            streams = run_streams(GPU_ENC, args.config, yuv, args.width, args.height, frames, args.qp, S, d, env, "s")
+            streams = run_streams(GPU_ENC, args.config, yuv, args.width, args.height, frames, args.qp, S, d, senv, "s")
             clocks = sampler.stop()
             barrier()
             dev_s, host_s, launches = 0.0, 0.0, 0
@@ -363,7 +377,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="thorcuda", choices=["thorcuda", "reference"])
-    ap.add_argument("--streams", type=int, default=8, help="independent encoder processes per GPU = frames per step")
+    ap.add_argument("--streams", type=int, default=16, help="independent encoder processes per GPU = frames per step")
+    ap.add_argument("--ctas-per-frame", type=int, default=9, help="CTAs k_encode_frame uses per frame in the multi-stream run (THORCUDA_ENC_CTAS): "
+                    "streams x this should not exceed the 148 SMs; the one-stream legs use the library default, min(rows, cols/2)")
     ap.add_argument("--config", default="LDB_medium_complexity")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
