@@ -32,13 +32,13 @@ struct SbMem {
   thor_enc_frame frame;              // the frame description: copied from the kernel parameters once per CTA
   Blk org, rec, best, pred, p0, p1;
   Coef tc, bc;                       // coefficients of the trial / of the best trial so far
-  int16_t resid[4096];               // transform input of the current transform block (stride = its size)
+  int16_t resid[3 * 1024];           // transform input (n <= 32 after pooling), slot t at t * 1024
   // transform scratch: three transform blocks (Y, U, V of a coding block) are in flight at once, slot t at t * stride
   int16_t mid[3 * 16 * 32];          // transform intermediate
   int16_t coeff[3 * 256];            // low q x q corner of the forward transform, stride q
   int16_t rcoeff[3 * 256];           // dequantised, stride q
   int16_t rblock[3 * 1024];          // inverse transform output (n <= 32), stride n
-  int32_t lin[3 * 256], lev[3 * 256];// quantiser: coefficients / levels in scan order
+  int16_t lin[3 * 256], lev[3 * 256];// quantiser: coefficients / levels in scan order (levels < 2^15: |c| * 26214 >> 15)
   int16_t itmp[69 * 64];             // interpolation: first-pass intermediate (rows -2 .. h+2)
   int16_t scan[3 * 256];             // bit counter: levels in scan order (three planes at once)
   int bits3[4];

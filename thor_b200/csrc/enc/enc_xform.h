@@ -63,7 +63,7 @@ TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coe
   int mylast = -1;
   TFOR(g, i, nq) {
     const int c = S.coeff[i], p = zz[i];
-    S.lin[p] = c;
+    S.lin[p] = (int16_t)c;
     if ((iabs(iabs(c) * scale + tail_off) >> shift) != 0) mylast = imax(mylast, p);
   }
   const int last = g.vmax(mylast);                         // last_pos (:95-104); barrier inside
@@ -77,7 +77,7 @@ TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coe
       mine |= l != 0;
       if (c < 0) l = -l;
     }
-    S.lev[p] = l;
+    S.lev[p] = (int16_t)l;
   }
   if (g.tid < 8) S.fire[g.tid] = 0;
 #ifdef THOR_HOSTEMU
@@ -260,7 +260,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     const int intra = (tb[t].ctype >> 1) & 1, shift = 21 - lg[t] + tb[t].qp / 6, scale = kQuant[tb[t].qp % 6];
     const int tail_off = (intra ? 38 : -26) * (1 << (shift - 8));
     const int c = S.coeff[t * 256 + j], p = zigzag(S, q[t])[j];
-    S.lin[t * 256 + p] = c;
+    S.lin[t * 256 + p] = (int16_t)c;
     if ((iabs(iabs(c) * scale + tail_off) >> shift) != 0) last[t] = imax(last[t], p);
   }
   g.vmax3(last);                                                       // barrier inside
@@ -277,7 +277,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
       if (l) mine |= 1 << t;
       if (c < 0) l = -l;
     }
-    S.lev[t * 256 + j] = l;
+    S.lev[t * 256 + j] = (int16_t)l;
   }
   TFOR(g, i, 24) S.fire[i] = 0;
   const int cbp = g.orall(mine);                                       // barrier inside
@@ -286,7 +286,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     TFOR(g, i, tot) {
       const int t = tb_of(i, c0, c1, j);
       const int N = (tb[t].ctype & 1) ? last[t] + 1 : q[t] * q[t];
-      const int32_t *lev = S.lev + t * 256;
+      const int16_t *lev = S.lev + t * 256;
       if (((cbp >> t) & 1) && j >= 2 && j < N && lev[j - 2] == 0 && lev[j - 1] == 0 && iabs(lev[j]) > 1) {
 #ifdef THOR_HOSTEMU
         S.fire[t * 8 + (j >> 5)] |= 1u << (j & 31);
@@ -301,8 +301,8 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
         if (!((cbp >> t) & 1)) continue;
         const int chroma = tb[t].ctype & 1, qp = tb[t].qp;
         const int thr = (73 * kDequant[qp % 6] << (qp / 6)) >> (4 + lg[t]);
-        int32_t *lev = S.lev + t * 256;
-        const int32_t *lin = S.lin + t * 256;
+        int16_t *lev = S.lev + t * 256;
+        const int16_t *lin = S.lin + t * 256;
         for (int w = 0; w < 8; w++) {
           uint32_t m = S.fire[t * 8 + w];
           while (m) {
