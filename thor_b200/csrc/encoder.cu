@@ -41,7 +41,10 @@ __device__ __forceinline__ void st_release(int *p, int v) { asm volatile("st.rel
 // is spent waiting for the row above while it holds an SM; pulling work lets fewer CTAs (about rows/2 + a few) finish the
 // frame in the same number of wavefront steps, which is what lets twice as many independent frames share the device.
 // The lowest unfinished row is always either ready or being worked on, so any number of resident CTAs >= 1 makes progress.
-__global__ void __launch_bounds__(NT, NT <= 128 ? 2 : 1) k_encode_frame(const thor_enc_frame F_arg, int *busy) {
+#ifndef THOR_ENC_MIN_CTAS
+#define THOR_ENC_MIN_CTAS (NT <= 128 ? 2 : 1)
+#endif
+__global__ void __launch_bounds__(NT, THOR_ENC_MIN_CTAS) k_encode_frame(const thor_enc_frame F_arg, int *busy) {
   extern __shared__ __align__(16) uint8_t smem[];
   SbMem &S = *reinterpret_cast<SbMem *>(smem);
   __shared__ int s_row, s_col;
