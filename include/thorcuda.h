@@ -275,6 +275,16 @@ typedef struct {
  * cbp bit is set, as in the reference.  Records are validated on the host (error, no launch).  host_bits is valid
  * after thorcuda_sync().                                                                                           */
 int thorcuda_block_bits(thorcuda_list l, const thorcuda_block_syntax *host_blocks, int nblocks, uint32_t *host_bits);
+/* The syntax bits of the same records (what thorcuda_block_bits(-1, ...) returns) through an entry point that ALLOCATES NOTHING.
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  The device-side copy of the records and of the results lives in a
+ * file-scope device array of the library, sized for THORCUDA_BLOCK_BITS_STATIC_MAX blocks (272 KiB, held by every GPU that loads the
+ * library until exit); more blocks are an error (split the call).  The call makes no cudaMalloc / cudaFree / pinned allocation: host
+ * buffers are copied directly.  It is synchronous (host_bits is valid on return).  Every call shares the one array, which keeps the
+ * previous call's contents (nothing in it needs clearing: the entries a call reads are the ones it has just written); calls that
+ * overlap on the GPU -- several host threads, or a caller driving several contexts -- race on it and must be serialised. */
+#define THORCUDA_BLOCK_BITS_STATIC_MAX 4096
+int thorcuda_block_bits_static(const thorcuda_block_syntax *host_blocks, int nblocks, uint32_t *host_bits);
 /* host arithmetic (no device work): quote_vlc (enc/putvlc.c:133-229; -1 where the reference aborts) and the bits of
  * write_mv (enc/write_bits.c:50-69) = quote_mv_bits (enc/encode_block.c:799-814) */
 int thorcuda_vlc_len(unsigned n, unsigned cn);

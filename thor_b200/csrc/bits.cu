@@ -270,6 +270,12 @@ __global__ void __launch_bounds__(128) k_block_bits(const thorcuda_block_syntax 
 }
 
 static DevBuf g_blk_in, g_blk_out;
+
+// Scratch of thorcuda_block_bits_static: the records of one call and their results, in a file-scope device array -- the
+// entry point must not allocate.  Every GPU that loads the library holds these 272 KiB until exit.  In host code the name
+// below is only a stand-in for the device symbol: its device address comes from cudaGetSymbolAddress, once per device.
+static __device__ __align__(256) uint8_t g_bb_static[THORCUDA_BLOCK_BITS_STATIC_MAX * (sizeof(thorcuda_block_syntax) + sizeof(uint32_t))];
+static uint8_t *g_bb_static_ptr[64];          // device address of g_bb_static, per device ordinal (nullptr: not looked up yet)
 static bool scan_ready = false;
 static int upload_scan() {
   if (scan_ready) return 0;
@@ -290,6 +296,21 @@ static int upload_scan() {
   return 0;
 }
 void bits_reset() { scan_ready = false; g_blk_in.release(); g_blk_out.release(); }
+
+// what k_block_bits would otherwise have to guard per thread; L: the list tb_first indexes, or nullptr
+static int validate_blocks(const char *who, const thorcuda_block_syntax *host_blocks, int nblocks, const List *L) {
+  for (int i = 0; i < nblocks; i++) {
+    const thorcuda_block_syntax &b = host_blocks[i];
+    if (b.size != 8 && b.size != 16 && b.size != 32 && b.size != 64) return fail("%s: block %d has size %d", who, i, b.size);
+    if (b.mode > 4 || b.frame_type > 2 || b.pb_part > 3 || b.intra_mode > 9) return fail("%s: block %d is malformed", who, i);
+    if (!b.tb_split && (b.cbp_y | b.cbp_u | b.cbp_v) > 1) return fail("%s: block %d has cbp masks without tb_split", who, i);
+    if (L && b.mode != 0 && b.tb_first != 0xffffffffu) {
+      const uint32_t cnt = !b.tb_split ? 3 : b.size > 8 ? 12 : 6;
+      if ((uint64_t)b.tb_first + cnt > (uint64_t)L->ntasks) return fail("%s: block %d: transform blocks %u..%u outside the list", who, i, b.tb_first, b.tb_first + cnt - 1);
+    }
+  }
+  return 0;
+}
 
 }  // namespace thor
 
@@ -325,16 +346,7 @@ int thorcuda_block_bits(thorcuda_list hl, const thorcuda_block_syntax *host_bloc
     L = get_list(hl);
     if (!L || L->kind != THORCUDA_LIST_TB) return fail("block_bits: not a transform-block list");
   }
-  for (int i = 0; i < nblocks; i++) {                     // what the kernel would otherwise have to guard per thread
-    const thorcuda_block_syntax &b = host_blocks[i];
-    if (b.size != 8 && b.size != 16 && b.size != 32 && b.size != 64) return fail("block_bits: block %d has size %d", i, b.size);
-    if (b.mode > 4 || b.frame_type > 2 || b.pb_part > 3 || b.intra_mode > 9) return fail("block_bits: block %d is malformed", i);
-    if (!b.tb_split && (b.cbp_y | b.cbp_u | b.cbp_v) > 1) return fail("block_bits: block %d has cbp masks without tb_split", i);
-    if (L && b.mode != 0 && b.tb_first != 0xffffffffu) {
-      const uint32_t cnt = !b.tb_split ? 3 : b.size > 8 ? 12 : 6;
-      if ((uint64_t)b.tb_first + cnt > (uint64_t)L->ntasks) return fail("block_bits: block %d: transform blocks %u..%u outside the list", i, b.tb_first, b.tb_first + cnt - 1);
-    }
-  }
+  if (validate_blocks("block_bits", host_blocks, nblocks, L)) return -1;
   // the previous call's output copy may still be reading g_blk_out
   if (copies_fence()) return -1;
   auto *d_in = (thorcuda_block_syntax *)g_blk_in.reserve((size_t)nblocks * sizeof(thorcuda_block_syntax));
@@ -344,6 +356,34 @@ int thorcuda_block_bits(thorcuda_list hl, const thorcuda_block_syntax *host_bloc
   k_block_bits<<<(nblocks + 127) / 128, 128, 0, c.stream>>>(d_in, nblocks, L ? L->bits : nullptr, L ? L->ntasks : 0, d_out);
   THOR_LAUNCHED();
   return d2h(host_bits, d_out, (size_t)nblocks * 4);
+}
+
+// The syntax bits of write_block without any allocation by the library: see thorcuda.h.  Synchronous.
+int thorcuda_block_bits_static(const thorcuda_block_syntax *host_blocks, int nblocks, uint32_t *host_bits) {
+  THOR_NEED_CTX();
+  Context &c = ctx();
+  if (nblocks <= 0) return 0;
+  if (!host_blocks || !host_bits) return fail("block_bits_static: null argument");
+  if (nblocks > THORCUDA_BLOCK_BITS_STATIC_MAX)
+    return fail("block_bits_static: %d blocks exceed the static scratch of %d (THORCUDA_BLOCK_BITS_STATIC_MAX); split the call or use thorcuda_block_bits", nblocks,
+                THORCUDA_BLOCK_BITS_STATIC_MAX);
+  if (c.device < 0 || c.device >= 64) return fail("block_bits_static: device ordinal %d", c.device);
+  if (validate_blocks("block_bits_static", host_blocks, nblocks, nullptr)) return -1;
+  if (!g_bb_static_ptr[c.device]) {             // set-up, once per device, with that device current (thorcuda_init made it so)
+    void *p = nullptr;
+    THOR_CUDA(cudaGetSymbolAddress(&p, g_bb_static));
+    g_bb_static_ptr[c.device] = (uint8_t *)p;
+  }
+  auto *d_in = (thorcuda_block_syntax *)g_bb_static_ptr[c.device];
+  auto *d_out = (uint32_t *)(g_bb_static_ptr[c.device] + (size_t)THORCUDA_BLOCK_BITS_STATIC_MAX * sizeof(thorcuda_block_syntax));
+  // the array keeps the previous call's contents; nothing in it has to start at zero: the first nblocks records and results are
+  // overwritten before they are read.  Straight copies from / to the caller's buffers (no staging ring, which may allocate).
+  THOR_CUDA(cudaMemcpyAsync(d_in, host_blocks, (size_t)nblocks * sizeof(thorcuda_block_syntax), cudaMemcpyHostToDevice, c.stream));
+  k_block_bits<<<(nblocks + 127) / 128, 128, 0, c.stream>>>(d_in, nblocks, nullptr, 0, d_out);
+  THOR_LAUNCHED();
+  THOR_CUDA(cudaMemcpyAsync(host_bits, d_out, (size_t)nblocks * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+  THOR_CUDA(cudaStreamSynchronize(c.stream));
+  return 0;
 }
 
 // pure host arithmetic, like thorcuda_clip_mv: the scalar glue of the bit-cost model

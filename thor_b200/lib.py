@@ -87,7 +87,7 @@ def cdll():
                 ("thorcuda_intra_reconstruct_levels", I, [V, I, V, V, V, V, I, V]),
                 ("thorcuda_interpolate_frames", I, [I, I, I, I, I]), ("thorcuda_interp_levels", I, [I, I]),
                 ("thorcuda_interp_field", I, [V, V, V]),
-                ("thorcuda_coeff_bits_list", I, [I, V, V]), ("thorcuda_block_bits", I, [I, V, I, V]), ("thorcuda_vlc_len", I, [C.c_uint, C.c_uint]),
+                ("thorcuda_coeff_bits_list", I, [I, V, V]), ("thorcuda_block_bits", I, [I, V, I, V]), ("thorcuda_block_bits_static", I, [V, I, V]), ("thorcuda_vlc_len", I, [C.c_uint, C.c_uint]),
                 ("thorcuda_mv_bits", I, [I, I, I, I]),
                 ("thorcuda_cost_list", I, [I, I, V]), ("thorcuda_cost_batch", I, [I, V, I, V, I, V])):
             fn = getattr(_lib, name)   # AttributeError here means a stale libthorcuda.so: rebuild

@@ -186,6 +186,15 @@ def block_bits(blocks, tb_list=None):
     return bits
 
 
+def block_bits_static(blocks):
+    """thorcuda_block_bits_static: the syntax bits of BLOCK_SYNTAX records through the entry point that allocates nothing
+    (scratch in a static device array, at most lib BLOCK_BITS_STATIC_MAX records per call); synchronous"""
+    b = np.ascontiguousarray(blocks, BLOCK_SYNTAX)
+    bits = np.zeros(b.size, np.uint32)
+    check(cdll().thorcuda_block_bits_static(_p(b), b.size, _p(bits)))
+    return bits
+
+
 def vlc_len(n, cn):
     """quote_vlc (enc/putvlc.c:133-229)"""
     return int(cdll().thorcuda_vlc_len(int(n), int(cn)))
