@@ -131,6 +131,9 @@ typedef int thorcuda_list;
 #define THORCUDA_LIST_PRED 0            /* thorcuda_pred_task                                        */
 #define THORCUDA_LIST_TB   1            /* thorcuda_tb_task                                          */
 #define THORCUDA_LIST_COST 2            /* thorcuda_cost_task                                        */
+/* Lifetime: a list is validated against the pictures it names (every vector against their padded extent -- the kernels never
+ * clamp).  Destroying or recreating one of those pictures invalidates the list: every *_list call then fails with an error
+ * instead of launching; destroy the list and create it again. */
 thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics, const void *tasks, int ntasks);
 void          thorcuda_list_destroy(thorcuda_list l);
 

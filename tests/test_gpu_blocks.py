@@ -663,3 +663,22 @@ def test_encode_blocks_extreme_residuals(tb, orc, qp):
         for pic in (org, pred, rec):
             pic.close()
     assert total == len(patterns) * 22
+
+
+def test_list_outliving_its_pictures_is_refused(tb):
+    """a resident list names pictures by handle and the kernels never clamp: once a picture of the list is destroyed (or its
+    handle recycled by a smaller one) every launch of the list must fail instead of touching freed memory"""
+    ref, dst = tb.Picture(128, 64, 96, 48), tb.Picture(128, 64)
+    tasks = np.zeros(2, tb.PRED_TASK)
+    tasks[0] = (0, 0, 16, 16, 0, -1, 40, -20, 0, 0, 0, 0, 1, 0)
+    tasks[1] = (64, 32, 16, 16, 0, -1, 300, 100, 0, 0, 0, 0, 1, 0)       # legal only with the 96-sample border
+    lst = tb.ops.TaskList(tb.LIST_PRED, [ref, dst], tasks)
+    lst.predict(1)
+    tb.sync()
+    ref.close()
+    with pytest.raises(tb.ThorCudaError, match="destroyed or recreated"):
+        lst.predict(1)
+    small = tb.Picture(64, 64, 16, 8)                                    # takes the freed handle, smaller geometry
+    with pytest.raises(tb.ThorCudaError, match="destroyed or recreated"):
+        lst.predict(1)
+    lst.close(); small.close(); dst.close()

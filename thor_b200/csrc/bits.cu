@@ -323,6 +323,7 @@ int thorcuda_coeff_bits_list(thorcuda_list hl, const int16_t *host_coeffq, uint3
   Context &c = ctx();
   List *L = get_list(hl);
   if (!L || L->kind != THORCUDA_LIST_TB) return fail("coeff_bits: not a transform-block list");
+  if (list_stale(L)) return -1;
   if (list_fence(L)) return -1;
   if (upload_scan()) return -1;
   if (host_coeffq && h2d(L->pool, host_coeffq, L->pool_entries * sizeof(int16_t))) return -1;

@@ -61,6 +61,15 @@ Pic *get_pic(thorcuda_pic h) {
   if (h < 0 || h >= THORCUDA_MAX_PICS || !g_ctx.pics[h].used) return nullptr;
   return &g_ctx.pics[h];
 }
+int list_stale(const List *L) {
+  for (size_t i = 0; i < L->pics.size(); i++) {
+    const Pic *p = get_pic(L->pics[i]);
+    if (!p || p->gen != L->pic_gens[i])
+      return fail("list: picture %d (handle %d) was destroyed or recreated after the list was made; recreate the list", (int)i, L->pics[i]);
+  }
+  return 0;
+}
+
 List *get_list(thorcuda_list h) {
   if (h < 0 || h >= 256 || !g_ctx.lists[h].used) return nullptr;
   return &g_ctx.lists[h];
@@ -377,6 +386,8 @@ thorcuda_pic thorcuda_pic_create(int width, int height, int pad_y, int pad_c) {
   p.bytes = (size_t)p.rows_y * p.stride_y + 2 * (size_t)p.rows_c * p.stride_c;
   if (cudaMalloc((void **)&p.buf[0], p.bytes + 256) != cudaSuccess) return fail("thorcuda_pic_create: cudaMalloc(%zu) failed", p.bytes);
   cudaMemsetAsync(p.buf[0], 0, p.bytes + 256, c.stream);
+  static uint32_t next_gen = 0;
+  p.gen = ++next_gen;
   p.used = true;
   if (sync_pic_view(h)) return -1;
   return h;
@@ -389,6 +400,7 @@ void thorcuda_pic_destroy(thorcuda_pic h) {
   for (int i = 0; i < 2; i++) if (p->buf[i]) cudaFree(p->buf[i]);
   if (p->info) cudaFree(p->info);
   *p = Pic();
+  sync_pic_view(h);                       // the device table entry becomes all-zero: a stale list cannot reach freed memory through it
 }
 
 int thorcuda_pic_stride(thorcuda_pic h, int plane) {

@@ -38,6 +38,7 @@ struct Pic {
   int cur = 0;
   uint16_t *info = nullptr;               // packed side information (2 bytes per 4x4 luma unit)
   bool info_ok = false;
+  uint32_t gen = 0;                       // bumped at every create: resident lists remember it (list_stale)
   PicView view(int which) const;
   PicView view() const { return view(cur); }
 };
@@ -48,6 +49,7 @@ struct List {
   int kind = -1, ntasks = 0, npics = 0, ntiles = 0, nbig = 0;
   int cost_w = 0, cost_h = 0;      // cost lists: the largest block (sizes the kernel's window buffer)
   std::vector<int> pics;                  // handles
+  std::vector<uint32_t> pic_gens;         // generation of each at list creation
   uint8_t *blob = nullptr;                // one device allocation: tasks | tiles | map
   size_t off_tiles = 0, off_map = 0, blob_bytes = 0;
   // TB lists
@@ -128,6 +130,9 @@ int d2h_bulk(void *dst, const void *src, size_t bytes);
 int copies_fence();    // make the main stream wait for the bulk copies queued so far
 struct List;
 int list_fence(List *L);
+// non-zero (and an error) if a picture the list was validated against has been destroyed or recreated since: the kernels
+// address pictures through the device table and never clamp, so such a list must not be launched
+int list_stale(const List *L);
 // transform.cu: the transform-block kernel over a sub-range of every size class of a TB list (nullptr: everything)
 int run_tb_classes(List *L, int decode, bool want_ssd, const int *class_first, const int *class_count);   // ... if the list has output copies in flight
 // refresh the device mirror entry of picture h

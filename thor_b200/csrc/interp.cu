@@ -321,6 +321,7 @@ int thorcuda_predict_list(thorcuda_list hl, int bipred_filter, int planes) {
   Context &c = ctx();
   List *L = get_list(hl);
   if (!L || L->kind != THORCUDA_LIST_PRED) return fail("predict: not a prediction list");
+  if (list_stale(L)) return -1;
   PredParams P;
   P.pics = c.d_pics;
   P.tiles = (const PredTile *)L->tiles();

@@ -125,6 +125,8 @@ thorcuda_list thorcuda_list_create(int kind, const thorcuda_pic *pics, int npics
   L = List();
   L.kind = kind; L.ntasks = ntasks; L.npics = npics;
   L.pics.assign(pics, pics + npics);
+  L.pic_gens.clear();
+  for (int i = 0; i < npics; i++) L.pic_gens.push_back(get_pic(pics[i])->gen);
 
   std::vector<PredTile> tiles;
   std::vector<uint32_t> order;

@@ -594,6 +594,7 @@ int thorcuda_sad_table_build(int n, const int *slots, const thorcuda_pic *orgs, 
     Pic *o = get_pic(orgs[i]), *r = get_pic(refs[i]);
     if (!o || !r) return fail("sad_table: bad picture handle in pair %d", i);
     if (o->w != r->w || o->h != r->h) return fail("sad_table: pair %d: picture size mismatch", i);
+    if (o->pad_y & 15) return fail("sad_table: pair %d: the original's border %d is not a multiple of 16 (its rows are fetched with 16-byte copies)", i, o->pad_y);
     if ((r->pad_y & 15) || r->pad_y < range) return fail("sad_table: pair %d: reference padding %d cannot hold range %d", i, r->pad_y, range);
     if (slots[i] < 0 || slots[i] >= THORCUDA_SAD_SLOTS) return fail("sad_table: slot %d out of range", slots[i]);
     for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail("sad_table: slot %d used twice in one call", slots[i]);
@@ -675,6 +676,7 @@ int thorcuda_cost_list(thorcuda_list hl, int kind, thorcuda_cost_result *host_re
   Context &c = ctx();
   List *L = get_list(hl);
   if (!L || L->kind != THORCUDA_LIST_COST) return fail("cost: not a cost list");
+  if (list_stale(L)) return -1;
   if (kind < 0 || kind > THORCUDA_COST_SSD) return fail("cost: unknown kind %d", kind);
   CostParams P;
   P.pics = c.d_pics; P.map = L->map();

@@ -251,6 +251,7 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
     if (row > 0) {
       const int need = min(2, ncols);
       while (ld_flag(L.progress + row - 1) < need) __nanosleep(20);
+      asm volatile("fence.acquire.gpu;" ::: "memory");                   // pairs with the row above's release store: its vectors are visible now
       u = ld_mv_l2(above);
       if (bw > 2) r = ld_mv_l2(above + 2);
     }
@@ -315,6 +316,7 @@ __global__ void __launch_bounds__(EW * 32) k_estimate(const LevelView L) {
           if (row > 0) {
             const int need = min(col + 3, ncols);
             while (ld_flag(L.progress + row - 1) < need) __nanosleep(20);
+            asm volatile("fence.acquire.gpu;" ::: "memory");             // one fence per block, after the poll: the loads stay relaxed
             if (bx + 4 < bw) r = ld_mv_l2(above + bx + 4);
           }
           S.nxt_ur[par ^ 1] = r;

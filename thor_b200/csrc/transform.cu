@@ -632,6 +632,7 @@ int thorcuda_encode_list(thorcuda_list hl, int16_t *host_coeffq, uint8_t *host_c
   THOR_NEED_CTX();
   List *L = get_list(hl);
   if (!L || L->kind != THORCUDA_LIST_TB) return fail("encode: not a transform-block list");
+  if (list_stale(L)) return -1;
   if (list_fence(L)) return -1;                 // a previous call's output copies must not be overwritten
   if (run_tb(L, 0, true)) return -1;
   if (host_coeffq && d2h_bulk(host_coeffq, L->pool, L->pool_entries * sizeof(int16_t))) return -1;
@@ -645,6 +646,7 @@ int thorcuda_reconstruct_list(thorcuda_list hl, const int16_t *host_coeffq) {
   THOR_NEED_CTX();
   List *L = get_list(hl);
   if (!L || L->kind != THORCUDA_LIST_TB) return fail("reconstruct: not a transform-block list");
+  if (list_stale(L)) return -1;
   if (list_fence(L)) return -1;
   if (host_coeffq && h2d(L->pool, host_coeffq, L->pool_entries * sizeof(int16_t))) return -1;
   return run_tb(L, 1, false);
