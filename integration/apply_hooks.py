@@ -10,7 +10,8 @@ usage: apply_hooks.py tail  <reference>/dec/decode_frame.c <out.c>     frame tai
        apply_hooks.py main  <reference>/dec/maindec.c <out.c>          output writes of the pipelined decoder (2.3)
        apply_hooks.py encgpu <reference>/enc/encode_frame.c <out.c>    the whole frame encoder on the device (2.4)
        apply_hooks.py encemu <reference>/enc/encode_frame.c <out.c>    superblock loop only (host emulation, tests)
-       apply_hooks.py mainenc <reference>/enc/mainenc.c <out.c>        interpolated references of the encoder (2.4)"""
+       apply_hooks.py mainenc <reference>/enc/mainenc.c <out.c>        interpolated references of the encoder (2.4) + segments
+       apply_hooks.py mainseg <reference>/enc/mainenc.c <out.c>        closed-GOP segment encoding only (2.5)"""
 import re
 import sys
 
@@ -115,19 +116,49 @@ if mode in ("encgpu", "encemu"):
     open(sys.argv[2], "w").write(src)
     raise SystemExit(0)
 
-if mode == "mainenc":
-    # enc/mainenc.c: interpolate_frames + pad_yuv_frame of the interpolated reference (:328-329, :385-386) on the device
+if mode in ("mainenc", "mainseg"):
+    # enc/mainenc.c.  Both modes: closed-GOP segment encoding (-seg_start / -seg_end, integration/enc_segment_hook.c);
+    # mainenc also puts interpolate_frames + pad_yuv_frame of the interpolated reference (:328-329, :385-386) on the device
+    def sub_once(text, old, new):
+        if text.count(old) != 1:
+            raise SystemExit(f"apply_hooks: expected exactly one '{old}' in mainenc.c, found {text.count(old)}")
+        return text.replace(old, new)
+    fn = "encoder_info.frame_info.frame_num"
     pat = re.compile(r"interpolate_frames\(encoder_info\.interp_frames\[0\], ref1, ref2, ([^;]*?)\);\s*pad_yuv_frame\(encoder_info\.interp_frames\[0\]\);")
     m = pat.findall(src)
     if len(m) != 2:
         raise SystemExit(f"apply_hooks: expected two interpolate_frames call sites in mainenc.c, found {len(m)}")
-    src = pat.sub(lambda mm: "thorcuda_enc_interpolate(encoder_info.interp_frames[0], ref1, ref2, " + mm.group(1) + ");", src)
+    if mode == "mainenc":
+        src = pat.sub(lambda mm: f"if (thor_seg_encodes({fn})) thorcuda_enc_interpolate(encoder_info.interp_frames[0], ref1, ref2, " + mm.group(1) + ");", src)
+    else:
+        src = pat.sub(lambda mm: f"if (thor_seg_encodes({fn})) {{ " + mm.group(0) + " }", src)
+    src = sub_once(src, "init_use_simd();", "init_use_simd();\n  thor_seg_args(&argc, argv);")
+    src = sub_once(src, "check_parameters(params);", "check_parameters(params);\n  thor_seg_check(params);")
+    src = sub_once(src, "last_PorI_frame = -1;", "last_PorI_frame = -1;\n  last_frame_output = thor_seg_first_output();")
+    src = sub_once(src, "encode_frame(&encoder_info);\n      rec_available[rec_buffer_idx]=1;",
+                   f"if (thor_seg_encodes({fn})) encode_frame(&encoder_info); else thor_seg_skip_frame(&encoder_info);\n"
+                   f"      rec_available[rec_buffer_idx]=thor_seg_emits({fn});")
+    src = sub_once(src, "flush_all_bits(&stream, strfile);", f"thor_seg_flush(&stream, strfile, {fn});")
+    src = sub_once(src, "read_yuv_frame(&orig,width,height,infile);", f"if (thor_seg_encodes({fn})) read_yuv_frame(&orig,width,height,infile);")
+    src = sub_once(src, "if (params->snrcalc){", f"if (params->snrcalc && thor_seg_encodes({fn})){{")
+    # the reference addresses the input with 32-bit arithmetic (:77, :222, :507): streams with enough segments for eight GPUs
+    # pass 2 GiB at 1080p, so the three places go to 64 bits (same values below 2 GiB)
+    src = sub_once(src, "uint32_t input_file_size;", "uint64_t input_file_size;")
+    src = sub_once(src, "input_file_size = ftell(infile);", "input_file_size = (uint64_t)ftello(infile);")
+    src = sub_once(src, "(frame_num0+1)*frame_size <= input_file_size;", "(uint64_t)(frame_num0+1)*frame_size <= input_file_size;")
+    src = sub_once(src, "if (((frame_num0+sub_gop+1)*frame_size > input_file_size", "if (((uint64_t)(frame_num0+sub_gop+1)*frame_size > input_file_size")
+    src = sub_once(src, "fseek(infile, frame_num*(frame_size+params->frame_headerlen)+params->file_headerlen+params->frame_headerlen, SEEK_SET);",
+                   "fseeko(infile, (off_t)frame_num*(frame_size+params->frame_headerlen)+params->file_headerlen+params->frame_headerlen, SEEK_SET);")
     anchor = "int main(int argc, char **argv)"
     if src.count(anchor) != 1:
         anchor = "int main(int argc, char** argv)"
     if src.count(anchor) != 1:
         raise SystemExit("apply_hooks: main() not found in mainenc.c")
-    src = src.replace(anchor, "void thorcuda_enc_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos);\n" + anchor)
+    proto = ("void thor_seg_args(int *argc, char **argv);\nvoid thor_seg_check(const enc_params *p);\nint thor_seg_encodes(int frame_num);\n"
+             "int thor_seg_emits(int frame_num);\nint thor_seg_first_output(void);\nvoid thor_seg_skip_frame(encoder_info_t *e);\n"
+             "void thor_seg_flush(stream_t *str, FILE *out, int frame_num);\n"
+             "void thorcuda_enc_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos);\n")
+    src = "#define _FILE_OFFSET_BITS 64\n" + src.replace(anchor, proto + anchor)
     open(sys.argv[2], "w").write(src)
     raise SystemExit(0)
 

@@ -72,3 +72,23 @@ def test_enc_frame_rejects_bad_arguments():
         assert b"enc_frame" in lib.thorcuda_last_error()
     finally:
         thor_b200.shutdown()
+
+
+def test_gpu_encoder_segments_join_into_the_serial_stream(tmp_path, binaries):
+    """closed-GOP segments with the device encoder: three Thorenc_gpu processes share the GPU, each encodes one
+    range of an RA stream (-seg_start / -seg_end, integration/enc_segment_hook.c); thor_b200/segments.py joins their chunks
+    into the stock encoder's serial stream, byte for byte"""
+    import sys
+    sys.path.insert(0, ROOT)
+    from thor_b200 import segments as sg
+    w, h, frames, period = 200, 136, 37, 16
+    yuv = str(tmp_path / "clip.yuv")
+    write_hard_clip(yuv, w, h, frames, seed=9)
+    args = ["-if", yuv, "-width", str(w), "-height", str(h), "-n", str(frames), "-f", "30", "-qp", "33"] + THOR_CONFIGS["RA_medium_complexity"] + ["-intra_period", str(period)]
+    subprocess.run([os.path.join(REF_DIR, "Thorenc")] + args + ["-of", str(tmp_path / "s.bit"), "-rf", str(tmp_path / "s.yuv")], check=True, capture_output=True, timeout=600)
+    ranges = sg.segment_ranges(frames, period, 3)
+    assert ranges == [(0, 16), (16, 32), (32, None)]
+    files = sg.encode_segments(GPU, args, ranges, str(tmp_path / "seg"), timeout=600)
+    bit = sg.join_segment_streams(ranges, [open(f[0], "rb").read() for f in files], frames, 7, period)
+    assert bit == (tmp_path / "s.bit").read_bytes(), "joined bitstream differs from the serial one"
+    assert b"".join(open(f[1], "rb").read() for f in files) == (tmp_path / "s.yuv").read_bytes(), "joined reconstruction differs"

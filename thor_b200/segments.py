@@ -112,3 +112,101 @@ def join(per_rank_chunks):
     if len(set(keys)) != len(keys):
         raise ValueError("a frame was emitted twice")
     return b"".join(c[1] for c in allc)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The product side: run one stream as closed-GOP segments in separate encoder processes and join what they wrote.
+# The encoder is integration/_build/Thorenc_gpu (or Thorenc_seg / Thorenc_emu in the CPU tests): the reference's main()
+# with -seg_start / -seg_end (integration/enc_segment_hook.c).  No pixel is touched here.
+
+def segment_ranges(num_frames, intra_period, parts):
+    """Cut frames [0, num_frames) at intra frames into `parts` contiguous ranges [(a, b), ...]; b is None for the last
+    range ("to the end").  Ranges hold whole intra periods and differ by at most one; fewer ranges come back when the
+    stream has fewer intra periods than `parts`.  One process per range: a range of several periods re-encodes no
+    intra frame inside it, only the one that ends it."""
+    if intra_period <= 0:
+        raise ValueError("only configurations with -intra_period have closed-GOP segments (SURVEY 0, fact 2)")
+    periods = max(1, (num_frames + intra_period - 1) // intra_period)      # I-frames at 0, P, 2P, ... < num_frames
+    parts = max(1, min(parts, periods))
+    cuts = [(periods * k) // parts * intra_period for k in range(parts + 1)]
+    return [(cuts[k], cuts[k + 1] if k + 1 < parts else None) for k in range(parts)]
+
+
+def split_chunks(bitstream):
+    """A .bit file as the list of its frame chunks, each WITH its 4-byte big-endian length prefix (flush_all_bits,
+    enc/putbits.c:57-95; the first chunk of a stream also carries the sequence header)."""
+    out, pos = [], 0
+    while pos < len(bitstream):
+        if pos + 4 > len(bitstream):
+            raise ValueError("truncated frame length")
+        n = int.from_bytes(bitstream[pos:pos + 4], "big")
+        if pos + 4 + n > len(bitstream):
+            raise ValueError("truncated frame chunk")
+        out.append(bitstream[pos:pos + 4 + n])
+        pos += 4 + n
+    return out
+
+
+def join_segment_streams(ranges, streams, num_frames, num_reorder_pics, intra_period, dyadic=True):
+    """ranges[k] = (a, b) and streams[k] = the bytes process k wrote.  Returns the serial stream: every chunk goes to
+    the position its frame has in the serial coding order (the leading B-frames of an intra frame are coded AFTER it
+    but belong to the segment BEFORE it, so plain concatenation of the files is not the serial order)."""
+    order = coding_order(num_frames, num_reorder_pics, intra_period, dyadic)
+    slot = {}
+    for (a, b), data in zip(ranges, streams):
+        mine = [f for f in order if f.frame_num >= a and (b is None or f.frame_num < b)]
+        chunks = split_chunks(data)
+        if len(chunks) != len(mine):
+            raise ValueError(f"segment [{a}, {b}) wrote {len(chunks)} frames, the coding order has {len(mine)}")
+        for f, c in zip(mine, chunks):
+            slot[f.num_encoded_before] = c
+    if sorted(slot) != list(range(len(order))):
+        raise ValueError("the segments do not cover the stream exactly once")
+    return b"".join(slot[i] for i in range(len(order)))
+
+
+def segment_args(a, b):
+    return ["-seg_start", str(a)] + (["-seg_end", str(b)] if b is not None else [])
+
+
+def encode_segments(exe, args, ranges, out_prefix, env=None, envs=None, max_parallel=None, timeout=3600):
+    """Start one encoder process per range (at most max_parallel at a time): `exe args -of <prefix>_k.bit -rf
+    <prefix>_k.yuv -seg_start a [-seg_end b]`.  envs[k] overrides env for process k (e.g. CUDA_VISIBLE_DEVICES).
+    Returns [(bit_path, rec_path)].  Raises if any process fails -- there is no fallback."""
+    import os
+    import subprocess
+    import time
+    files = [(f"{out_prefix}_{k}.bit", f"{out_prefix}_{k}_rec.yuv") for k in range(len(ranges))]
+    pending = list(range(len(ranges)))
+    running = {}
+    limit = max_parallel or len(ranges)
+    t_end = time.monotonic() + timeout
+    try:
+        while pending or running:
+            while pending and len(running) < limit:
+                k = pending.pop(0)
+                a, b = ranges[k]
+                cmd = [exe] + list(args) + ["-of", files[k][0], "-rf", files[k][1]] + segment_args(a, b)
+                e = dict(os.environ if env is None else env)
+                if envs is not None:
+                    e.update(envs[k])
+                log = open(f"{out_prefix}_{k}.log", "w")
+                running[k] = (subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, env=e), log)
+            for k in list(running):
+                p, log = running[k]
+                rc = p.poll()
+                if rc is None:
+                    continue
+                log.close()
+                del running[k]
+                if rc != 0:
+                    raise RuntimeError(f"segment {ranges[k]} failed ({rc}): " + open(f"{out_prefix}_{k}.log").read()[-1500:])
+            if time.monotonic() > t_end:
+                raise TimeoutError("segment encoders did not finish")
+            time.sleep(0.02)
+    finally:
+        for p, log in running.values():
+            p.kill()
+            p.wait()
+            log.close()
+    return files
