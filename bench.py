@@ -231,6 +231,94 @@ def decoder_e2e_leg(args, workdir):
     return out
 
 
+# ------------------------------------------------------------ closed-GOP segments of ONE stream ----
+def segments_leg(args, rank, world, env, shared, barrier, allmax):
+    """BASELINE.json configs[2]'s partitioning: ONE RA stream cut at its intra frames (config: -intra_period 64), its segments
+    sharded contiguously over the ranks (weak: --segments-per-gpu each), one Thorenc_gpu process per segment (-seg_start /
+    -seg_end, integration/enc_segment_hook.c), the processes of a rank sharing its GPU.  Ranks exchange nothing; rank 0 joins
+    the chunks (thor_b200/segments.py) and checks the join with the STOCK decoder: the stream up to the end of rank 0's shard
+    (which needs the next rank's intra frame) must decode to exactly the reconstructions rank 0's encoders wrote."""
+    from thorref import THOR_CONFIGS
+    from thor_b200 import segments as sg
+    cfg, w, h = args.segments_config, args.width, args.height
+    opts = THOR_CONFIGS[cfg]
+    period, reorder = int(opts[opts.index("-intra_period") + 1]), int(opts[opts.index("-num_reorder_pics") + 1])
+    spg = args.segments_per_gpu
+    nseg = world * spg
+    frames = nseg * period + 1
+    fsize = w * h * 3 // 2
+    ranges = sg.segment_ranges(frames, period, nseg)
+    mine = sg.shard(list(enumerate(ranges)), rank, world)
+    lo, hi = mine[0][1][0], mine[-1][1][1]
+    hi = frames - 1 if hi is None else hi                    # the range's closing intra frame is encoded too
+    base = os.path.join(shared, f"seg_base_{w}x{h}.yuv")
+    if rank == 0:
+        make_clip(base, w, h, period, seed=44)
+    barrier()
+    # the rank's input: a sparse file of the whole stream's length holding only the frames its encoders read
+    yuv = os.path.join(shared, f"seg_in_rank{rank}.yuv")
+    with open(base, "rb") as src, open(yuv, "wb") as dst:
+        dst.truncate(frames * fsize)
+        for n in range(lo, hi + 1):
+            src.seek((n % period) * fsize)
+            dst.seek(n * fsize)
+            dst.write(src.read(fsize))
+    sargs = ["-if", yuv, "-width", str(w), "-height", str(h), "-n", str(frames), "-f", "60", "-qp", str(args.qp), "-snrcalc", "0"] + opts
+    penv = dict(os.environ, **env, THORCUDA_ENC_CTAS=str(args.segments_ctas), THORCUDA_BLOCKING_SYNC="1")
+    prefix = os.path.join(shared, f"seg_rank{rank}")
+    barrier()
+    t0 = time.perf_counter()
+    files = sg.encode_segments(GPU_ENC, sargs, [r for _, r in mine], prefix, env=penv, rec=(rank == 0), timeout=3000)
+    dt = time.perf_counter() - t0
+    os.remove(yuv)
+    barrier()
+    dt = allmax(dt)
+    if rank != 0:
+        barrier()
+        return None
+    res = {"config": f"Thorenc config_{cfg}.txt {w}x{h} qp {args.qp}: ONE stream of {frames} frames = {nseg} closed-GOP segments of {period}, "
+                     f"{spg} per GPU, one encoder process per segment ({args.segments_ctas} CTAs per frame each)",
+           "frames": frames, "segments": nseg, "n_gpus": world, "scaling": "weak", "seconds": round(dt, 2), "fps": round(frames / dt, 3),
+           "redundant_intra_frames": nseg - 1,
+           "timing": "wall clock from the start barrier to the last encoder process's exit, max over ranks: process and CUDA start-up, "
+                     "file reads, device work, entropy coding, bitstream and reconstruction writes"}
+    streams = []
+    for r in range(world):
+        for k in range(len(sg.shard(ranges, r, world))):
+            streams.append(open(os.path.join(shared, f"seg_rank{r}_{k}.bit"), "rb").read())
+    joined = sg.join_segment_streams(ranges, streams, frames, reorder, period)
+    import hashlib
+    res["joined_bytes"], res["joined_sha256"] = len(joined), hashlib.sha256(joined).hexdigest()
+    # decode check with the stock decoder: every coded frame up to the last one of rank 0's shard
+    end = mine[-1][1][1]
+    order = sg.coding_order(frames, reorder, period)
+    last = max(f.num_encoded_before for f in order if end is None or f.frame_num < end)
+    cut, pos = 0, 0
+    for _ in range(last + 1):
+        pos += 4 + int.from_bytes(joined[pos:pos + 4], "big")
+    open(prefix + "_joined.bit", "wb").write(joined[:pos])
+    if os.path.exists(REF_DEC):
+        subprocess.run([REF_DEC, prefix + "_joined.bit", prefix + "_dec.yuv"], check=True, capture_output=True, timeout=3000)
+        nshow = frames if end is None else end
+        ok, off = True, 0
+        with open(prefix + "_dec.yuv", "rb") as dec:
+            for _, rec in files:
+                with open(rec, "rb") as rf:
+                    while True:
+                        a = rf.read(fsize)
+                        if not a:
+                            break
+                        ok = ok and a == dec.read(fsize)
+                        off += 1
+        res["stock_decoder_reproduces_the_encoders_reconstruction"] = bool(ok and off == nshow)
+        res["decode_check"] = f"stock Thordec on the joined stream's first {last + 1} coded frames vs the {off} frames rank 0's segment encoders reconstructed"
+    for p in [prefix + "_joined.bit", prefix + "_dec.yuv"] + [x for fl in files for x in fl]:
+        if os.path.exists(p):
+            os.remove(p)
+    barrier()
+    return res
+
+
 # ------------------------------------------------------------------------------ arms ----
 def workload_config(args, streams):
     return {"workload": f"Thorenc config_{args.config}.txt {args.width}x{args.height} 8-bit synthetic (hard clip, noise 5), qp {args.qp}: "
@@ -360,6 +448,20 @@ def run_gpu_arm(args, rank, world, local_rank):
                                         "sample": f"stock Thorenc (SSE4 build, single-threaded by design), frames 3..{args.e2e_frames} of the same clip and "
                                                   f"configuration, {ref1['seconds']} s"}
             barrier()
+            if not args.no_segments:
+                shared = f"/dev/shm/thor_seg_{os.environ.get('MASTER_PORT', os.getpid())}" if shm_dir() else f"/tmp/thor_seg_{os.environ.get('MASTER_PORT', os.getpid())}"
+                need = (args.segments_per_gpu * 64 + 1) * fbytes * (2 if rank == 0 else 1) * world
+                if shutil.disk_usage(os.path.dirname(shared)).free < 1.3 * need:
+                    shared = shared.replace("/dev/shm/", "/tmp/")
+                os.makedirs(shared, exist_ok=True)
+                try:
+                    seg = segments_leg(args, rank, world, {k: v for k, v in env.items()}, shared, barrier, allmax)
+                finally:
+                    barrier()
+                    if rank == 0:
+                        shutil.rmtree(shared, ignore_errors=True)
+                if rank == 0:
+                    line["segments"] = seg
         finally:
             if rank == 0:
                 mps.stop()
@@ -388,6 +490,10 @@ def main():
     ap.add_argument("--no-mps", action="store_true", help="do not start the CUDA MPS daemon (the streams then time-slice the GPU)")
     ap.add_argument("--no-cpu", action="store_true", help="skip cpu_baseline / encoder_e2e")
     ap.add_argument("--no-decoder", action="store_true", help="skip decoder_e2e (about a minute)")
+    ap.add_argument("--no-segments", action="store_true", help="skip the closed-GOP segment leg (one RA stream sharded over the GPUs)")
+    ap.add_argument("--segments-config", default="RA_medium_complexity")
+    ap.add_argument("--segments-per-gpu", type=int, default=8, help="segments (= encoder processes) per GPU; the stream has gpus x this x 64 + 1 frames")
+    ap.add_argument("--segments-ctas", type=int, default=15, help="CTAs per frame of each segment encoder")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":

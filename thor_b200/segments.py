@@ -169,10 +169,11 @@ def segment_args(a, b):
     return ["-seg_start", str(a)] + (["-seg_end", str(b)] if b is not None else [])
 
 
-def encode_segments(exe, args, ranges, out_prefix, env=None, envs=None, max_parallel=None, timeout=3600):
+def encode_segments(exe, args, ranges, out_prefix, env=None, envs=None, max_parallel=None, timeout=3600, rec=True):
     """Start one encoder process per range (at most max_parallel at a time): `exe args -of <prefix>_k.bit -rf
-    <prefix>_k.yuv -seg_start a [-seg_end b]`.  envs[k] overrides env for process k (e.g. CUDA_VISIBLE_DEVICES).
-    Returns [(bit_path, rec_path)].  Raises if any process fails -- there is no fallback."""
+    <prefix>_k_rec.yuv -seg_start a [-seg_end b]`.  envs[k] overrides env for process k (e.g. CUDA_VISIBLE_DEVICES);
+    rec=False leaves the reconstruction files out.  Returns [(bit_path, rec_path)].  Raises if any process fails --
+    there is no fallback."""
     import os
     import subprocess
     import time
@@ -186,7 +187,7 @@ def encode_segments(exe, args, ranges, out_prefix, env=None, envs=None, max_para
             while pending and len(running) < limit:
                 k = pending.pop(0)
                 a, b = ranges[k]
-                cmd = [exe] + list(args) + ["-of", files[k][0], "-rf", files[k][1]] + segment_args(a, b)
+                cmd = [exe] + list(args) + ["-of", files[k][0]] + (["-rf", files[k][1]] if rec else []) + segment_args(a, b)
                 e = dict(os.environ if env is None else env)
                 if envs is not None:
                     e.update(envs[k])
