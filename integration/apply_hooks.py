@@ -8,10 +8,10 @@ usage: apply_hooks.py tail  <reference>/dec/decode_frame.c <out.c>     frame tai
        apply_hooks.py block <reference>/dec/decode_block.c <out.c>     the block-level call sites of 2.3
        apply_hooks.py enc   <reference>/enc/encode_frame.c <out.c>     frame tail of the encoder (2.2)
        apply_hooks.py main  <reference>/dec/maindec.c <out.c>          output writes of the pipelined decoder (2.3)
-       apply_hooks.py encgpu <reference>/enc/encode_frame.c <out.c>    the whole frame encoder on the device (2.4)
+       apply_hooks.py encgpu <reference>/enc/encode_frame.c <out.c>    the whole frame encoder on the device (2.7)
        apply_hooks.py encemu <reference>/enc/encode_frame.c <out.c>    superblock loop only (host emulation, tests)
-       apply_hooks.py mainenc <reference>/enc/mainenc.c <out.c>        interpolated references of the encoder (2.4) + segments
-       apply_hooks.py mainseg <reference>/enc/mainenc.c <out.c>        closed-GOP segment encoding only (2.5)"""
+       apply_hooks.py mainenc <reference>/enc/mainenc.c <out.c>        interpolated references of the encoder (2.7) + segments (2.8)
+       apply_hooks.py mainseg <reference>/enc/mainenc.c <out.c>        closed-GOP segment encoding only (2.8)"""
 import re
 import sys
 

@@ -1,4 +1,4 @@
-/* Reference-side binding of libthorcuda's FRAME ENCODER for Thorenc (INTEGRATION.md 2.4).
+/* Reference-side binding of libthorcuda's FRAME ENCODER for Thorenc (INTEGRATION.md 2.7).
  *
  * encode_frame() (enc/encode_frame.c:65-192) keeps its frame header, calls
  *     thorcuda_enc_superblocks(encoder_info)          instead of the superblock loop (:112-148)

@@ -1,4 +1,4 @@
-/* Closed-GOP segment encoding for the reference's sequence loop (INTEGRATION.md 2.5, SURVEY 8e).
+/* Closed-GOP segment encoding for the reference's sequence loop (INTEGRATION.md 2.8, SURVEY 8e).
  *
  * main() of enc/mainenc.c (a scratch copy patched by integration/apply_hooks.py, mode "mainseg"/"mainenc") takes two
  * extra arguments that the reference's own parser never sees:

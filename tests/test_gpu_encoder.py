@@ -1,4 +1,4 @@
-"""The reference ENCODER with every block decision on the B200 (INTEGRATION.md 2.4): integration/_build/Thorenc_gpu is the
+"""The reference ENCODER with every block decision on the B200 (INTEGRATION.md 2.7): integration/_build/Thorenc_gpu is the
 reference's encoder objects with the superblock loop, the frame tail and reference creation of encode_frame() going through
 integration/enc_gpu_hook.c -> thorcuda_enc_frame / thorcuda_loopfilter_frame.  Motion search, trial encodes, rate-distortion
 decisions and the quad tree run in k_encode_frame (thor_b200/csrc/encoder.cu); the host only entropy-codes the decided trees

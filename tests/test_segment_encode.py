@@ -1,4 +1,4 @@
-"""Closed-GOP segment sharding with REAL encoders (SURVEY 8e, INTEGRATION.md 2.5), on the CPU.
+"""Closed-GOP segment sharding with REAL encoders (SURVEY 8e, INTEGRATION.md 2.8), on the CPU.
 
 One RA stream is encoded serially by the stock Thorenc and as several segments by separate processes of the encoder whose
 main() takes -seg_start / -seg_end (integration/enc_segment_hook.c; Thorenc_seg = the stock pixel path, Thorenc_emu = the
