@@ -321,11 +321,10 @@ void thorcuda_enc_make_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
   if (frame_log) { fprintf(frame_log, "%d %.3f %.3f %llu\n", t_frames - 1, t_last, t_dev_events, (unsigned long long)thorcuda_launch_count()); fflush(frame_log); }
 }
 
-/* interpolate_frames + pad_yuv_frame (enc/mainenc.c:328-329, :385-386).  Default: the reference's own interpolate_frames on
- * the host, fed with the two references fetched from the device (two padded pictures down, one up per B frame).
- * THORCUDA_ENC_DEVICE_INTERP=1 runs thorcuda_interpolate_frames on the device twins instead -- nothing crosses PCIe -- but
- * that kernel has a known defect (round 2): wrong vectors in the bottom partial block row of some pictures whose height is
- * not a multiple of 16 (tests/test_gpu_tinterp.py, the xfail cases), so byte identity is not guaranteed with it. */
+/* interpolate_frames + pad_yuv_frame (enc/mainenc.c:328-329, :385-386): thorcuda_interpolate_frames on the device twins of
+ * the two references -- nothing crosses PCIe.  THORCUDA_ENC_HOST_INTERP=1 runs the reference's own interpolate_frames on
+ * the host instead, fed with the two references fetched from the device (two padded pictures down, one up per B frame):
+ * the cross-check used when an RA stream differs. */
 void interpolate_frames(yuv_frame_t *new_frame, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos);
 void pad_yuv_frame(yuv_frame_t *f);
 static uint8_t *plane0(const yuv_frame_t *f, int pl) {
@@ -333,7 +332,7 @@ static uint8_t *plane0(const yuv_frame_t *f, int pl) {
 }
 void thorcuda_enc_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *ref1, int ratio, int pos) {
   static int on_device = -1;
-  if (on_device < 0) on_device = getenv("THORCUDA_ENC_DEVICE_INTERP") != NULL;
+  if (on_device < 0) on_device = getenv("THORCUDA_ENC_HOST_INTERP") == NULL;
   if (dev_interp < 0) {
     dev_interp = thorcuda_pic_create(dst->width, dst->height, PADDING_Y, PADDING_Y / 2);
     if (dev_interp < 0) fatalerror((char *)thorcuda_last_error());

@@ -38,11 +38,20 @@
 #else
 #define THOR_ASSUME_SHARED(p) __builtin_assume(__isShared(p))
 // Measured on the B200 (round 2, one build variant per group, .bit compared with the reference's): the hint on the SbMem
-// reference (S) and on the reduction scratch (R) keep the streams byte-identical and take a 416x240 frame from 115 to 95 ms;
-// the same hint on pointer PARAMETERS into SbMem (P) changed decisions in the bi-prediction configurations although every
-// such pointer does point into shared memory, and on the frame description (F) it was slower.  P and F stay off.
+// reference (S) and on the reduction scratch (R) kept the streams byte-identical in the 255-register build and took a
+// 416x240 frame from 115 to 95 ms (1080p: 1214 -> 1141 ms).  But the same source compiled for 128 registers
+// (__launch_bounds__(256, 2) or 512 threads) dies with an illegal memory access in the first bi-predicted frame WITH the S / R
+// hints and runs byte-identically WITHOUT them (profiles/r2/crash_matrix.py), the hint on pointer PARAMETERS into SbMem (P)
+// changed decisions although every such pointer does point into shared memory, and on the frame description (F) it was
+// slower.  Whatever the cause, a 6 % gain does not pay for code whose correctness depends on the register allocation:
+// ALL hints are off unless the build asks for them (-DTHOR_ENC_HINTS, plus -DTHOR_HINT_P / -DTHOR_HINT_F).
+#ifdef THOR_ENC_HINTS
 #define THOR_SHS(p) THOR_ASSUME_SHARED(p)
 #define THOR_SHR(p) THOR_ASSUME_SHARED(p)
+#else
+#define THOR_SHS(p) ((void)0)
+#define THOR_SHR(p) ((void)0)
+#endif
 #ifdef THOR_HINT_P
 #define THOR_SHARED(p) THOR_ASSUME_SHARED(p)
 #else
@@ -191,7 +200,18 @@ struct Prof {
 #endif
 
 // iterations i = 0 .. cnt-1 spread over the group; NOT followed by a barrier (call g.sync() where a reader follows)
+#if defined(THOR_ENC_PARANOID) && !defined(THOR_HOSTEMU)
+// diagnostic build: a barrier before and after every cooperative loop (finds a missing g.sync() by making it unnecessary)
+struct TforGuard {
+  const Grp &g;
+  bool once;
+  __device__ TforGuard(const Grp &g_) : g(g_), once(true) { g.sync(); }
+  __device__ ~TforGuard() { g.sync(); }
+};
+#define TFOR(g, i, cnt) for (TforGuard tfor_guard_(g); tfor_guard_.once; tfor_guard_.once = false) for (int i = (g).tid; i < (cnt); i += (g).n)
+#else
 #define TFOR(g, i, cnt) for (int i = (g).tid; i < (cnt); i += (g).n)
+#endif
 
 // ---- small helpers ---------------------------------------------------------------------------------------------
 TD int imin(int a, int b) { return a < b ? a : b; }

@@ -121,7 +121,7 @@ struct HalveParams {
 
 // one thread = 4 adjacent output samples (border included: source coordinates clamp to the visible picture)
 __global__ void __launch_bounds__(256) k_halve(const HalveParams P) {
-  const int words = (P.wo + 2 * P.pad) / 4, rows = P.ho + 2 * P.pad;
+  const int words = (P.wo + 2 * P.pad + 3) / 4, rows = P.ho + 2 * P.pad;   // a width that is not a multiple of 4 ends in a partial word (the stride has room)
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= words * rows) return;
   const int k = blockIdx.y, row = idx / words - P.pad, col = (idx % words) * 4 - P.pad;
