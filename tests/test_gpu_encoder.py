@@ -18,6 +18,9 @@ GPU = os.path.join(ROOT, "integration", "_build", "Thorenc_gpu")
 CASES = [
     ("LDB_low_complexity", 416, 240, 10, 32),       # BASELINE.json configs[0]
     ("LDB_low_complexity", 1920, 1080, 3, 32),      # the 1080p geometry: 30 x 17 superblocks, last row 56 samples
+    ("LDB_medium_complexity", 1920, 1080, 12, 32),  # configs[1] at its own size (12 of its 60 frames: 15 s of device time)
+    ("RA_medium_complexity", 1920, 1080, 9, 32),    # north_star's operating point at 1080p: one sub-GOP, references interpolated on the device
+    ("LDB_low_complexity", 3840, 2160, 2, 32),      # the 2160p geometry of configs[3] / [4]: 60 x 34 superblocks, last row 48 samples
     ("LDB_medium_complexity", 416, 240, 6, 32),     # configs[1]'s operating point (bi-prediction, intra RDO, telescope search)
     ("LDB_medium_complexity", 200, 136, 5, 30),     # partial superblocks on both sides
     ("LDB_medium_complexity", 128, 64, 3, 44),
