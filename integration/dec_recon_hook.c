@@ -31,7 +31,7 @@ extern uint8_t *thorcuda_dec_out_compact;
 /* THORCUDA_HOOK_TIMING=1: host milliseconds per phase and frame, printed at exit */
 static double tp[6], t_mark, t_hk[5];
 #define HK_T0 const double hk0_ = tp_on > 0 ? ms_now() : 0
-#define HK_T1(i) do { if (tp_on > 0 && tp_seen >= 36) t_hk[i] += ms_now() - hk0_; } while (0)
+#define HK_T1(i) do { if (tp_on > 0 && tp_seen >= tp_skip) t_hk[i] += ms_now() - hk0_; } while (0)
 static double dev_ms, t_steady0, t_finish;       /* wall clock when the 37th frame starts / when the output is complete */
 static int tp_frames, tp_on = -1, tp_levels, tp_intra, tp_pred, tp_tbs;
 static double ms_now(void) {
@@ -39,11 +39,12 @@ static double ms_now(void) {
   clock_gettime(CLOCK_MONOTONIC, &ts);
   return 1e3 * ts.tv_sec + 1e-6 * ts.tv_nsec;
 }
-static int tp_seen;            /* frames seen; the first 36 (CUDA start-up, first use of every reference slot) are not counted */
+static int tp_seen;            /* frames seen; the first tp_skip (CUDA start-up, first use of every reference slot) are not counted */
+static int tp_skip = 36;       /* THORCUDA_HOOK_STEADY_FROM overrides (short 2160p streams) */
 static void lap(int i) {
   if (tp_on <= 0) return;
   const double t = ms_now();
-  if (tp_seen >= 36) tp[i] += t - t_mark;
+  if (tp_seen >= tp_skip) tp[i] += t - t_mark;
   t_mark = t;
 }
 static void tp_report(void) {
@@ -51,8 +52,8 @@ static void tp_report(void) {
   const int n = tp_frames ? tp_frames : 1;
   for (int i = 0; i < 6; i++) fprintf(stderr, "thorcuda recon hook: %-18s %8.3f ms/frame\n", name[i], tp[i] / n);
   if (t_finish > t_steady0 && t_steady0 > 0 && tp_frames)
-    fprintf(stderr, "thorcuda recon hook: steady state %.3f ms/frame wall clock = %.1f frames/s (frame 37 .. output complete, %d frames)\n",
-            (t_finish - t_steady0) / tp_frames, 1e3 * tp_frames / (t_finish - t_steady0), tp_frames);
+    fprintf(stderr, "thorcuda recon hook: steady state %.3f ms/frame wall clock = %.1f frames/s (frame %d .. output complete, %d frames)\n",
+            (t_finish - t_steady0) / tp_frames, 1e3 * tp_frames / (t_finish - t_steady0), tp_skip + 1, tp_frames);
   fprintf(stderr, "thorcuda recon hook: inside hk_luma %.3f, hk_recon_inter %.3f, hk_recon_intra %.3f ms/frame\n", t_hk[0] / n, t_hk[1] / n, t_hk[2] / n);
   fprintf(stderr, "thorcuda recon hook: inside thorcuda_dec_write_frame %.3f, thorcuda_dec_interpolate %.3f ms/frame (both between frames)\n", t_hk[3] / n, t_hk[4] / n);
   fprintf(stderr, "thorcuda recon hook: device time of a frame's reconstruction (CUDA events, without interpolate_frames) %.3f ms/frame\n", dev_ms / n);
@@ -103,9 +104,9 @@ static void *grow(void *p, int *cap, int need_n, size_t elem) {
 void thorcuda_dec_frame_begin(decoder_info_t *di) {
   g_di = di;
   if (dry < 0) dry = getenv("THORCUDA_HOOK_DRY") != NULL;
-  if (tp_on < 0) { tp_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (tp_on) { atexit(tp_report); t_mark = ms_now(); } }
+  if (tp_on < 0) { tp_on = getenv("THORCUDA_HOOK_TIMING") != NULL; if (tp_on) { atexit(tp_report); t_mark = ms_now(); if (getenv("THORCUDA_HOOK_STEADY_FROM")) tp_skip = atoi(getenv("THORCUDA_HOOK_STEADY_FROM")); } }
   lap(5);
-  if (tp_on > 0 && tp_seen == 36) t_steady0 = ms_now();
+  if (tp_on > 0 && tp_seen == tp_skip) t_steady0 = ms_now();
   if (dry) return;
   if (dev_rec < 0) {
     const char *dev = getenv("THORCUDA_DEVICE");
@@ -316,7 +317,7 @@ static void complete_inflight(void) {
   /* waits for this frame's last event only: work queued after it (the next frame's interpolation) keeps running */
   const float ms = thorcuda_timer_elapsed_ms(inflight.timer);
   if (ms < 0) fatalerror("thorcuda hook: waiting for the frame failed");
-  if (tp_seen >= 36) dev_ms += ms;
+  if (tp_seen >= tp_skip) dev_ms += ms;
   inflight.rec = NULL;
 }
 
@@ -425,7 +426,7 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
   if (!dry) { complete_inflight(); lap(4); }
   const int frame_timer = dry ? -1 : thorcuda_timer_begin();
   if (dry) { if (di->clpf && getbits(stream, 1)) fatalerror("dry run needs a stream without CLPF"); return; }
-  if (tp_seen >= 36) { tp_pred += npred; tp_tbs += ntbs; tp_intra += nintra; }
+  if (tp_seen >= tp_skip) { tp_pred += npred; tp_tbs += ntbs; tp_intra += nintra; }
   /* 1. every inter block: prediction straight into the picture, then the coded ones are reconstructed in place */
   if (npred) need(thorcuda_predict_blocks(pics, npics, pred, npred, di->bipred, 3));
   int ninter = 0;
@@ -473,7 +474,7 @@ void thorcuda_dec_flush(decoder_info_t *di, stream_t *stream, int qp) {
     /* all levels in ONE call: predictions and coded transform blocks in level order, two launches per level */
     thorcuda_intra_task *batch = (thorcuda_intra_task *)malloc((size_t)(nintra + 1) * sizeof(*batch));
     int *ifirst = (int *)malloc((size_t)(maxl + 2) * sizeof(int)), *tfirst = (int *)malloc((size_t)(maxl + 2) * sizeof(int));
-    if (tp_seen >= 36) tp_levels += maxl;
+    if (tp_seen >= tp_skip) tp_levels += maxl;
     lt = (thorcuda_tb_task *)grow(lt, &clt, nintra + 1, sizeof(*lt));
     size_t need_pool = 0;
     for (int k = 0; k < nintra; k++) {
@@ -531,5 +532,5 @@ void thorcuda_dec_interpolate(yuv_frame_t *dst, yuv_frame_t *ref0, yuv_frame_t *
  * reads from now on (prediction and interpolation are on the device); nothing to wait for here */
 void thorcuda_dec_fetch_reference(yuv_frame_t *ref, yuv_frame_t *rec) {
   ref->frame_num = rec->frame_num;
-  if (tp_seen++ >= 36) tp_frames++;
+  if (tp_seen++ >= tp_skip) tp_frames++;
 }

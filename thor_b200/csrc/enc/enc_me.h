@@ -5,42 +5,89 @@
 namespace thorenc {
 
 // sad_calc (enc/encode_block.c:740-755) for K candidate positions at once: the width x height block `a` (shared, stride
-// as) against ref + off[k] (reference picture, stride bs).  Results in S.acc[0..K).  Ends with a barrier.
-// `wide`: each candidate is widesad_calc's five positions x + {-3,-1,0,1,3} (:757-780); results in S.acc[5k .. 5k+5).
+// as) against ref + off[k] (reference picture, stride bs; off[] = S.me_off, written by the caller before the call).  Results in S.acc[0..K).  Ends with a
+// barrier.  `wide`: each candidate is widesad_calc's five positions x + {-3,-1,0,1,3} (:757-780); results in
+// S.acc[5k .. 5k+5).
+//
+// Device mapping: a candidate belongs to ONE WARP (or, when there are fewer candidates than warps, to 2 / 4 / 8 warps that
+// split its rows): a lane walks 4-sample words of the block, the warp reduces once per candidate, nobody divides (block
+// sides are powers of two) and the five wide positions come out of the same four aligned words.  Before round 2's last
+// profile this function was a flat item loop over all candidates with four integer divisions and a shuffle reduction per
+// word: 21 % of k_encode_frame's samples at LDB medium (profiles/r2_ncu_encode_frame_1080p.txt).
+#ifndef THOR_HOSTEMU
+TD uint32_t window_word(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, int off) {      // 4 bytes at byte offset off (0..9) of w0..w3
+  const unsigned sh = (unsigned)(off & 3) * 8;
+  return off < 4 ? __funnelshift_r(w0, w1, sh) : off < 8 ? __funnelshift_r(w1, w2, sh) : __funnelshift_r(w2, w3, sh);
+}
+#endif
 TDN void sad_batch(Grp &g, SbMem &S, const uint8_t *a, int as, const uint8_t *ref, int bs, const int *off, int K, int width, int height, int wide) {
   PROF(PF_SAD);
   THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHARED(a);
   const int per = wide ? 5 : 1, wq = width >> 2, items = height * wq;
-  g.sync();                                                // readers of the previous batch's results are done
-  TFOR(g, i, K * per) S.acc[i] = 0;
-  g.sync();
-  const int total = K * per * items;
-#ifndef THOR_HOSTEMU
-  const bool warp_uniform = (items & 31) == 0;             // a warp's 32 items belong to one candidate: reduce first
-#endif
-  for (int i0 = 0; i0 < total; i0 += g.n) {
-    const int i = i0 + g.tid;
-    int v = 0, slot = 0;
-    if (i < total) {
-      slot = i / items;
-      const int it = i % items, r = it / wq, c = (it % wq) * 4;
-      const int k = slot / per, w = slot % per;
-      const int dx = wide ? (w == 0 ? -3 : w == 1 ? -1 : w == 2 ? 0 : w == 3 ? 1 : 3) : 0;
-      v = (int)sad4(*reinterpret_cast<const uint32_t *>(a + r * as + c), ld_ro32u(ref + off[k] + dx + r * bs + c));
-    }
+  g.sync();                                                // readers of the previous batch's results are done; off[] is written
 #ifdef THOR_HOSTEMU
-    if (i < total) S.acc[slot] += v;
+  for (int k = 0; k < K; k++)
+    for (int w = 0; w < per; w++) {
+      const int dx = wide ? (w == 0 ? -3 : w == 1 ? -1 : w == 2 ? 0 : w == 3 ? 1 : 3) : 0;
+      int v = 0;
+      for (int it = 0; it < items; it++) {
+        const int r = it / wq, c = (it % wq) * 4;
+        v += (int)sad4(*reinterpret_cast<const uint32_t *>(a + r * as + c), ld_ro32u(ref + off[k] + dx + r * bs + c));
+      }
+      S.acc[k * per + w] = v;
+    }
 #else
-    if (warp_uniform) {
+  const int lane = g.tid & 31, warp = g.tid >> 5;
+  const int lwq = 31 - __clz(wq);                          // width is 4, 8, 16, 32 or 64
+  // warps per candidate: as many as keeps every warp busy, but no more than there are 32-word slices of the block
+  int sp = 1;
+  while (K * sp * 2 <= NW && sp * 2 * 32 <= items) sp *= 2;
+  if (sp > 1) {
+    TFOR(g, i, K * per) S.acc[i] = 0;
+    g.sync();
+  }
+  const int chunk = items / sp;                            // items and sp are powers of two
+  for (int u = warp; u < K * sp; u += NW) {
+    const int k = u / sp, part = u - k * sp;
+    const uint8_t *rp = ref + off[k];
+    const int it0 = part * chunk, it1 = it0 + chunk;
+    if (!wide) {
+      int v = 0;
+      for (int it = it0 + lane; it < it1; it += 32) {
+        const int r = it >> lwq, c = (it & (wq - 1)) << 2;
+        v += (int)sad4(*reinterpret_cast<const uint32_t *>(a + r * as + c), ld_ro32u(rp + r * bs + c));
+      }
 #pragma unroll
       for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if ((g.tid & 31) == 0 && i < total) atomicAdd(&S.acc[slot], v);
-    } else if (i < total) {
-      atomicAdd(&S.acc[slot], v);
+      if (lane == 0) { if (sp > 1) atomicAdd(&S.acc[k], v); else S.acc[k] = v; }
+    } else {
+      int v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0;
+      for (int it = it0 + lane; it < it1; it += 32) {
+        const int r = it >> lwq, c = (it & (wq - 1)) << 2;
+        const uint32_t A = *reinterpret_cast<const uint32_t *>(a + r * as + c);
+        const uintptr_t p = reinterpret_cast<uintptr_t>(rp + r * bs + c - 3);
+        const uint32_t *q = reinterpret_cast<const uint32_t *>(p & ~(uintptr_t)3);
+        const int o0 = (int)(p & 3);
+        const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2), w3 = __ldg(q + 3);
+        v0 += (int)sad4(A, window_word(w0, w1, w2, w3, o0));          // x - 3
+        v1 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 2));      // x - 1
+        v2 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 3));      // x
+        v3 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 4));      // x + 1
+        v4 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 6));      // x + 3
+      }
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o); v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+        v3 += __shfl_xor_sync(0xffffffffu, v3, o); v4 += __shfl_xor_sync(0xffffffffu, v4, o);
+      }
+      if (lane < 5) {
+        const int v = lane == 0 ? v0 : lane == 1 ? v1 : lane == 2 ? v2 : lane == 3 ? v3 : v4;
+        if (sp > 1) atomicAdd(&S.acc[5 * k + lane], v); else S.acc[5 * k + lane] = v;
+      }
     }
-#endif
   }
+#endif
   g.sync();
 }
 
@@ -177,6 +224,28 @@ TD void add_mvcandidate(Grp &g, SbMem &S, SbState &st, int ref_idx, Mv mv) {
   st.mvcand_mask[ref_idx] |= m;
 }
 
+// The searches below price up to 64 candidates and keep the first cheapest one (the reference's `if (sad < min_sad)` walk).
+// On the device a lane owns candidates k = lane, lane + 32: it forms the vector, prices it, and the warp agrees on
+// (smallest cost, then smallest k) with shuffles -- the same answer as the sequential walk, in a 25th of the instructions
+// every warp used to replay.  The host emulation is one lane and walks all candidates in order.
+#ifdef THOR_HOSTEMU
+constexpr int ME_LANES = 1;
+TD int me_lane(const Grp &) { return 0; }
+TD void me_argmin(unsigned &, int &, Mv &) {}
+#else
+constexpr int ME_LANES = 32;
+TD int me_lane(const Grp &g) { return g.tid & 31; }
+TD void me_argmin(unsigned &sad, int &k, Mv &mv) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    const unsigned s2 = __shfl_xor_sync(0xffffffffu, sad, o);
+    const int k2 = __shfl_xor_sync(0xffffffffu, k, o);
+    const int m2 = __shfl_xor_sync(0xffffffffu, ((int)(uint16_t)mv.x) | ((int)mv.y << 16), o);
+    if (s2 < sad || (s2 == sad && k2 < k)) { sad = s2; k = k2; mv = mkmv((int16_t)(m2 & 0xffff), (int16_t)(m2 >> 16)); }
+  }
+}
+#endif
+
 // motion_estimate (enc/encode_block.c:830-1016).  orig: shared, stride `size` (the coding block's size); ref: block origin
 // in the reference luma plane.  Returns min(cmin, min_sad) and the vector.
 TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const uint8_t *orig, const uint8_t *ref, int size, int stride_r, int width,
@@ -186,35 +255,38 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
   THOR_LOCAL(&g);
   THOR_SHS(&S); THOR_SHARED(orig); THOR_SHARED(mvcand); THOR_SHF(&F);
   const int s = sign ? -1 : 1, speed = F.encoder_speed, fw = F.width, fh = F.height;
-  unsigned min_sad = 1u << 31, sad;
-  Mv mv_opt = mkmv(0, 0), mv_ref = mkmv(((mvc.x + 2) >> 2) << 2, ((mvc.y + 2) >> 2) << 2), cand;
-  int off[64];
-  Mv cands[64];
+  const int lane = me_lane(g);
+  unsigned min_sad = 1u << 31;
+  Mv mv_opt = mkmv(0, 0), mv_ref = mkmv(((mvc.x + 2) >> 2) << 2, ((mvc.y + 2) >> 2) << 2);
 
   if ((size == 16 && enable_bipred) || speed == 0) {
-    // telescope search: 5x5 grids of +-2 step, step = 32, 16, 8, 4 quarter-samples (:843-874)
+    // telescope search: 5x5 grids of +-2 step, step = 32, 16, 8, 4 quarter-samples (:843-874); the centre only at step 32
     for (int step = 32; step >= 4; step >>= 1) {
-      const int range = 2 * step;
       const int wide = step == 32 && size == 16 && speed < 2 && speed > 0;
-      int K = 0;
-      for (int k = -range; k <= range; k += step)
-        for (int l = -range; l <= range; l += step) {
-          if (step < 32 && !k && !l) continue;
-          cand = clip_mv(mkmv(mv_ref.x + l, mv_ref.y + k), ypos, xpos, fw, fh, size, sign);
-          cands[K] = cand;
-          off[K++] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;
-        }
-      sad_batch(g, S, orig, size, ref, stride_r, off, K, width, height, wide);
-      for (int k = 0; k < K; k++) {
-        cand = cands[k];
+      const int K = step < 32 ? 24 : 25;
+      for (int k = lane; k < K; k += ME_LANES) {
+        const int e = (step < 32 && k >= 12) ? k + 1 : k;
+        const Mv cand = clip_mv(mkmv(mv_ref.x + (e % 5 - 2) * step, mv_ref.y + (e / 5 - 2) * step), ypos, xpos, fw, fh, size, sign);
+        S.me_off[k] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;      // every warp writes the same values
+      }
+      sad_batch(g, S, orig, size, ref, stride_r, S.me_off, K, width, height, wide);
+      unsigned bsad = ~0u;
+      int bk = 1 << 30;
+      Mv bmv = mkmv(0, 0);
+      for (int k = lane; k < K; k += ME_LANES) {
+        const int e = (step < 32 && k >= 12) ? k + 1 : k;
+        Mv cand = clip_mv(mkmv(mv_ref.x + (e % 5 - 2) * step, mv_ref.y + (e / 5 - 2) * step), ypos, xpos, fw, fh, size, sign);
+        unsigned sad;
         if (wide) {
           int x;
           sad = widesad_pick(S.acc + 5 * k, &x);
           cand.x = (int16_t)(cand.x + (s * x << 2));
         } else sad = (unsigned)S.acc[k];
         sad += mv_cost(lambda, cand, mvp);
-        if (sad < min_sad) { min_sad = sad; mv_opt = cand; }
+        if (sad < bsad) { bsad = sad; bk = k; bmv = cand; }
       }
+      me_argmin(bsad, bk, bmv);
+      if (bsad < min_sad) { min_sad = bsad; mv_opt = bmv; }
       mv_ref = mv_opt;
     }
   }
@@ -222,20 +294,26 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
   // candidate search (:876-893)
   if (mvcand_num) {
     const int wide = size == 16;
-    for (int k = 0; k < mvcand_num; k++) {
-      cands[k] = clip_mv(mkmv(mvcand[k].x << 2, mvcand[k].y << 2), ypos, xpos, fw, fh, size, sign);
-      off[k] = s * (cands[k].x >> 2) + s * (cands[k].y >> 2) * stride_r;
+    for (int k = lane; k < mvcand_num; k += ME_LANES) {
+      const Mv cand = clip_mv(mkmv(mvcand[k].x << 2, mvcand[k].y << 2), ypos, xpos, fw, fh, size, sign);
+      S.me_off[k] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;
     }
-    sad_batch(g, S, orig, size, ref, stride_r, off, mvcand_num, width, height, wide);
-    for (int k = 0; k < mvcand_num; k++) {
-      cand = cands[k];
+    sad_batch(g, S, orig, size, ref, stride_r, S.me_off, mvcand_num, width, height, wide);
+    unsigned bsad = ~0u;
+    int bk = 1 << 30;
+    Mv bmv = mkmv(0, 0);
+    for (int k = lane; k < mvcand_num; k += ME_LANES) {
+      Mv cand = clip_mv(mkmv(mvcand[k].x << 2, mvcand[k].y << 2), ypos, xpos, fw, fh, size, sign);
       int x = 0;
+      unsigned sad;
       if (wide) sad = widesad_pick(S.acc + 5 * k, &x);
       else sad = (unsigned)S.acc[k];
       cand.x = (int16_t)(cand.x + (s * x << 2));
       sad += mv_cost(lambda, cand, mvp);
-      if (sad < min_sad) { min_sad = sad; mv_opt = cand; }
+      if (sad < bsad) { bsad = sad; bk = k; bmv = cand; }
     }
+    me_argmin(bsad, bk, bmv);
+    if (bsad < min_sad) { min_sad = bsad; mv_opt = bmv; }
   }
   mv_ref = mv_opt;
 
@@ -244,28 +322,29 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
     const int maxsteps = (size <= 16 || speed == 0) ? 6 : 0;
     int start = 0, end = 5;
     for (int step = 1; step < maxsteps; step++) {
-      int dirs[6], nd = 0;                                 // the directions visited this round, in order
-      {
-        int dir = start - 1;
-        do {
-          dir++;
-          dir = dir == 6 ? 0 : dir;
-          dirs[nd++] = dir;
-        } while (dir != end);
-      }
-      for (int k = 0; k < nd; k++) {
-        const int d = dirs[k];
+      const int nd = (end - start + 6) % 6 + 1;            // the directions visited this round: start, start + 1, .. end (mod 6)
+      for (int k = lane; k < nd; k += ME_LANES) {
+        const int d = (start + k) % 6;
         const int diy = d == 0 ? 1 : d == 1 ? 2 : d == 2 ? 1 : d == 3 ? -1 : d == 4 ? -2 : -1;
         const int dix = d == 0 ? -1 : d == 1 ? 0 : d == 2 ? 1 : d == 3 ? 1 : d == 4 ? 0 : -1;
-        cands[k] = clip_mv(mkmv(mv_ref.x + diy * 4, mv_ref.y + dix * 4), ypos, xpos, fw, fh, size, sign);
-        off[k] = s * (cands[k].x >> 2) + s * (cands[k].y >> 2) * stride_r;
+        const Mv cand = clip_mv(mkmv(mv_ref.x + diy * 4, mv_ref.y + dix * 4), ypos, xpos, fw, fh, size, sign);
+        S.me_off[k] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;
       }
-      sad_batch(g, S, orig, size, ref, stride_r, off, nd, width, height, 0);
+      sad_batch(g, S, orig, size, ref, stride_r, S.me_off, nd, width, height, 0);
+      unsigned bsad = ~0u;
+      int bk = 1 << 30;
+      Mv bmv = mkmv(0, 0);
+      for (int k = lane; k < nd; k += ME_LANES) {
+        const int d = (start + k) % 6;
+        const int diy = d == 0 ? 1 : d == 1 ? 2 : d == 2 ? 1 : d == 3 ? -1 : d == 4 ? -2 : -1;
+        const int dix = d == 0 ? -1 : d == 1 ? 0 : d == 2 ? 1 : d == 3 ? 1 : d == 4 ? 0 : -1;
+        const Mv cand = clip_mv(mkmv(mv_ref.x + diy * 4, mv_ref.y + dix * 4), ypos, xpos, fw, fh, size, sign);
+        const unsigned sad = (unsigned)S.acc[k] + mv_cost(lambda, cand, mvp);
+        if (sad < bsad) { bsad = sad; bk = k; bmv = cand; }
+      }
+      me_argmin(bsad, bk, bmv);
       int best_dir = -1;
-      for (int k = 0; k < nd; k++) {
-        sad = (unsigned)S.acc[k] + mv_cost(lambda, cands[k], mvp);
-        if (sad < min_sad) { min_sad = sad; mv_opt = cands[k]; best_dir = dirs[k]; }
-      }
+      if (bsad < min_sad) { min_sad = bsad; mv_opt = bmv; best_dir = (start + bk) % 6; }
       mv_ref = mv_opt;
       start = best_dir ? best_dir - 1 : 5;
       end = start + 2;
@@ -275,7 +354,8 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
   }
 
   int ydelta_hp = 0, xdelta_hp = 0, ydelta_qp = 0, xdelta_qp = 0;
-  unsigned cmin = min_sad;
+  unsigned cmin = min_sad, sad;
+  Mv cand;
   if (speed == 0) {
     // true interpolation at the 8 half-pel and then the 8 quarter-pel positions (:938-976)
     for (int pass = 0; pass < 2; pass++) {

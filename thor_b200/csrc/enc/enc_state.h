@@ -51,6 +51,7 @@ struct SbMem {
   uint8_t zz[16 + 64 + 256];
   uint32_t fire[3 * 8];              // quantiser: positions the RDOQ-light pass has to look at
   int acc[64 * 5 + 8];               // SAD accumulators of a batch of candidates
+  int me_off[64];                    // the batch's candidate offsets into the reference plane (motion_estimate)
   Mv mvcand[THOR_ENC_MAX_REF][64];   // frame_info.mvcand (enc/mainenc.h:124), reset per superblock
   // decision of a 16x16 block kept while its 8x8 children are tried (top-down split, enc/encode_block.c:2983-2995)
   uint8_t keep_y[256], keep_u[64], keep_v[64];
