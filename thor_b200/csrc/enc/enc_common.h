@@ -98,37 +98,40 @@ struct Grp {
   int *red;                          // shared: 2 * NW * 8 ints
   int flip;
   __device__ void sync() const { __syncthreads(); }
+  // Reductions over the group: one redux.sync per value inside a warp, the warps' partial results through `red` (double
+  // buffered: the next reduction writes the other half, so nobody waits for readers), and a second redux over the partials --
+  // no thread walks all warps' slots.
   __device__ int sum(int v) {
-#pragma unroll
-    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    v = __reduce_add_sync(0xffffffffu, v);
     THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = v;
     __syncthreads();
+    const int lane = tid & 31;
     int t = 0;
 #pragma unroll
-    for (int w = 0; w < NW; w++) t += r[w];
-    return t;
+    for (int i = 0; i < (NW + 31) / 32; i++) t += lane + 32 * i < NW ? r[lane + 32 * i] : 0;
+    return __reduce_add_sync(0xffffffffu, t);
   }
   template <int K> __device__ void sumk(int (&v)[K]) {
     static_assert(K <= 8, "reduction scratch holds 8 values per warp");
 #pragma unroll
-    for (int k = 0; k < K; k++)
-#pragma unroll
-      for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    for (int k = 0; k < K; k++) v[k] = __reduce_add_sync(0xffffffffu, v[k]);
     THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0)
 #pragma unroll
-      for (int k = 0; k < K; k++) r[(tid >> 5) * 8 + k] = v[k];
+      for (int k = 0; k < 8; k++) r[(tid >> 5) * 8 + k] = k < K ? v[k] : 0;
     __syncthreads();
+    // slot w * 8 + k: lane l adds the slots l, l + 32, .. (all of value l % 8), then the four lanes of a value add up
+    const int lane = tid & 31;
+    int x = 0;
 #pragma unroll
-    for (int k = 0; k < K; k++) {
-      int t = 0;
+    for (int i = lane; i < NW * 8; i += 32) x += r[i];
+    x += __shfl_xor_sync(0xffffffffu, x, 8);
+    x += __shfl_xor_sync(0xffffffffu, x, 16);
 #pragma unroll
-      for (int w = 0; w < NW; w++) t += r[w * 8 + k];
-      v[k] = t;
-    }
+    for (int k = 0; k < K; k++) v[k] = __shfl_sync(0xffffffffu, x, k);
   }
   __device__ int any(int p) { return __syncthreads_or(p); }
   __device__ int orall(int m) {                                        // bitwise OR of m over the group
@@ -137,41 +140,43 @@ struct Grp {
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = m;
     __syncthreads();
-    int t = r[0];
+    const int lane = tid & 31;
+    unsigned t = 0;
 #pragma unroll
-    for (int w = 1; w < NW; w++) t |= r[w];
-    return t;
+    for (int i = 0; i < (NW + 31) / 32; i++) t |= lane + 32 * i < NW ? (unsigned)r[lane + 32 * i] : 0u;
+    return (int)__reduce_or_sync(0xffffffffu, t);
   }
   __device__ void vmax3(int (&v)[3]) {                                 // three maxima with one barrier
 #pragma unroll
-    for (int k = 0; k < 3; k++)
-#pragma unroll
-      for (int o = 16; o; o >>= 1) v[k] = max(v[k], __shfl_xor_sync(0xffffffffu, v[k], o));
+    for (int k = 0; k < 3; k++) v[k] = __reduce_max_sync(0xffffffffu, v[k]);
     THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0)
 #pragma unroll
       for (int k = 0; k < 3; k++) r[(tid >> 5) * 8 + k] = v[k];
     __syncthreads();
+    const int lane = tid & 31;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-      int t = r[k];
+      int t = r[k];                                                    // warp 0's partial: a valid value for idle lanes
 #pragma unroll
-      for (int w = 1; w < NW; w++) t = max(t, r[w * 8 + k]);
-      v[k] = t;
+      for (int i = 0; i < (NW + 31) / 32; i++)
+        if (lane + 32 * i < NW) t = max(t, r[(lane + 32 * i) * 8 + k]);
+      v[k] = __reduce_max_sync(0xffffffffu, t);
     }
   }
   __device__ int vmax(int v) {
-#pragma unroll
-    for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    v = __reduce_max_sync(0xffffffffu, v);
     THOR_SHR(red);
     int *r = red + (flip ^= 1) * NW * 8;
     if ((tid & 31) == 0) r[tid >> 5] = v;
     __syncthreads();
+    const int lane = tid & 31;
     int t = r[0];
 #pragma unroll
-    for (int w = 1; w < NW; w++) t = max(t, r[w]);
-    return t;
+    for (int i = 0; i < (NW + 31) / 32; i++)
+      if (lane + 32 * i < NW) t = max(t, r[lane + 32 * i]);
+    return __reduce_max_sync(0xffffffffu, t);
   }
 #endif
 };
@@ -327,6 +332,16 @@ TD uint32_t havg4(uint32_t a, uint32_t b) {          // (a + b) >> 1 per byte
   return __vhaddu4(a, b);
 #endif
 }
+
+// Index arithmetic of the cooperative loops.  The GPU has no integer divide: `i / w` by a run-time w is a 20-instruction
+// sequence, and every loop body starts with one.  Block and transform sides are powers of two (p2div / p2mod); widths that
+// come from a picture edge (B.bwidth) can be 24, 40, 56: Div tests once, outside the loop.
+TD int p2div(int i, int d) { return i >> ilog2((uint32_t)d); }
+TD int p2mod(int i, int d) { return i & (d - 1); }
+struct Div { int d, sh; };
+TD Div mkdiv(int d) { Div v; v.d = d; v.sh = (d & (d - 1)) ? -1 : ilog2((uint32_t)d); return v; }
+TD int dq(const Div &v, int i) { return v.sh >= 0 ? i >> v.sh : i / v.d; }
+TD int dr(const Div &v, int i) { return v.sh >= 0 ? i & (v.d - 1) : i % v.d; }
 
 struct Mv { int16_t x, y; };
 TD Mv mkmv(int x, int y) { Mv m; m.x = (int16_t)x; m.y = (int16_t)y; return m; }

@@ -39,14 +39,16 @@ TDN void load_org(Enc &E, const BlockCtx &B) {
   Grp &g = E.g;
   const thor_enc_pic &o = E.F.orig;
   const int size = B.size, wq = B.bwidth / 4;
+  const Div dwq = mkdiv(wq);
   g.sync();
   TFOR(g, i, B.bheight * wq) {
-    const int r = i / wq, c = (i % wq) * 4;
+    const int r = dq(dwq, i), c = dr(dwq, i) * 4;
     *reinterpret_cast<uint32_t *>(E.S.org.y + r * size + c) = ld_ro32u(o.y + (B.ypos + r) * o.stride_y + B.xpos + c);
   }
   const int wc = B.bwidth / 2, sc = size / 2;
+  const Div dwc = mkdiv(wc);
   TFOR(g, i, (B.bheight / 2) * wc) {
-    const int r = i / wc, c = i % wc;
+    const int r = dq(dwc, i), c = dr(dwc, i);
     const int off = (B.ypos / 2 + r) * o.stride_c + B.xpos / 2 + c;
     E.S.org.u[r * sc + c] = ld_ro8(o.u + off);
     E.S.org.v[r * sc + c] = ld_ro8(o.v + off);
@@ -275,7 +277,7 @@ TDN int skip_test_luma(Enc &E, const uint8_t *org, int ostride, int size0, int q
   SbMem &S = E.S;
   const int n = size0 / 2, lg = ilog2((uint32_t)n);
   TFOR(g, i, n * n) {
-    const int r = 2 * (i / n), c = 2 * (i % n);
+    const int r = 2 * p2div(i, n), c = 2 * p2mod(i, n);
     const int s = ((int)org[r * ostride + c] - (int)pred[r * size0 + c]) + ((int)org[r * ostride + c + 1] - (int)pred[r * size0 + c + 1]) +
                   ((int)org[(r + 1) * ostride + c] - (int)pred[(r + 1) * size0 + c]) + ((int)org[(r + 1) * ostride + c + 1] - (int)pred[(r + 1) * size0 + c + 1]);
     S.resid[i] = (int16_t)((s + 2) >> 2);
@@ -656,13 +658,15 @@ TDN void finalize_block(Enc &E, const BlockCtx &B, const Param &P) {
   {                                                                    // copy_block_to_frame
     const thor_enc_pic &rec = F.rec;
     const int wq = B.bwidth / 4;
+    const Div dwq = mkdiv(wq);
     TFOR(g, i, B.bheight * wq) {
-      const int r = i / wq, c = (i % wq) * 4;
+      const int r = dq(dwq, i), c = dr(dwq, i) * 4;
       *reinterpret_cast<uint32_t *>(rec.y + (B.ypos + r) * rec.stride_y + B.xpos + c) = *reinterpret_cast<const uint32_t *>(S.best.y + r * size + c);
     }
     const int wc = B.bwidth / 2, sc = size / 2;
+    const Div dwc = mkdiv(wc);
     TFOR(g, i, (B.bheight / 2) * wc) {
-      const int r = i / wc, c = i % wc, off = (B.ypos / 2 + r) * rec.stride_c + B.xpos / 2 + c;
+      const int r = dq(dwc, i), c = dr(dwc, i), off = (B.ypos / 2 + r) * rec.stride_c + B.xpos / 2 + c;
       rec.u[off] = S.best.u[r * sc + c];
       rec.v[off] = S.best.v[r * sc + c];
     }
@@ -670,8 +674,9 @@ TDN void finalize_block(Enc &E, const BlockCtx &B, const Param &P) {
   const int tb_split = imax(0, P.tb_param);
   {                                                                    // copy_deblock_data
     const int uw = B.bwidth / 4, div = size / 8, ustride = F.width / 4;
+    const Div duw = mkdiv(uw);
     TFOR(g, i, (B.bheight / 4) * uw) {
-      const int m = i / uw, n = i % uw, index = 2 * (m / div) + n / div;
+      const int m = dq(duw, i), n = dr(duw, i), index = 2 * p2div(m, div) + p2div(n, div);
       thor_enc_unit u;
       u.mv0x = P.mv0[index].x; u.mv0y = P.mv0[index].y; u.mv1x = P.mv1[index].x; u.mv1y = P.mv1[index].y;
       u.mode = (uint8_t)P.mode;

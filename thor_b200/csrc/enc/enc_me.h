@@ -115,7 +115,7 @@ TDN unsigned sad_fasthalf(Grp &g, const uint8_t *a, int as, const uint8_t *b, in
   THOR_SHARED(a);
   int s[8] = {0, 0, 0, 0, 0, 0, 0, 0};                     // top down left right tl tr bl br
   TFOR(g, i, width * height) {
-    const int r = i / width, c = i % width;
+    const int r = p2div(i, width), c = p2mod(i, width);
     const uint8_t *p = b + r * bs + c;
     const int A = a[r * as + c];
     // the neighbourhood rows -2..+2 (only the samples the trees use)
@@ -177,7 +177,7 @@ TDN unsigned sad_fastquarter(Grp &g, const uint8_t *o, int os, const uint8_t *rf
   const int sel = (*x & *y) ? 0 : (*x ? 1 : (*y ? 2 : 3));
   int s[8] = {0, 0, 0, 0, 0, 0, 0, 0};                     // tl top tr left right bl down br
   TFOR(g, i, width * height) {
-    const int r0 = i / width, j = i % width;
+    const int r0 = p2div(i, width), j = p2mod(i, width);
     const uint8_t *r = rf + r0 * rs + j;
     const int O = o[r0 * os + j];
     const int a = ld_ro8(r), b = ld_ro8(r - rs), c = ld_ro8(r - rs + 1), d = ld_ro8(r + 1), e = ld_ro8(r + rs + 1), f = ld_ro8(r + rs),
@@ -366,7 +366,7 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
         cand = mkmv((pass ? mv_opt.x : mv_ref.x) + n, (pass ? mv_opt.y : mv_ref.y) + m);
         inter_luma(g, S, S.ipred, width, ref, stride_r, width, height, cand, sign, enable_bipred);
         int acc = 0;
-        TFOR(g, j, width * height) acc += iabs((int)orig[(j / width) * size + (j % width)] - (int)S.ipred[j]);
+        TFOR(g, j, width * height) acc += iabs((int)orig[p2div(j, width) * size + p2mod(j, width)] - (int)S.ipred[j]);
         sad = (unsigned)g.sum(acc);
         if (pass) sad += (unsigned)(int)dadd(dmul(lambda, (double)mv_bits(cand.y - mvp.y, cand.x - mvp.x)), 0.5);
         else sad += mv_cost(lambda, cand, mvp);

@@ -26,9 +26,10 @@ TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *
   const int fx = mx & 3, fy = my & 3;
   const uint8_t *src = ref + (my >> 2) * stride + (mx >> 2);
   const int wq = width >> 2;                              // 4-sample groups per row (width is a multiple of 4)
+  const Div dwq = mkdiv(wq);
   if (!fx && !fy) {
     TFOR(g, i, height * wq) {
-      const int r = i / wq, c = (i % wq) * 4;
+      const int r = dq(dwq, i), c = dr(dwq, i) * 4;
       *reinterpret_cast<uint32_t *>(dst + r * pstride + c) = ld_ro32u(src + r * stride + c);
     }
     g.sync();
@@ -37,7 +38,7 @@ TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *
   if (fx == 2 && fy == 2) {
     // centre position: [0 1 1 0; 1 2 2 1; 1 2 2 1; 0 1 1 0] / 16 (:146-160)
     TFOR(g, i, height * wq) {
-      const int r = i / wq, c = (i % wq) * 4;
+      const int r = dq(dwq, i), c = dr(dwq, i) * 4;
       int acc[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int dy = 0; dy < 4; dy++) {
@@ -66,7 +67,7 @@ TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *
   // intermediate rounding the order is immaterial)
   const int rows = height + 5;
   TFOR(g, i, rows * wq) {
-    const int r = i / wq, c = (i % wq) * 4;
+    const int r = dq(dwq, i), c = dr(dwq, i) * 4;
     const uint8_t *p = src + (r - 2) * stride + c - 2;
     const uint32_t w0 = ld_ro32u(p), w1 = ld_ro32u(p + 4), w2 = ld_ro32u(p + 8);
     int b[9];
@@ -80,7 +81,7 @@ TDN void inter_luma(Grp &g, SbMem &S, uint8_t *dst, int pstride, const uint8_t *
   g.sync();
   const int v0 = ky[0], v1 = ky[1], v2 = ky[2], v3 = ky[3], v4 = ky[4], v5 = ky[5];
   TFOR(g, i, height * wq) {
-    const int r = i / wq, c = (i % wq) * 4;
+    const int r = dq(dwq, i), c = dr(dwq, i) * 4;
     uint32_t out = 0;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
@@ -103,9 +104,10 @@ TDN void inter_chroma(Grp &g, uint8_t *dst_u, uint8_t *dst_v, int pstride, const
   const int fx = mx & 7, fy = my & 7;
   const int off = (my >> 3) * stride + (mx >> 3);
   const int n = width * height;
+  const Div dw = mkdiv(width);
   if (!fx && !fy) {
     TFOR(g, i, 2 * n) {
-      const int pl = i >= n, j = pl ? i - n : i, r = j / width, c = j % width;
+      const int pl = i >= n, j = pl ? i - n : i, r = dq(dw, j), c = dr(dw, j);
       (pl ? dst_v : dst_u)[r * pstride + c] = ld_ro8((pl ? ref_v : ref_u) + off + r * stride + c);
     }
     g.sync();
@@ -115,7 +117,7 @@ TDN void inter_chroma(Grp &g, uint8_t *dst_u, uint8_t *dst_v, int pstride, const
   const int h0 = kx[0], h1 = kx[1], h2 = kx[2], h3 = kx[3];
   const int v0 = ky[0], v1 = ky[1], v2 = ky[2], v3 = ky[3];
   TFOR(g, i, 2 * n) {
-    const int pl = i >= n, j = pl ? i - n : i, r = j / width, c = j % width;
+    const int pl = i >= n, j = pl ? i - n : i, r = dq(dw, j), c = dr(dw, j);
     const uint8_t *p = (pl ? ref_v : ref_u) + off + (r - 1) * stride + c - 1;
     int acc = 0;
 #pragma unroll
@@ -164,13 +166,15 @@ TDN void average_blocks(Grp &g, Blk &dst, const Blk &a, const Blk &b, const Bloc
   THOR_SHARED(&dst); THOR_SHARED(&a); THOR_SHARED(&b);
   THOR_LOCAL(&B); THOR_LOCAL(&g);
   const int size = B.size, wq = B.bwidth / 4, ny = B.bheight * wq;
+  const Div dwq = mkdiv(wq);
   TFOR(g, i, ny) {
-    const int o = (i / wq) * size + (i % wq) * 4;
+    const int o = dq(dwq, i) * size + dr(dwq, i) * 4;
     *reinterpret_cast<uint32_t *>(dst.y + o) = havg4(*reinterpret_cast<const uint32_t *>(a.y + o), *reinterpret_cast<const uint32_t *>(b.y + o));
   }
   const int wc = B.bwidth / 2, nc = (B.bheight / 2) * wc, sc = size / 2;
+  const Div dwc = mkdiv(wc);
   TFOR(g, i, nc) {
-    const int o = (i / wc) * sc + (i % wc);
+    const int o = dq(dwc, i) * sc + dr(dwc, i);
     dst.u[o] = (uint8_t)((a.u[o] + b.u[o]) >> 1);
     dst.v[o] = (uint8_t)((a.v[o] + b.v[o]) >> 1);
   }

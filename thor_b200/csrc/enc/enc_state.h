@@ -303,7 +303,7 @@ TDN int coeff_bits(Grp &g, SbMem &S, const int16_t *coeff, int size, int type) {
   g.sync();                                      // earlier readers of S.scan are done
   int mylast = -1;
   TFOR(g, i, N) {
-    const int16_t c = coeff[(i / q) * size + (i % q)];
+    const int16_t c = coeff[(p2div(i, q)) * size + (p2mod(i, q))];
     S.scan[zz[i]] = c;
     if (c) mylast = imax(mylast, (int)zz[i]);
   }
@@ -324,7 +324,7 @@ TDN int coeff_bits3(Grp &g, SbMem &S, const int16_t *cy, const int16_t *cu, cons
     int j, t;
     if (i < c0) { j = i; t = 0; } else if (i < c0 + c1) { j = i - c0; t = 1; } else { j = i - c0 - c1; t = 2; }
     const int q = t ? qc : qy, sz = t ? size / 2 : size;
-    const int16_t c = (t == 0 ? cy : t == 1 ? cu : cv)[(j / q) * sz + (j % q)];
+    const int16_t c = (t == 0 ? cy : t == 1 ? cu : cv)[(p2div(j, q)) * sz + (p2mod(j, q))];
     const int p = zigzag(S, q)[j];
     S.scan[t * 256 + p] = c;
     if (c) last[t] = imax(last[t], p);

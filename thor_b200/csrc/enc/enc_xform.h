@@ -14,14 +14,14 @@ TDN void forward_core(Grp &g, SbMem &S, int n, int sh1, int sh2) {
   const int16_t *in = S.resid;
   const int8_t *M = dct_matrix(S, n);
   TFOR(g, i, keep * n) {                                   // rows of the block -> horizontal frequency k
-    const int r = i / keep, k = i % keep;
+    const int r = p2div(i, keep), k = p2mod(i, keep);
     int acc = 0;
     for (int c = 0; c < n; c++) acc += M[k * n + c] * in[r * n + c];
     S.mid[k * 32 + r] = (int16_t)((acc + (1 << (sh1 - 1))) >> sh1);
   }
   g.sync();
   TFOR(g, i, keep * keep) {                                // vertical frequency v
-    const int v = i / keep, k = i % keep;
+    const int v = p2div(i, keep), k = p2mod(i, keep);
     int acc = 0;
     for (int r = 0; r < n; r++) acc += M[v * n + r] * S.mid[k * 32 + r];
     S.coeff[v * keep + k] = (int16_t)((acc + (1 << (sh2 - 1))) >> sh2);
@@ -39,7 +39,7 @@ TDN void forward_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uin
   if (size > 16 && fast) { n = 16; f = size / 16; sh1 = size == 64 ? 8 : 6; sh2 = 9; }
   else if (size == 64) { n = 32; f = 2; sh1 = 7; sh2 = 10; }
   TFOR(g, i, n * n) {
-    const int r = i / n, c = i % n;
+    const int r = p2div(i, n), c = p2mod(i, n);
     int s = 0;
     for (int a = 0; a < f; a++)
       for (int b = 0; b < f; b++) s += (int)org[(r * f + a) * ostride + c * f + b] - (int)pred[(r * f + a) * pstride + c * f + b];
@@ -121,7 +121,7 @@ TDN int quantize_tb(Grp &g, SbMem &S, int16_t *coeffq, int qp, int size, int coe
     }
     g.sync();
   }
-  TFOR(g, i, nq) coeffq[(i / q) * size + (i % q)] = (int16_t)S.lev[zz[i]];
+  TFOR(g, i, nq) coeffq[(p2div(i, q)) * size + (p2mod(i, q))] = (int16_t)S.lev[zz[i]];
   g.sync();
   return cbp;
 }
@@ -134,20 +134,20 @@ TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *
   const int lg = ilog2((uint32_t)size), q = imin(size, 16), n = size == 64 ? 32 : size, keep = imin(n, 16);
   const int lshift = qp / 6, rshift = lg - 1, scale = kDequant[qp % 6], add = 1 << (rshift - 1);
   TFOR(g, i, q * q) {
-    const int c = coeffq[(i / q) * size + (i % q)];
+    const int c = coeffq[(p2div(i, q)) * size + (p2mod(i, q))];
     S.rcoeff[i] = (int16_t)((((c * scale) << lshift) + add) >> rshift);
   }
   g.sync();
   const int8_t *M = dct_matrix(S, n);
   TFOR(g, i, keep * n) {                                   // column k of the coefficients -> spatial column
-    const int r = i / keep, k = i % keep;
+    const int r = p2div(i, keep), k = p2mod(i, keep);
     int acc = 0;
     for (int v = 0; v < keep; v++) acc += M[v * n + r] * S.rcoeff[v * q + k];
     S.mid[k * 32 + r] = (int16_t)iclip((acc + 64) >> 7, -32768, 32767);
   }
   g.sync();
   TFOR(g, i, n * n) {
-    const int r = i / n, c = i % n;
+    const int r = p2div(i, n), c = p2mod(i, n);
     int acc = 0;
     for (int k = 0; k < keep; k++) acc += M[k * n + c] * S.mid[k * 32 + r];
     S.rblock[i] = (int16_t)iclip((acc + 2048) >> 12, -32768, 32767);
@@ -160,7 +160,7 @@ TDN void reconstruct_tb(Grp &g, SbMem &S, const int16_t *coeffq, const uint8_t *
     }
   } else {
     TFOR(g, i, n * n) {
-      const int r = i / n, c = i % n;
+      const int r = p2div(i, n), c = p2mod(i, n);
       rec[r * rstride + c] = (uint8_t)clip255(S.rblock[i] + pred[r * pstride + c]);
     }
   }
@@ -179,7 +179,7 @@ TDN int encode_tb(Grp &g, SbMem &S, const uint8_t *org, int ostride, const uint8
   if (cbp) reconstruct_tb(g, S, coeffq, pred, pstride, rec, rstride, qp, size);
   else {
     TFOR(g, i, size * size) {
-      const int r = i / size, c = i % size;
+      const int r = p2div(i, size), c = p2mod(i, size);
       rec[r * rstride + c] = pred[r * pstride + c];
     }
     g.sync();
@@ -224,7 +224,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   // 1. transform input
   c0 = n[0] * n[0]; c1 = n[1] * n[1]; tot = c0 + c1 + n[2] * n[2];
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), nn = n[t], ff = f[t], r = j / nn, c = j % nn;
+    const int t = tb_of(i, c0, c1, j), nn = n[t], ff = f[t], r = p2div(j, nn), c = p2mod(j, nn);
     const uint8_t *o = tb[t].org + (r * ff) * tb[t].ostride + c * ff, *p = tb[t].pred + (r * ff) * tb[t].pstride + c * ff;
     int sum = 0;
     for (int a = 0; a < ff; a++)
@@ -235,7 +235,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   // 2. rows -> horizontal frequencies
   c0 = q[0] * n[0]; c1 = q[1] * n[1]; tot = c0 + c1 + q[2] * n[2];
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], r = j / keep, k = j % keep;
+    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], r = p2div(j, keep), k = p2mod(j, keep);
     const int8_t *M = dct_matrix(S, nn) + k * nn;
     const int16_t *in = S.resid + t * 1024 + r * nn;
     int acc = 0;
@@ -246,7 +246,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   // 3. vertical frequencies; 4. scan order + last significant position
   c0 = q[0] * q[0]; c1 = q[1] * q[1]; tot = c0 + c1 + q[2] * q[2];
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], v = j / keep, k = j % keep;
+    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], v = p2div(j, keep), k = p2mod(j, keep);
     const int8_t *M = dct_matrix(S, nn) + v * nn;
     const int16_t *m = S.mid + t * 512 + k * 32;
     int acc = 0;
@@ -327,7 +327,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   TFOR(g, i, tot) {
     const int t = tb_of(i, c0, c1, j), qq = q[t], qp = tb[t].qp, rshift = lg[t] - 1;
     const int l = (int16_t)S.lev[t * 256 + zigzag(S, qq)[j]];
-    tb[t].coeffq[(j / qq) * tb[t].size + (j % qq)] = (int16_t)l;
+    tb[t].coeffq[(p2div(j, qq)) * tb[t].size + (p2mod(j, qq))] = (int16_t)l;
     S.rcoeff[t * 256 + j] = (int16_t)((((l * kDequant[qp % 6]) << (qp / 6)) + (1 << (rshift - 1))) >> rshift);
   }
   g.sync();
@@ -335,7 +335,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     // 8. inverse transform (common/transform.c:432-518), blocks with levels only
     int k0 = ((cbp >> 0) & 1) ? q[0] * ni[0] : 0, k1 = ((cbp >> 1) & 1) ? q[1] * ni[1] : 0, k2 = ((cbp >> 2) & 1) ? q[2] * ni[2] : 0;
     TFOR(g, i, k0 + k1 + k2) {
-      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = j / keep, k = j % keep;
+      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = p2div(j, keep), k = p2mod(j, keep);
       const int8_t *M = dct_matrix(S, nn) + r;
       const int16_t *rc = S.rcoeff + t * 256 + k;
       int acc = 0;
@@ -345,7 +345,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     g.sync();
     k0 = ((cbp >> 0) & 1) ? ni[0] * ni[0] : 0; k1 = ((cbp >> 1) & 1) ? ni[1] * ni[1] : 0; k2 = ((cbp >> 2) & 1) ? ni[2] * ni[2] : 0;
     TFOR(g, i, k0 + k1 + k2) {
-      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = j / nn, c = j % nn;
+      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = p2div(j, nn), c = p2mod(j, nn);
       const int8_t *M = dct_matrix(S, nn) + c;
       const int16_t *m = S.mid + t * 512 + r;
       int acc = 0;
@@ -357,7 +357,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   // 9. reconstruction (common/common_block.c:148-156): prediction + residual where the block has levels, else the prediction
   c0 = tb[0].size * tb[0].size; c1 = ntb > 1 ? tb[1].size * tb[1].size : 0; tot = c0 + c1 + (ntb > 2 ? tb[2].size * tb[2].size : 0);
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), size = tb[t].size, r = j / size, c = j % size;
+    const int t = tb_of(i, c0, c1, j), size = tb[t].size, r = p2div(j, size), c = p2mod(j, size);
     int v = tb[t].pred[r * tb[t].pstride + c];
     if ((cbp >> t) & 1) v = clip255(v + (size == 64 ? S.rblock[t * 1024 + (r >> 1) * 32 + (c >> 1)] : S.rblock[t * 1024 + j]));
     tb[t].rec[r * tb[t].rstride + c] = (uint8_t)v;
@@ -372,14 +372,22 @@ TDN int ssd_yuv(Grp &g, const Blk &a, const Blk &b, int stride, int width, int h
   THOR_SHARED(&a); THOR_SHARED(&b);
   THOR_LOCAL(&g);
   int s = 0;
-  TFOR(g, i, width * height) {
-    const int o = (i / width) * stride + (i % width);
-    const int d = (int)a.y[o] - (int)b.y[o];
-    s += d * d;
+  // four luma samples per item (rows are 4-byte aligned, widths multiples of 8)
+  const int wq = width / 4;
+  const Div dwq = mkdiv(wq);
+  TFOR(g, i, wq * height) {
+    const int o = dq(dwq, i) * stride + dr(dwq, i) * 4;
+    const uint32_t x = *reinterpret_cast<const uint32_t *>(a.y + o), y = *reinterpret_cast<const uint32_t *>(b.y + o);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int d = (int)((x >> (8 * k)) & 255) - (int)((y >> (8 * k)) & 255);
+      s += d * d;
+    }
   }
   const int wc = width / 2, sc = stride / 2;
+  const Div dwc = mkdiv(wc);
   TFOR(g, i, wc * (height / 2)) {
-    const int o = (i / wc) * sc + (i % wc);
+    const int o = dq(dwc, i) * sc + dr(dwc, i);
     const int du = (int)a.u[o] - (int)b.u[o], dv = (int)a.v[o] - (int)b.v[o];
     s += du * du + dv * dv;
   }
