@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 for v in "$@"; do
   if [ "$v" = base ]; then export LD_LIBRARY_PATH=; else export LD_LIBRARY_PATH=$PWD/build/variants/$v; fi
   echo "=== $v" >> gpurun_out/variants.log
-  timeout 600 python profiles/r2/enc_gpu_check.py LDB_medium_complexity:416:240:6:32 LDB_medium_complexity:1920:1080:4:32 2>&1 | python -c "
+  [ -n "$SKIP_SINGLE" ] || timeout 600 python profiles/r2/enc_gpu_check.py LDB_medium_complexity:416:240:6:32 LDB_medium_complexity:1920:1080:4:32 2>&1 | python -c "
 import sys, json
 for ln in sys.stdin:
     try: d = json.loads(ln)
@@ -15,7 +15,7 @@ for ln in sys.stdin:
 " >> gpurun_out/variants.log
   for sc in ${STREAMS:-16:9}; do
     s=${sc%%:*}; c=${sc##*:}
-    timeout 900 python bench.py --no-cpu --no-decoder --no-segments --streams $s --ctas-per-frame $c --steps 6 --warmup 3 2>&1 | python -c "
+    timeout 900 python bench.py --no-cpu --no-decoder --no-segments --streams $s --ctas-per-frame $c --steps 6 --warmup 3 $BENCH_EXTRA 2>&1 | python -c "
 import sys, json
 for ln in sys.stdin:
     try: d = json.loads(ln)

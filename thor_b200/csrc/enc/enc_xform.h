@@ -206,12 +206,28 @@ TD int tb_of(int i, int c0, int c1, int &j) {
   return 2;
 }
 
+// Per-block values are picked with two selects (T3) from arrays that are only indexed by constants, so they live in
+// registers: indexing them -- or the descriptors -- by the run-time block number meant a local-memory load per use.
+#define T3(a) (t == 0 ? a[0] : t == 1 ? a[1] : a[2])
 TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   PROF(PF_TB);
   THOR_SHS(&S);
+  const uint8_t *t_org[3], *t_pred[3];
+  uint8_t *t_rec[3];
+  int16_t *t_cq[3];
+  int t_os[3], t_ps[3], t_rs[3], t_size[3] = {0, 0, 0}, t_qp[3], t_ct[3];
+#pragma unroll
+  for (int t = 0; t < 3; t++) {
+    const TbDesc &d = tb[t < ntb ? t : 0];
+    t_org[t] = d.org; t_pred[t] = d.pred; t_rec[t] = d.rec; t_cq[t] = d.coeffq;
+    t_os[t] = d.ostride; t_ps[t] = d.pstride; t_rs[t] = d.rstride; t_qp[t] = d.qp; t_ct[t] = d.ctype;
+    if (t < ntb) t_size[t] = d.size;
+  }
   // geometry per block: forward transform size n (after pooling by f), shifts, kept corner q, inverse size ni
   int n[3] = {0, 0, 0}, f[3] = {1, 1, 1}, sh1[3] = {0, 0, 0}, sh2[3] = {0, 0, 0}, q[3] = {0, 0, 0}, ni[3] = {0, 0, 0}, lg[3] = {0, 0, 0};
-  for (int t = 0; t < ntb; t++) {
+#pragma unroll
+  for (int t = 0; t < 3; t++) {
+    if (t >= ntb) continue;
     const int size = tb[t].size;
     lg[t] = ilog2((uint32_t)size);
     n[t] = size; sh1[t] = lg[t]; sh2[t] = lg[t] + 5;
@@ -224,44 +240,44 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   // 1. transform input
   c0 = n[0] * n[0]; c1 = n[1] * n[1]; tot = c0 + c1 + n[2] * n[2];
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), nn = n[t], ff = f[t], r = p2div(j, nn), c = p2mod(j, nn);
-    const uint8_t *o = tb[t].org + (r * ff) * tb[t].ostride + c * ff, *p = tb[t].pred + (r * ff) * tb[t].pstride + c * ff;
+    const int t = tb_of(i, c0, c1, j), nn = T3(n), ff = T3(f), r = p2div(j, nn), c = p2mod(j, nn);
+    const uint8_t *o = T3(t_org) + (r * ff) * T3(t_os) + c * ff, *p = T3(t_pred) + (r * ff) * T3(t_ps) + c * ff;
     int sum = 0;
     for (int a = 0; a < ff; a++)
-      for (int b = 0; b < ff; b++) sum += (int)o[a * tb[t].ostride + b] - (int)p[a * tb[t].pstride + b];
+      for (int b = 0; b < ff; b++) sum += (int)o[a * T3(t_os) + b] - (int)p[a * T3(t_ps) + b];
     S.resid[t * 1024 + j] = (int16_t)sum;
   }
   g.sync();
   // 2. rows -> horizontal frequencies
   c0 = q[0] * n[0]; c1 = q[1] * n[1]; tot = c0 + c1 + q[2] * n[2];
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], r = p2div(j, keep), k = p2mod(j, keep);
+    const int t = tb_of(i, c0, c1, j), nn = T3(n), keep = T3(q), r = p2div(j, keep), k = p2mod(j, keep);
     const int8_t *M = dct_matrix(S, nn) + k * nn;
     const int16_t *in = S.resid + t * 1024 + r * nn;
     int acc = 0;
     for (int c = 0; c < nn; c++) acc += M[c] * in[c];
-    S.mid[t * 512 + k * 32 + r] = (int16_t)((acc + (1 << (sh1[t] - 1))) >> sh1[t]);
+    S.mid[t * 512 + k * 32 + r] = (int16_t)((acc + (1 << (T3(sh1) - 1))) >> T3(sh1));
   }
   g.sync();
   // 3. vertical frequencies; 4. scan order + last significant position
   c0 = q[0] * q[0]; c1 = q[1] * q[1]; tot = c0 + c1 + q[2] * q[2];
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), nn = n[t], keep = q[t], v = p2div(j, keep), k = p2mod(j, keep);
+    const int t = tb_of(i, c0, c1, j), nn = T3(n), keep = T3(q), v = p2div(j, keep), k = p2mod(j, keep);
     const int8_t *M = dct_matrix(S, nn) + v * nn;
     const int16_t *m = S.mid + t * 512 + k * 32;
     int acc = 0;
     for (int r = 0; r < nn; r++) acc += M[r] * m[r];
-    S.coeff[t * 256 + j] = (int16_t)((acc + (1 << (sh2[t] - 1))) >> sh2[t]);
+    S.coeff[t * 256 + j] = (int16_t)((acc + (1 << (T3(sh2) - 1))) >> T3(sh2));
   }
   g.sync();
   int last[3] = {-1, -1, -1};
   TFOR(g, i, tot) {
     const int t = tb_of(i, c0, c1, j);
-    const int intra = (tb[t].ctype >> 1) & 1, shift = 21 - lg[t] + tb[t].qp / 6, scale = kQuant[tb[t].qp % 6];
+    const int intra = (T3(t_ct) >> 1) & 1, shift = 21 - T3(lg) + T3(t_qp) / 6, scale = kQuant[T3(t_qp) % 6];
     const int tail_off = (intra ? 38 : -26) * (1 << (shift - 8));
-    const int c = S.coeff[t * 256 + j], p = zigzag(S, q[t])[j];
+    const int c = S.coeff[t * 256 + j], p = zigzag(S, T3(q))[j];
     S.lin[t * 256 + p] = (int16_t)c;
-    if ((iabs(iabs(c) * scale + tail_off) >> shift) != 0) last[t] = imax(last[t], p);
+    if ((iabs(iabs(c) * scale + tail_off) >> shift) != 0) { if (t == 0) last[0] = imax(last[0], p); else if (t == 1) last[1] = imax(last[1], p); else last[2] = imax(last[2], p); }
   }
   g.vmax3(last);                                                       // barrier inside
   // 5. levels with the dead-zone offsets (:106-131)
@@ -269,9 +285,9 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   TFOR(g, i, tot) {
     const int t = tb_of(i, c0, c1, j);
     int l = 0;
-    if (j <= last[t]) {
-      const int intra = (tb[t].ctype >> 1) & 1, chroma = tb[t].ctype & 1, shift = 21 - lg[t] + tb[t].qp / 6;
-      const int c = S.lin[t * 256 + j], mag = kQuant[tb[t].qp % 6] * iabs(c);
+    if (j <= T3(last)) {
+      const int intra = (T3(t_ct) >> 1) & 1, chroma = T3(t_ct) & 1, shift = 21 - T3(lg) + T3(t_qp) / 6;
+      const int c = S.lin[t * 256 + j], mag = kQuant[T3(t_qp) % 6] * iabs(c);
       const int off = (((mag >> shift) == 0 || chroma) ? (intra ? 102 : 51) : (intra ? 115 : 90)) << (shift - 8);
       l = (mag + off) >> shift;
       if (l) mine |= 1 << t;
@@ -285,7 +301,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   if (cbp) {
     TFOR(g, i, tot) {
       const int t = tb_of(i, c0, c1, j);
-      const int N = (tb[t].ctype & 1) ? last[t] + 1 : q[t] * q[t];
+      const int N = (T3(t_ct) & 1) ? T3(last) + 1 : T3(q) * T3(q);
       const int16_t *lev = S.lev + t * 256;
       if (((cbp >> t) & 1) && j >= 2 && j < N && lev[j - 2] == 0 && lev[j - 1] == 0 && iabs(lev[j]) > 1) {
 #ifdef THOR_HOSTEMU
@@ -299,8 +315,8 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     if ((g.tid & 31) == 0)
       for (int t = g.tid >> 5; t < ntb; t += (g.n + 31) >> 5) {
         if (!((cbp >> t) & 1)) continue;
-        const int chroma = tb[t].ctype & 1, qp = tb[t].qp;
-        const int thr = (73 * kDequant[qp % 6] << (qp / 6)) >> (4 + lg[t]);
+        const int chroma = T3(t_ct) & 1, qp = T3(t_qp);
+        const int thr = (73 * kDequant[qp % 6] << (qp / 6)) >> (4 + T3(lg));
         int16_t *lev = S.lev + t * 256;
         const int16_t *lin = S.lin + t * 256;
         for (int w = 0; w < 8; w++) {
@@ -312,7 +328,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
             int ok = 1;
             if (p > 2 && iabs(lev[p - 3]) > 1) ok = 0;
             if (p > 3 && iabs(lev[p - 4]) > 1 && iabs(lev[p - 3]) > 0) ok = 0;
-            if (p == 2 && (!chroma || last[t] >= 6)) ok = 0;
+            if (p == 2 && (!chroma || T3(last) >= 6)) ok = 0;
             if (!(ok && lev[p - 2] == 0 && lev[p - 1] == 0 && iabs(lev[p]) > 1)) continue;
             const int k1 = iabs(lin[p]), k2 = iabs(lin[p - 1]), k3 = iabs(lin[p - 2]);
             if (k1 + imax(k2, k3) < thr) lev[p] = lin[p] < 0 ? -1 : 1;
@@ -325,9 +341,9 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   }
   // 7. levels back to raster order (the block's coefficient array) and dequantised (common/common_block.c:132-146)
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), qq = q[t], qp = tb[t].qp, rshift = lg[t] - 1;
+    const int t = tb_of(i, c0, c1, j), qq = T3(q), qp = T3(t_qp), rshift = T3(lg) - 1;
     const int l = (int16_t)S.lev[t * 256 + zigzag(S, qq)[j]];
-    tb[t].coeffq[(p2div(j, qq)) * tb[t].size + (p2mod(j, qq))] = (int16_t)l;
+    T3(t_cq)[(p2div(j, qq)) * T3(t_size) + (p2mod(j, qq))] = (int16_t)l;
     S.rcoeff[t * 256 + j] = (int16_t)((((l * kDequant[qp % 6]) << (qp / 6)) + (1 << (rshift - 1))) >> rshift);
   }
   g.sync();
@@ -335,7 +351,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     // 8. inverse transform (common/transform.c:432-518), blocks with levels only
     int k0 = ((cbp >> 0) & 1) ? q[0] * ni[0] : 0, k1 = ((cbp >> 1) & 1) ? q[1] * ni[1] : 0, k2 = ((cbp >> 2) & 1) ? q[2] * ni[2] : 0;
     TFOR(g, i, k0 + k1 + k2) {
-      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = p2div(j, keep), k = p2mod(j, keep);
+      const int t = tb_of(i, k0, k1, j), nn = T3(ni), keep = T3(q), r = p2div(j, keep), k = p2mod(j, keep);
       const int8_t *M = dct_matrix(S, nn) + r;
       const int16_t *rc = S.rcoeff + t * 256 + k;
       int acc = 0;
@@ -345,7 +361,7 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
     g.sync();
     k0 = ((cbp >> 0) & 1) ? ni[0] * ni[0] : 0; k1 = ((cbp >> 1) & 1) ? ni[1] * ni[1] : 0; k2 = ((cbp >> 2) & 1) ? ni[2] * ni[2] : 0;
     TFOR(g, i, k0 + k1 + k2) {
-      const int t = tb_of(i, k0, k1, j), nn = ni[t], keep = q[t], r = p2div(j, nn), c = p2mod(j, nn);
+      const int t = tb_of(i, k0, k1, j), nn = T3(ni), keep = T3(q), r = p2div(j, nn), c = p2mod(j, nn);
       const int8_t *M = dct_matrix(S, nn) + c;
       const int16_t *m = S.mid + t * 512 + r;
       int acc = 0;
@@ -357,14 +373,16 @@ TDN int encode_tb3(Grp &g, SbMem &S, const TbDesc *tb, int ntb) {
   // 9. reconstruction (common/common_block.c:148-156): prediction + residual where the block has levels, else the prediction
   c0 = tb[0].size * tb[0].size; c1 = ntb > 1 ? tb[1].size * tb[1].size : 0; tot = c0 + c1 + (ntb > 2 ? tb[2].size * tb[2].size : 0);
   TFOR(g, i, tot) {
-    const int t = tb_of(i, c0, c1, j), size = tb[t].size, r = p2div(j, size), c = p2mod(j, size);
-    int v = tb[t].pred[r * tb[t].pstride + c];
+    const int t = tb_of(i, c0, c1, j), size = T3(t_size), r = p2div(j, size), c = p2mod(j, size);
+    int v = T3(t_pred)[r * T3(t_ps) + c];
     if ((cbp >> t) & 1) v = clip255(v + (size == 64 ? S.rblock[t * 1024 + (r >> 1) * 32 + (c >> 1)] : S.rblock[t * 1024 + j]));
-    tb[t].rec[r * tb[t].rstride + c] = (uint8_t)v;
+    T3(t_rec)[r * T3(t_rs) + c] = (uint8_t)v;
   }
   g.sync();
   return cbp;
 }
+
+#undef T3
 
 // ssd_calc (enc/encode_block.c:782-797) over the three planes of a block: cost_calc's distortion (:1218-1228)
 TDN int ssd_yuv(Grp &g, const Blk &a, const Blk &b, int stride, int width, int height) {
