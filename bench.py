@@ -362,6 +362,7 @@ def run_gpu_arm(args, rank, world, local_rank):
             raise SystemExit(f"{need} is missing: run __graft_entry__.build() where /root/reference is mounted")
     dist = None
     if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("THOR_BENCH_NCCL_DEBUG", "WARN")     # rank 0's stdout is ONE JSON line: no NCCL version banner
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
