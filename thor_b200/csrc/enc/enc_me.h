@@ -48,39 +48,50 @@ TDN void sad_batch(Grp &g, SbMem &S, const uint8_t *a, int as, const uint8_t *re
     g.sync();
   }
   const int chunk = items / sp;                            // items and sp are powers of two
+  // A lane keeps its word column (32 is a multiple of the words per row) and steps down the rows with two pointer
+  // increments; the reference rows share one byte alignment (the picture stride is a multiple of 16), so the aligned
+  // word pointer and the funnel shift are set up once per candidate.
+  const int c = (lane & (wq - 1)) << 2, rstep = 32 >> lwq;
+  const int passes = chunk >= 32 ? chunk >> 5 : 1;
+  const bool active = lane < chunk;
   for (int u = warp; u < K * sp; u += NW) {
     const int k = u / sp, part = u - k * sp;
-    const uint8_t *rp = ref + off[k];
-    const int it0 = part * chunk, it1 = it0 + chunk;
+    const int row0 = ((part * chunk) >> lwq) + (lane >> lwq);
+    const uint8_t *pa = a + row0 * as + c;
     if (!wide) {
+      const uintptr_t ad = reinterpret_cast<uintptr_t>(ref + off[k] + row0 * bs + c);
+      const uint32_t *q = reinterpret_cast<const uint32_t *>(ad & ~(uintptr_t)3);
+      const unsigned sh = (unsigned)(ad & 3) * 8;
+      const int qstep = (rstep * bs) >> 2, astep = rstep * as;
       int v = 0;
-      for (int it = it0 + lane; it < it1; it += 32) {
-        const int r = it >> lwq, c = (it & (wq - 1)) << 2;
-        v += (int)sad4(*reinterpret_cast<const uint32_t *>(a + r * as + c), ld_ro32u(rp + r * bs + c));
-      }
-#pragma unroll
-      for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (active)
+        for (int j = 0; j < passes; j++) {
+          v += (int)sad4(*reinterpret_cast<const uint32_t *>(pa), __funnelshift_r(__ldg(q), __ldg(q + 1), sh));
+          pa += astep;
+          q += qstep;
+        }
+      v = __reduce_add_sync(0xffffffffu, v);
       if (lane == 0) { if (sp > 1) atomicAdd(&S.acc[k], v); else S.acc[k] = v; }
     } else {
+      const uintptr_t ad = reinterpret_cast<uintptr_t>(ref + off[k] + row0 * bs + c - 3);
+      const uint32_t *q = reinterpret_cast<const uint32_t *>(ad & ~(uintptr_t)3);
+      const int o0 = (int)(ad & 3);
+      const int qstep = (rstep * bs) >> 2, astep = rstep * as;
       int v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0;
-      for (int it = it0 + lane; it < it1; it += 32) {
-        const int r = it >> lwq, c = (it & (wq - 1)) << 2;
-        const uint32_t A = *reinterpret_cast<const uint32_t *>(a + r * as + c);
-        const uintptr_t p = reinterpret_cast<uintptr_t>(rp + r * bs + c - 3);
-        const uint32_t *q = reinterpret_cast<const uint32_t *>(p & ~(uintptr_t)3);
-        const int o0 = (int)(p & 3);
-        const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2), w3 = __ldg(q + 3);
-        v0 += (int)sad4(A, window_word(w0, w1, w2, w3, o0));          // x - 3
-        v1 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 2));      // x - 1
-        v2 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 3));      // x
-        v3 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 4));      // x + 1
-        v4 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 6));      // x + 3
-      }
-#pragma unroll
-      for (int o = 16; o; o >>= 1) {
-        v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o); v2 += __shfl_xor_sync(0xffffffffu, v2, o);
-        v3 += __shfl_xor_sync(0xffffffffu, v3, o); v4 += __shfl_xor_sync(0xffffffffu, v4, o);
-      }
+      if (active)
+        for (int j = 0; j < passes; j++) {
+          const uint32_t A = *reinterpret_cast<const uint32_t *>(pa);
+          const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2), w3 = __ldg(q + 3);
+          v0 += (int)sad4(A, window_word(w0, w1, w2, w3, o0));          // x - 3
+          v1 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 2));      // x - 1
+          v2 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 3));      // x
+          v3 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 4));      // x + 1
+          v4 += (int)sad4(A, window_word(w0, w1, w2, w3, o0 + 6));      // x + 3
+          pa += astep;
+          q += qstep;
+        }
+      v0 = __reduce_add_sync(0xffffffffu, v0); v1 = __reduce_add_sync(0xffffffffu, v1); v2 = __reduce_add_sync(0xffffffffu, v2);
+      v3 = __reduce_add_sync(0xffffffffu, v3); v4 = __reduce_add_sync(0xffffffffu, v4);
       if (lane < 5) {
         const int v = lane == 0 ? v0 : lane == 1 ? v1 : lane == 2 ? v2 : lane == 3 ? v3 : v4;
         if (sp > 1) atomicAdd(&S.acc[5 * k + lane], v); else S.acc[5 * k + lane] = v;

@@ -32,9 +32,9 @@ struct SbMem {
   thor_enc_frame frame;              // the frame description: copied from the kernel parameters once per CTA
   Blk org, rec, best, pred, p0, p1;
   Coef tc, bc;                       // coefficients of the trial / of the best trial so far
-  int16_t resid[3 * 1024];           // transform input (n <= 32 after pooling), slot t at t * 1024
+  alignas(16) int16_t resid[3 * 1024];           // transform input (n <= 32 after pooling), slot t at t * 1024
   // transform scratch: three transform blocks (Y, U, V of a coding block) are in flight at once, slot t at t * stride
-  int16_t mid[3 * 16 * 32];          // transform intermediate
+  alignas(16) int16_t mid[3 * 16 * 32];          // transform intermediate
   int16_t coeff[3 * 256];            // low q x q corner of the forward transform, stride q
   int16_t rcoeff[3 * 256];           // dequantised, stride q
   int16_t rblock[3 * 1024];          // inverse transform output (n <= 32), stride n
@@ -47,7 +47,7 @@ struct SbMem {
   uint8_t top[3][132], left[3][132]; // intra neighbours per plane
   uint8_t topleft[4];
   uint8_t tf[132], lf[132];          // smoothed neighbour rows
-  int8_t dct[32 * 32 + 16 * 16 + 8 * 8 + 4 * 4];
+  alignas(16) int8_t dct[32 * 32 + 16 * 16 + 8 * 8 + 4 * 4];
   uint8_t zz[16 + 64 + 256];
   uint32_t fire[3 * 8];              // quantiser: positions the RDOQ-light pass has to look at
   int acc[64 * 5 + 8];               // SAD accumulators of a batch of candidates
