@@ -249,7 +249,7 @@ TD int super_mode_len(const thor_enc_frame &F, const BlockCtx &B, int mode, int 
 }
 
 // the two-mode scan of write_coeff (:160-250) over levels in scan order, as a length
-TD int scan_bits(const int16_t *s, int N, int last_pos, bool chroma, bool intra, int size) {
+TDN int scan_bits(const int16_t *s, int N, int last_pos, bool chroma, bool intra, int size) {
   const bool small_chroma = chroma && size <= 8;
   int bits = 0, pos = 0;
   if (chroma) {
@@ -314,7 +314,7 @@ TD int warp_latest(int local_before, int mine_incl, int lane) {       // exclusi
   if (lane == 0) excl = -1;
   return max(local_before, excl);
 }
-TD int scan_bits_warp(const int16_t *s, int N, int last_pos, bool chroma, bool intra, int size, int lane) {
+TDN int scan_bits_warp(const int16_t *s, int N, int last_pos, bool chroma, bool intra, int size, int lane) {
   // a warp prices eight positions per lane in ~500 instructions whatever the block holds; the sequential walk costs ~25 per
   // position up to the last level, and most blocks end early (measured: always-parallel was 5 % faster per frame and 5 %
   // slower for 24 streams together)
