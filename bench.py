@@ -7,7 +7,7 @@ reference's Thorenc with every block decision of encode_frame on the B200 (integ
 thorcuda_enc_frame + thorcuda_loopfilter_frame; entropy coding = the reference's own write_block on the host).
 
 An LDB stream is one unbroken P chain and one frame's superblock wavefront keeps at most 15 of the 148 SMs busy
-(DESIGN.md 4.10), so the unit of parallelism is the INDEPENDENT STREAM: `--streams` (24) encoder processes per GPU
+(DESIGN.md 4.10), so the unit of parallelism is the INDEPENDENT STREAM: `--streams` (36) encoder processes per GPU
 share it through CUDA MPS.  A step = one frame of every stream.
 
   value : frames/s from the CUDA-event time of the frames' device work (frame upload .. decisions .. loop filter .. download),
@@ -487,8 +487,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="thorcuda", choices=["thorcuda", "reference"])
-    ap.add_argument("--streams", type=int, default=24, help="independent encoder processes per GPU = frames per step")
-    ap.add_argument("--ctas-per-frame", type=int, default=6, help="CTAs k_encode_frame uses per frame in the multi-stream run (THORCUDA_ENC_CTAS): "
+    ap.add_argument("--streams", type=int, default=36, help="independent encoder processes per GPU = frames per step")
+    ap.add_argument("--ctas-per-frame", type=int, default=4, help="CTAs k_encode_frame uses per frame in the multi-stream run (THORCUDA_ENC_CTAS): "
                     "streams x this should not exceed the 148 SMs; the one-stream legs use the library default, min(rows, cols/2)")
     ap.add_argument("--allow-oversubscription", action="store_true", help="run although streams x CTAs per frame exceeds the 148 resident CTAs of a B200 "
                     "(one k_encode_frame CTA per SM): such runs died with an illegal memory access about every second time (DESIGN.md 4.10, open issue)")

@@ -722,12 +722,77 @@ TD void mark_split(Enc &E, const BlockCtx &B) {
   }
 }
 
+// The parts of process_block that do not depend on the block size as a compile-time constant live in functions of their own:
+// process_block is instantiated four times (64 / 32 / 16 / 8) and the kernel is bound by instruction fetch.
+TDN void block_begin(Enc &E, BlockCtx &B, Param &best, int size, int ypos, int xpos, int qp) {
+  THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&best);
+  const thor_enc_frame &F = E.F;
+  B.size = size; B.ypos = ypos; B.xpos = xpos;
+  B.bwidth = imin(size, F.width - xpos);
+  B.bheight = imin(size, F.height - ypos);
+  B.max_num_tb_part = F.enable_tb_split == 1 ? 2 : 1;
+  B.max_num_pb_part = F.enable_pb_split ? 4 : 1;
+  B.delta_qp = qp - F.qp;
+  B.mvp = mkmv(0, 0);
+  B.num_skip_vec = B.num_merge_vec = 0;
+  find_block_contexts(F, ypos, xpos, size, B);
+  if (F.frame_type != 0) {
+    B.num_skip_vec = get_mv_skip(F, ypos, xpos, size, B.skip_cand);
+    B.num_merge_vec = get_mv_skip(F, ypos, xpos, size, B.merge_cand);  // get_mv_merge is the same function under LIMITED_SKIP
+  }
+  best.mode = 0; best.intra_mode = 0; best.skip_idx = 0; best.pb_part = 0; best.ref_idx0 = best.ref_idx1 = 0; best.dir = 0;
+  best.cbp_y = best.cbp_u = best.cbp_v = 0; best.tb_param = 0; best.tb_split = 0;
+  for (int i = 0; i < 4; i++) best.mv0[i] = best.mv1[i] = mkmv(0, 0);
+}
+
+// search_early_skip_candidates (:2743-2783): true when a skip candidate passed the test; the block is then finished
+TDN bool early_skip_block(Enc &E, BlockCtx &B, Param &best, uint32_t *cost_out) {
+  THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&best);
+  load_org(E, B);
+  uint32_t min_cost = 1u << 31;
+  int early = 0;
+  Param P = best;
+  for (int idx = 0; idx < B.num_skip_vec; idx++) {
+    param_from_cand(P, B.skip_cand[idx], idx, 0);
+    P.tb_param = 0;
+    if (check_early_skip(E, B, P)) {
+      early = 1;
+      try_cost(E, B, P, best, min_cost, B.size, B.size, nullptr);
+    }
+  }
+  if (early) finalize_block(E, B, best);
+  *cost_out = min_cost;
+  return early != 0;
+}
+
+// the decision of a 16x16 block waits while its four children are tried (top-down split, enc/encode_block.c:2983-2995)
+TDN void keep_16(Enc &E, int restore) {
+  THOR_LOCAL(&E);
+  Grp &g = E.g;
+  SbMem &S = E.S;
+  g.sync();
+  if (!restore) {
+    TFOR(g, i, 256) { S.keep_y[i] = S.best.y[i]; S.keep_cy[i] = S.bc.y[i]; }
+    TFOR(g, i, 64) { S.keep_u[i] = S.best.u[i]; S.keep_v[i] = S.best.v[i]; S.keep_cu[i] = S.bc.u[i]; S.keep_cv[i] = S.bc.v[i]; }
+  } else {
+    TFOR(g, i, 256) { S.best.y[i] = S.keep_y[i]; S.bc.y[i] = S.keep_cy[i]; }
+    TFOR(g, i, 64) { S.best.u[i] = S.keep_u[i]; S.best.v[i] = S.keep_v[i]; S.bc.u[i] = S.keep_cu[i]; S.bc.v[i] = S.keep_cv[i]; }
+  }
+  g.sync();
+}
+
+// mode_decision of a whole or picture-edge block and, if it beats the smaller blocks, its final encode
+TDN uint32_t decide_block(Enc &E, BlockCtx &B, Param &best) {
+  THOR_LOCAL(&E); THOR_LOCAL(&B); THOR_LOCAL(&best);
+  load_org(E, B);
+  return mode_decision(E, B, best);
+}
+TDN void split_mark(Enc &E, const BlockCtx &B) { mark_split(E, B); }
+
 template <int SIZE>
 TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
   THOR_LOCAL(&E);
   THOR_SHS(&E.S); THOR_SHF(&E.F);
-  Grp &g = E.g;
-  SbMem &S = E.S;
   const thor_enc_frame &F = E.F;
   if (ypos >= F.height || xpos >= F.width) return 0;
   const int encode_this_size = ypos + SIZE <= F.height && xpos + SIZE <= F.width;
@@ -738,46 +803,16 @@ TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
   uint32_t cost_small = 1u << 28, cost = 1u << 28;
 
   BlockCtx B;
-  B.size = SIZE; B.ypos = ypos; B.xpos = xpos;
-  B.bwidth = imin(SIZE, F.width - xpos);
-  B.bheight = imin(SIZE, F.height - ypos);
-  B.max_num_tb_part = F.enable_tb_split == 1 ? 2 : 1;
-  B.max_num_pb_part = F.enable_pb_split ? 4 : 1;
-  B.delta_qp = qp - F.qp;
-  B.mvp = mkmv(0, 0);
-  B.num_skip_vec = B.num_merge_vec = 0;
-  find_block_contexts(F, ypos, xpos, SIZE, B);
-  if (F.frame_type != 0) {
-    B.num_skip_vec = get_mv_skip(F, ypos, xpos, SIZE, B.skip_cand);
-    B.num_merge_vec = get_mv_skip(F, ypos, xpos, SIZE, B.merge_cand);  // get_mv_merge is the same function under LIMITED_SKIP
-  }
   Param best;
-  best.mode = 0; best.intra_mode = 0; best.skip_idx = 0; best.pb_part = 0; best.ref_idx0 = best.ref_idx1 = 0; best.dir = 0;
-  best.cbp_y = best.cbp_u = best.cbp_v = 0; best.tb_param = 0; best.tb_split = 0;
-  for (int i = 0; i < 4; i++) best.mv0[i] = best.mv1[i] = mkmv(0, 0);
+  block_begin(E, B, best, SIZE, ypos, xpos, qp);
 
   if (encode_this_size && F.frame_type != 0 && F.early_skip_thr > 0.0f) {
-    // search_early_skip_candidates (:2743-2783)
-    load_org(E, B);
-    uint32_t min_cost = 1u << 31;
-    int early = 0;
-    Param P = best;
-    for (int idx = 0; idx < B.num_skip_vec; idx++) {
-      param_from_cand(P, B.skip_cand[idx], idx, 0);
-      P.tb_param = 0;
-      if (check_early_skip(E, B, P)) {
-        early = 1;
-        try_cost(E, B, P, best, min_cost, SIZE, SIZE, nullptr);
-      }
-    }
-    if (early) {
-      finalize_block(E, B, best);
-      return (int)min_cost;
-    }
+    uint32_t min_cost;
+    if (early_skip_block(E, B, best, &min_cost)) return (int)min_cost;
   }
 
   if (encode_smaller_size) {
-    mark_split(E, B);
+    split_mark(E, B);
     if constexpr (SIZE > 8) {
       constexpr int NS = SIZE / 2;
       cost_small = 0;
@@ -789,17 +824,12 @@ TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
   }
 
   if (encode_this_size) {
-    load_org(E, B);
-    cost = mode_decision(E, B, best);
+    cost = decide_block(E, B, best);
     const int me_threshold = SIZE * SIZE * kIq8x8[qp] / 8;
     bool kept = false;
     if (top_down && cost > (uint32_t)me_threshold) {
       if constexpr (SIZE == 16) {
-        // the decision of this block waits while its four children are tried
-        g.sync();
-        TFOR(g, i, 256) { S.keep_y[i] = S.best.y[i]; S.keep_cy[i] = S.bc.y[i]; }
-        TFOR(g, i, 64) { S.keep_u[i] = S.best.u[i]; S.keep_v[i] = S.best.v[i]; S.keep_cu[i] = S.bc.u[i]; S.keep_cv[i] = S.bc.v[i]; }
-        g.sync();
+        keep_16(E, 0);
         kept = true;
         cost_small = 0;
         cost_small += (uint32_t)process_block<8>(E, ypos, xpos, qp);
@@ -809,19 +839,13 @@ TDN int process_block(Enc &E, int ypos, int xpos, int qp) {
       }
     }
     if (cost <= cost_small) {
-      if (kept) {
-        g.sync();
-        TFOR(g, i, 256) { S.best.y[i] = S.keep_y[i]; S.bc.y[i] = S.keep_cy[i]; }
-        TFOR(g, i, 64) { S.best.u[i] = S.keep_u[i]; S.best.v[i] = S.keep_v[i]; S.bc.u[i] = S.keep_cu[i]; S.bc.v[i] = S.keep_cv[i]; }
-        g.sync();
-      }
+      if (kept) keep_16(E, 1);
       finalize_block(E, B, best);
     } else {
-      mark_split(E, B);
+      split_mark(E, B);
     }
   } else if (encode_rectangular_size) {
-    load_org(E, B);
-    cost = mode_decision(E, B, best);
+    cost = decide_block(E, B, best);
     if (cost <= cost_small) finalize_block(E, B, best);
   }
   return (int)(cost < cost_small ? cost : cost_small);

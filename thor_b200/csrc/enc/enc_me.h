@@ -269,24 +269,25 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
   const int lane = me_lane(g);
   unsigned min_sad = 1u << 31;
   Mv mv_opt = mkmv(0, 0), mv_ref = mkmv(((mvc.x + 2) >> 2) << 2, ((mvc.y + 2) >> 2) << 2);
+  Mv mine[64 / ME_LANES];                                  // this lane's candidates of the current batch (k = lane, lane + 32)
 
   if ((size == 16 && enable_bipred) || speed == 0) {
     // telescope search: 5x5 grids of +-2 step, step = 32, 16, 8, 4 quarter-samples (:843-874); the centre only at step 32
     for (int step = 32; step >= 4; step >>= 1) {
       const int wide = step == 32 && size == 16 && speed < 2 && speed > 0;
       const int K = step < 32 ? 24 : 25;
-      for (int k = lane; k < K; k += ME_LANES) {
+      for (int k = lane, n = 0; k < K; k += ME_LANES, n++) {
         const int e = (step < 32 && k >= 12) ? k + 1 : k;
         const Mv cand = clip_mv(mkmv(mv_ref.x + (e % 5 - 2) * step, mv_ref.y + (e / 5 - 2) * step), ypos, xpos, fw, fh, size, sign);
+        mine[n] = cand;
         S.me_off[k] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;      // every warp writes the same values
       }
       sad_batch(g, S, orig, size, ref, stride_r, S.me_off, K, width, height, wide);
       unsigned bsad = ~0u;
       int bk = 1 << 30;
       Mv bmv = mkmv(0, 0);
-      for (int k = lane; k < K; k += ME_LANES) {
-        const int e = (step < 32 && k >= 12) ? k + 1 : k;
-        Mv cand = clip_mv(mkmv(mv_ref.x + (e % 5 - 2) * step, mv_ref.y + (e / 5 - 2) * step), ypos, xpos, fw, fh, size, sign);
+      for (int k = lane, n = 0; k < K; k += ME_LANES, n++) {
+        Mv cand = mine[n];
         unsigned sad;
         if (wide) {
           int x;
@@ -305,16 +306,17 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
   // candidate search (:876-893)
   if (mvcand_num) {
     const int wide = size == 16;
-    for (int k = lane; k < mvcand_num; k += ME_LANES) {
+    for (int k = lane, n = 0; k < mvcand_num; k += ME_LANES, n++) {
       const Mv cand = clip_mv(mkmv(mvcand[k].x << 2, mvcand[k].y << 2), ypos, xpos, fw, fh, size, sign);
+      mine[n] = cand;
       S.me_off[k] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;
     }
     sad_batch(g, S, orig, size, ref, stride_r, S.me_off, mvcand_num, width, height, wide);
     unsigned bsad = ~0u;
     int bk = 1 << 30;
     Mv bmv = mkmv(0, 0);
-    for (int k = lane; k < mvcand_num; k += ME_LANES) {
-      Mv cand = clip_mv(mkmv(mvcand[k].x << 2, mvcand[k].y << 2), ypos, xpos, fw, fh, size, sign);
+    for (int k = lane, n = 0; k < mvcand_num; k += ME_LANES, n++) {
+      Mv cand = mine[n];
       int x = 0;
       unsigned sad;
       if (wide) sad = widesad_pick(S.acc + 5 * k, &x);
@@ -334,22 +336,20 @@ TDN unsigned motion_estimate(Grp &g, SbMem &S, const thor_enc_frame &F, const ui
     int start = 0, end = 5;
     for (int step = 1; step < maxsteps; step++) {
       const int nd = (end - start + 6) % 6 + 1;            // the directions visited this round: start, start + 1, .. end (mod 6)
-      for (int k = lane; k < nd; k += ME_LANES) {
+      for (int k = lane, n = 0; k < nd; k += ME_LANES, n++) {
         const int d = (start + k) % 6;
         const int diy = d == 0 ? 1 : d == 1 ? 2 : d == 2 ? 1 : d == 3 ? -1 : d == 4 ? -2 : -1;
         const int dix = d == 0 ? -1 : d == 1 ? 0 : d == 2 ? 1 : d == 3 ? 1 : d == 4 ? 0 : -1;
         const Mv cand = clip_mv(mkmv(mv_ref.x + diy * 4, mv_ref.y + dix * 4), ypos, xpos, fw, fh, size, sign);
+        mine[n] = cand;
         S.me_off[k] = s * (cand.x >> 2) + s * (cand.y >> 2) * stride_r;
       }
       sad_batch(g, S, orig, size, ref, stride_r, S.me_off, nd, width, height, 0);
       unsigned bsad = ~0u;
       int bk = 1 << 30;
       Mv bmv = mkmv(0, 0);
-      for (int k = lane; k < nd; k += ME_LANES) {
-        const int d = (start + k) % 6;
-        const int diy = d == 0 ? 1 : d == 1 ? 2 : d == 2 ? 1 : d == 3 ? -1 : d == 4 ? -2 : -1;
-        const int dix = d == 0 ? -1 : d == 1 ? 0 : d == 2 ? 1 : d == 3 ? 1 : d == 4 ? 0 : -1;
-        const Mv cand = clip_mv(mkmv(mv_ref.x + diy * 4, mv_ref.y + dix * 4), ypos, xpos, fw, fh, size, sign);
+      for (int k = lane, n = 0; k < nd; k += ME_LANES, n++) {
+        const Mv cand = mine[n];
         const unsigned sad = (unsigned)S.acc[k] + mv_cost(lambda, cand, mvp);
         if (sad < bsad) { bsad = sad; bk = k; bmv = cand; }
       }
