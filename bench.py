@@ -17,6 +17,7 @@ share it through CUDA MPS.  A step = one frame of every stream.
   cpu_baseline / --impl reference : the UNMODIFIED reference encoder (oracle/_ref/Thorenc, SSE4 build) on the same clip and
           configuration: one process (cpu_baseline, cores 1) / one process per host thread (--impl reference).
   encoder_e2e / decoder_e2e : one stream, stock binary vs hooked binary, outputs compared byte for byte.
+  segments : ONE RA stream cut into closed-GOP segments, sharded over the ranks, joined and checked with the stock decoder.
 
 One rank per GPU under torchrun; ranks exchange nothing but the start barrier and the MAX of their times.
 """
