@@ -221,7 +221,11 @@ struct TforGuard {
 #ifdef THOR_HOSTEMU
 #define TFOR(g, i, cnt) for (int i = (g).tid; i < (cnt); i += (g).n)
 #else
+#ifdef THOR_TFOR_UNROLL2
+#define TFOR(g, i, cnt) _Pragma("unroll 2") for (int i = (g).tid; i < (cnt); i += (g).n)
+#else
 #define TFOR(g, i, cnt) _Pragma("unroll 1") for (int i = (g).tid; i < (cnt); i += (g).n)
+#endif
 #endif
 #endif
 

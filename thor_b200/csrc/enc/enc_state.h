@@ -318,7 +318,10 @@ TDN int scan_bits_warp(const int16_t *s, int N, int last_pos, bool chroma, bool 
   // a warp prices eight positions per lane in ~500 instructions whatever the block holds; the sequential walk costs ~25 per
   // position up to the last level, and most blocks end early (measured: always-parallel was 5 % faster per frame and 5 %
   // slower for 24 streams together)
-  if (last_pos < 24) return scan_bits(s, N, last_pos, chroma, intra, size);
+#ifndef THOR_SCAN_MIN
+#define THOR_SCAN_MIN 24
+#endif
+  if (last_pos < THOR_SCAN_MIN) return scan_bits(s, N, last_pos, chroma, intra, size);
   const bool small_chroma = chroma && size <= 8;
   int a[8];
   unsigned neg = 0;
