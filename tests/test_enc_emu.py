@@ -23,6 +23,15 @@ CASES = [
     ("HDB16_low_complexity", 128, 72, 17, 34),      # 16-picture hierarchy
     ("LDB_high_efficiency", 64, 64, 3, 30),         # tb / pb split, delta qp search, encoder_speed 0, 4 references
     ("RA_high_efficiency", 64, 64, 9, 32),          # + motion_estimate_bi on B frames
+    # the remaining shipped operating points, so that all 15 configuration files pass through the device decision source
+    ("RA_medium_complexity", 128, 72, 9, 33),
+    ("HDB_low_complexity", 128, 64, 5, 32),
+    ("HDB_high_efficiency", 64, 64, 5, 30),
+    ("HDB16_medium_complexity", 64, 64, 17, 32),
+    ("HDB16_high_efficiency", 64, 64, 17, 34),
+    ("RA16_low_complexity", 128, 64, 17, 32),
+    ("RA16_medium_complexity", 64, 64, 17, 30),
+    ("RA16_high_efficiency", 64, 64, 17, 33),
 ]
 
 
